@@ -1,0 +1,773 @@
+// C ABI of libfluidsim_b200.so (include/fluid_sim_b200.h): simulation handle, host-side
+// orchestration of FluidSim::step, lazy host mirror for the per-cell getters.
+//
+// Pass order follows the reference exactly (velocityStep src/fluid_sim.cpp:370-406, densityStep
+// :409-422); what changes is where data lives and how passes are fused:
+//   - six float32 fields resident in HBM (the reference's six live arrays);
+//     the std::copy calls to prev* (:386-387, :397-398, :412, :418) become pointer swaps or
+//     vanish, because every device pass writes to a different buffer than it gathers from or is
+//     safe in place;
+//   - the two velocity advects share one RK4 back-trace (:401-402 trace through the same fields);
+//   - density "diffusion" with DIFFUSION == 0 (include/fluid_sim.h:14) is the identity d + 0.0f plus
+//     the boundary update and is folded into the advect gather.
+#include "../../include/fluid_sim_b200.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "fsb_internal.h"
+
+using namespace fsb;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string &msg)
+{
+    g_last_error = msg;
+    return code;
+}
+
+int fail_cuda(cudaError_t e, const char *what)
+{
+    g_last_error = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    return e == cudaErrorMemoryAllocation ? FSB_ENOMEM : FSB_ECUDA;
+}
+
+#define FSB_CUDA(call)                                         \
+    do {                                                       \
+        cudaError_t e__ = (call);                              \
+        if (e__ != cudaSuccess) return fail_cuda(e__, #call);  \
+    } while (0)
+
+#define FSB_TRY(call)                  \
+    do {                               \
+        int r__ = (call);              \
+        if (r__ != FSB_OK) return r__; \
+    } while (0)
+
+constexpr int kNumFields = 6;
+
+}  // namespace
+
+struct fsb_sim {
+    fsb_params prm;
+    int W = 0, H = 0;
+    size_t ncells = 0;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    float *f[kNumFields] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    float *temp[2] = {nullptr, nullptr};   // MacCormack scratch (src/fluid_sim.cpp:52-53 tempField1/2), lazy
+    SweepScratch sweep;
+    NoiseTables noise_tables;
+    uint32_t noise_win[kRandDeg];          // window of the emulated rand() stream at noise_pos
+    uint64_t noise_pos = 0;
+    RandJump noise_step_jump;              // advance by 2*W*H outputs
+    std::vector<SourceEntry> pending;
+    SourceEntry *d_entries = nullptr;
+    int *d_segs = nullptr;
+    size_t d_entries_cap = 0, d_segs_cap = 0;
+    std::vector<float> mirror[3];
+    bool mirror_valid[3] = {false, false, false};
+    uint64_t launches = 0;
+    int tune_warps = 0;
+    int tune_levels = 0;
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    explicit DeviceGuard(int dev)
+    {
+        if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) {
+            cudaSetDevice(dev);
+            switched = true;
+        }
+    }
+    ~DeviceGuard()
+    {
+        if (switched) cudaSetDevice(prev);
+    }
+};
+
+inline float sign_i(int b) { return b == 1 ? -1.0f : 1.0f; }
+inline float sign_j(int b) { return b == 2 ? -1.0f : 1.0f; }
+
+std::vector<int> split_levels(int n, int cap)
+{
+    static const int sizes[] = {20, 10, 5, 2, 1};
+    std::vector<int> out;
+    if (cap <= 0 || cap > kWfMaxLevels) cap = kWfMaxLevels;
+    while (n > 0) {
+        for (int s : sizes)
+            if (s <= n && s <= cap) {
+                out.push_back(s);
+                n -= s;
+                break;
+            }
+    }
+    return out;
+}
+
+int set_noise_window(fsb_sim *s, uint32_t seed, uint64_t pos)
+{
+    rand_seed_window(seed, s->noise_win);
+    if (pos) {
+        RandJump J = jump_matrix(pos);
+        apply_jump(J, s->noise_win);
+    }
+    s->noise_pos = pos;
+    s->prm.noise_seed = seed;
+    return FSB_OK;
+}
+
+int set_boundary(fsb_sim *s, const BndJob *jobs, int n)
+{
+    FSB_CUDA(launch_set_boundary(jobs, n, s->W, s->H, s->stream));
+    s->launches += 1;
+    return FSB_OK;
+}
+
+int set_boundary1(fsb_sim *s, float *x, int b, int plus_zero = 0)
+{
+    BndJob j{x, b, plus_zero};
+    return set_boundary(s, &j, 1);
+}
+
+int flush_sources(fsb_sim *s)
+{
+    if (s->pending.empty()) return FSB_OK;
+    // group by (field, cell) keeping call order inside a group: `+=` is applied in the order of the calls
+    std::vector<SourceEntry> &e = s->pending;
+    std::stable_sort(e.begin(), e.end(), [](const SourceEntry &a, const SourceEntry &b) {
+        return a.field != b.field ? a.field < b.field : a.cell < b.cell;
+    });
+    std::vector<int> segs;
+    for (size_t k = 0; k < e.size(); ++k)
+        if (k == 0 || e[k].field != e[k - 1].field || e[k].cell != e[k - 1].cell) segs.push_back((int)k);
+    const int nseg = (int)segs.size();
+    segs.push_back((int)e.size());
+    if (e.size() > s->d_entries_cap) {
+        if (s->d_entries) cudaFree(s->d_entries);
+        s->d_entries = nullptr;
+        s->d_entries_cap = std::max<size_t>(e.size() * 2, 1024);
+        FSB_CUDA(cudaMalloc(&s->d_entries, s->d_entries_cap * sizeof(SourceEntry)));
+    }
+    if (segs.size() > s->d_segs_cap) {
+        if (s->d_segs) cudaFree(s->d_segs);
+        s->d_segs = nullptr;
+        s->d_segs_cap = std::max<size_t>(segs.size() * 2, 1024);
+        FSB_CUDA(cudaMalloc(&s->d_segs, s->d_segs_cap * sizeof(int)));
+    }
+    FSB_CUDA(cudaMemcpyAsync(s->d_entries, e.data(), e.size() * sizeof(SourceEntry), cudaMemcpyHostToDevice, s->stream));
+    FSB_CUDA(cudaMemcpyAsync(s->d_segs, segs.data(), segs.size() * sizeof(int), cudaMemcpyHostToDevice, s->stream));
+    FSB_CUDA(launch_apply_sources(s->f[FSB_DENSITY], s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->d_entries,
+                                  s->d_segs, nseg, s->stream));
+    s->launches += 1;
+    // the host vectors are reused right away: wait for the staged copies
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    e.clear();
+    return FSB_OK;
+}
+
+// diffuse() of src/fluid_sim.cpp:43-62 on up to two fields sharing the coefficient `diff`.
+// fold_identity: with a == 0 only the boundary is updated and *folded is set, the caller then reads
+// interior values as (v + 0.0f).
+int diffuse_fields(fsb_sim *s, int nf, float *const *xs, const int *bs, float diff, float dt, bool fold_identity,
+                   int *folded)
+{
+    if (folded) *folded = 0;
+    const int D = s->prm.diff_iters;
+    if (D <= 0) return FSB_OK;
+    const float a = dt * diff * (float)s->W * (float)s->H;   // ((dt*diff)*W)*H, :45
+    const float c_recip = 1.0f / (1.0f + 4.0f * a);          // :46
+    if (a == 0.0f) {
+        BndJob jobs[2];
+        for (int i = 0; i < nf; ++i) {
+            if (!fold_identity) {
+                FSB_CUDA(launch_add_zero(xs[i], s->ncells, s->stream));
+                s->launches += 1;
+            }
+            jobs[i] = BndJob{xs[i], bs[i], fold_identity ? 1 : 0};
+        }
+        FSB_TRY(set_boundary(s, jobs, nf));
+        if (folded && fold_identity) *folded = 1;
+        return FSB_OK;
+    }
+    const std::vector<int> passes = split_levels(D, s->tune_levels);
+    const bool multi = passes.size() > 1;
+    float *rhs[2] = {xs[0], nf > 1 ? xs[1] : nullptr};
+    if (multi) {
+        // the source must stay the pre-diffusion field for every pass: keep a copy (prev* in the reference)
+        float *scratch[2] = {s->f[FSB_PREV_VEL_X], s->f[FSB_PREV_VEL_Y]};
+        for (int i = 0; i < nf; ++i) {
+            if (scratch[i] == xs[i]) scratch[i] = s->f[FSB_PREV_DENSITY];
+            FSB_CUDA(cudaMemcpyAsync(scratch[i], xs[i], s->ncells * sizeof(float), cudaMemcpyDeviceToDevice, s->stream));
+            rhs[i] = scratch[i];
+        }
+    }
+    for (size_t pi = 0; pi < passes.size(); ++pi) {
+        SweepLaunch L{};
+        L.nfields = nf;
+        for (int i = 0; i < nf; ++i) L.fld[i] = SweepField{xs[i], rhs[i], xs[i], sign_i(bs[i]), sign_j(bs[i])};
+        L.W = s->W;
+        L.H = s->H;
+        L.mode = kSor;
+        L.levels = passes[pi];
+        L.a = a;
+        L.c_recip = c_recip;
+        L.omega = s->prm.omega;
+        L.warps_per_cta = s->tune_warps;
+        int nl = 0;
+        FSB_CUDA(launch_sweep_pass(L, s->sweep, s->stream, &nl));
+        s->launches += nl;
+        BndJob jobs[2];
+        for (int i = 0; i < nf; ++i) jobs[i] = BndJob{xs[i], bs[i], 0};
+        FSB_TRY(set_boundary(s, jobs, nf));
+    }
+    return FSB_OK;
+}
+
+// project() of src/fluid_sim.cpp:301-344
+int project(fsb_sim *s, float *u, float *v, float *p, float *div)
+{
+    FSB_CUDA(launch_divergence(u, v, div, s->W, s->H, s->stream));
+    s->launches += 1;
+    const std::vector<int> passes = split_levels(s->prm.proj_iters, s->tune_levels);
+    if (passes.empty()) FSB_CUDA(cudaMemsetAsync(p, 0, s->ncells * sizeof(float), s->stream));
+    for (size_t pi = 0; pi < passes.size(); ++pi) {
+        SweepLaunch L{};
+        L.nfields = 1;
+        L.fld[0] = SweepField{pi == 0 ? nullptr : p, div, p, 1.0f, 1.0f};   // p starts at 0 (:313, :316)
+        L.W = s->W;
+        L.H = s->H;
+        L.mode = kGaussSeidel;
+        L.levels = passes[pi];
+        L.a = 0.0f;
+        L.c_recip = 1.0f;
+        L.omega = 1.0f;
+        L.warps_per_cta = s->tune_warps;
+        int nl = 0;
+        FSB_CUDA(launch_sweep_pass(L, s->sweep, s->stream, &nl));
+        s->launches += nl;
+        FSB_TRY(set_boundary1(s, p, 0));
+    }
+    FSB_CUDA(launch_gradient(u, v, p, s->W, s->H, s->stream));
+    s->launches += 1;
+    BndJob jobs[2] = {BndJob{u, 1, 0}, BndJob{v, 2, 0}};
+    return set_boundary(s, jobs, 2);
+}
+
+int ensure_temps(fsb_sim *s)
+{
+    for (int i = 0; i < 2; ++i)
+        if (!s->temp[i]) {
+            FSB_CUDA(cudaMalloc(&s->temp[i], s->ncells * sizeof(float)));
+            FSB_CUDA(cudaMemsetAsync(s->temp[i], 0, s->ncells * sizeof(float), s->stream));
+        }
+    return FSB_OK;
+}
+
+// advect() of src/fluid_sim.cpp:212-228 for one field (dst must not alias src, u or v)
+int advect_one(fsb_sim *s, int b, float *dst, const float *src, const float *u, const float *v, float dt, int pz)
+{
+    const int scheme = s->prm.advect_scheme;
+    if (scheme == FSB_ADVECT_RK4) {
+        FSB_CUDA(launch_advect_rk4(dst, src, nullptr, nullptr, u, v, pz, s->W, s->H, dt, s->stream));
+        s->launches += 1;
+    } else if (scheme == FSB_ADVECT_SEMI_LAGRANGIAN) {
+        FSB_CUDA(launch_advect_sl(dst, src, u, v, pz, s->W, s->H, dt, -1.0f, s->stream));
+        s->launches += 1;
+    } else {
+        FSB_TRY(ensure_temps(s));
+        FSB_CUDA(launch_advect_sl(s->temp[0], src, u, v, pz, s->W, s->H, dt, -1.0f, s->stream));
+        FSB_TRY(set_boundary1(s, s->temp[0], b));
+        FSB_CUDA(launch_advect_sl(s->temp[1], s->temp[0], u, v, 0, s->W, s->H, dt, +1.0f, s->stream));
+        FSB_TRY(set_boundary1(s, s->temp[1], b));
+        FSB_CUDA(launch_maccormack_combine(dst, src, s->temp[0], s->temp[1], pz, s->W, s->H, s->stream));
+        s->launches += 3;
+    }
+    return set_boundary1(s, dst, b);
+}
+
+int add_noise(fsb_sim *s)
+{
+    NoiseWindow nw;
+    std::memcpy(nw.w, s->noise_win, sizeof(nw.w));
+    const int zero = s->prm.noise_mode == FSB_NOISE_ZERO;
+    FSB_CUDA(launch_noise(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->ncells, nw, s->noise_tables, zero, s->stream));
+    s->launches += zero ? 2 : 1;
+    // the reference consumes 2*W*H outputs per step in either case (the zero mode replaces rand() itself)
+    if (!zero) {
+        apply_jump(s->noise_step_jump, s->noise_win);
+        s->noise_pos += 2ull * s->ncells;
+    }
+    return FSB_OK;
+}
+
+int velocity_step(fsb_sim *s, float dt)
+{
+    FSB_TRY(add_noise(s));
+    {
+        float *xs[2] = {s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y]};
+        const int bs[2] = {1, 2};
+        FSB_TRY(diffuse_fields(s, 2, xs, bs, s->prm.viscosity, dt, false, nullptr));
+    }
+    FSB_TRY(project(s, s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_X], s->f[FSB_PREV_VEL_Y]));
+    // advect both components out of (u, v) into the free prev buffers, then swap roles
+    float *u = s->f[FSB_VELOCITY_X], *v = s->f[FSB_VELOCITY_Y];
+    float *nu = s->f[FSB_PREV_VEL_X], *nv = s->f[FSB_PREV_VEL_Y];
+    if (s->prm.advect_scheme == FSB_ADVECT_RK4) {
+        FSB_CUDA(launch_advect_rk4(nu, u, nv, v, u, v, 0, s->W, s->H, dt, s->stream));
+        s->launches += 1;
+        BndJob jobs[2] = {BndJob{nu, 1, 0}, BndJob{nv, 2, 0}};
+        FSB_TRY(set_boundary(s, jobs, 2));
+    } else {
+        FSB_TRY(advect_one(s, 1, nu, u, u, v, dt, 0));
+        FSB_TRY(advect_one(s, 2, nv, v, u, v, dt, 0));
+    }
+    std::swap(s->f[FSB_VELOCITY_X], s->f[FSB_PREV_VEL_X]);
+    std::swap(s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_Y]);
+    return project(s, s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_X], s->f[FSB_PREV_VEL_Y]);
+}
+
+int density_step(fsb_sim *s, float dt)
+{
+    float *xs[1] = {s->f[FSB_DENSITY]};
+    const int bs[1] = {0};
+    int folded = 0;
+    FSB_TRY(diffuse_fields(s, 1, xs, bs, s->prm.diffusion, dt, true, &folded));
+    FSB_TRY(advect_one(s, 0, s->f[FSB_PREV_DENSITY], s->f[FSB_DENSITY], s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], dt,
+                       folded));
+    std::swap(s->f[FSB_DENSITY], s->f[FSB_PREV_DENSITY]);
+    return FSB_OK;
+}
+
+void invalidate_mirror(fsb_sim *s) { s->mirror_valid[0] = s->mirror_valid[1] = s->mirror_valid[2] = false; }
+
+int refresh_mirror(fsb_sim *s, int field)
+{
+    if (s->mirror_valid[field]) return FSB_OK;
+    FSB_TRY(flush_sources(s));
+    s->mirror[field].resize(s->ncells);
+    FSB_CUDA(cudaMemcpyAsync(s->mirror[field].data(), s->f[field], s->ncells * sizeof(float), cudaMemcpyDeviceToHost,
+                             s->stream));
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    s->mirror_valid[field] = true;
+    return FSB_OK;
+}
+
+inline bool in_range(const fsb_sim *s, int x, int y) { return x >= 0 && x < s->W && y >= 0 && y < s->H; }
+
+bool valid_field(int f) { return f >= 0 && f < kNumFields; }
+
+}  // namespace
+
+// ===================================== C ABI ============================================
+
+extern "C" {
+
+void fsb_default_params(fsb_params *p)
+{
+    if (!p) return;
+    std::memset(p, 0, sizeof(*p));
+    p->width = 200;
+    p->height = 200;
+    p->proj_iters = 20;
+    p->diff_iters = 5;
+    p->viscosity = 0.0001f;
+    p->diffusion = 0.0f;
+    p->omega = 1.5f;
+    p->advect_scheme = FSB_ADVECT_RK4;
+    p->noise_mode = FSB_NOISE_GLIBC;
+    p->noise_seed = 1;
+    p->noise_pos = 0;
+    p->device = -1;
+}
+
+int fsb_create(const fsb_params *p, fsb_sim **out)
+{
+    if (!out) return fail(FSB_EINVAL, "fsb_create: out is null");
+    *out = nullptr;
+    fsb_params prm;
+    if (p) prm = *p;
+    else fsb_default_params(&prm);
+    if (prm.width < 3 || prm.height < 3) return fail(FSB_EINVAL, "fsb_create: grid must be at least 3x3");
+    if (prm.proj_iters < 0 || prm.diff_iters < 0) return fail(FSB_EINVAL, "fsb_create: negative sweep count");
+    if (prm.advect_scheme < 0 || prm.advect_scheme > 2) return fail(FSB_EINVAL, "fsb_create: unknown advection scheme");
+    if ((long long)prm.width * prm.height > (1ll << 31) - 1) return fail(FSB_ELIMIT, "fsb_create: more than 2^31-1 cells");
+
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(FSB_ECUDA, "fsb_create: no CUDA device (this library has no CPU fallback)");
+    int dev = prm.device;
+    if (dev < 0) FSB_CUDA(cudaGetDevice(&dev));
+    if (dev >= ndev) return fail(FSB_EINVAL, "fsb_create: device ordinal out of range");
+
+    fsb_sim *s = new (std::nothrow) fsb_sim();
+    if (!s) return fail(FSB_ENOMEM, "fsb_create: host allocation failed");
+    s->prm = prm;
+    s->W = prm.width;
+    s->H = prm.height;
+    s->ncells = (size_t)prm.width * prm.height;
+    s->device = dev;
+    DeviceGuard guard(dev);
+
+    auto bail = [&](int code) {
+        fsb_destroy(s);
+        return code;
+    };
+#define FSB_CREATE_CUDA(call)                                           \
+    do {                                                                \
+        cudaError_t e__ = (call);                                       \
+        if (e__ != cudaSuccess) return bail(fail_cuda(e__, #call));     \
+    } while (0)
+
+    FSB_CREATE_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    for (int k = 0; k < kNumFields; ++k) {
+        FSB_CREATE_CUDA(cudaMalloc(&s->f[k], s->ncells * sizeof(float)));
+        FSB_CREATE_CUDA(cudaMemsetAsync(s->f[k], 0, s->ncells * sizeof(float), s->stream));
+    }
+    s->sweep.xchg_floats = sweep_xchg_floats(s->H);
+    FSB_CREATE_CUDA(cudaMalloc(&s->sweep.xchg, s->sweep.xchg_floats * sizeof(float)));
+    FSB_CREATE_CUDA(cudaMemsetAsync(s->sweep.xchg, 0, s->sweep.xchg_floats * sizeof(float), s->stream));
+    FSB_CREATE_CUDA(cudaMalloc(&s->sweep.flags, sweep_flag_words() * sizeof(unsigned long long)));
+    FSB_CREATE_CUDA(cudaMemsetAsync(s->sweep.flags, 0, sweep_flag_words() * sizeof(unsigned long long), s->stream));
+    FSB_CREATE_CUDA(noise_tables_create(s->noise_tables));
+    s->noise_step_jump = jump_matrix(2ull * s->ncells);
+    set_noise_window(s, prm.noise_seed, prm.noise_pos);
+    FSB_CREATE_CUDA(cudaStreamSynchronize(s->stream));
+#undef FSB_CREATE_CUDA
+    *out = s;
+    return FSB_OK;
+}
+
+int fsb_destroy(fsb_sim *s)
+{
+    if (!s) return FSB_OK;
+    {
+        DeviceGuard guard(s->device);
+        // tolerate a runtime that is already shutting down (a namespace-scope FluidSim, src/main.cpp:7,
+        // is destroyed after main returns): errors are ignored here on purpose
+        if (s->stream) cudaStreamSynchronize(s->stream);
+        for (int k = 0; k < kNumFields; ++k)
+            if (s->f[k]) cudaFree(s->f[k]);
+        for (int k = 0; k < 2; ++k)
+            if (s->temp[k]) cudaFree(s->temp[k]);
+        if (s->sweep.xchg) cudaFree(s->sweep.xchg);
+        if (s->sweep.flags) cudaFree(s->sweep.flags);
+        if (s->d_entries) cudaFree(s->d_entries);
+        if (s->d_segs) cudaFree(s->d_segs);
+        noise_tables_destroy(s->noise_tables);
+        if (s->stream) cudaStreamDestroy(s->stream);
+        (void)cudaGetLastError();
+    }
+    delete s;
+    return FSB_OK;
+}
+
+int fsb_reset(fsb_sim *s)
+{
+    if (!s) return fail(FSB_EINVAL, "fsb_reset: null handle");
+    DeviceGuard guard(s->device);
+    s->pending.clear();
+    for (int k = 0; k < kNumFields; ++k) FSB_CUDA(cudaMemsetAsync(s->f[k], 0, s->ncells * sizeof(float), s->stream));
+    for (int k = 0; k < 2; ++k)
+        if (s->temp[k]) FSB_CUDA(cudaMemsetAsync(s->temp[k], 0, s->ncells * sizeof(float), s->stream));
+    invalidate_mirror(s);
+    return FSB_OK;
+}
+
+int fsb_step(fsb_sim *s, float dt)
+{
+    if (!s) return fail(FSB_EINVAL, "fsb_step: null handle");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    invalidate_mirror(s);
+    FSB_TRY(velocity_step(s, dt));   // src/fluid_sim.cpp:26
+    FSB_TRY(density_step(s, dt));    // src/fluid_sim.cpp:27
+    return FSB_OK;
+}
+
+int fsb_sync(fsb_sim *s)
+{
+    if (!s) return fail(FSB_EINVAL, "fsb_sync: null handle");
+    DeviceGuard guard(s->device);
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    return FSB_OK;
+}
+
+int fsb_add_density(fsb_sim *s, int x, int y, float amount)
+{
+    if (!s) return fail(FSB_EINVAL, "fsb_add_density: null handle");
+    if (!in_range(s, x, y)) return FSB_OK;   // silently ignored, src/fluid_sim.cpp:426
+    const int cell = x * s->H + y;
+    s->pending.push_back(SourceEntry{cell, 0, amount});
+    if (s->mirror_valid[0]) s->mirror[0][cell] += amount;
+    return FSB_OK;
+}
+
+int fsb_add_velocity(fsb_sim *s, int x, int y, float ax, float ay)
+{
+    if (!s) return fail(FSB_EINVAL, "fsb_add_velocity: null handle");
+    if (!in_range(s, x, y)) return FSB_OK;   // src/fluid_sim.cpp:434
+    const int cell = x * s->H + y;
+    s->pending.push_back(SourceEntry{cell, 1, ax});
+    s->pending.push_back(SourceEntry{cell, 2, ay});
+    if (s->mirror_valid[1]) s->mirror[1][cell] += ax;
+    if (s->mirror_valid[2]) s->mirror[2][cell] += ay;
+    return FSB_OK;
+}
+
+int fsb_add_density_n(fsb_sim *s, int n, const int *xs, const int *ys, const float *amounts)
+{
+    if (!s || n < 0 || (n > 0 && (!xs || !ys || !amounts))) return fail(FSB_EINVAL, "fsb_add_density_n: bad argument");
+    for (int k = 0; k < n; ++k) FSB_TRY(fsb_add_density(s, xs[k], ys[k], amounts[k]));
+    return FSB_OK;
+}
+
+int fsb_add_velocity_n(fsb_sim *s, int n, const int *xs, const int *ys, const float *axs, const float *ays)
+{
+    if (!s || n < 0 || (n > 0 && (!xs || !ys || !axs || !ays))) return fail(FSB_EINVAL, "fsb_add_velocity_n: bad argument");
+    for (int k = 0; k < n; ++k) FSB_TRY(fsb_add_velocity(s, xs[k], ys[k], axs[k], ays[k]));
+    return FSB_OK;
+}
+
+int fsb_get_density(fsb_sim *s, int x, int y, float *out)
+{
+    if (!s || !out) return fail(FSB_EINVAL, "fsb_get_density: bad argument");
+    *out = 0.0f;
+    if (!in_range(s, x, y)) return FSB_OK;   // src/fluid_sim.cpp:447
+    DeviceGuard guard(s->device);
+    FSB_TRY(refresh_mirror(s, 0));
+    *out = s->mirror[0][(size_t)x * s->H + y];
+    return FSB_OK;
+}
+
+int fsb_get_velocity(fsb_sim *s, int x, int y, float *out_xy)
+{
+    if (!s || !out_xy) return fail(FSB_EINVAL, "fsb_get_velocity: bad argument");
+    out_xy[0] = out_xy[1] = 0.0f;
+    if (!in_range(s, x, y)) return FSB_OK;   // src/fluid_sim.cpp:456
+    DeviceGuard guard(s->device);
+    FSB_TRY(refresh_mirror(s, 1));
+    FSB_TRY(refresh_mirror(s, 2));
+    out_xy[0] = s->mirror[1][(size_t)x * s->H + y];
+    out_xy[1] = s->mirror[2][(size_t)x * s->H + y];
+    return FSB_OK;
+}
+
+int fsb_get_velocity_magnitude(fsb_sim *s, int x, int y, float *out)
+{
+    float v[2];
+    if (!out) return fail(FSB_EINVAL, "fsb_get_velocity_magnitude: bad argument");
+    FSB_TRY(fsb_get_velocity(s, x, y, v));
+    *out = in_range(s, x, y) ? std::sqrt(v[0] * v[0] + v[1] * v[1]) : 0.0f;   // glm::length, src/fluid_sim.cpp:477
+    return FSB_OK;
+}
+
+int fsb_get_normalized_velocity(fsb_sim *s, int x, int y, float *out_xy)
+{
+    float v[2];
+    if (!out_xy) return fail(FSB_EINVAL, "fsb_get_normalized_velocity: bad argument");
+    FSB_TRY(fsb_get_velocity(s, x, y, v));
+    out_xy[0] = out_xy[1] = 0.0f;
+    if (in_range(s, x, y)) {
+        const float m = std::sqrt(v[0] * v[0] + v[1] * v[1]);
+        if (m > 0.001f) {   // src/fluid_sim.cpp:465
+            out_xy[0] = v[0] / m;
+            out_xy[1] = v[1] / m;
+        }
+    }
+    return FSB_OK;
+}
+
+int fsb_get_velocity_color(fsb_sim *s, int x, int y, float *rgb)
+{
+    float speed = 0.0f;
+    if (!rgb) return fail(FSB_EINVAL, "fsb_get_velocity_color: bad argument");
+    FSB_TRY(fsb_get_velocity_magnitude(s, x, y, &speed));
+    // four-segment blue -> cyan -> green -> yellow -> red ramp, src/fluid_sim.cpp:482-519
+    const float q = speed / 10.0f;
+    const float n = (q < 1.0f) ? q : 1.0f;
+    if (n < 0.25f) {
+        rgb[0] = 0.0f; rgb[1] = n / 0.25f; rgb[2] = 1.0f;
+    } else if (n < 0.5f) {
+        rgb[0] = 0.0f; rgb[1] = 1.0f; rgb[2] = 1.0f - (n - 0.25f) / 0.25f;
+    } else if (n < 0.75f) {
+        rgb[0] = (n - 0.5f) / 0.25f; rgb[1] = 1.0f; rgb[2] = 0.0f;
+    } else {
+        rgb[0] = 1.0f; rgb[1] = 1.0f - (n - 0.75f) / 0.25f; rgb[2] = 0.0f;
+    }
+    return FSB_OK;
+}
+
+int fsb_get_width(const fsb_sim *s) { return s ? s->W : 0; }
+int fsb_get_height(const fsb_sim *s) { return s ? s->H : 0; }
+
+int fsb_read_field(fsb_sim *s, int field, float *host_dst)
+{
+    if (!s || !host_dst || !valid_field(field)) return fail(FSB_EINVAL, "fsb_read_field: bad argument");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    FSB_CUDA(cudaMemcpyAsync(host_dst, s->f[field], s->ncells * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    return FSB_OK;
+}
+
+int fsb_write_field(fsb_sim *s, int field, const float *host_src)
+{
+    if (!s || !host_src || !valid_field(field)) return fail(FSB_EINVAL, "fsb_write_field: bad argument");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    FSB_CUDA(cudaMemcpyAsync(s->f[field], host_src, s->ncells * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    if (field < 3) s->mirror_valid[field] = false;
+    return FSB_OK;
+}
+
+int fsb_add_field(fsb_sim *s, int field, const float *host_src)
+{
+    if (!s || !host_src || field < 0 || field > 2) return fail(FSB_EINVAL, "fsb_add_field: bad argument");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    // stage through a scratch field that no pass reads between steps
+    float *stage = s->f[FSB_PREV_DENSITY];
+    FSB_CUDA(cudaMemcpyAsync(stage, host_src, s->ncells * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    FSB_CUDA(launch_axpy_field(s->f[field], stage, s->ncells, s->stream));
+    s->launches += 1;
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    s->mirror_valid[field] = false;
+    return FSB_OK;
+}
+
+int fsb_device_field(fsb_sim *s, int field, void **dptr)
+{
+    if (!s || !dptr || !valid_field(field)) return fail(FSB_EINVAL, "fsb_device_field: bad argument");
+    *dptr = s->f[field];
+    return FSB_OK;
+}
+
+int fsb_get_noise_pos(const fsb_sim *s, uint64_t *pos)
+{
+    if (!s || !pos) return fail(FSB_EINVAL, "fsb_get_noise_pos: bad argument");
+    *pos = s->noise_pos;
+    return FSB_OK;
+}
+
+int fsb_set_noise(fsb_sim *s, int mode, uint32_t seed, uint64_t pos)
+{
+    if (!s || (mode != FSB_NOISE_GLIBC && mode != FSB_NOISE_ZERO)) return fail(FSB_EINVAL, "fsb_set_noise: bad argument");
+    s->prm.noise_mode = mode;
+    return set_noise_window(s, seed, pos);
+}
+
+int fsb_op_add_noise(fsb_sim *s)
+{
+    if (!s) return fail(FSB_EINVAL, "null handle");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    invalidate_mirror(s);
+    return add_noise(s);
+}
+
+int fsb_op_set_boundary(fsb_sim *s, int b, int field)
+{
+    if (!s || !valid_field(field) || b < 0 || b > 2) return fail(FSB_EINVAL, "fsb_op_set_boundary: bad argument");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    invalidate_mirror(s);
+    return set_boundary1(s, s->f[field], b);
+}
+
+int fsb_op_diffuse(fsb_sim *s, int b, int field, float diff, float dt)
+{
+    if (!s || !valid_field(field) || b < 0 || b > 2) return fail(FSB_EINVAL, "fsb_op_diffuse: bad argument");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    invalidate_mirror(s);
+    float *xs[1] = {s->f[field]};
+    const int bs[1] = {b};
+    return diffuse_fields(s, 1, xs, bs, diff, dt, false, nullptr);
+}
+
+int fsb_op_project(fsb_sim *s)
+{
+    if (!s) return fail(FSB_EINVAL, "null handle");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    invalidate_mirror(s);
+    return project(s, s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_X], s->f[FSB_PREV_VEL_Y]);
+}
+
+int fsb_op_advect(fsb_sim *s, int b, int dst, int src, int u, int v, float dt)
+{
+    if (!s || !valid_field(dst) || !valid_field(src) || !valid_field(u) || !valid_field(v) || b < 0 || b > 2)
+        return fail(FSB_EINVAL, "fsb_op_advect: bad argument");
+    if (dst == src || dst == u || dst == v) return fail(FSB_EINVAL, "fsb_op_advect: dst must not alias an input");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    invalidate_mirror(s);
+    return advect_one(s, b, s->f[dst], s->f[src], s->f[u], s->f[v], dt, 0);
+}
+
+int fsb_op_velocity_step(fsb_sim *s, float dt)
+{
+    if (!s) return fail(FSB_EINVAL, "null handle");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    invalidate_mirror(s);
+    return velocity_step(s, dt);
+}
+
+int fsb_op_density_step(fsb_sim *s, float dt)
+{
+    if (!s) return fail(FSB_EINVAL, "null handle");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    invalidate_mirror(s);
+    return density_step(s, dt);
+}
+
+int fsb_launch_count(const fsb_sim *s, uint64_t *count)
+{
+    if (!s || !count) return fail(FSB_EINVAL, "fsb_launch_count: bad argument");
+    *count = s->launches;
+    return FSB_OK;
+}
+
+int fsb_set_tuning(fsb_sim *s, int warps_per_cta, int max_sweeps_per_pass)
+{
+    if (!s || warps_per_cta < 0 || warps_per_cta > 8 || max_sweeps_per_pass < 0)
+        return fail(FSB_EINVAL, "fsb_set_tuning: bad argument");
+    s->tune_warps = warps_per_cta;
+    s->tune_levels = max_sweeps_per_pass;
+    return FSB_OK;
+}
+
+void *fsb_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+        g_last_error = "fsb_host_alloc: cudaHostAlloc failed";
+        return nullptr;
+    }
+    return p;
+}
+
+void fsb_host_free(void *p)
+{
+    if (p) cudaFreeHost(p);
+}
+
+const char *fsb_last_error(void) { return g_last_error.c_str(); }
+const char *fsb_version(void) { return "fluid_sim_b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,146 @@
+// Velocity noise of velocityStep (src/fluid_sim.cpp:374-383) on the device.
+//
+// The reference draws 2 rand() numbers per cell, X then Y, i-outer / j-inner over the FULL grid,
+// from glibc's never-seeded generator.  That stream is a linear recurrence over Z/2^32
+// (glibc_rand.h), so any position can be reached with a 31x31 matrix product.  Work split:
+//   warp  -> 8192 consecutive cells; its window is reached from the step's base window by the
+//            binary decomposition of the warp index (<= 24 cooperative mat-vecs, one word per lane)
+//   lane  -> 256 consecutive cells of that run; lane windows are derived one after the other with
+//            the fixed 512-output jump, then each lane keeps its 31 words in registers and
+//            generates sequentially with static indexing (31 outputs per rotation)
+//   store -> noise is staged in shared memory and applied with the warp walking one lane's run at a
+//            time, so u / v are read and written in 124-byte contiguous pieces.
+#include "fsb_internal.h"
+
+namespace fsb {
+
+namespace {
+
+constexpr int kWarpsPerBlock = 4;
+constexpr int kMatStride = kRandDeg * 32;   // transposed 31x31 matrix, rows padded to 32 words
+constexpr int kStagePitch = 63;             // 62 noise floats per lane per round, odd pitch: no bank conflicts
+constexpr int kWinPitch = 33;
+
+__device__ __forceinline__ uint32_t matvec(const uint32_t *__restrict__ mt, uint32_t win, int lane)
+{
+    uint32_t acc = 0;
+#pragma unroll
+    for (int j = 0; j < kRandDeg; ++j) acc += __ldg(mt + j * 32 + lane) * __shfl_sync(0xffffffffu, win, j);
+    return acc;
+}
+
+__device__ __forceinline__ float noise_of(uint32_t word)
+{
+    const int r = (int)(word >> 1);                       // rand() output
+    const float f = __fmul_rn((float)r, 4.656612873077393e-10f);   // (float)rand() / RAND_MAX, RAND_MAX -> 2^31
+    return __fmul_rn(__fsub_rn(f, 0.5f), 1e-4f);
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) noise_kernel(float *__restrict__ u, float *__restrict__ v,
+                                                                   size_t ncells, const NoiseWindow base,
+                                                                   const uint32_t *__restrict__ tables)
+{
+    __shared__ uint32_t s_win[kWarpsPerBlock][32 * kWinPitch];
+    __shared__ float s_stage[kWarpsPerBlock][32 * kStagePitch];
+
+    const int lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5;
+    const size_t warp_global = (size_t)blockIdx.x * kWarpsPerBlock + wib;
+    const size_t cell_base = warp_global * kNoiseCellsPerWarp;
+    if (cell_base >= ncells) return;
+
+    // 1. window of this warp's first cell, one word per lane
+    uint32_t win = (lane < kRandDeg) ? base.w[lane] : 0u;
+    for (int b = 0; b < kNoiseMaxLevels; ++b)
+        if ((warp_global >> b) & 1) win = matvec(tables + (size_t)(1 + b) * kMatStride, win, lane);
+
+    // 2. windows of the 32 lanes, 512 outputs apart
+    uint32_t *sw = s_win[wib];
+    for (int r = 0; r < 32; ++r) {
+        if (lane < kRandDeg) sw[r * kWinPitch + lane] = win;
+        win = matvec(tables, win, lane);
+    }
+    __syncwarp();
+    uint32_t w[kRandDeg];
+#pragma unroll
+    for (int m = 0; m < kRandDeg; ++m) w[m] = sw[lane * kWinPitch + m];
+
+    // 3. generate and apply: 8 rounds of 31 cells, then a tail of 8 cells
+    float *stg = s_stage[wib];
+    const size_t lane_cell0 = cell_base + (size_t)lane * kNoiseCellsPerLane;
+    for (int round = 0; round <= 8; ++round) {
+        const int ncell_round = (round < 8) ? 31 : 8;
+        __syncwarp();
+        if (round < 8) {
+#pragma unroll
+            for (int n = 0; n < 62; ++n) {
+                const uint32_t nw = w[n % kRandDeg] + w[(n + 28) % kRandDeg];
+                w[n % kRandDeg] = nw;
+                stg[lane * kStagePitch + n] = noise_of(nw);
+            }
+        } else {
+#pragma unroll
+            for (int n = 0; n < 16; ++n) {
+                const uint32_t nw = w[n % kRandDeg] + w[(n + 28) % kRandDeg];
+                w[n % kRandDeg] = nw;
+                stg[lane * kStagePitch + n] = noise_of(nw);
+            }
+        }
+        __syncwarp();
+        if (lane < ncell_round) {
+            for (int r = 0; r < 32; ++r) {
+                const size_t c = cell_base + (size_t)r * kNoiseCellsPerLane + (size_t)round * 31 + lane;
+                if (c < ncells) {
+                    u[c] = __fadd_rn(u[c], stg[r * kStagePitch + 2 * lane]);
+                    v[c] = __fadd_rn(v[c], stg[r * kStagePitch + 2 * lane + 1]);
+                }
+            }
+        }
+    }
+    (void)lane_cell0;
+}
+
+}  // namespace
+
+cudaError_t noise_tables_create(NoiseTables &t)
+{
+    const size_t words = (size_t)(1 + kNoiseMaxLevels) * kMatStride;
+    std::vector<uint32_t> host(words, 0u);
+    auto put = [&](int slot, const RandJump &J) {
+        for (int m = 0; m < kRandDeg; ++m)
+            for (int j = 0; j < kRandDeg; ++j) host[(size_t)slot * kMatStride + j * 32 + m] = J.m[m][j];
+    };
+    put(0, jump_matrix(2ull * kNoiseCellsPerLane));
+    RandPoly p = poly_x_pow(2ull * kNoiseCellsPerWarp);
+    for (int b = 0; b < kNoiseMaxLevels; ++b) {
+        put(1 + b, jump_from_poly(p));
+        p = poly_mul(p, p);
+    }
+    cudaError_t e = cudaMalloc(&t.dev, words * sizeof(uint32_t));
+    if (e != cudaSuccess) return e;
+    return cudaMemcpy(t.dev, host.data(), words * sizeof(uint32_t), cudaMemcpyHostToDevice);
+}
+
+void noise_tables_destroy(NoiseTables &t)
+{
+    if (t.dev) cudaFree(t.dev);
+    t.dev = nullptr;
+}
+
+cudaError_t launch_noise(float *u, float *v, size_t ncells, const NoiseWindow &base, const NoiseTables &t,
+                         int zero_mode, cudaStream_t st)
+{
+    if (zero_mode) {
+        // rand() == 0x3FFFFFFF: ((float)r / RAND_MAX - 0.5f) * 1e-4f == +0.0f, and the reference still adds it.
+        cudaError_t e = launch_add_zero(u, ncells, st);
+        if (e != cudaSuccess) return e;
+        return launch_add_zero(v, ncells, st);
+    }
+    const size_t warps = (ncells + kNoiseCellsPerWarp - 1) / kNoiseCellsPerWarp;
+    if (warps >> kNoiseMaxLevels) return cudaErrorInvalidValue;
+    const unsigned blocks = (unsigned)((warps + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    noise_kernel<<<blocks, kWarpsPerBlock * 32, 0, st>>>(u, v, ncells, base, t.dev);
+    return cudaGetLastError();
+}
+
+}  // namespace fsb

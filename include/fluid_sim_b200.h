@@ -1,0 +1,154 @@
+/*
+ * fluid_sim_b200 -- C ABI of the B200-native FluidSim::step.
+ *
+ * This is the drop-in boundary underneath the reference's C++ class
+ * (reference: include/fluid_sim.h:17-37).  The reference has no FFI layer of its
+ * own; each entry point below names the class member (or private method) of the
+ * reference that it replaces.  Plain pointers and sizes only: no C++ or torch types.
+ *
+ * Conventions
+ *   - every function returns FSB_OK (0) or a negative FSB_E* code; the message of
+ *     the last failure on the calling thread is available from fsb_last_error().
+ *   - fields are float32, row-major [width][height] with the y index contiguous,
+ *     exactly like the reference's float f[GRID_SIZE_X][GRID_SIZE_Y]
+ *     (reference: include/fluid_sim.h:42-47); linear index = x * height + y.
+ *   - a simulation is bound to one CUDA device and one stream and is not
+ *     thread-safe, like the reference object (single-threaded main loop,
+ *     reference: src/main.cpp:369-519).
+ *   - there is no CPU fallback: without a CUDA device fsb_create fails.
+ */
+#ifndef FLUID_SIM_B200_H
+#define FLUID_SIM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fsb_sim fsb_sim;
+
+enum {
+    FSB_OK = 0,
+    FSB_EINVAL = -1,   /* bad argument */
+    FSB_ECUDA = -2,    /* CUDA runtime / launch failure */
+    FSB_ENOMEM = -3,   /* host or device allocation failed */
+    FSB_ELIMIT = -4    /* size beyond what this build supports */
+};
+
+/* field ids (the reference's member arrays, include/fluid_sim.h:42-47) */
+enum {
+    FSB_DENSITY = 0,      /* density       */
+    FSB_VELOCITY_X = 1,   /* velocityX     */
+    FSB_VELOCITY_Y = 2,   /* velocityY     */
+    FSB_PREV_DENSITY = 3, /* prevDensity   (scratch) */
+    FSB_PREV_VEL_X = 4,   /* prevVelocityX (scratch; pressure during project) */
+    FSB_PREV_VEL_Y = 5    /* prevVelocityY (scratch; divergence during project) */
+};
+
+/* advection schemes (reference: src/fluid_sim.cpp:212-228; RK4 is the live call :219) */
+enum { FSB_ADVECT_RK4 = 0, FSB_ADVECT_MACCORMACK = 1, FSB_ADVECT_SEMI_LAGRANGIAN = 2 };
+
+/* velocity-noise modes (reference: src/fluid_sim.cpp:374-383) */
+enum {
+    FSB_NOISE_GLIBC = 0,  /* glibc rand() stream, addressed by position (bit-exact with the reference) */
+    FSB_NOISE_ZERO = 1    /* rand() == 0x3FFFFFFF for every call: the noise term is exactly 0 */
+};
+
+typedef struct fsb_params {
+    int width;             /* GRID_SIZE_X, include/fluid_sim.h:11 (default 200) */
+    int height;            /* GRID_SIZE_Y, include/fluid_sim.h:12 (default 200) */
+    int proj_iters;        /* Gauss-Seidel sweeps per projection, src/fluid_sim.cpp:319 (20) */
+    int diff_iters;        /* SOR sweeps per diffusion, src/fluid_sim.cpp:50 (5) */
+    float viscosity;       /* VISCOSITY, include/fluid_sim.h:13 (1e-4) */
+    float diffusion;       /* DIFFUSION, include/fluid_sim.h:14 (0) */
+    float omega;           /* SOR relaxation factor, src/fluid_sim.cpp:47 (1.5) */
+    int advect_scheme;     /* FSB_ADVECT_*, src/fluid_sim.cpp:219-227 (RK4) */
+    int noise_mode;        /* FSB_NOISE_* */
+    uint32_t noise_seed;   /* srand() seed of the emulated stream (1 = glibc default) */
+    uint64_t noise_pos;    /* number of rand() outputs already consumed by the process */
+    int device;            /* CUDA device ordinal, -1 = current device */
+    int reserved[7];
+} fsb_params;
+
+/* Fill *p with the reference's literals (200x200, 20/5 sweeps, ...). */
+void fsb_default_params(fsb_params *p);
+
+/* Replaces FluidSim::FluidSim() (src/fluid_sim.cpp:4-21): zero-filled fields on the device. */
+int fsb_create(const fsb_params *p, fsb_sim **out);
+int fsb_destroy(fsb_sim *s);
+
+/* Replaces `sim = FluidSim();` (src/main.cpp:289): zero all fields; like the
+ * reference, the position in the rand() stream is NOT rewound. */
+int fsb_reset(fsb_sim *s);
+
+/* Replaces FluidSim::step (src/fluid_sim.cpp:23-28).  Asynchronous: returns once the
+ * work is queued on the simulation's stream; readers synchronise. */
+int fsb_step(fsb_sim *s, float dt);
+int fsb_sync(fsb_sim *s);
+
+/* Replace FluidSim::addDensity / addVelocity (src/fluid_sim.cpp:424-439): out-of-range
+ * coordinates are silently ignored, amounts are += in call order. */
+int fsb_add_density(fsb_sim *s, int x, int y, float amount);
+int fsb_add_velocity(fsb_sim *s, int x, int y, float ax, float ay);
+/* Batched forms of the same (one call per mouse event / injection pattern). */
+int fsb_add_density_n(fsb_sim *s, int n, const int *xs, const int *ys, const float *amounts);
+int fsb_add_velocity_n(fsb_sim *s, int n, const int *xs, const int *ys, const float *axs, const float *ays);
+
+/* Replace FluidSim::getDensity / getVelocity (src/fluid_sim.cpp:441-457): out of range
+ * yields 0.  Served from a host mirror that is refreshed lazily after a step. */
+int fsb_get_density(fsb_sim *s, int x, int y, float *out);
+int fsb_get_velocity(fsb_sim *s, int x, int y, float *out_xy);
+/* Replace getNormalizedVelocity / getVelocityMagnitude / getVelocityColor
+ * (src/fluid_sim.cpp:459-519). */
+int fsb_get_normalized_velocity(fsb_sim *s, int x, int y, float *out_xy);
+int fsb_get_velocity_magnitude(fsb_sim *s, int x, int y, float *out);
+int fsb_get_velocity_color(fsb_sim *s, int x, int y, float *out_rgb);
+/* Replace getWidth / getHeight (include/fluid_sim.h:36-37). */
+int fsb_get_width(const fsb_sim *s);
+int fsb_get_height(const fsb_sim *s);
+
+/* Whole-field transfers with HOST buffers of width*height floats (the bulk form of the
+ * per-cell getters the reference's render loop issues, src/main.cpp:388-396). */
+int fsb_read_field(fsb_sim *s, int field, float *host_dst);
+int fsb_write_field(fsb_sim *s, int field, const float *host_src);
+/* density += host_src (one addDensity per cell); velocity likewise */
+int fsb_add_field(fsb_sim *s, int field, const float *host_src);
+
+/* Page-locked host buffers for the whole-field transfers above (optional; any host pointer works,
+ * pinned ones copy at full PCIe rate).  No counterpart in the reference. */
+void *fsb_host_alloc(size_t bytes);
+void fsb_host_free(void *p);
+
+/* Device pointer of a field (valid until the next step swaps buffers); for callers
+ * that keep their data on the GPU. */
+int fsb_device_field(fsb_sim *s, int field, void **dptr);
+
+/* Position bookkeeping of the emulated rand() stream (2*width*height outputs per step). */
+int fsb_get_noise_pos(const fsb_sim *s, uint64_t *pos);
+int fsb_set_noise(fsb_sim *s, int mode, uint32_t seed, uint64_t pos);
+
+/* The reference's private passes, exposed for per-kernel parity tests.  `b` is the
+ * boundary kind of setBoundary (0 scalar, 1 x-velocity, 2 y-velocity). */
+int fsb_op_add_noise(fsb_sim *s);                                          /* src/fluid_sim.cpp:374-383 */
+int fsb_op_set_boundary(fsb_sim *s, int b, int field);                     /* :347-367 */
+int fsb_op_diffuse(fsb_sim *s, int b, int field, float diff, float dt);    /* :43-62 (src == field's content on entry) */
+int fsb_op_project(fsb_sim *s);                                            /* :301-344 on velocityX/velocityY */
+int fsb_op_advect(fsb_sim *s, int b, int dst, int src, int u, int v, float dt); /* :212-298 */
+int fsb_op_velocity_step(fsb_sim *s, float dt);                            /* :370-406 */
+int fsb_op_density_step(fsb_sim *s, float dt);                             /* :409-422 */
+
+/* Number of kernels this library has launched on behalf of `s` so far. */
+int fsb_launch_count(const fsb_sim *s, uint64_t *count);
+
+/* Tuning knobs for experiments (0 = library default). */
+int fsb_set_tuning(fsb_sim *s, int warps_per_cta, int max_sweeps_per_pass);
+
+const char *fsb_last_error(void);
+const char *fsb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLUID_SIM_B200_H */

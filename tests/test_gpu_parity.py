@@ -1,0 +1,271 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle on the same
+seeded inputs.  The bar is bit-exact (float32 fields compared as uint32); north_star's tolerance of
+1e-5 relative max-abs per field is therefore met with zero error.
+"""
+import numpy as np
+import pytest
+
+import fluid_sim_b200 as fsb
+from oracle import orasim, refsim
+from oracle.orasim import OracleSim
+from tests.util import (apply_golden_inputs, assert_bits, demo_injection, load_golden, random_field, rel_max_abs,
+                        vortex_lattice)
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5  # north_star: relative max-abs per field (expected: exactly 0)
+
+SIZES = [(16, 16), (48, 40), (33, 70), (131, 257), (200, 200), (96, 1100)]
+
+
+def make_pair(w, h, p=20, d=5, **kw):
+    gpu = fsb.FluidSim(w, h, p, d, **kw)
+    okw = {}
+    for k in ("viscosity", "diffusion", "omega"):
+        if k in kw:
+            okw[{"viscosity": "visc", "diffusion": "diff", "omega": "omega"}[k]] = kw[k]
+    if "advect_scheme" in kw:
+        okw["scheme"] = kw["advect_scheme"]
+    if "noise" in kw:
+        okw["noise"] = kw["noise"]
+    ora = OracleSim(w, h, p, d, **okw)
+    return gpu, ora
+
+
+def seed_state(gpu, ora, rng, w, h, scale=0.5):
+    for fid in (0, 1, 2):
+        f = random_field(rng, w, h, scale)
+        if fid == 0:
+            f = np.abs(f)
+        gpu.write(fid, f)
+        ora.write(fid, f)
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+@pytest.mark.parametrize("b", [0, 1, 2])
+def test_set_boundary(w, h, b):
+    gpu, ora = make_pair(w, h)
+    rng = np.random.default_rng(b + w)
+    f = random_field(rng, w, h)
+    gpu.write(fsb.VELOCITY_X, f); ora.write(orasim.VEL_X, f)
+    gpu.setBoundary(b, fsb.VELOCITY_X); ora.setBoundary(b, orasim.VEL_X)
+    assert_bits(gpu.read(fsb.VELOCITY_X), ora.read(orasim.VEL_X), f"setBoundary b={b}")
+
+
+@pytest.mark.parametrize("w,h", SIZES + [(300, 300)])
+def test_noise_matches_glibc_stream(w, h):
+    gpu, ora = make_pair(w, h)
+    rng = np.random.default_rng(w)
+    seed_state(gpu, ora, rng, w, h)
+    for _ in range(3):   # three steps' worth: checks the position bookkeeping between steps
+        gpu.addNoise(); ora.addNoise()
+    assert gpu.noise_pos() == 3 * 2 * w * h
+    assert_bits(gpu.read(fsb.VELOCITY_X), ora.read(orasim.VEL_X), "noise velX")
+    assert_bits(gpu.read(fsb.VELOCITY_Y), ora.read(orasim.VEL_Y), "noise velY")
+
+
+def test_noise_at_arbitrary_stream_position():
+    w, h = 64, 48
+    pos = 1234567
+    gpu = fsb.FluidSim(w, h, noise_pos=pos)
+    ora = OracleSim(w, h, skip=pos)
+    gpu.addNoise(); ora.addNoise()
+    assert_bits(gpu.read(fsb.VELOCITY_X), ora.read(orasim.VEL_X), "velX")
+    assert_bits(gpu.read(fsb.VELOCITY_Y), ora.read(orasim.VEL_Y), "velY")
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+@pytest.mark.parametrize("b", [0, 1, 2])
+def test_diffuse(w, h, b):
+    gpu, ora = make_pair(w, h)
+    rng = np.random.default_rng(10 * b + h)
+    f = random_field(rng, w, h)
+    gpu.write(fsb.VELOCITY_X, f); ora.write(orasim.VEL_X, f); ora.write(orasim.PREV_VEL_X, f)
+    diff = 0.0001 * 30
+    gpu.diffuse(b, fsb.VELOCITY_X, diff, 0.01)
+    ora.diffuse(b, orasim.VEL_X, orasim.PREV_VEL_X, diff, 0.01)
+    assert_bits(gpu.read(fsb.VELOCITY_X), ora.read(orasim.VEL_X), f"diffuse b={b}")
+
+
+@pytest.mark.parametrize("D,cap", [(1, 0), (3, 0), (7, 0), (5, 2), (12, 5), (0, 0)])
+def test_diffuse_sweep_counts(D, cap):
+    """Sweep counts that need several passes (the source field must stay the pre-diffusion copy)."""
+    w, h = 70, 90
+    gpu = fsb.FluidSim(w, h, 20, D, max_sweeps_per_pass=cap)
+    ora = OracleSim(w, h, 20, D)
+    rng = np.random.default_rng(D)
+    f = random_field(rng, w, h)
+    gpu.write(fsb.VELOCITY_Y, f); ora.write(orasim.VEL_Y, f); ora.write(orasim.PREV_VEL_Y, f)
+    gpu.diffuse(2, fsb.VELOCITY_Y, 0.002, 0.01)
+    ora.diffuse(2, orasim.VEL_Y, orasim.PREV_VEL_Y, 0.002, 0.01)
+    assert_bits(gpu.read(fsb.VELOCITY_Y), ora.read(orasim.VEL_Y), f"diffuse D={D}")
+
+
+def test_diffuse_zero_coefficient():
+    """DIFFUSION == 0 (include/fluid_sim.h:14): identity on the interior plus the boundary update."""
+    w, h = 50, 64
+    gpu, ora = make_pair(w, h)
+    rng = np.random.default_rng(5)
+    f = random_field(rng, w, h)
+    f[3, 4] = -0.0
+    gpu.write(fsb.DENSITY, f); ora.write(orasim.DENSITY, f); ora.write(orasim.PREV_DENSITY, f)
+    gpu.diffuse(0, fsb.DENSITY, 0.0, 0.01)
+    ora.diffuse(0, orasim.DENSITY, orasim.PREV_DENSITY, 0.0, 0.01)
+    assert_bits(gpu.read(fsb.DENSITY), ora.read(orasim.DENSITY), "diffuse a=0")
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+def test_project(w, h):
+    gpu, ora = make_pair(w, h)
+    rng = np.random.default_rng(w * h)
+    seed_state(gpu, ora, rng, w, h)
+    gpu.project(); ora.project()
+    assert_bits(gpu.read(fsb.PREV_VEL_X), ora.read(orasim.PREV_VEL_X), "pressure")
+    assert_bits(gpu.read(fsb.VELOCITY_X), ora.read(orasim.VEL_X), "velX after project")
+    assert_bits(gpu.read(fsb.VELOCITY_Y), ora.read(orasim.VEL_Y), "velY after project")
+
+
+@pytest.mark.parametrize("P,cap,warps", [(1, 0, 0), (3, 0, 1), (7, 0, 2), (40, 0, 0), (20, 5, 8), (33, 10, 4), (0, 0, 0)])
+def test_project_sweep_counts(P, cap, warps):
+    w, h = 90, 150
+    gpu = fsb.FluidSim(w, h, P, 5, max_sweeps_per_pass=cap, warps_per_cta=warps)
+    ora = OracleSim(w, h, P, 5)
+    rng = np.random.default_rng(P)
+    seed_state(gpu, ora, rng, w, h)
+    gpu.project(); ora.project()
+    assert_bits(gpu.read(fsb.VELOCITY_X), ora.read(orasim.VEL_X), f"velX P={P}")
+    assert_bits(gpu.read(fsb.VELOCITY_Y), ora.read(orasim.VEL_Y), f"velY P={P}")
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+@pytest.mark.parametrize("scheme", [fsb.ADVECT_RK4, fsb.ADVECT_MACCORMACK, fsb.ADVECT_SEMI_LAGRANGIAN])
+def test_advect(w, h, scheme):
+    gpu, ora = make_pair(w, h, advect_scheme=scheme)
+    rng = np.random.default_rng(scheme + w)
+    seed_state(gpu, ora, rng, w, h, scale=3.0)
+    for b in (0, 1, 2):
+        gpu.advect(b, fsb.PREV_DENSITY, fsb.DENSITY, fsb.VELOCITY_X, fsb.VELOCITY_Y, 0.01)
+        ora.advect(b, orasim.PREV_DENSITY, orasim.DENSITY, orasim.VEL_X, orasim.VEL_Y, 0.01)
+        assert_bits(gpu.read(fsb.PREV_DENSITY), ora.read(orasim.PREV_DENSITY), f"advect scheme={scheme} b={b}")
+
+
+@pytest.mark.parametrize("name", ["config1_200x200_p20_d5", "small_48x40_p3_d2", "odd_257x131_p20_d5",
+                                  "tall_131x257_p7_d3"])
+def test_step_against_reference_golden(name):
+    """Whole-step parity against fields produced by the unmodified reference (tests/golden)."""
+    g = load_golden(name)
+    w, h, p, d = int(g["w"]), int(g["h"]), int(g["p"]), int(g["d"])
+    gpu = fsb.FluidSim(w, h, p, d)
+    apply_golden_inputs(gpu, g)
+    checkpoints = sorted(int(k[2:]) for k in g.files if k.startswith("d_"))
+    step = 0
+    for cp in checkpoints:
+        while step < cp:
+            gpu.step(0.01)
+            step += 1
+        dd, uu, vv = gpu.fields()
+        for got, key in ((dd, "d"), (uu, "u"), (vv, "v")):
+            want = g[f"{key}_{cp}"]
+            assert rel_max_abs(got, want) <= TOL, f"{name} {key} step {cp}"
+            assert_bits(got, want, f"{name} {key} step {cp}")
+
+
+@pytest.mark.parametrize("scheme", [fsb.ADVECT_MACCORMACK, fsb.ADVECT_SEMI_LAGRANGIAN])
+def test_step_alternative_schemes(scheme):
+    w, h = 80, 72
+    gpu, ora = make_pair(w, h, advect_scheme=scheme)
+    for s in (gpu, ora):
+        demo_injection(s, w, h)
+    for _ in range(5):
+        gpu.step(0.01); ora.step(0.01)
+    for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+        assert_bits(a, b, f"scheme {scheme} field {n}")
+
+
+def test_step_with_diffusion_and_zero_noise():
+    w, h = 60, 84
+    gpu, ora = make_pair(w, h, 7, 3, diffusion=0.0003, viscosity=0.002, noise="zero")
+    d, u, v = vortex_lattice(w, h)
+    for s, ids in ((gpu, (fsb.DENSITY, fsb.VELOCITY_X, fsb.VELOCITY_Y)), (ora, (0, 1, 2))):
+        s.write(ids[0], d); s.write(ids[1], u); s.write(ids[2], v)
+    for _ in range(4):
+        gpu.step(0.01); ora.step(0.01)
+    for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+        assert_bits(a, b, f"field {n}")
+
+
+def test_step_2048_config2():
+    """Config 2 (2048^2, P=20): two steps of the vortex lattice against the oracle."""
+    w = h = 2048
+    gpu, ora = make_pair(w, h)
+    d, u, v = vortex_lattice(w, h)
+    gpu.add_field(fsb.DENSITY, d); gpu.add_field(fsb.VELOCITY_X, u); gpu.add_field(fsb.VELOCITY_Y, v)
+    ora.write(0, d); ora.write(1, u); ora.write(2, v)
+    for _ in range(2):
+        gpu.step(0.01); ora.step(0.01)
+    for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+        assert_bits(a, b, f"2048^2 field {n}")
+
+
+def test_step_real_reference_wide():
+    """A wide grid (35 strips, several CTAs in the chain) against the real reference, if prebuilt."""
+    w, h, p, d = 96, 1100, 20, 5
+    if not refsim.available(w, h, p, d):
+        pytest.skip("oracle/_ref not present")
+    ref = refsim.RefSim(w, h, p, d, seed=1)
+    gpu = fsb.FluidSim(w, h, p, d)
+    rng = np.random.default_rng(2)
+    for fid in (0, 1, 2):
+        f = random_field(rng, w, h, 0.5)
+        ref.write(fid, f); gpu.write(fid, f)
+    for _ in range(3):
+        ref.step(0.01); gpu.step(0.01)
+    for a, b, n in zip(gpu.fields(), ref.fields(), "duv"):
+        assert_bits(a, b, f"wide field {n}")
+
+
+def test_api_semantics():
+    """Bounds behaviour and immediate visibility of adds (src/fluid_sim.cpp:424-457), reset (main.cpp:289)."""
+    gpu = fsb.FluidSim(32, 24, noise="zero")
+    gpu.addDensity(-1, 0, 5.0); gpu.addDensity(32, 0, 5.0); gpu.addDensity(0, 24, 5.0)   # ignored
+    gpu.addVelocity(3, -1, 1.0, 1.0)                                                        # ignored
+    assert gpu.getDensity(-1, 0) == 0 and gpu.getDensity(40, 2) == 0
+    assert gpu.getVelocity(0, 99) == (0, 0)
+    gpu.addDensity(3, 4, 1.5); gpu.addDensity(3, 4, 2.25)
+    assert gpu.getDensity(3, 4) == np.float32(3.75)
+    gpu.addVelocity(5, 6, 3.0, 4.0)
+    assert gpu.getVelocity(5, 6) == (3.0, 4.0)
+    assert gpu.getVelocityMagnitude(5, 6) == np.float32(5.0)
+    assert gpu.getNormalizedVelocity(5, 6) == (np.float32(0.6), np.float32(0.8))
+    gpu.addDensity(3, 4, 1.0)                     # after a read: mirror and device both see it
+    assert gpu.getDensity(3, 4) == np.float32(4.75)
+    assert gpu.read(fsb.DENSITY)[3, 4] == np.float32(4.75)
+    assert gpu.read(fsb.DENSITY).sum() == np.float32(4.75)
+    assert gpu.getWidth() == 32 and gpu.getHeight() == 24
+    gpu.step(0.01)
+    assert gpu.read(fsb.DENSITY).sum() > 0
+    gpu.reset()
+    assert not gpu.read(fsb.DENSITY).any() and not gpu.read(fsb.VELOCITY_X).any()
+    assert gpu.launch_count() > 0
+
+
+def test_getters_match_oracle():
+    gpu, ora = make_pair(40, 40)
+    for s in (gpu, ora):
+        s.addVelocity(5, 6, 3.0, 4.0); s.addVelocity(7, 8, 0.0005, 0.0); s.addVelocity(9, 9, 30.0, 40.0)
+        s.addVelocity(1, 1, 2.0, 1.0); s.addVelocity(2, 2, 5.5, 2.0)
+    for (x, y) in [(5, 6), (7, 8), (9, 9), (1, 1), (2, 2), (0, 0), (-1, 3), (40, 0)]:
+        assert gpu.getVelocityMagnitude(x, y) == ora.getVelocityMagnitude(x, y)
+        assert gpu.getNormalizedVelocity(x, y) == ora.getNormalizedVelocity(x, y)
+        assert gpu.getVelocityColor(x, y) == ora.getVelocityColor(x, y)
+
+
+def test_two_sims_share_nothing():
+    a = fsb.FluidSim(64, 64); b = fsb.FluidSim(64, 64)
+    demo_injection(a, 64, 64); demo_injection(b, 64, 64)
+    for _ in range(3):
+        a.step(0.01)
+    for _ in range(3):
+        b.step(0.01)
+    for x, y in zip(a.fields(), b.fields()):
+        assert_bits(x, y, "independent sims")
