@@ -1,0 +1,366 @@
+#!/usr/bin/env python3
+"""Benchmark of the B200-native FluidSim::step (contract: see the task description / DESIGN.md).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference]
+
+A "step" is one FluidSim::step (velocityStep + densityStep, src/fluid_sim.cpp:23-28) over the whole
+grid.  At N=1 the workload is BASELINE.json configs[2]: 8192 x 8192, 40 projection sweeps, 5 diffusion
+sweeps, dt 0.01, vortex-lattice input, glibc rand() noise.  The metric is
+cell-updates/s = W*H*steps / time.  One JSON line is printed by rank 0.
+
+Keys beyond the base contract:
+  roofline      dominant kernel (one fused Gauss-Seidel pass): effective GB/s = algorithmic bytes of
+                the reference's pass structure (12 B per cell per sweep) / measured
+                launch time, against MEASURED_PEAKS.json; `compulsory_gbs` is the same launch counted
+                at its own compulsory traffic (inputs read once, result written once).
+  step_roofline whole step at B(P) = 356 + 24 P bytes per cell.
+  cpu_baseline  the real reference (oracle/_ref) timed on this host on a bounded sample.
+  e2e           the reference's frame loop through the C ABI with host buffers: mouse-patch injection
+                (src/main.cpp:216-252), step, full density read-back (src/main.cpp:388-396).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "cell_updates_per_sec"
+UNIT = "cell-updates/s"
+
+
+def algorithmic_bytes_per_cell(P, D=5):
+    """B(P) of SURVEY.md 8(d): noise 16 + copies 48 + diffuse 3*12*D + 2*(36 + 12 P) + advect 40."""
+    return 16 + 48 + 3 * 12 * D + 2 * (36 + 12 * P) + 40
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------------------------
+# reference arm / CPU baseline: the real reference built by oracle/build_ref.py
+# --------------------------------------------------------------------------------------------
+REF_SAMPLES = [(8192, 8192), (1024, 8192), (512, 8192), (256, 8192), (128, 8192)]
+REF_RATE_GUESS = 1.0e6   # cell-updates/s of one host core, to size the sample
+
+
+def pick_reference_sample(H, P, nsteps, budget_s):
+    from oracle import refsim
+    for (w, h) in REF_SAMPLES:
+        if h == H and refsim.available(w, h, P, 5) and w * h * nsteps / REF_RATE_GUESS <= budget_s:
+            return w, h
+    for (w, h) in reversed(REF_SAMPLES):
+        if h == H and refsim.available(w, h, P, 5):
+            return w, h
+    return None
+
+
+def run_reference_sample(w, h, P, nsteps, warmup):
+    """Times the real reference's step() on a w x h grid (same columns as the workload)."""
+    from oracle import refsim
+    from tests.util import vortex_lattice
+    sim = refsim.RefSim(w, h, P, 5, seed=1)
+    d, u, v = vortex_lattice(w, h)
+    sim.write(refsim.DENSITY, d); sim.write(refsim.VEL_X, u); sim.write(refsim.VEL_Y, v)
+    for _ in range(warmup):
+        sim.step(0.01)
+    t0 = time.perf_counter()
+    for _ in range(nsteps):
+        sim.step(0.01)
+    dt = time.perf_counter() - t0
+    sim.close()
+    return w * h * nsteps / dt, dt / nsteps
+
+
+def run_oracle_sample(w, h, P, nsteps, warmup):
+    from oracle.orasim import OracleSim
+    from tests.util import vortex_lattice
+    sim = OracleSim(w, h, P, 5)
+    d, u, v = vortex_lattice(w, h)
+    sim.write(0, d); sim.write(1, u); sim.write(2, v)
+    for _ in range(warmup):
+        sim.step(0.01)
+    t0 = time.perf_counter()
+    for _ in range(nsteps):
+        sim.step(0.01)
+    dt = time.perf_counter() - t0
+    return w * h * nsteps / dt, dt / nsteps
+
+
+def cpu_reference(H, P, nsteps, warmup, budget_s):
+    """(value, ms_per_step, kind, sample description)"""
+    pick = pick_reference_sample(H, P, nsteps + warmup, budget_s)
+    if pick is not None:
+        w, h = pick
+        v, spt = run_reference_sample(w, h, P, nsteps, warmup)
+        return v, spt * 1e3, "reference", f"{w}x{h} rows x cols of the {H}-column workload, P={P}, {nsteps} step(s), real reference (oracle/_ref)"
+    w = max(16, int(budget_s * REF_RATE_GUESS / max(1, (nsteps + warmup) * H)))
+    v, spt = run_oracle_sample(w, H, P, nsteps, warmup)
+    return v, spt * 1e3, "port", f"{w}x{H} slab, P={P}, {nsteps} step(s), C restatement (oracle/fluid_oracle.c)"
+
+
+def workload_for(n_gpus, args):
+    if args.width and args.height:
+        return args.width, args.height, args.proj or 40, "custom"
+    if n_gpus == 1:
+        return 8192, 8192, args.proj or 40, "config3: 8192x8192 grid, 40 projection sweeps, 1xB200"
+    # config 5 of BASELINE.json, weak-scaled: 4096 rows x 32768 columns per GPU, P = 100
+    return 4096, 32768, args.proj or 100, "config5: 32768-column grid, 4096 rows per GPU, 100 projection sweeps"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--width", type=int, default=0)
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--proj", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--warps-per-cta", type=int, default=0)
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    n_gpus = max(args.gpus, world)
+    K, Wm = args.steps, max(args.warmup, 0)
+    W, H, P, workload = workload_for(n_gpus, args)
+
+    # ------------------------------------------------------------------ reference arm
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        value, ms, kind, sample = cpu_reference(H, P, K, Wm, budget_s=150.0)
+        line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": K,
+                "warmup": Wm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": workload, "grid": [W, H], "proj_iters": P, "diff_iters": 5, "dt": 0.01,
+                           "input": "vortex lattice (SURVEY.md 8(d) I3) + glibc rand() noise"},
+                "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample},
+                "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return 0
+
+    # ------------------------------------------------------------------ native arm
+    import torch
+    import torch.distributed as dist
+    import fluid_sim_b200 as fsb
+    from tests.util import vortex_lattice
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device: the native arm has no CPU fallback"}))
+        return 1
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sim = fsb.FluidSim(W, H, P, 5, device=local_rank, warps_per_cta=args.warps_per_cta)
+    stream = torch.cuda.ExternalStream(sim.stream(), device=torch.device("cuda", local_rank))
+
+    # synthetic input, built on the host in page-locked memory and injected through the C ABI
+    d, u, v = vortex_lattice(W, H)
+    buf = sim.pinned_array()
+    for fid, arr in ((fsb.DENSITY, d), (fsb.VELOCITY_X, u), (fsb.VELOCITY_Y, v)):
+        buf[...] = arr
+        sim.add_field(fid, buf)
+    del d, u, v
+
+    for _ in range(max(Wm, 3) if K > 0 else 0):
+        sim.step(0.01)
+    sim.sync()
+
+    # -------- value: K steps, state resident in HBM, CUDA events on the launching stream
+    sim.profile_enable(True)
+    sim.profile_read(reset=True)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    l0 = sim.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for _ in range(K):
+        sim.step(0.01)
+    ev1.record(stream)
+    sim.sync()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = sim.launch_count() - l0
+    prof = sim.profile_read(reset=True)
+    sim.profile_enable(False)
+    if world > 1:
+        t = torch.tensor([ms_total], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_per_step = ms_total / K
+    cells_total = W * H * world
+    value = cells_total * K / (ms_total * 1e-3)
+
+    # -------- e2e: the reference's frame loop with host buffers (inject patch, step, read density back)
+    patch = [(i, j) for i in range(-3, 4) for j in range(-3, 4)]
+    xs = np.array([W // 2 + i for i, _ in patch], np.int32)
+    ys = np.array([H // 3 + j for _, j in patch], np.int32)
+    ones = np.full(len(patch), 1.0, np.float32)
+    dx = np.full(len(patch), 0.05, np.float32)
+    dy = np.full(len(patch), -0.02, np.float32)
+    h2d = xs.nbytes * 2 + ys.nbytes * 2 + ones.nbytes + dx.nbytes + dy.nbytes
+    d2h = W * H * 4
+    for _ in range(2):
+        sim.addDensityN(xs, ys, ones); sim.addVelocityN(xs, ys, dx, dy); sim.step(0.01); sim.read(fsb.DENSITY, buf)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(K):
+        sim.addDensityN(xs, ys, ones)
+        sim.addVelocityN(xs, ys, dx, dy)
+        sim.step(0.01)
+        sim.read(fsb.DENSITY, buf)
+    e1.record(stream)
+    sim.sync()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    e2e_value = cells_total * K / (e2e_ms * 1e-3)
+    checksum = float(buf.astype(np.float64).sum())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # -------- roofline of the dominant kernel and of the whole step
+    peak, peak_src = measured_peak_gbs()
+    gs_ms, gs_n = prof["gs"]
+    levels = 20 if P >= 20 else P
+    gs_launch_ms = gs_ms / max(gs_n, 1)
+    cells = W * H
+    algo_bytes = 12.0 * levels * cells               # reference pass structure: 12 B per cell per sweep
+    npass = max(1, -(-P // 20))
+    compulsory = (8.0 + 12.0 * (npass - 1)) / npass * cells   # rhs read + result written (+ iterate read after pass 1)
+    achieved = algo_bytes / (gs_launch_ms * 1e-3) / 1e9 if gs_launch_ms > 0 else 0.0
+    roofline = {"kernel": f"wf_kernel<{levels}, GaussSeidel> (one fused pass of {levels} sweeps)",
+                "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "launch_ms": gs_launch_ms, "launches_timed": gs_n,
+                "algorithmic_bytes_per_launch": algo_bytes,
+                "compulsory_gbs": compulsory / (gs_launch_ms * 1e-3) / 1e9 if gs_launch_ms > 0 else 0.0,
+                "note": "effective GB/s: sweeps are fused in registers, so real DRAM traffic is far below the "
+                        "reference's pass structure; see profiles/ for ncu dram bytes"}
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            tr = json.load(open(traffic_file))
+            key = f"{W}x{H}_gs{levels}"
+            if key in tr:
+                roofline["traffic"] = tr[key]
+        except Exception:
+            pass
+    Bp = algorithmic_bytes_per_cell(P)
+    step_gbs = Bp * cells / (ms_per_step * 1e-3) / 1e9
+    step_roofline = {"bytes_per_cell": Bp, "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak}
+    shares = {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items()}
+
+    # -------- CPU baseline: the real reference on this host, bounded sample
+    if args.no_cpu_baseline or world > 1:
+        cpu = None
+    else:
+        cv, cms, kind, sample = cpu_reference(H, P, 1, 0, budget_s=25.0)
+        cpu = {"value": cv, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample, "ms_per_step_of_sample": cms,
+               "host_cores_visible": os.cpu_count()}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(Wm, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload, "grid_per_gpu": [W, H], "proj_iters": P, "diff_iters": 5, "dt": 0.01,
+                       "input": "vortex lattice (SURVEY.md 8(d) I3) + glibc rand() noise",
+                       "l2": "fields are larger than L2 (no flush needed)" if cells * 4 > 126e6 else "fields fit in L2",
+                       "decomposition": "single GPU" if world == 1 else
+                       "independent 4096-row slabs, one per GPU (slab coupling across GPUs is not implemented yet)"},
+            "roofline": roofline, "step_roofline": step_roofline, "kernel_ms_per_step": shares,
+            "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": e2e_ms / K, "density_checksum": checksum},
+            "gpu_launches": int(launches), "clocks": clocks}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

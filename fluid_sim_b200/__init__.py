@@ -88,6 +88,9 @@ ABI = [
     ("fsb_op_advect", C.c_int, [_SIM, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float]),
     ("fsb_op_velocity_step", C.c_int, [_SIM, C.c_float]),
     ("fsb_op_density_step", C.c_int, [_SIM, C.c_float]),
+    ("fsb_get_stream", C.c_int, [_SIM, C.POINTER(C.c_void_p)]),
+    ("fsb_profile_enable", C.c_int, [_SIM, C.c_int]),
+    ("fsb_profile_read", C.c_int, [_SIM, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
     ("fsb_launch_count", C.c_int, [_SIM, C.POINTER(C.c_uint64)]),
     ("fsb_set_tuning", C.c_int, [_SIM, C.c_int, C.c_int]),
     ("fsb_last_error", C.c_char_p, []),
@@ -262,6 +265,24 @@ class FluidSim:
         v = C.c_uint64()
         self._check(self._lib.fsb_launch_count(self._h, C.byref(v)))
         return v.value
+
+    def stream(self):
+        p = C.c_void_p()
+        self._check(self._lib.fsb_get_stream(self._h, C.byref(p)))
+        return p.value
+
+    PROF_NAMES = ("noise", "sor", "gs", "divergence", "gradient", "advect_velocity", "advect_scalar", "boundary")
+
+    def profile_enable(self, on=True):
+        self._check(self._lib.fsb_profile_enable(self._h, 1 if on else 0))
+
+    def profile_read(self, reset=True):
+        """{class: (total_ms, launches)} accumulated since the last reset; synchronises."""
+        n = len(self.PROF_NAMES)
+        ms = (C.c_double * n)()
+        cnt = (C.c_uint64 * n)()
+        self._check(self._lib.fsb_profile_read(self._h, ms, cnt, 1 if reset else 0))
+        return {name: (ms[i], cnt[i]) for i, name in enumerate(self.PROF_NAMES)}
 
     def set_tuning(self, warps_per_cta=0, max_sweeps_per_pass=0):
         self._check(self._lib.fsb_set_tuning(self._h, warps_per_cta, max_sweeps_per_pass))

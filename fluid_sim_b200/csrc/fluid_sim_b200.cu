@@ -76,6 +76,13 @@ struct fsb_sim {
     uint64_t launches = 0;
     int tune_warps = 0;
     int tune_levels = 0;
+    // optional per-kernel-class timing (CUDA events on the simulation's stream)
+    bool profiling = false;
+    struct ProfRec { int cat; cudaEvent_t a, b; };
+    std::vector<ProfRec> prof_open;                 // recorded, not yet read back
+    std::vector<cudaEvent_t> prof_free;             // recycled events
+    double prof_ms[FSB_PROF_COUNT] = {0};
+    uint64_t prof_n[FSB_PROF_COUNT] = {0};
 };
 
 namespace {
@@ -93,6 +100,37 @@ struct DeviceGuard {
     ~DeviceGuard()
     {
         if (switched) cudaSetDevice(prev);
+    }
+};
+
+cudaEvent_t prof_event(fsb_sim *s)
+{
+    cudaEvent_t e = nullptr;
+    if (!s->prof_free.empty()) {
+        e = s->prof_free.back();
+        s->prof_free.pop_back();
+    } else if (cudaEventCreate(&e) != cudaSuccess) {
+        e = nullptr;
+    }
+    return e;
+}
+
+// Brackets the kernels launched inside its scope with two events when profiling is on.
+struct ProfScope {
+    fsb_sim *s;
+    int cat;
+    cudaEvent_t a = nullptr;
+    ProfScope(fsb_sim *sim, int c) : s(sim), cat(c)
+    {
+        if (s->profiling && (a = prof_event(s))) cudaEventRecord(a, s->stream);
+    }
+    ~ProfScope()
+    {
+        if (!a) return;
+        cudaEvent_t b = prof_event(s);
+        if (!b) { s->prof_free.push_back(a); return; }
+        cudaEventRecord(b, s->stream);
+        s->prof_open.push_back(fsb_sim::ProfRec{cat, a, b});
     }
 };
 
@@ -129,6 +167,7 @@ int set_noise_window(fsb_sim *s, uint32_t seed, uint64_t pos)
 
 int set_boundary(fsb_sim *s, const BndJob *jobs, int n)
 {
+    ProfScope ps(s, FSB_PROF_BOUNDARY);
     FSB_CUDA(launch_set_boundary(jobs, n, s->W, s->H, s->stream));
     s->launches += 1;
     return FSB_OK;
@@ -225,7 +264,10 @@ int diffuse_fields(fsb_sim *s, int nf, float *const *xs, const int *bs, float di
         L.omega = s->prm.omega;
         L.warps_per_cta = s->tune_warps;
         int nl = 0;
-        FSB_CUDA(launch_sweep_pass(L, s->sweep, s->stream, &nl));
+        {
+            ProfScope ps(s, FSB_PROF_SOR);
+            FSB_CUDA(launch_sweep_pass(L, s->sweep, s->stream, &nl));
+        }
         s->launches += nl;
         BndJob jobs[2];
         for (int i = 0; i < nf; ++i) jobs[i] = BndJob{xs[i], bs[i], 0};
@@ -237,7 +279,10 @@ int diffuse_fields(fsb_sim *s, int nf, float *const *xs, const int *bs, float di
 // project() of src/fluid_sim.cpp:301-344
 int project(fsb_sim *s, float *u, float *v, float *p, float *div)
 {
-    FSB_CUDA(launch_divergence(u, v, div, s->W, s->H, s->stream));
+    {
+        ProfScope ps(s, FSB_PROF_DIVERGENCE);
+        FSB_CUDA(launch_divergence(u, v, div, s->W, s->H, s->stream));
+    }
     s->launches += 1;
     const std::vector<int> passes = split_levels(s->prm.proj_iters, s->tune_levels);
     if (passes.empty()) FSB_CUDA(cudaMemsetAsync(p, 0, s->ncells * sizeof(float), s->stream));
@@ -254,11 +299,17 @@ int project(fsb_sim *s, float *u, float *v, float *p, float *div)
         L.omega = 1.0f;
         L.warps_per_cta = s->tune_warps;
         int nl = 0;
-        FSB_CUDA(launch_sweep_pass(L, s->sweep, s->stream, &nl));
+        {
+            ProfScope ps(s, FSB_PROF_GS);
+            FSB_CUDA(launch_sweep_pass(L, s->sweep, s->stream, &nl));
+        }
         s->launches += nl;
         FSB_TRY(set_boundary1(s, p, 0));
     }
-    FSB_CUDA(launch_gradient(u, v, p, s->W, s->H, s->stream));
+    {
+        ProfScope ps(s, FSB_PROF_GRADIENT);
+        FSB_CUDA(launch_gradient(u, v, p, s->W, s->H, s->stream));
+    }
     s->launches += 1;
     BndJob jobs[2] = {BndJob{u, 1, 0}, BndJob{v, 2, 0}};
     return set_boundary(s, jobs, 2);
@@ -279,6 +330,7 @@ int advect_one(fsb_sim *s, int b, float *dst, const float *src, const float *u, 
 {
     const int scheme = s->prm.advect_scheme;
     if (scheme == FSB_ADVECT_RK4) {
+        ProfScope ps(s, FSB_PROF_ADVECT_SCALAR);
         FSB_CUDA(launch_advect_rk4(dst, src, nullptr, nullptr, u, v, pz, s->W, s->H, dt, s->stream));
         s->launches += 1;
     } else if (scheme == FSB_ADVECT_SEMI_LAGRANGIAN) {
@@ -301,6 +353,7 @@ int add_noise(fsb_sim *s)
     NoiseWindow nw;
     std::memcpy(nw.w, s->noise_win, sizeof(nw.w));
     const int zero = s->prm.noise_mode == FSB_NOISE_ZERO;
+    ProfScope ps(s, FSB_PROF_NOISE);
     FSB_CUDA(launch_noise(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->ncells, nw, s->noise_tables, zero, s->stream));
     s->launches += zero ? 2 : 1;
     // the reference consumes 2*W*H outputs per step in either case (the zero mode replaces rand() itself)
@@ -324,7 +377,10 @@ int velocity_step(fsb_sim *s, float dt)
     float *u = s->f[FSB_VELOCITY_X], *v = s->f[FSB_VELOCITY_Y];
     float *nu = s->f[FSB_PREV_VEL_X], *nv = s->f[FSB_PREV_VEL_Y];
     if (s->prm.advect_scheme == FSB_ADVECT_RK4) {
-        FSB_CUDA(launch_advect_rk4(nu, u, nv, v, u, v, 0, s->W, s->H, dt, s->stream));
+        {
+            ProfScope ps(s, FSB_PROF_ADVECT_VELOCITY);
+            FSB_CUDA(launch_advect_rk4(nu, u, nv, v, u, v, 0, s->W, s->H, dt, s->stream));
+        }
         s->launches += 1;
         BndJob jobs[2] = {BndJob{nu, 1, 0}, BndJob{nv, 2, 0}};
         FSB_TRY(set_boundary(s, jobs, 2));
@@ -466,6 +522,8 @@ int fsb_destroy(fsb_sim *s)
         if (s->d_entries) cudaFree(s->d_entries);
         if (s->d_segs) cudaFree(s->d_segs);
         noise_tables_destroy(s->noise_tables);
+        for (auto &r : s->prof_open) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+        for (auto &e : s->prof_free) cudaEventDestroy(e);
         if (s->stream) cudaStreamDestroy(s->stream);
         (void)cudaGetLastError();
     }
@@ -749,6 +807,43 @@ int fsb_set_tuning(fsb_sim *s, int warps_per_cta, int max_sweeps_per_pass)
         return fail(FSB_EINVAL, "fsb_set_tuning: bad argument");
     s->tune_warps = warps_per_cta;
     s->tune_levels = max_sweeps_per_pass;
+    return FSB_OK;
+}
+
+int fsb_get_stream(fsb_sim *s, void **stream)
+{
+    if (!s || !stream) return fail(FSB_EINVAL, "fsb_get_stream: bad argument");
+    *stream = (void *)s->stream;
+    return FSB_OK;
+}
+
+int fsb_profile_enable(fsb_sim *s, int on)
+{
+    if (!s) return fail(FSB_EINVAL, "fsb_profile_enable: null handle");
+    s->profiling = on != 0;
+    return FSB_OK;
+}
+
+int fsb_profile_read(fsb_sim *s, double *ms, uint64_t *counts, int reset)
+{
+    if (!s) return fail(FSB_EINVAL, "fsb_profile_read: null handle");
+    DeviceGuard guard(s->device);
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    for (auto &r : s->prof_open) {
+        float t = 0.0f;
+        if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) {
+            s->prof_ms[r.cat] += t;
+            s->prof_n[r.cat] += 1;
+        }
+        s->prof_free.push_back(r.a);
+        s->prof_free.push_back(r.b);
+    }
+    s->prof_open.clear();
+    for (int c = 0; c < FSB_PROF_COUNT; ++c) {
+        if (ms) ms[c] = s->prof_ms[c];
+        if (counts) counts[c] = s->prof_n[c];
+        if (reset) { s->prof_ms[c] = 0.0; s->prof_n[c] = 0; }
+    }
     return FSB_OK;
 }
 

@@ -94,9 +94,16 @@ __device__ __forceinline__ void cp_async_f32x4(float *smem_dst, const float *gsr
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
+// Which boundary logic a step needs (warp-uniform, chosen per batch of 16 steps):
+//   kPathFast   every (lane, level) of the strip sits on an interior cell
+//   kPathLeft   interior rows only; the strip contains the j == 0 wall (one level per lane)
+//   kPathRight  interior rows only; the strip contains the j == H-1 wall
+//   kPathFull   anything (first / last rows of the grid, tiny grids): all walls, branch-free
+enum { kPathFast = 0, kPathLeft = 1, kPathRight = 2, kPathFull = 3 };
+
 // One global time step of one strip.  U receives lane g-1's x of the previous step, Up is
 // the U of the step before (needed for the centre value of SOR and for first-level walls).
-template <int S, int MODE, bool HAS_X0, bool FAST>
+template <int S, int MODE, bool HAS_X0, int PATH>
 __device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], const float (&Up)[S + 1],
                                         float (&Dc)[S + 1], const int t, const int lane, const int g,
                                         const WfCtx &cx)
@@ -131,44 +138,80 @@ __device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], co
     Dc[0] = cx.t_rhs[slot];
     const int ib = t - kToff - g;
     const float cold1 = Up[0];
+    // The S updates of a step are independent of each other (they read only values of step t-1), so
+    // they are written stage by stage across all levels: consecutive instructions belong to different
+    // dependency chains, which lets a single warp keep its FP pipe busy.
+    //   down = U[k-1] (i+1, j) sweep k-1      up    = x[k]   (i-1, j) sweep k
+    //   left = U[k]   (i, j-1) sweep k        right = x[k-1] (i, j+1) sweep k-1     centre = Up[k-1]
+    float acc[S + 1];
+    acc[0] = 0.0f;
+    if (MODE == kGaussSeidel) {
+        // src/fluid_sim.cpp:325-327: ((((div + down) + up) + right) + left) / 4
 #pragma unroll
-    for (int k = S; k >= 1; --k) {
-        const float down = U[k - 1];   // (i+1, j) sweep k-1
-        const float up = x[k];         // (i-1, j) sweep k
-        const float right = x[k - 1];  // (i, j+1) sweep k-1
-        const float left = U[k];       // (i, j-1) sweep k
-        float val;
-        if (MODE == kGaussSeidel) {
-            // src/fluid_sim.cpp:325-327
-            val = __fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(Dc[k], down), up), right), left), 0.25f);
-        } else {
-            // src/fluid_sim.cpp:56-57
-            const float cold = Up[k - 1];  // (i, j) sweep k-1
-            const float nb = __fadd_rn(__fadd_rn(__fadd_rn(down, up), right), left);
-            const float nv = __fmul_rn(__fadd_rn(Dc[k], __fmul_rn(cx.a, nb)), cx.c_recip);
-            val = __fadd_rn(cold, __fmul_rn(cx.omega, __fsub_rn(nv, cold)));
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Dc[k], U[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], U[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(acc[k], 0.25f);
+    } else {
+        // src/fluid_sim.cpp:56-57: nv = (src + a*(((down + up) + right) + left)) * cRecip; x += omega*(nv - x)
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(U[k - 1], x[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], U[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(cx.a, acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Dc[k], acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(acc[k], cx.c_recip);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fsub_rn(acc[k], Up[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(cx.omega, acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Up[k - 1], acc[k]);
+    }
+    // Cells on a wall carry what setBoundary() (src/fluid_sim.cpp:347-361) left in the array at the
+    // moment the reference reads them during sweep k: the array's own value before the first sweep,
+    // +-(the adjacent interior cell's sweep k-1 value) afterwards.  Cells outside the grid are never
+    // consumed by a cell inside it.
+    if (PATH == kPathLeft) {
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wv = (k == 1) ? cold1 : __fmul_rn(cx.sj, x[k - 1]);
+            acc[k] = (g == k) ? wv : acc[k];
         }
-        if (!FAST) {
-            // Cells on a wall carry what setBoundary() (src/fluid_sim.cpp:347-361) left in the array
-            // when the reference reads them during sweep k; everything outside the grid is 0.
+    } else if (PATH == kPathRight) {
+        const int gw = g - (cx.H - 1);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = (gw == k) ? __fmul_rn(cx.sj, U[k]) : acc[k];
+    } else if (PATH == kPathFull) {
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
             const int i = ib - k;
             const int j = g - k;
-            const bool inrow = (i >= 1) && (i <= cx.W - 2);
-            const bool incol = (j >= 1) && (j <= cx.H - 2);
-            float r = 0.0f;
-            if (inrow && incol) {
-                r = val;
-            } else if (incol) {
-                if (i == 0) r = (k == 1) ? cold1 : __fmul_rn(cx.si, down);
-                else if (i == cx.W - 1) r = __fmul_rn(cx.si, up);
-            } else if (inrow) {
-                if (j == 0) r = (k == 1) ? cold1 : __fmul_rn(cx.sj, right);
-                else if (j == cx.H - 1) r = __fmul_rn(cx.sj, left);
-            }
-            val = r;
+            const bool inrow = (unsigned)(i - 1) <= (unsigned)(cx.W - 3);
+            const bool incol = (unsigned)(j - 1) <= (unsigned)(cx.H - 3);
+            const float wtop = (k == 1) ? cold1 : __fmul_rn(cx.si, U[k - 1]);
+            const float wi = (i == 0) ? wtop : __fmul_rn(cx.si, x[k]);
+            const bool on_i = (i == 0) | (i == cx.W - 1);
+            const float wleft = (k == 1) ? cold1 : __fmul_rn(cx.sj, x[k - 1]);
+            const float wj = (j == 0) ? wleft : __fmul_rn(cx.sj, U[k]);
+            const bool on_j = (j == 0) | (j == cx.H - 1);
+            const float row_in = incol ? acc[k] : (on_j ? wj : 0.0f);
+            const float row_out = (on_i & incol) ? wi : 0.0f;
+            acc[k] = inrow ? row_in : row_out;
         }
-        x[k] = val;
     }
+#pragma unroll
+    for (int k = 1; k <= S; ++k) x[k] = acc[k];
     x[0] = nx0;
     if (lane == 31) {
         float4 *ex = reinterpret_cast<float4 *>(cx.exp + (t & cx.exp_mask) * L::EXW);
@@ -193,6 +236,22 @@ __device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], co
         }
     }
     cx.t_out[slot] = x[S];
+}
+
+// Sixteen steps of one path (kept out of line per path so the batch loop stays small).
+template <int S, int MODE, bool HAS_X0, int PATH>
+__device__ __forceinline__ void wf_batch(float (&x)[S + 1], float (&Ua)[S + 1], float (&Ub)[S + 1], float (&Da)[S + 1],
+                                         float (&Db)[S + 1], const int t0, const int lane, const int g,
+                                         const WfCtx &cx)
+{
+#pragma unroll 1
+    for (int s2 = 0; s2 < kWfBatch / 2; ++s2) {
+        const int t = t0 + 2 * s2;
+        wf_step<S, MODE, HAS_X0, PATH>(x, Ua, Ub, Da, t, lane, g, cx);
+        __syncthreads();
+        wf_step<S, MODE, HAS_X0, PATH>(x, Ub, Ua, Db, t + 1, lane, g, cx);
+        __syncthreads();
+    }
 }
 
 template <int S, int MODE, bool HAS_X0>
@@ -261,7 +320,8 @@ __global__ void __launch_bounds__(256, 1) wf_kernel(const WfKernelParams P)
     }
 
     const bool vec_ok = ((H & 3) == 0);
-    const bool cols_interior = (j0 - S >= 1) && (j0 + 30 <= H - 2);
+    const bool has_left = (j0 - S <= 0);            // some (lane, level) of the strip has column <= 0
+    const bool has_right = (j0 + 30 >= H - 1);      // ... or column >= H-1
 
     for (int n = n_first; n <= n_last; ++n) {
         const int t0 = n * kWfBatch;
@@ -329,18 +389,18 @@ __global__ void __launch_bounds__(256, 1) wf_kernel(const WfKernelParams P)
         }
         __syncthreads();
 
-        // (e) sixteen time steps
-        const bool fast = cols_interior && (t0 - kToff - j0 - 31 - S >= 1) && (t0 + kWfBatch - 1 - kToff - j0 - 1 <= W - 2);
-#pragma unroll 1
-        for (int s2 = 0; s2 < kWfBatch / 2; ++s2) {
-            const int t = t0 + 2 * s2;
-            if (fast) wf_step<S, MODE, HAS_X0, true>(x, Ua, Ub, Da, t, lane, g, cx);
-            else wf_step<S, MODE, HAS_X0, false>(x, Ua, Ub, Da, t, lane, g, cx);
-            __syncthreads();
-            if (fast) wf_step<S, MODE, HAS_X0, true>(x, Ub, Ua, Db, t + 1, lane, g, cx);
-            else wf_step<S, MODE, HAS_X0, false>(x, Ub, Ua, Db, t + 1, lane, g, cx);
-            __syncthreads();
+        // (e) sixteen time steps; every warp executes the same number of barriers on every path
+        const bool rows_interior = (t0 - kToff - j0 - 31 - S >= 1) && (t0 + kWfBatch - 1 - kToff - j0 - 1 <= W - 2);
+        int path = kPathFull;
+        if (rows_interior) {
+            if (!has_left && !has_right) path = kPathFast;
+            else if (has_left && !has_right && S <= 31 && j0 == 0) path = kPathLeft;
+            else if (has_right && !has_left) path = kPathRight;
         }
+        if (path == kPathFast) wf_batch<S, MODE, HAS_X0, kPathFast>(x, Ua, Ub, Da, Db, t0, lane, g, cx);
+        else if (path == kPathLeft) wf_batch<S, MODE, HAS_X0, kPathLeft>(x, Ua, Ub, Da, Db, t0, lane, g, cx);
+        else if (path == kPathRight) wf_batch<S, MODE, HAS_X0, kPathRight>(x, Ua, Ub, Da, Db, t0, lane, g, cx);
+        else wf_batch<S, MODE, HAS_X0, kPathFull>(x, Ua, Ub, Da, Db, t0, lane, g, cx);
 
         // (f) hand this batch's right edge to the CTA on the right
         if (c + 1 < P.ncta) {

@@ -139,6 +139,27 @@ int fsb_op_advect(fsb_sim *s, int b, int dst, int src, int u, int v, float dt); 
 int fsb_op_velocity_step(fsb_sim *s, float dt);                            /* :370-406 */
 int fsb_op_density_step(fsb_sim *s, float dt);                             /* :409-422 */
 
+/* The CUDA stream (cudaStream_t) all work of `s` is queued on, for callers that time or order
+ * their own work against it. */
+int fsb_get_stream(fsb_sim *s, void **stream);
+
+/* Optional per-kernel-class timing with CUDA events on that stream.  fsb_profile_read synchronises,
+ * then fills ms[FSB_PROF_COUNT] (accumulated milliseconds) and counts[FSB_PROF_COUNT] (number of
+ * bracketed launches); reset != 0 clears the accumulators. */
+enum {
+    FSB_PROF_NOISE = 0,            /* velocity noise                      src/fluid_sim.cpp:374-383 */
+    FSB_PROF_SOR = 1,              /* diffusion sweeps (one fused pass)   :50-61   */
+    FSB_PROF_GS = 2,               /* projection sweeps (one fused pass)  :319-331 */
+    FSB_PROF_DIVERGENCE = 3,       /* :307-314 */
+    FSB_PROF_GRADIENT = 4,         /* :334-341 */
+    FSB_PROF_ADVECT_VELOCITY = 5,  /* both velocity components, :401-402  */
+    FSB_PROF_ADVECT_SCALAR = 6,    /* one field, :421                     */
+    FSB_PROF_BOUNDARY = 7,         /* setBoundary, :347-367               */
+    FSB_PROF_COUNT = 8
+};
+int fsb_profile_enable(fsb_sim *s, int on);
+int fsb_profile_read(fsb_sim *s, double *ms, uint64_t *counts, int reset);
+
 /* Number of kernels this library has launched on behalf of `s` so far. */
 int fsb_launch_count(const fsb_sim *s, uint64_t *count);
 

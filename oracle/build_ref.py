@@ -39,7 +39,10 @@ DEFAULT_VARIANTS = [
     (96, 1100, 20, 5),     # wide: many column strips
     (512, 512, 40, 5),     # P = 40 (two solver passes)
     (2048, 2048, 20, 5),   # config 2
-    (1024, 8192, 40, 5),   # bounded sample of config 3 (same columns, 1/8 of the rows)
+    (128, 8192, 40, 5),    # bounded samples of config 3 (same columns, fewer rows) for the CPU baseline
+    (256, 8192, 40, 5),
+    (512, 8192, 40, 5),
+    (1024, 8192, 40, 5),
     (8192, 8192, 40, 5),   # config 3 (one step costs about a minute of CPU)
 ]
 

@@ -1,0 +1,14 @@
+"""Development aid: run a few projections on one grid shape (for ncu captures)."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import fluid_sim_b200 as fsb
+W, H, P, nw = (int(a) for a in sys.argv[1:5])
+sim = fsb.FluidSim(W, H, P, 5, warps_per_cta=nw, noise="zero")
+rng = np.random.default_rng(0)
+sim.write(fsb.VELOCITY_X, rng.standard_normal((W, H)).astype(np.float32))
+sim.write(fsb.VELOCITY_Y, rng.standard_normal((W, H)).astype(np.float32))
+for _ in range(3):
+    sim.project()
+sim.sync()
+print("done")
