@@ -182,7 +182,9 @@ def main():
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--proj", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--warps-per-cta", type=int, default=0)
+    ap.add_argument("--strips-per-cta", type=int, default=0)
+    ap.add_argument("--sweeps-per-warp", type=int, default=0)
+    ap.add_argument("--max-stages", type=int, default=0)
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -227,7 +229,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    sim = fsb.FluidSim(W, H, P, 5, device=local_rank, warps_per_cta=args.warps_per_cta)
+    sim = fsb.FluidSim(W, H, P, 5, device=local_rank, strips_per_cta=args.strips_per_cta, sweeps_per_warp=args.sweeps_per_warp, max_stages=args.max_stages)
     stream = torch.cuda.ExternalStream(sim.stream(), device=torch.device("cuda", local_rank))
 
     # synthetic input, built on the host in page-locked memory and injected through the C ABI

@@ -92,7 +92,7 @@ ABI = [
     ("fsb_profile_enable", C.c_int, [_SIM, C.c_int]),
     ("fsb_profile_read", C.c_int, [_SIM, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
     ("fsb_launch_count", C.c_int, [_SIM, C.POINTER(C.c_uint64)]),
-    ("fsb_set_tuning", C.c_int, [_SIM, C.c_int, C.c_int]),
+    ("fsb_set_tuning", C.c_int, [_SIM, C.c_int, C.c_int, C.c_int]),
     ("fsb_last_error", C.c_char_p, []),
     ("fsb_version", C.c_char_p, []),
 ]
@@ -121,7 +121,7 @@ class FluidSim:
 
     def __init__(self, width=200, height=200, proj_iters=20, diff_iters=5, viscosity=1e-4, diffusion=0.0,
                  omega=1.5, advect_scheme=ADVECT_RK4, noise="glibc", noise_seed=1, noise_pos=0, device=-1,
-                 warps_per_cta=0, max_sweeps_per_pass=0):
+                 strips_per_cta=0, sweeps_per_warp=0, max_stages=0):
         self._lib = load_library()
         p = Params()
         self._lib.fsb_default_params(C.byref(p))
@@ -133,8 +133,8 @@ class FluidSim:
         self._h = _SIM()
         self.width, self.height = width, height
         self._check(self._lib.fsb_create(C.byref(p), C.byref(self._h)))
-        if warps_per_cta or max_sweeps_per_pass:
-            self._check(self._lib.fsb_set_tuning(self._h, warps_per_cta, max_sweeps_per_pass))
+        if strips_per_cta or sweeps_per_warp or max_stages:
+            self._check(self._lib.fsb_set_tuning(self._h, strips_per_cta, sweeps_per_warp, max_stages))
 
     # -- plumbing ---------------------------------------------------------------------------
     def _check(self, rc):
@@ -284,8 +284,8 @@ class FluidSim:
         self._check(self._lib.fsb_profile_read(self._h, ms, cnt, 1 if reset else 0))
         return {name: (ms[i], cnt[i]) for i, name in enumerate(self.PROF_NAMES)}
 
-    def set_tuning(self, warps_per_cta=0, max_sweeps_per_pass=0):
-        self._check(self._lib.fsb_set_tuning(self._h, warps_per_cta, max_sweeps_per_pass))
+    def set_tuning(self, strips_per_cta=0, sweeps_per_warp=0, max_stages=0):
+        self._check(self._lib.fsb_set_tuning(self._h, strips_per_cta, sweeps_per_warp, max_stages))
 
     # -- the reference's private passes (per-kernel parity) -------------------------------------------
     def addNoise(self):

@@ -74,8 +74,9 @@ struct fsb_sim {
     std::vector<float> mirror[3];
     bool mirror_valid[3] = {false, false, false};
     uint64_t launches = 0;
-    int tune_warps = 0;
-    int tune_levels = 0;
+    int tune_strips = 0;   // strips per CTA (0 = automatic)
+    int tune_levels = 0;   // sweeps per warp (0 = automatic)
+    int tune_stages = 0;   // cap on chained warps per strip (0 = automatic)
     // optional per-kernel-class timing (CUDA events on the simulation's stream)
     bool profiling = false;
     struct ProfRec { int cat; cudaEvent_t a, b; };
@@ -137,16 +138,32 @@ struct ProfScope {
 inline float sign_i(int b) { return b == 1 ? -1.0f : 1.0f; }
 inline float sign_j(int b) { return b == 2 ? -1.0f : 1.0f; }
 
-std::vector<int> split_levels(int n, int cap)
+struct SweepPlan { int levels, stages; };
+
+// Splits n sweeps into launches of (levels per warp) x (stages): one launch when n factors into an
+// instantiated size, otherwise greedily.  pref / max_stages are tuning overrides (0 = automatic).
+std::vector<SweepPlan> plan_sweeps(int n, int pref, int max_stages)
 {
-    static const int sizes[] = {20, 10, 5, 2, 1};
-    std::vector<int> out;
-    if (cap <= 0 || cap > kWfMaxLevels) cap = kWfMaxLevels;
+    std::vector<int> sizes;
+    if (pref > 0 && sweep_max_stages(pref) > 0) sizes.push_back(pref);
+    for (int s : {5, 10, 20, 2, 1})
+        if (s != pref) sizes.push_back(s);
+    auto cap = [&](int s) {
+        int m = sweep_max_stages(s);
+        return (max_stages > 0 && max_stages < m) ? max_stages : m;
+    };
+    std::vector<SweepPlan> out;
+    for (int s : sizes)
+        if (n > 0 && n % s == 0 && n / s <= cap(s)) {
+            out.push_back(SweepPlan{s, n / s});
+            return out;
+        }
     while (n > 0) {
         for (int s : sizes)
-            if (s <= n && s <= cap) {
-                out.push_back(s);
-                n -= s;
+            if (s <= n) {
+                const int st = std::min(n / s, cap(s));
+                out.push_back(SweepPlan{s, st});
+                n -= s * st;
                 break;
             }
     }
@@ -239,7 +256,7 @@ int diffuse_fields(fsb_sim *s, int nf, float *const *xs, const int *bs, float di
         if (folded && fold_identity) *folded = 1;
         return FSB_OK;
     }
-    const std::vector<int> passes = split_levels(D, s->tune_levels);
+    const std::vector<SweepPlan> passes = plan_sweeps(D, s->tune_levels, s->tune_stages);
     const bool multi = passes.size() > 1;
     float *rhs[2] = {xs[0], nf > 1 ? xs[1] : nullptr};
     if (multi) {
@@ -258,11 +275,12 @@ int diffuse_fields(fsb_sim *s, int nf, float *const *xs, const int *bs, float di
         L.W = s->W;
         L.H = s->H;
         L.mode = kSor;
-        L.levels = passes[pi];
+        L.levels = passes[pi].levels;
+        L.stages = passes[pi].stages;
         L.a = a;
         L.c_recip = c_recip;
         L.omega = s->prm.omega;
-        L.warps_per_cta = s->tune_warps;
+        L.strips_per_cta = s->tune_strips;
         int nl = 0;
         {
             ProfScope ps(s, FSB_PROF_SOR);
@@ -284,7 +302,7 @@ int project(fsb_sim *s, float *u, float *v, float *p, float *div)
         FSB_CUDA(launch_divergence(u, v, div, s->W, s->H, s->stream));
     }
     s->launches += 1;
-    const std::vector<int> passes = split_levels(s->prm.proj_iters, s->tune_levels);
+    const std::vector<SweepPlan> passes = plan_sweeps(s->prm.proj_iters, s->tune_levels, s->tune_stages);
     if (passes.empty()) FSB_CUDA(cudaMemsetAsync(p, 0, s->ncells * sizeof(float), s->stream));
     for (size_t pi = 0; pi < passes.size(); ++pi) {
         SweepLaunch L{};
@@ -293,11 +311,12 @@ int project(fsb_sim *s, float *u, float *v, float *p, float *div)
         L.W = s->W;
         L.H = s->H;
         L.mode = kGaussSeidel;
-        L.levels = passes[pi];
+        L.levels = passes[pi].levels;
+        L.stages = passes[pi].stages;
         L.a = 0.0f;
         L.c_recip = 1.0f;
         L.omega = 1.0f;
-        L.warps_per_cta = s->tune_warps;
+        L.strips_per_cta = s->tune_strips;
         int nl = 0;
         {
             ProfScope ps(s, FSB_PROF_GS);
@@ -491,9 +510,6 @@ int fsb_create(const fsb_params *p, fsb_sim **out)
         FSB_CREATE_CUDA(cudaMalloc(&s->f[k], s->ncells * sizeof(float)));
         FSB_CREATE_CUDA(cudaMemsetAsync(s->f[k], 0, s->ncells * sizeof(float), s->stream));
     }
-    s->sweep.xchg_floats = sweep_xchg_floats(s->H);
-    FSB_CREATE_CUDA(cudaMalloc(&s->sweep.xchg, s->sweep.xchg_floats * sizeof(float)));
-    FSB_CREATE_CUDA(cudaMemsetAsync(s->sweep.xchg, 0, s->sweep.xchg_floats * sizeof(float), s->stream));
     FSB_CREATE_CUDA(cudaMalloc(&s->sweep.flags, sweep_flag_words() * sizeof(unsigned long long)));
     FSB_CREATE_CUDA(cudaMemsetAsync(s->sweep.flags, 0, sweep_flag_words() * sizeof(unsigned long long), s->stream));
     FSB_CREATE_CUDA(noise_tables_create(s->noise_tables));
@@ -801,12 +817,15 @@ int fsb_launch_count(const fsb_sim *s, uint64_t *count)
     return FSB_OK;
 }
 
-int fsb_set_tuning(fsb_sim *s, int warps_per_cta, int max_sweeps_per_pass)
+int fsb_set_tuning(fsb_sim *s, int strips_per_cta, int sweeps_per_warp, int max_stages)
 {
-    if (!s || warps_per_cta < 0 || warps_per_cta > 8 || max_sweeps_per_pass < 0)
+    if (!s || strips_per_cta < 0 || strips_per_cta > 16 || sweeps_per_warp < 0 || max_stages < 0)
         return fail(FSB_EINVAL, "fsb_set_tuning: bad argument");
-    s->tune_warps = warps_per_cta;
-    s->tune_levels = max_sweeps_per_pass;
+    if (sweeps_per_warp > 0 && sweep_max_stages(sweeps_per_warp) == 0)
+        return fail(FSB_EINVAL, "fsb_set_tuning: sweeps_per_warp must be 1, 2, 5, 10 or 20");
+    s->tune_strips = strips_per_cta;
+    s->tune_levels = sweeps_per_warp;
+    s->tune_stages = max_stages;
     return FSB_OK;
 }
 

@@ -163,8 +163,9 @@ int fsb_profile_read(fsb_sim *s, double *ms, uint64_t *counts, int reset);
 /* Number of kernels this library has launched on behalf of `s` so far. */
 int fsb_launch_count(const fsb_sim *s, uint64_t *count);
 
-/* Tuning knobs for experiments (0 = library default). */
-int fsb_set_tuning(fsb_sim *s, int warps_per_cta, int max_sweeps_per_pass);
+/* Tuning knobs of the relaxation pipeline, for experiments (0 = library default): column strips per
+ * CTA, sweeps kept in flight per warp (1, 2, 5, 10 or 20), cap on warps chained per strip. */
+int fsb_set_tuning(fsb_sim *s, int strips_per_cta, int sweeps_per_warp, int max_stages);
 
 const char *fsb_last_error(void);
 const char *fsb_version(void);

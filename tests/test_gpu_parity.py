@@ -87,11 +87,12 @@ def test_diffuse(w, h, b):
     assert_bits(gpu.read(fsb.VELOCITY_X), ora.read(orasim.VEL_X), f"diffuse b={b}")
 
 
-@pytest.mark.parametrize("D,cap", [(1, 0), (3, 0), (7, 0), (5, 2), (12, 5), (0, 0)])
-def test_diffuse_sweep_counts(D, cap):
-    """Sweep counts that need several passes (the source field must stay the pre-diffusion copy)."""
+@pytest.mark.parametrize("D,spw,stg", [(1, 0, 0), (3, 0, 0), (7, 0, 0), (5, 2, 0), (12, 5, 1), (5, 1, 0), (10, 5, 0), (0, 0, 0)])
+def test_diffuse_sweep_counts(D, spw, stg):
+    """Sweep counts split over several stages and / or several launches (the source field must stay the
+    pre-diffusion copy across launches)."""
     w, h = 70, 90
-    gpu = fsb.FluidSim(w, h, 20, D, max_sweeps_per_pass=cap)
+    gpu = fsb.FluidSim(w, h, 20, D, sweeps_per_warp=spw, max_stages=stg)
     ora = OracleSim(w, h, 20, D)
     rng = np.random.default_rng(D)
     f = random_field(rng, w, h)
@@ -125,10 +126,12 @@ def test_project(w, h):
     assert_bits(gpu.read(fsb.VELOCITY_Y), ora.read(orasim.VEL_Y), "velY after project")
 
 
-@pytest.mark.parametrize("P,cap,warps", [(1, 0, 0), (3, 0, 1), (7, 0, 2), (40, 0, 0), (20, 5, 8), (33, 10, 4), (0, 0, 0)])
-def test_project_sweep_counts(P, cap, warps):
+@pytest.mark.parametrize("P,spw,stg,strips", [(1, 0, 0, 0), (3, 0, 0, 1), (7, 0, 0, 2), (40, 0, 0, 0), (20, 5, 0, 2),
+                                               (33, 10, 0, 4), (20, 20, 0, 4), (40, 10, 2, 2), (16, 1, 0, 1),
+                                               (100, 10, 0, 1), (0, 0, 0, 0)])
+def test_project_sweep_counts(P, spw, stg, strips):
     w, h = 90, 150
-    gpu = fsb.FluidSim(w, h, P, 5, max_sweeps_per_pass=cap, warps_per_cta=warps)
+    gpu = fsb.FluidSim(w, h, P, 5, sweeps_per_warp=spw, max_stages=stg, strips_per_cta=strips)
     ora = OracleSim(w, h, P, 5)
     rng = np.random.default_rng(P)
     seed_state(gpu, ora, rng, w, h)
