@@ -140,32 +140,54 @@ inline float sign_j(int b) { return b == 2 ? -1.0f : 1.0f; }
 
 struct SweepPlan { int levels, stages; };
 
-// Splits n sweeps into launches of (levels per warp) x (stages): one launch when n factors into an
-// instantiated size, otherwise greedily.  pref / max_stages are tuning overrides (0 = automatic).
-std::vector<SweepPlan> plan_sweeps(int n, int pref, int max_stages)
+// Splits n sweeps into launches of (sweeps per warp) x (stages): one launch when n factors into an
+// instantiated size that can be launched with every CTA resident, otherwise greedily.
+// pref / max_stages are tuning overrides (0 = automatic).
+std::vector<SweepPlan> plan_sweeps(const fsb_sim *s, int n, int nfields, int mode)
 {
+    const int pref = s->tune_levels, max_stages = s->tune_stages;
     std::vector<int> sizes;
     if (pref > 0 && sweep_max_stages(pref) > 0) sizes.push_back(pref);
-    for (int s : {5, 10, 20, 2, 1})
-        if (s != pref) sizes.push_back(s);
-    auto cap = [&](int s) {
-        int m = sweep_max_stages(s);
+    for (int lv : {10, 20, 5, 2, 1})
+        if (lv != pref) sizes.push_back(lv);
+    auto cap = [&](int lv) {
+        int m = sweep_max_stages(lv);
         return (max_stages > 0 && max_stages < m) ? max_stages : m;
     };
+    auto fits = [&](int lv, int st) {
+        SweepLaunch L{};
+        L.nfields = nfields;
+        L.W = s->W;
+        L.H = s->H;
+        L.mode = mode;
+        L.levels = lv;
+        L.stages = st;
+        L.strips_per_cta = s->tune_strips;
+        for (int i = 0; i < nfields; ++i) L.fld[i] = SweepField{s->f[0], s->f[0], s->f[0], 1.0f, 1.0f};
+        return sweep_config_fits(L);
+    };
     std::vector<SweepPlan> out;
-    for (int s : sizes)
-        if (n > 0 && n % s == 0 && n / s <= cap(s)) {
-            out.push_back(SweepPlan{s, n / s});
+    for (int lv : sizes)
+        if (n > 0 && n % lv == 0 && n / lv <= cap(lv) && fits(lv, n / lv)) {
+            out.push_back(SweepPlan{lv, n / lv});
             return out;
         }
     while (n > 0) {
-        for (int s : sizes)
-            if (s <= n) {
-                const int st = std::min(n / s, cap(s));
-                out.push_back(SweepPlan{s, st});
-                n -= s * st;
-                break;
-            }
+        bool placed = false;
+        for (int lv : sizes) {
+            if (lv > n) continue;
+            int st = std::min(n / lv, cap(lv));
+            while (st > 1 && !fits(lv, st)) --st;
+            if (!fits(lv, st)) continue;
+            out.push_back(SweepPlan{lv, st});
+            n -= lv * st;
+            placed = true;
+            break;
+        }
+        if (!placed) {   // nothing launchable: let the launch report the error
+            out.push_back(SweepPlan{1, 1});
+            n -= 1;
+        }
     }
     return out;
 }
@@ -256,7 +278,7 @@ int diffuse_fields(fsb_sim *s, int nf, float *const *xs, const int *bs, float di
         if (folded && fold_identity) *folded = 1;
         return FSB_OK;
     }
-    const std::vector<SweepPlan> passes = plan_sweeps(D, s->tune_levels, s->tune_stages);
+    const std::vector<SweepPlan> passes = plan_sweeps(s, D, nf, kSor);
     const bool multi = passes.size() > 1;
     float *rhs[2] = {xs[0], nf > 1 ? xs[1] : nullptr};
     if (multi) {
@@ -302,7 +324,7 @@ int project(fsb_sim *s, float *u, float *v, float *p, float *div)
         FSB_CUDA(launch_divergence(u, v, div, s->W, s->H, s->stream));
     }
     s->launches += 1;
-    const std::vector<SweepPlan> passes = plan_sweeps(s->prm.proj_iters, s->tune_levels, s->tune_stages);
+    const std::vector<SweepPlan> passes = plan_sweeps(s, s->prm.proj_iters, 1, kGaussSeidel);
     if (passes.empty()) FSB_CUDA(cudaMemsetAsync(p, 0, s->ncells * sizeof(float), s->stream));
     for (size_t pi = 0; pi < passes.size(); ++pi) {
         SweepLaunch L{};

@@ -11,9 +11,10 @@
 //     time step t (in the warp's own frame).  Each step every lane moves one row down; level k
 //     trails level k-1 by one row and one column.  With that skew all four neighbours a sweep
 //     needs are values of step t-1: own registers (up / right) or the registers of lane g-1
-//     (left / down), fetched with one shuffle per level.  Hence S sweeps are in flight per warp.
-//   * the right-hand side (divergence or diffusion source) travels with the cell through a second
-//     shuffle pipeline (two steps per level).
+//     (left / down), read as float4s from the warp's state buffer in shared memory.  Hence S sweeps
+//     are in flight per warp.
+//   * the right-hand side (divergence or diffusion source) travels with the cell through the same
+//     buffer (two steps per level).
 //   * stages: the sweeps of a pass are split over `nstg` warps per strip.  Stage g is the same
 //     program shifted by g*S columns and 2*g*S time steps; it takes its level-0 stream (x and
 //     right-hand side, lane-aligned) from the shared-memory ring stage g-1 writes its level-S
@@ -21,10 +22,13 @@
 //     result rows back.  All sweeps of a pass therefore read and write each cell of HBM once.
 //   * strips: lane 0 takes its left neighbours from the previous strip of the same stage: through a
 //     shared-memory ring inside a CTA, through a global ring with acquire/release progress flags
-//     between CTAs (batches of 16 steps).  The launch is cooperative so that every CTA of a chain
+//     between CTAs (batches of 16 steps, moved by the comm warp).  The launch is cooperative so that every CTA of a chain
 //     is resident while its right neighbour waits for it.
-//   * the warps of a CTA advance in lockstep, one __syncthreads per time step; stage g runs
-//     g*stage_off steps behind stage 0 (a multiple of 16, so batch boundaries coincide).
+//   * there is no CTA-wide barrier in the main loop: every compute warp publishes the last step it
+//     has completed in shared memory and, before each group of 4 steps, checks that its producers
+//     (left strip, previous stage) are far enough ahead and its consumers (right strip, next stage)
+//     have freed the ring slots it is about to overwrite.  One extra "comm" warp per CTA moves the
+//     CTA-edge rings to and from global memory, so compute warps never wait on L2 latency.
 //   * wall cells are evaluated in the pipeline with the value setBoundary() would have left in the
 //     array at the moment the reference reads it (warp-uniform fix-ups, only near walls).
 //
@@ -38,12 +42,11 @@ namespace {
 constexpr int kToff = 32;        // time offset: lane g sits on row t - kToff - g at level 0
 constexpr int kTileRows = 64;    // rows of an HBM staging ring (input tiles, result tile)
 constexpr int kTileFloats = kTileRows * 32;
-constexpr int kHandRows = 32;    // steps held by a stage-to-stage ring
-constexpr int kHandFloats = kHandRows * 32;
-constexpr int kEdgeDepth = 32;   // steps held by the CTA-edge rings (two batches)
-constexpr int kMidDepth = 4;     // steps held by the rings between strips of a CTA
+constexpr int kGroup = 4;        // steps a warp runs between two progress checks
+constexpr int kEdgeDepth = 64;   // steps held by the CTA-edge rings (four batches)
+constexpr int kMidDepth = 16;    // steps held by the rings between strips of a CTA
 constexpr int kBatchBias = 64;   // keeps published batch numbers positive (later stages start at t < 0)
-constexpr int kMaxStages = 32;
+constexpr int kMaxStages = 16;
 
 template <int S>
 struct WfLayout {
@@ -51,14 +54,23 @@ struct WfLayout {
     static constexpr int DW = (S + 3) & ~3;       // rhs levels 0..S-1
     static constexpr int EXW = XW + DW;           // floats one lane hands to the next strip per step
     static constexpr int kBoundaryFloats = kWfSlots * kWfBatch * EXW;
-    static constexpr int kMaxThreads = (S <= 5) ? 512 : 256;
+    // per-lane strides of a warp's own state buffers: an odd number of 16-byte chunks keeps the
+    // 128-bit shared-memory accesses of a quarter warp on distinct banks
+    static constexpr int XP = ((XW / 4) & 1) ? XW : XW + 4;
+    static constexpr int DP = ((DW / 4) & 1) ? DW : DW + 4;
+    static constexpr int kStateFloats = 2 * 32 * XP + 4 * 32 * DP;   // x of 2 steps, rhs of 4 steps
+    // stage-to-stage ring: the writer runs 2S steps (plus up to two groups) ahead of the reader
+    static constexpr int kHandRows = (2 * S + 2 * kGroup + 2 <= 16) ? 16 : ((2 * S + 2 * kGroup + 2 <= 32) ? 32 : 64);
+    static constexpr int kHandFloats = kHandRows * 32;
+    static constexpr int kMaxStagesS = (S <= 2) ? 16 : 8;
+    static constexpr int kMaxThreads = (kMaxStagesS + 2) * 32;   // compute warps + the two comm warps
+    static constexpr int kMinBlocks = (S == 5) ? 2 : 1;
 };
 
 struct WfKernelParams {
     SweepField fld[kMaxSweepFields];
     int W, H;
     int nstr, nstg, ncta;   // strips per CTA, stages per strip, CTAs per chain
-    int stage_off;          // wall-clock steps between consecutive stages (multiple of 16, >= 2S+2)
     float a, c_recip, omega;
     float *xchg;
     unsigned long long *flags;
@@ -77,6 +89,8 @@ struct WfWarp {
     float *out_x;       // level-S stream (next stage, or the result tile of the last stage)
     float *out_d;       // level-S right-hand side for the next stage (nullptr on the last stage)
     int out_mask;
+    float *bx;          // this warp's x[0..S] of the last 2 steps, [2][32 lanes][XP]
+    float *bd;          // this warp's rhs levels 0..S-1 of the last 4 steps, [4][32 lanes][DP]
     bool first;         // stage 0: level 1 is the first sweep of the pass (walls read from the array)
     int W, H;
     float si, sj, a, c_recip, omega;
@@ -94,6 +108,18 @@ __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long
 __device__ __forceinline__ void st_release_u64(unsigned long long *p, unsigned long long v)
 {
     asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__device__ __forceinline__ int ld_acquire_cta_s32(const int *p)
+{
+    int v;
+    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void st_release_cta_s32(int *p, int v)
+{
+    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
 }
 
 __device__ __forceinline__ void cp_async_f32(float *smem_dst, const float *gsrc, bool valid)
@@ -114,21 +140,23 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 
-// One time step of one warp.  U receives lane g-1's x of the previous step, Up is the U of the step
-// before (needed for the centre value of SOR and for first-sweep walls).
+// One time step of one warp.  Every lane publishes its x[0..S] and right-hand-side levels in the warp's
+// state buffer (lane 31: in the ring read by the next strip instead) and reads lane g-1's state of the
+// previous steps from there (lane 0: from the ring written by the previous strip).  U receives lane
+// g-1's x of step t-1; Up is the U of the step before (centre value of SOR, first-sweep walls).
 template <int S, int MODE>
-__device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], const float (&Up)[S + 1],
-                                        float (&Dc)[S + 1], const int t, const int lane, const int gp,
-                                        const int fix, const WfWarp &cx)
+__device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], const float (&Up)[S + 1], const int t,
+                                        const int lane, const int gp, const int fix, const WfWarp &cx)
 {
     using L = WfLayout<S>;
-#pragma unroll
-    for (int k = 0; k <= S; ++k) U[k] = __shfl_up_sync(0xffffffffu, x[k], 1);
-#pragma unroll
-    for (int k = S; k >= 1; --k) Dc[k] = __shfl_up_sync(0xffffffffu, Dc[k - 1], 1);
-    if (lane == 0) {
-        const float4 *ix = reinterpret_cast<const float4 *>(cx.imp + ((t - 1) & cx.imp_mask) * L::EXW);
-        const float4 *id = reinterpret_cast<const float4 *>(cx.imp + ((t - 2) & cx.imp_mask) * L::EXW + L::XW);
+    float Dc[S + 1];
+    {
+        const float *px = (lane == 0) ? cx.imp + ((t - 1) & cx.imp_mask) * L::EXW
+                                      : cx.bx + (((t - 1) & 1) * 32 + (lane - 1)) * L::XP;
+        const float *pd = (lane == 0) ? cx.imp + ((t - 2) & cx.imp_mask) * L::EXW + L::XW
+                                      : cx.bd + (((t - 2) & 3) * 32 + (lane - 1)) * L::DP;
+        const float4 *ix = reinterpret_cast<const float4 *>(px);
+        const float4 *id = reinterpret_cast<const float4 *>(pd);
 #pragma unroll
         for (int q = 0; q < L::XW / 4; ++q) {
             const float4 v = ix[q];
@@ -225,8 +253,10 @@ __device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], co
 #pragma unroll
     for (int k = 1; k <= S; ++k) x[k] = acc[k];
     x[0] = nx0;
-    if (lane == 31) {
-        float4 *ex = reinterpret_cast<float4 *>(cx.exp + (t & cx.exp_mask) * L::EXW);
+    {
+        float *wx = (lane == 31) ? cx.exp + (t & cx.exp_mask) * L::EXW : cx.bx + ((t & 1) * 32 + lane) * L::XP;
+        float *wd = (lane == 31) ? cx.exp + (t & cx.exp_mask) * L::EXW + L::XW : cx.bd + ((t & 3) * 32 + lane) * L::DP;
+        float4 *ex = reinterpret_cast<float4 *>(wx);
 #pragma unroll
         for (int q = 0; q < L::XW / 4; ++q) {
             float4 v;
@@ -236,7 +266,7 @@ __device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], co
             v.w = x[(4 * q + 3 <= S) ? 4 * q + 3 : 0];
             ex[q] = v;
         }
-        float4 *ed = ex + L::XW / 4;
+        float4 *ed = reinterpret_cast<float4 *>(wd);
 #pragma unroll
         for (int q = 0; q < L::DW / 4; ++q) {
             float4 v;
@@ -250,40 +280,140 @@ __device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], co
     const int oslot = ((t - lane) & cx.out_mask) * 32 + lane;
     cx.out_x[oslot] = x[S];
     if (cx.out_d) cx.out_d[oslot] = Dc[S];
+    __syncwarp();
 }
 
 template <int S, int MODE, bool HAS_X0>
-__global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, 1) wf_kernel(const WfKernelParams P)
+__global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlocks) wf_kernel(const WfKernelParams P)
 {
     using L = WfLayout<S>;
     extern __shared__ float4 smem4[];
     float *smem = reinterpret_cast<float *>(smem4);
 
     const int NSTR = P.nstr, NSTG = P.nstg;
-    const int nthreads = NSTR * NSTG * 32;
+    const int NW = NSTR * NSTG;                  // compute warps; warps NW and NW+1 move the CTA-edge rings
+    const int nthreads = (NW + 2) * 32;
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int w = tid >> 5;
-    const int sidx = w / NSTG;
-    const int g = w - sidx * NSTG;
     const int c = blockIdx.x;
     const int fi = blockIdx.y;
     const SweepField F = P.fld[fi];
     const int W = P.W, H = P.H;
+    const int j0_first = 32 * NSTR * c;
 
     // ---- shared memory carve-up -------------------------------------------------------------
-    float *edge_in = smem;                                              // [NSTG][kEdgeDepth * EXW]
+    int *prog = reinterpret_cast<int *>(smem);                          // [NW] last step completed by a compute warp
+    int *imp_steps = prog + 64;                                         // [NSTG] last step present in edge_in
+    int *exp_steps = imp_steps + 16;                                    // [NSTG] last step moved out of edge_out
+    float *edge_in = smem + 96;                                         // [NSTG][kEdgeDepth * EXW]
     float *edge_out = edge_in + NSTG * kEdgeDepth * L::EXW;             // [NSTG][kEdgeDepth * EXW]
     float *mid = edge_out + NSTG * kEdgeDepth * L::EXW;                 // [NSTR-1][NSTG][kMidDepth * EXW]
     float *tiles = mid + (NSTR - 1) * NSTG * kMidDepth * L::EXW;        // [NSTR][rhs | x0 | result]
     float *hand = tiles + NSTR * 3 * kTileFloats;                       // [NSTR][NSTG-1][x | rhs]
+    float *state = hand + NSTR * (NSTG - 1) * 2 * L::kHandFloats;       // [NW][kStateFloats]
     {
-        const int total = 2 * NSTG * kEdgeDepth * L::EXW + (NSTR - 1) * NSTG * kMidDepth * L::EXW +
-                          NSTR * 3 * kTileFloats + NSTR * (NSTG - 1) * 2 * kHandFloats;
+        const int total = 96 + 2 * NSTG * kEdgeDepth * L::EXW + (NSTR - 1) * NSTG * kMidDepth * L::EXW +
+                          NSTR * 3 * kTileFloats + NSTR * (NSTG - 1) * 2 * L::kHandFloats + NW * L::kStateFloats;
         for (int i = tid; i < total; i += nthreads) smem[i] = 0.0f;
     }
     __syncthreads();
+    // geometry helpers (a warp's own time / column frame): first step, last step
+    auto warp_j0w = [&](int sidx_, int g_) { return j0_first + 32 * sidx_ - g_ * S; };
+    auto first_step = [&](int j0w_) { return (j0w_ >> 4) << 4; };                   // batch aligned, may be < 0
+    auto last_needed = [&](int j0w_) { return (W - 1) + S + kToff + j0w_ + 31; };   // level S reaches the bottom wall row
+    auto last_step = [&](int j0w_) { return ((last_needed(j0w_) >> 4) << 4) + 15; };
+    if (tid < NW) prog[tid] = first_step(warp_j0w(tid / NSTG, tid % NSTG)) - 1;
+    if (tid < NSTG) {
+        imp_steps[tid] = first_step(warp_j0w(0, tid)) - 1;
+        exp_steps[tid] = first_step(warp_j0w(NSTR - 1, tid)) - 1;
+    }
+    __syncthreads();
 
+    // =============================== comm warps ==================================================
+    // Warp NW moves the left neighbours in (global ring written by the CTA on the left -> edge_in), warp
+    // NW+1 moves the right edge out (edge_out -> global ring read by the CTA on the right); lane gi serves
+    // stage gi.  Every round handles all transfers that are ready, with one fence for all of them, so the
+    // cost of a round does not grow with the number of stages.
+    if (w >= NW) {
+        const bool is_exp = (w == NW + 1);
+        const int gi = lane;
+        const bool valid = (gi < NSTG) && (is_exp ? (c + 1 < P.ncta) : (c > 0));
+        int n = 0, n_end = -1, n_first_right = 0;
+        if (valid) {
+            if (!is_exp) {
+                n = first_step(warp_j0w(0, gi)) >> 4;
+                n_end = last_needed(warp_j0w(0, gi) - 32) >> 4;           // last batch of the strip on the left
+            } else {
+                n = first_step(warp_j0w(NSTR - 1, gi)) >> 4;
+                n_end = last_needed(warp_j0w(NSTR - 1, gi)) >> 4;
+                n_first_right = first_step(warp_j0w(NSTR, gi)) >> 4;
+            }
+        }
+        unsigned long long *fl = P.flags + ((size_t)fi * kMaxStages + (gi < kMaxStages ? gi : 0)) * kWfMaxCtas * 2;
+        const volatile unsigned long long *poll_flag =
+            is_exp ? fl + (size_t)c * 2 + 1 : fl + (size_t)(c > 0 ? c - 1 : 0) * 2;
+        const int *poll_prog = is_exp ? prog + (NSTR - 1) * NSTG + (gi < NSTG ? gi : 0) : prog + (gi < NSTG ? gi : 0);
+        bool done = !valid || n > n_end;
+        while (!__all_sync(0xffffffffu, done)) {
+            bool ready = false;
+            if (!done) {
+                if (!is_exp) {
+                    // batch n replaces batch n - kEdgeDepth/16 in edge_in, whose last slot is read one and two steps later
+                    ready = ld_acquire_cta_s32(poll_prog) >= 16 * (n - kEdgeDepth / kWfBatch + 1) + 1 &&
+                            *poll_flag >= P.seq_base + (unsigned long long)(n + kBatchBias + 1);
+                } else {
+                    ready = ld_acquire_cta_s32(poll_prog) >= 16 * n + 15 &&
+                            (n - kWfSlots < n_first_right ||
+                             *poll_flag >= P.seq_base + (unsigned long long)(n - kWfSlots + kBatchBias + 1));
+                }
+            }
+            unsigned m = __ballot_sync(0xffffffffu, ready);
+            if (m == 0) {
+                __nanosleep(32);
+                continue;
+            }
+            __threadfence();   // acquire side of the flags just observed
+            for (unsigned mm = m; mm; mm &= mm - 1) {
+                const int src = __ffs(mm) - 1;
+                const int bn = __shfl_sync(0xffffffffu, n, src);
+                float *xg = P.xchg + ((size_t)fi * NSTG + src) * P.ncta * L::kBoundaryFloats;
+                if (!is_exp) {
+                    const float4 *gsrc = reinterpret_cast<const float4 *>(
+                        xg + (size_t)(c - 1) * L::kBoundaryFloats + (size_t)(bn & (kWfSlots - 1)) * kWfBatch * L::EXW);
+                    float4 *sdst = reinterpret_cast<float4 *>(edge_in + src * kEdgeDepth * L::EXW +
+                                                              ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
+#pragma unroll 2
+                    for (int i = lane; i < kWfBatch * L::EXW / 4; i += 32) sdst[i] = __ldcg(gsrc + i);
+                } else {
+                    float4 *gdst = reinterpret_cast<float4 *>(
+                        xg + (size_t)c * L::kBoundaryFloats + (size_t)(bn & (kWfSlots - 1)) * kWfBatch * L::EXW);
+                    const float4 *ssrc = reinterpret_cast<const float4 *>(edge_out + src * kEdgeDepth * L::EXW +
+                                                                          ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
+#pragma unroll 2
+                    for (int i = lane; i < kWfBatch * L::EXW / 4; i += 32) gdst[i] = ssrc[i];
+                }
+            }
+            if (is_exp) __threadfence();
+            __syncwarp();
+            if (ready) {
+                if (!is_exp) {
+                    st_release_cta_s32(imp_steps + gi, 16 * n + 15);
+                    st_release_u64(fl + (size_t)(c - 1) * 2 + 1, P.seq_base + (unsigned long long)(n + kBatchBias + 1));
+                } else {
+                    st_release_u64(fl + (size_t)c * 2, P.seq_base + (unsigned long long)(n + kBatchBias + 1));
+                    st_release_cta_s32(exp_steps + gi, 16 * n + 15);
+                }
+                n += 1;
+                done = n > n_end;
+            }
+        }
+        return;
+    }
+
+    // =============================== compute warps =================================================
+    const int sidx = w / NSTG;
+    const int g = w - sidx * NSTG;
     float *t_rhs = tiles + sidx * 3 * kTileFloats;
     float *t_x0 = t_rhs + kTileFloats;
     float *t_out = t_x0 + kTileFloats;
@@ -300,9 +430,9 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, 1) wf_kernel(const W
         cx.in_off = 0;
         cx.has_in_x = HAS_X0;
     } else {
-        cx.in_x = hand + (sidx * (NSTG - 1) + (g - 1)) * 2 * kHandFloats;
-        cx.in_d = cx.in_x + kHandFloats;
-        cx.in_mask = kHandRows - 1;
+        cx.in_x = hand + (sidx * (NSTG - 1) + (g - 1)) * 2 * L::kHandFloats;
+        cx.in_d = cx.in_x + L::kHandFloats;
+        cx.in_mask = L::kHandRows - 1;
         cx.in_off = 2 * S;
         cx.has_in_x = true;
     }
@@ -311,10 +441,12 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, 1) wf_kernel(const W
         cx.out_d = nullptr;
         cx.out_mask = kTileRows - 1;
     } else {
-        cx.out_x = hand + (sidx * (NSTG - 1) + g) * 2 * kHandFloats;
-        cx.out_d = cx.out_x + kHandFloats;
-        cx.out_mask = kHandRows - 1;
+        cx.out_x = hand + (sidx * (NSTG - 1) + g) * 2 * L::kHandFloats;
+        cx.out_d = cx.out_x + L::kHandFloats;
+        cx.out_mask = L::kHandRows - 1;
     }
+    cx.bx = state + w * L::kStateFloats;
+    cx.bd = cx.bx + 2 * 32 * L::XP;
     cx.first = (g == 0);
     cx.W = W;
     cx.H = H;
@@ -324,34 +456,49 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, 1) wf_kernel(const W
     cx.c_recip = P.c_recip;
     cx.omega = P.omega;
 
-    // ---- geometry of this warp (its own time / column frame) ------------------------------------
-    const int koff = g * S;                      // sweeps done by earlier stages
-    const int j0_first = 32 * NSTR * c;
     const int j0 = j0_first + 32 * sidx;         // strip base column in stage 0's frame
-    const int j0w = j0 - koff;                   // ... in this stage's frame
+    const int j0w = warp_j0w(sidx, g);           // ... in this stage's frame
     const int gp = j0w + lane;
-    const int off_w = g * P.stage_off;           // wall-clock lag behind stage 0
-    const int tau_b = (j0w >> 4) << 4;           // first step (batch aligned; arithmetic shift: may be < 0)
-    const int tau_last = (W - 1) + S + kToff + j0w + 31;   // level S reaches the bottom wall row (the next stage reads it)
-    const int tau_e = ((tau_last >> 4) << 4) + 15;
-    const int n_last_left = ((W - 1) + S + kToff + (j0_first - 32 - koff) + 31) >> 4;
-    const int n_first_right = (j0_first + 32 * NSTR - koff) >> 4;
-    const int T0 = j0_first;
-    int T1;
-    {
-        const int kl = (NSTG - 1) * S;
-        const int jl = j0_first + 32 * (NSTR - 1) - kl;
-        const int tl = (W - 1) + S + kToff + jl + 31;
-        T1 = (((tl >> 4) << 4) + 15) + (NSTG - 1) * P.stage_off;
+    const int tau_b = first_step(j0w);
+    const int tau_e = last_step(j0w);
+
+    // ---- what this warp waits for before a group of steps starting at t: counter >= min(t + add, clamp) ----
+    //   lane 0: left neighbours present      lane 1: previous stage far enough ahead
+    //   lane 2: right strip / export freed the slots we overwrite      lane 3: next stage freed its ring slots
+    const int *wait_ptr = nullptr;
+    int wait_add = 0, wait_clamp = 0x7fffffff;
+    if (lane == 0) {
+        if (sidx > 0) {
+            wait_ptr = prog + (w - NSTG);
+            wait_clamp = last_step(j0w - 32);
+        } else if (c > 0) {
+            wait_ptr = imp_steps + g;
+            wait_clamp = 16 * (last_needed(j0w - 32) >> 4) + 15;
+        }
+        wait_add = kGroup - 2;
+    } else if (lane == 1) {
+        if (g > 0) {
+            wait_ptr = prog + (w - 1);
+            wait_clamp = last_step(j0w + S);
+        }
+        wait_add = kGroup - 1 + 2 * S;
+    } else if (lane == 2) {
+        if (sidx < NSTR - 1) {
+            wait_ptr = prog + (w + NSTG);
+            wait_add = kGroup - 1 - (kMidDepth - 2);
+        } else if (c + 1 < P.ncta) {
+            wait_ptr = exp_steps + g;
+            wait_add = kGroup - 1 - kEdgeDepth;
+        }
+    } else if (lane == 3) {
+        if (g < NSTG - 1) wait_ptr = prog + (w + 1);
+        wait_add = kGroup - 1 - L::kHandRows - 2 * S;
     }
 
-    unsigned long long *flags_g = P.flags + ((size_t)fi * kMaxStages + g) * kWfMaxCtas * 2;
-    float *xchg_g = P.xchg + ((size_t)fi * NSTG + g) * P.ncta * L::kBoundaryFloats;
-
-    float x[S + 1], Ua[S + 1], Ub[S + 1], Da[S + 1], Db[S + 1];
+    float x[S + 1], Ua[S + 1], Ub[S + 1];
 #pragma unroll
     for (int k = 0; k <= S; ++k) {
-        x[k] = 0.0f; Ua[k] = 0.0f; Ub[k] = 0.0f; Da[k] = 0.0f; Db[k] = 0.0f;
+        x[k] = 0.0f; Ua[k] = 0.0f; Ub[k] = 0.0f;
     }
 
     const bool vec_ok = ((H & 3) == 0);
@@ -360,173 +507,150 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, 1) wf_kernel(const W
     if (j0w - S <= H - 1 && j0w + 30 >= H - 1) fix_cols |= kFixRight;
     int fix = fix_cols;
 
-    // Work of a warp at the first step of a batch.
-    auto batch_begin = [&](const int t0) {
-        const int n = t0 >> 4;
-        // left neighbours of this batch from the CTA on the left (same stage)
-        if (sidx == 0 && c > 0 && n <= n_last_left) {
-            if (lane == 0) {
-                const unsigned long long want = P.seq_base + (unsigned long long)(n + kBatchBias + 1);
-                const unsigned long long *pf = flags_g + (size_t)(c - 1) * 2;
-                while (ld_acquire_u64(pf) < want) __nanosleep(32);
+#pragma unroll 1
+    for (int t = tau_b; t <= tau_e; t += kGroup) {
+        // ---- wait for producers / consumers ------------------------------------------------------
+        {
+            const int need = min(t + wait_add, wait_clamp);
+            for (;;) {
+                bool ok = true;
+                if (wait_ptr) ok = ld_acquire_cta_s32(wait_ptr) >= need;
+                if (__all_sync(0xffffffffu, ok)) break;
             }
-            __syncwarp();
-            const float4 *src = reinterpret_cast<const float4 *>(
-                xchg_g + (size_t)(c - 1) * L::kBoundaryFloats + (size_t)(n & (kWfSlots - 1)) * kWfBatch * L::EXW);
-            float4 *dst = reinterpret_cast<float4 *>(const_cast<float *>(cx.imp) + (t0 & (kEdgeDepth - 1)) * L::EXW);
-            for (int i = lane; i < kWfBatch * L::EXW / 4; i += 32) dst[i] = __ldcg(src + i);
-            __syncwarp();
-            if (lane == 0) st_release_u64(flags_g + (size_t)(c - 1) * 2 + 1, P.seq_base + (unsigned long long)(n + kBatchBias + 1));
         }
-        // stage 0: stage the rows this strip reaches during the next batch
-        if (g == 0) {
-            cp_async_wait_all();
-            const int q0 = t0 + kWfBatch;
-            if (vec_ok) {
-                const int rr = lane >> 3, cg = lane & 7;
+        // ---- once per batch of 16 steps ----------------------------------------------------------
+        if ((t & (kWfBatch - 1)) == 0) {
+            if (g == 0) {
+                // stage the rows this strip reaches during the next batch
+                cp_async_wait_all();
+                const int q0 = t + kWfBatch;
+                if (vec_ok) {
+                    const int rr = lane >> 3, cg = lane & 7;
 #pragma unroll
-                for (int it = 0; it < kWfBatch / 4; ++it) {
-                    const int q = q0 + it * 4 + rr;
-                    const int row = q - kToff - j0;
-                    const int col = j0 + cg * 4;
-                    const bool ok = (row >= 0) && (row < W) && (col < H);
-                    const size_t off = ok ? ((size_t)row * H + col) : 0;
-                    const int so = (q & (kTileRows - 1)) * 32 + cg * 4;
-                    cp_async_f32x4(t_rhs + so, F.rhs + off, ok);
-                    if (HAS_X0) cp_async_f32x4(t_x0 + so, F.x0 + off, ok);
+                    for (int it = 0; it < kWfBatch / 4; ++it) {
+                        const int q = q0 + it * 4 + rr;
+                        const int row = q - kToff - j0;
+                        const int col = j0 + cg * 4;
+                        const bool ok = (row >= 0) && (row < W) && (col < H);
+                        const size_t off = ok ? ((size_t)row * H + col) : 0;
+                        const int so = (q & (kTileRows - 1)) * 32 + cg * 4;
+                        cp_async_f32x4(t_rhs + so, F.rhs + off, ok);
+                        if (HAS_X0) cp_async_f32x4(t_x0 + so, F.x0 + off, ok);
+                    }
+                } else {
+#pragma unroll 4
+                    for (int it = 0; it < kWfBatch; ++it) {
+                        const int q = q0 + it;
+                        const int row = q - kToff - j0;
+                        const int col = j0 + lane;
+                        const bool ok = (row >= 0) && (row < W) && (col < H);
+                        const size_t off = ok ? ((size_t)row * H + col) : 0;
+                        const int so = (q & (kTileRows - 1)) * 32 + lane;
+                        cp_async_f32(t_rhs + so, F.rhs + off, ok);
+                        if (HAS_X0) cp_async_f32(t_x0 + so, F.x0 + off, ok);
+                    }
                 }
-            } else {
+                cp_async_commit();
+            }
+            if (g == NSTG - 1) {
+                // write back the result rows that every lane has finished
+                const int col = gp - S;
+                const bool colok = (col >= 1) && (col <= H - 2);
 #pragma unroll 4
                 for (int it = 0; it < kWfBatch; ++it) {
-                    const int q = q0 + it;
-                    const int row = q - kToff - j0;
-                    const int col = j0 + lane;
-                    const bool ok = (row >= 0) && (row < W) && (col < H);
-                    const size_t off = ok ? ((size_t)row * H + col) : 0;
-                    const int so = (q & (kTileRows - 1)) * 32 + lane;
-                    cp_async_f32(t_rhs + so, F.rhs + off, ok);
-                    if (HAS_X0) cp_async_f32(t_x0 + so, F.x0 + off, ok);
+                    const int q = t - 48 + it;
+                    const int row = q - kToff - S - j0w;
+                    if (colok && row >= 1 && row <= W - 2)
+                        F.out[(size_t)row * H + col] = t_out[(q & (kTileRows - 1)) * 32 + lane];
                 }
             }
-            cp_async_commit();
-        }
-        // last stage: write back the result rows that every lane has finished
-        if (g == NSTG - 1) {
-            const int col = gp - S;
-            const bool colok = (col >= 1) && (col <= H - 2);
-#pragma unroll 4
-            for (int it = 0; it < kWfBatch; ++it) {
-                const int q = t0 - 48 + it;
-                const int row = q - kToff - S - j0w;
-                if (colok && row >= 1 && row <= W - 2)
-                    F.out[(size_t)row * H + col] = t_out[(q & (kTileRows - 1)) * 32 + lane];
-            }
-        }
-        // which walls the (lane, level) cells of this batch can touch
-        const int i_min = t0 - kToff - j0w - 31 - S;
-        const int i_max = t0 + kWfBatch - 1 - kToff - j0w - 1;
-        fix = fix_cols;
-        if (i_min <= 0 && i_max >= 0) fix |= kFixTop;
-        if (i_min <= W - 1 && i_max >= W - 1) fix |= kFixBottom;
-    };
-
-    // Work of a warp after the last step of a batch.
-    auto batch_end = [&](const int t0) {
-        const int n = t0 >> 4;
-        if (sidx == NSTR - 1 && c + 1 < P.ncta) {
+            // which walls the (lane, level) cells of this batch can touch
+            const int i_min = t - kToff - j0w - 31 - S;
+            const int i_max = t + kWfBatch - 1 - kToff - j0w - 1;
+            fix = fix_cols;
+            if (i_min <= 0 && i_max >= 0) fix |= kFixTop;
+            if (i_min <= W - 1 && i_max >= W - 1) fix |= kFixBottom;
             __syncwarp();
-            if (n - kWfSlots >= n_first_right) {
-                if (lane == 0) {
-                    const unsigned long long want = P.seq_base + (unsigned long long)(n - kWfSlots + kBatchBias + 1);
-                    const unsigned long long *pf = flags_g + (size_t)c * 2 + 1;
-                    while (ld_acquire_u64(pf) < want) __nanosleep(32);
-                }
-                __syncwarp();
-            }
-            float4 *dst = reinterpret_cast<float4 *>(
-                xchg_g + (size_t)c * L::kBoundaryFloats + (size_t)(n & (kWfSlots - 1)) * kWfBatch * L::EXW);
-            const float4 *src = reinterpret_cast<const float4 *>(cx.exp + (t0 & (kEdgeDepth - 1)) * L::EXW);
-            for (int i = lane; i < kWfBatch * L::EXW / 4; i += 32) dst[i] = src[i];
-            __threadfence();
-            __syncwarp();
-            if (lane == 0) st_release_u64(flags_g + (size_t)c * 2, P.seq_base + (unsigned long long)(n + kBatchBias + 1));
         }
-        if (g == NSTG - 1 && t0 + kWfBatch - 1 == tau_e) {
-            // drain: rows finished during the last three batches
-            __syncwarp();
-            const int col = gp - S;
-            const bool colok = (col >= 1) && (col <= H - 2);
-            for (int q = tau_e + 1 - 48; q <= tau_e; ++q) {
-                const int row = q - kToff - S - j0w;
-                if (colok && row >= 1 && row <= W - 2)
-                    F.out[(size_t)row * H + col] = t_out[(q & (kTileRows - 1)) * 32 + lane];
-            }
-        }
-    };
-
-#pragma unroll 1
-    for (int T = T0; T <= T1; T += 2) {
-        const int t = T - off_w;   // even
-        const bool active = (t >= tau_b) && (t <= tau_e);
-        if (active) {
-            if ((t & (kWfBatch - 1)) == 0) batch_begin(t);
-            wf_step<S, MODE>(x, Ua, Ub, Da, t, lane, gp, fix, cx);
-        }
-        __syncthreads();
-        if (active) {
-            wf_step<S, MODE>(x, Ub, Ua, Db, t + 1, lane, gp, fix, cx);
-            if (((t + 1) & (kWfBatch - 1)) == kWfBatch - 1) batch_end(t + 1 - (kWfBatch - 1));
-        }
-        __syncthreads();
+        // ---- four time steps ----------------------------------------------------------------------
+        wf_step<S, MODE>(x, Ua, Ub, t, lane, gp, fix, cx);
+        wf_step<S, MODE>(x, Ub, Ua, t + 1, lane, gp, fix, cx);
+        wf_step<S, MODE>(x, Ua, Ub, t + 2, lane, gp, fix, cx);
+        wf_step<S, MODE>(x, Ub, Ua, t + 3, lane, gp, fix, cx);
+        if (lane == 0) st_release_cta_s32(prog + w, t + kGroup - 1);
     }
     cp_async_wait_all();
+    if (g == NSTG - 1) {
+        // drain: rows finished during the last three batches
+        __syncwarp();
+        const int col = gp - S;
+        const bool colok = (col >= 1) && (col <= H - 2);
+        for (int q = tau_e + 1 - 48; q <= tau_e; ++q) {
+            const int row = q - kToff - S - j0w;
+            if (colok && row >= 1 && row <= W - 2)
+                F.out[(size_t)row * H + col] = t_out[(q & (kTileRows - 1)) * 32 + lane];
+        }
+    }
 }
 
 template <int S>
 size_t wf_smem_bytes(int nstr, int nstg)
 {
     using L = WfLayout<S>;
-    return sizeof(float) * ((size_t)2 * nstg * kEdgeDepth * L::EXW + (size_t)(nstr - 1) * nstg * kMidDepth * L::EXW +
-                            (size_t)nstr * 3 * kTileFloats + (size_t)nstr * (nstg - 1) * 2 * kHandFloats);
+    return sizeof(float) * ((size_t)96 + (size_t)2 * nstg * kEdgeDepth * L::EXW +
+                            (size_t)(nstr - 1) * nstg * kMidDepth * L::EXW + (size_t)nstr * 3 * kTileFloats +
+                            (size_t)nstr * (nstg - 1) * 2 * L::kHandFloats + (size_t)nstr * nstg * L::kStateFloats);
 }
 
+struct WfConfig { int nstr, ncta; size_t smem; };
+
+// Chooses strips per CTA so that every CTA of the launch is co-resident (cooperative launch).
 template <int S, int MODE, bool HAS_X0>
-cudaError_t wf_launch_inst(const SweepLaunch &Lc, SweepScratch &scr, cudaStream_t st)
+cudaError_t wf_configure(const SweepLaunch &Lc, WfConfig &cfg)
 {
     using L = WfLayout<S>;
     auto kern = wf_kernel<S, MODE, HAS_X0>;
-    const int H = Lc.H;
     const int nstg = Lc.stages;
-    const int total_levels = S * nstg;
-    const int NS = (H + total_levels + 31) / 32;     // strips: the last stage's frame is shifted left by all earlier sweeps
+    const int NS = (Lc.H + S * nstg + 31) / 32;     // strips: the last stage's frame is shifted left by all earlier sweeps
     int dev = 0, nsm = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     e = cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return e;
-    if (nstg < 1 || nstg > kMaxStages || nstg * 32 > L::kMaxThreads) return cudaErrorInvalidValue;
-
+    if (nstg < 1 || nstg > L::kMaxStagesS) return cudaErrorInvalidValue;
+    const int max_compute_warps = L::kMaxThreads / 32 - 2;
     int nstr = Lc.strips_per_cta > 0 ? Lc.strips_per_cta : 1;
-    while (nstr > 1 && nstr * nstg * 32 > L::kMaxThreads) nstr >>= 1;
+    while (nstr > 1 && nstr * nstg > max_compute_warps) nstr >>= 1;
     if (nstr > NS) nstr = NS;
-    int ncta = 0;
-    size_t smem = 0;
     for (;;) {
-        ncta = (NS + nstr - 1) / nstr;
-        smem = wf_smem_bytes<S>(nstr, nstg);
-        bool fits = smem <= 227 * 1024 && ncta <= kWfMaxCtas;
+        cfg.nstr = nstr;
+        cfg.ncta = (NS + nstr - 1) / nstr;
+        cfg.smem = wf_smem_bytes<S>(nstr, nstg);
+        bool fits = cfg.smem <= 227 * 1024 && cfg.ncta <= kWfMaxCtas;
         if (fits) {
-            e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem);
             if (e != cudaSuccess) return e;
             int per_sm = 0;
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nstr * nstg * 32, smem);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, (nstr * nstg + 2) * 32, cfg.smem);
             if (e != cudaSuccess) return e;
-            fits = (long long)ncta * Lc.nfields <= (long long)per_sm * nsm;
+            fits = (long long)cfg.ncta * Lc.nfields <= (long long)per_sm * nsm;
         }
-        if (fits) break;
-        if ((nstr * 2) * nstg * 32 > L::kMaxThreads) return cudaErrorCooperativeLaunchTooLarge;
+        if (fits) return cudaSuccess;
+        if ((nstr * 2) * nstg > max_compute_warps || wf_smem_bytes<S>(nstr * 2, nstg) > 227 * 1024 || nstr >= NS)
+            return cudaErrorCooperativeLaunchTooLarge;
         nstr *= 2;
     }
+}
+
+template <int S, int MODE, bool HAS_X0>
+cudaError_t wf_launch_inst(const SweepLaunch &Lc, SweepScratch &scr, cudaStream_t st, bool query_only)
+{
+    using L = WfLayout<S>;
+    auto kern = wf_kernel<S, MODE, HAS_X0>;
+    WfConfig cfg;
+    cudaError_t e = wf_configure<S, MODE, HAS_X0>(Lc, cfg);
+    if (e != cudaSuccess || query_only) return e;
+    const int nstg = Lc.stages, nstr = cfg.nstr, ncta = cfg.ncta;
     const size_t need = (size_t)Lc.nfields * nstg * ncta * L::kBoundaryFloats;
     if (need > scr.xchg_floats) {
         // grow-only scratch for the global boundary rings (first use of a larger configuration)
@@ -548,7 +672,6 @@ cudaError_t wf_launch_inst(const SweepLaunch &Lc, SweepScratch &scr, cudaStream_
     P.nstr = nstr;
     P.nstg = nstg;
     P.ncta = ncta;
-    P.stage_off = ((2 * S + 2) + 15) / 16 * 16;
     P.a = Lc.a;
     P.c_recip = Lc.c_recip;
     P.omega = Lc.omega;
@@ -556,18 +679,19 @@ cudaError_t wf_launch_inst(const SweepLaunch &Lc, SweepScratch &scr, cudaStream_
     P.flags = scr.flags;
     P.seq_base = scr.seq << 32;
     void *args[] = {&P};
-    return cudaLaunchCooperativeKernel((const void *)kern, dim3(ncta, Lc.nfields), dim3(nstr * nstg * 32), args, smem, st);
+    return cudaLaunchCooperativeKernel((const void *)kern, dim3(ncta, Lc.nfields), dim3((nstr * nstg + 2) * 32), args,
+                                       cfg.smem, st);
 }
 
 template <int S>
-cudaError_t wf_launch_levels(const SweepLaunch &Lc, SweepScratch &scr, cudaStream_t st)
+cudaError_t wf_launch_levels(const SweepLaunch &Lc, SweepScratch &scr, cudaStream_t st, bool query_only)
 {
-    if (Lc.mode == kSor) return wf_launch_inst<S, kSor, true>(Lc, scr, st);
+    if (Lc.mode == kSor) return wf_launch_inst<S, kSor, true>(Lc, scr, st, query_only);
     bool has_x0 = Lc.fld[0].x0 != nullptr;
     for (int i = 1; i < Lc.nfields; ++i)
         if ((Lc.fld[i].x0 != nullptr) != has_x0) return cudaErrorInvalidValue;
-    if (has_x0) return wf_launch_inst<S, kGaussSeidel, true>(Lc, scr, st);
-    return wf_launch_inst<S, kGaussSeidel, false>(Lc, scr, st);
+    if (has_x0) return wf_launch_inst<S, kGaussSeidel, true>(Lc, scr, st, query_only);
+    return wf_launch_inst<S, kGaussSeidel, false>(Lc, scr, st, query_only);
 }
 
 }  // namespace
@@ -577,24 +701,40 @@ size_t sweep_flag_words() { return (size_t)kMaxSweepFields * kMaxStages * kWfMax
 int sweep_max_stages(int levels)
 {
     switch (levels) {
-    case 1: case 2: case 5: return 512 / 32;
-    case 10: case 20: return 256 / 32;
+    case 1: return WfLayout<1>::kMaxStagesS;
+    case 2: return WfLayout<2>::kMaxStagesS;
+    case 5: return WfLayout<5>::kMaxStagesS;
+    case 10: return WfLayout<10>::kMaxStagesS;
+    case 20: return WfLayout<20>::kMaxStagesS;
     default: return 0;
     }
 }
 
-cudaError_t launch_sweep_pass(const SweepLaunch &L, SweepScratch &scr, cudaStream_t st, int *launches)
+static cudaError_t sweep_dispatch(const SweepLaunch &L, SweepScratch &scr, cudaStream_t st, bool query_only)
 {
     if (L.nfields < 1 || L.nfields > kMaxSweepFields || L.W < 3 || L.H < 3) return cudaErrorInvalidValue;
-    if (launches) *launches += 1;
     switch (L.levels) {
-    case 1: return wf_launch_levels<1>(L, scr, st);
-    case 2: return wf_launch_levels<2>(L, scr, st);
-    case 5: return wf_launch_levels<5>(L, scr, st);
-    case 10: return wf_launch_levels<10>(L, scr, st);
-    case 20: return wf_launch_levels<20>(L, scr, st);
+    case 1: return wf_launch_levels<1>(L, scr, st, query_only);
+    case 2: return wf_launch_levels<2>(L, scr, st, query_only);
+    case 5: return wf_launch_levels<5>(L, scr, st, query_only);
+    case 10: return wf_launch_levels<10>(L, scr, st, query_only);
+    case 20: return wf_launch_levels<20>(L, scr, st, query_only);
     default: return cudaErrorInvalidValue;
     }
+}
+
+bool sweep_config_fits(const SweepLaunch &L)
+{
+    SweepScratch none;
+    const cudaError_t e = sweep_dispatch(L, none, nullptr, true);
+    if (e != cudaSuccess) (void)cudaGetLastError();
+    return e == cudaSuccess;
+}
+
+cudaError_t launch_sweep_pass(const SweepLaunch &L, SweepScratch &scr, cudaStream_t st, int *launches)
+{
+    if (launches) *launches += 1;
+    return sweep_dispatch(L, scr, st, false);
 }
 
 }  // namespace fsb

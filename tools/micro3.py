@@ -1,3 +1,5 @@
+"""Development aid: time one projection for several (sweeps per warp, strips per CTA) configurations.
+usage: micro3.py [W H P spw strips]...   (default: a sweep over 8192^2 P=40 and 2048^2 P=20)"""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -20,10 +22,11 @@ def run(W, H, P, spw, strips, reps=3):
     sim.close()
 
 if __name__ == "__main__":
-    for (W, H, P) in [(8192, 8192, 40), (2048, 2048, 20)]:
-        for spw in (20, 10, 5, 2):
-            for strips in (1, 2, 4):
-                try:
-                    run(W, H, P, spw, strips)
-                except Exception as e:
-                    print("FAIL", W, H, P, spw, strips, str(e)[:100], flush=True)
+    a = [int(v) for v in sys.argv[1:]]
+    cfgs = [tuple(a[i:i + 5]) for i in range(0, len(a), 5)] if a else \
+        [(W, H, P, spw, st) for (W, H, P) in [(8192, 8192, 40), (2048, 2048, 20)] for spw in (20, 10, 5) for st in (1, 2, 4)]
+    for cfg in cfgs:
+        try:
+            run(*cfg)
+        except Exception as e:
+            print("FAIL", cfg, str(e)[:100], flush=True)
