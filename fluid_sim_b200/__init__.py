@@ -39,7 +39,8 @@ class Params(C.Structure):
 
 
 def library_path():
-    return os.path.join(_HERE, "libfluidsim_b200.so")
+    # FSB_LIBRARY selects an experimental build of the same ABI (development only)
+    return os.environ.get("FSB_LIBRARY") or os.path.join(_HERE, "libfluidsim_b200.so")
 
 
 def build_library(verbose=False):

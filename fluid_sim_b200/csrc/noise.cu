@@ -88,11 +88,23 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) noise_kernel(float *__res
         }
         __syncwarp();
         if (lane < ncell_round) {
-            for (int r = 0; r < 32; ++r) {
-                const size_t c = cell_base + (size_t)r * kNoiseCellsPerLane + (size_t)round * 31 + lane;
-                if (c < ncells) {
-                    u[c] = __fadd_rn(u[c], stg[r * kStagePitch + 2 * lane]);
-                    v[c] = __fadd_rn(v[c], stg[r * kStagePitch + 2 * lane + 1]);
+            // eight runs at a time: all loads are issued before the first add / store
+#pragma unroll 1
+            for (int r0 = 0; r0 < 32; r0 += 8) {
+                float uu[8], vv[8];
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    const size_t c = cell_base + (size_t)(r0 + r) * kNoiseCellsPerLane + (size_t)round * 31 + lane;
+                    uu[r] = (c < ncells) ? u[c] : 0.0f;
+                    vv[r] = (c < ncells) ? v[c] : 0.0f;
+                }
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    const size_t c = cell_base + (size_t)(r0 + r) * kNoiseCellsPerLane + (size_t)round * 31 + lane;
+                    if (c < ncells) {
+                        u[c] = __fadd_rn(uu[r], stg[(r0 + r) * kStagePitch + 2 * lane]);
+                        v[c] = __fadd_rn(vv[r], stg[(r0 + r) * kStagePitch + 2 * lane + 1]);
+                    }
                 }
             }
         }

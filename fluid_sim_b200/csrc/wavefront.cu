@@ -42,7 +42,10 @@ namespace {
 constexpr int kToff = 32;        // time offset: lane g sits on row t - kToff - g at level 0
 constexpr int kTileRows = 64;    // rows of an HBM staging ring (input tiles, result tile)
 constexpr int kTileFloats = kTileRows * 32;
-constexpr int kGroup = 4;        // steps a warp runs between two progress checks
+#ifndef WF_GROUP
+#define WF_GROUP 4
+#endif
+constexpr int kGroup = WF_GROUP;  // steps a warp runs between two progress checks (4, 8 or 16)
 constexpr int kEdgeDepth = 64;   // steps held by the CTA-edge rings (four batches)
 constexpr int kMidDepth = 16;    // steps held by the rings between strips of a CTA
 constexpr int kBatchBias = 64;   // keeps published batch numbers positive (later stages start at t < 0)
@@ -520,7 +523,11 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         }
         // ---- once per batch of 16 steps ----------------------------------------------------------
         if ((t & (kWfBatch - 1)) == 0) {
+#ifdef WF_EXP_NOFILL
+            if (false) {
+#else
             if (g == 0) {
+#endif
                 // stage the rows this strip reaches during the next batch
                 cp_async_wait_all();
                 const int q0 = t + kWfBatch;
@@ -552,16 +559,24 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 }
                 cp_async_commit();
             }
+#ifdef WF_EXP_NOFLUSH
+            if (false) {
+#else
             if (g == NSTG - 1) {
-                // write back the result rows that every lane has finished
+#endif
+                // write back the result rows that every lane has finished (all loads first, then all stores)
                 const int col = gp - S;
                 const bool colok = (col >= 1) && (col <= H - 2);
-#pragma unroll 4
-                for (int it = 0; it < kWfBatch; ++it) {
-                    const int q = t - 48 + it;
-                    const int row = q - kToff - S - j0w;
-                    if (colok && row >= 1 && row <= W - 2)
-                        F.out[(size_t)row * H + col] = t_out[(q & (kTileRows - 1)) * 32 + lane];
+                const int row0 = (t - 48) - kToff - S - j0w;
+                float vals[kWfBatch];
+#pragma unroll
+                for (int it = 0; it < kWfBatch; ++it) vals[it] = t_out[((t - 48 + it) & (kTileRows - 1)) * 32 + lane];
+                if (colok && row0 + kWfBatch - 1 >= 1 && row0 <= W - 2) {
+                    float *dst = F.out + ((long long)row0 * H + col);
+#pragma unroll
+                    for (int it = 0; it < kWfBatch; ++it) {
+                        if (row0 + it >= 1 && row0 + it <= W - 2) dst[(long long)it * H] = vals[it];
+                    }
                 }
             }
             // which walls the (lane, level) cells of this batch can touch
@@ -573,10 +588,13 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
             __syncwarp();
         }
         // ---- four time steps ----------------------------------------------------------------------
-        wf_step<S, MODE>(x, Ua, Ub, t, lane, gp, fix, cx);
-        wf_step<S, MODE>(x, Ub, Ua, t + 1, lane, gp, fix, cx);
-        wf_step<S, MODE>(x, Ua, Ub, t + 2, lane, gp, fix, cx);
-        wf_step<S, MODE>(x, Ub, Ua, t + 3, lane, gp, fix, cx);
+#pragma unroll 1
+        for (int u4 = 0; u4 < kGroup; u4 += 4) {
+            wf_step<S, MODE>(x, Ua, Ub, t + u4, lane, gp, fix, cx);
+            wf_step<S, MODE>(x, Ub, Ua, t + u4 + 1, lane, gp, fix, cx);
+            wf_step<S, MODE>(x, Ua, Ub, t + u4 + 2, lane, gp, fix, cx);
+            wf_step<S, MODE>(x, Ub, Ua, t + u4 + 3, lane, gp, fix, cx);
+        }
         if (lane == 0) st_release_cta_s32(prog + w, t + kGroup - 1);
     }
     cp_async_wait_all();
