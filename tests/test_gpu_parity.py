@@ -272,3 +272,24 @@ def test_two_sims_share_nothing():
         b.step(0.01)
     for x, y in zip(a.fields(), b.fields()):
         assert_bits(x, y, "independent sims")
+
+
+def test_cpp_dropin_headless_main():
+    """examples/headless_main.cpp (the reference's main loop without GL, src/main.cpp:350-396) linked against
+    the drop-in class: same sums as the unmodified reference after 100 frames, and the reset idiom works."""
+    import os
+    import subprocess
+    from tests.util import ROOT
+    exe = os.path.join(ROOT, "examples", "headless_main")
+    if not os.path.exists(exe):
+        pytest.skip("examples/headless_main not built")
+    out = subprocess.run([exe, "100"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    g = load_golden("config1_200x200_p20_d5")
+    sd = float(np.sum(g["d_100"].astype(np.float64)))
+    su = float(np.sum(g["u_100"].astype(np.float64)))
+    sv = float(np.sum(g["v_100"].astype(np.float64)))
+    want = "frames 100  sum(d) %.8f  sum(u) %.8f  sum(v) %.8f  d[100][110] %.9g" % (sd, su, sv, float(g["d_100"][100, 110]))
+    lines = out.stdout.strip().splitlines()
+    assert lines[0] == want, (lines[0], want)
+    assert lines[1] == "after reset d[100][110] 0"
