@@ -92,6 +92,7 @@ ABI = [
     ("fsb_get_stream", C.c_int, [_SIM, C.POINTER(C.c_void_p)]),
     ("fsb_profile_enable", C.c_int, [_SIM, C.c_int]),
     ("fsb_profile_read", C.c_int, [_SIM, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
+    ("fsb_pressure_sweeps_noalloc", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     ("fsb_launch_count", C.c_int, [_SIM, C.POINTER(C.c_uint64)]),
     ("fsb_set_tuning", C.c_int, [_SIM, C.c_int, C.c_int, C.c_int]),
     ("fsb_last_error", C.c_char_p, []),

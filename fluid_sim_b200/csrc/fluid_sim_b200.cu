@@ -888,6 +888,18 @@ int fsb_profile_read(fsb_sim *s, double *ms, uint64_t *counts, int reset)
     return FSB_OK;
 }
 
+int fsb_pressure_sweeps_noalloc(const float *d_divergence, float *d_pressure, int width, int height, int sweeps,
+                                void *stream)
+{
+    std::string msg;
+    const int rc = pressure_sweeps_noalloc(d_divergence, d_pressure, width, height, sweeps, (cudaStream_t)stream, msg);
+    if (rc == 0) return FSB_OK;
+    g_last_error = msg;
+    if (rc == 1) return FSB_ELIMIT;
+    if (rc == 2) return FSB_EINVAL;
+    return FSB_ECUDA;
+}
+
 void *fsb_host_alloc(size_t bytes)
 {
     void *p = nullptr;

@@ -35,6 +35,8 @@
 // All arithmetic uses explicit round-to-nearest intrinsics: no FMA contraction (F7).
 #include "fsb_internal.h"
 
+#include <cstdio>
+
 namespace fsb {
 
 namespace {
@@ -726,6 +728,169 @@ int sweep_max_stages(int levels)
     case 20: return WfLayout<20>::kMaxStagesS;
     default: return 0;
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Pressure sweeps for hosts that must not allocate (extern "C" fsb_pressure_sweeps_noalloc, declared in
+// include/fluid_sim_b200.h).  Same kernels as the projection of fsb_step, but the boundary rings and
+// progress words the sweep pipeline needs between CTAs live in one fixed array inside the library image.
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t kNaFlagBytes = (size_t)kMaxStages * kWfMaxCtas * 2 * sizeof(unsigned long long);   // 256 KiB
+constexpr size_t kNaRingBytes = (size_t)8 << 20;                                                      // 8 MiB
+constexpr size_t kNaScratchBytes = kNaFlagBytes + kNaRingBytes;
+
+// Resident on every GPU that loads the library, until the process exits.  The name below is only a
+// host-side handle; the device address is obtained once per device with cudaGetSymbolAddress.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaScratchBytes];
+
+constexpr int kNaMaxDevices = 64;
+void *g_na_addr[kNaMaxDevices];                 // device address of g_noalloc_scratch, per device ordinal
+unsigned long long g_na_seq[kNaMaxDevices];     // launch sequence number carried by the progress words
+
+template <int S>
+cudaError_t na_launch(const SweepLaunch &Lc, float *rings, size_t ring_floats, unsigned long long *flags,
+                      unsigned long long seq, cudaStream_t st, bool *too_big)
+{
+    using L = WfLayout<S>;
+    *too_big = false;
+    WfConfig cfg;
+    const bool has_x0 = Lc.fld[0].x0 != nullptr;
+    cudaError_t e = has_x0 ? wf_configure<S, kGaussSeidel, true>(Lc, cfg) : wf_configure<S, kGaussSeidel, false>(Lc, cfg);
+    if (e != cudaSuccess) return e;
+    const size_t need = (size_t)Lc.stages * cfg.ncta * L::kBoundaryFloats;
+    if (need > ring_floats) {
+        *too_big = true;
+        return cudaSuccess;
+    }
+    WfKernelParams P;
+    for (int i = 0; i < kMaxSweepFields; ++i) P.fld[i] = Lc.fld[0];
+    P.W = Lc.W;
+    P.H = Lc.H;
+    P.nstr = cfg.nstr;
+    P.nstg = Lc.stages;
+    P.ncta = cfg.ncta;
+    P.a = 0.0f;
+    P.c_recip = 1.0f;
+    P.omega = 1.0f;
+    P.xchg = rings;
+    P.flags = flags;
+    P.seq_base = seq << 32;
+    void *args[] = {&P};
+    const void *kern = has_x0 ? (const void *)wf_kernel<S, kGaussSeidel, true> : (const void *)wf_kernel<S, kGaussSeidel, false>;
+    return cudaLaunchCooperativeKernel(kern, dim3(cfg.ncta, 1), dim3((cfg.nstr * Lc.stages + 2) * 32), args, cfg.smem, st);
+}
+
+cudaError_t na_launch_levels(const SweepLaunch &Lc, float *rings, size_t ring_floats, unsigned long long *flags,
+                             unsigned long long seq, cudaStream_t st, bool *too_big)
+{
+    switch (Lc.levels) {
+    case 1: return na_launch<1>(Lc, rings, ring_floats, flags, seq, st, too_big);
+    case 2: return na_launch<2>(Lc, rings, ring_floats, flags, seq, st, too_big);
+    case 5: return na_launch<5>(Lc, rings, ring_floats, flags, seq, st, too_big);
+    case 10: return na_launch<10>(Lc, rings, ring_floats, flags, seq, st, too_big);
+    case 20: return na_launch<20>(Lc, rings, ring_floats, flags, seq, st, too_big);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace
+
+// Returns 0 on success, 1 if the request does not fit the built-in scratch, 2 for a bad argument, otherwise
+// -(cudaError_t).  `msg` receives a short description on failure.
+int pressure_sweeps_noalloc(const float *d_div, float *d_p, int W, int H, int sweeps, cudaStream_t st, std::string &msg)
+{
+    if (!d_div || !d_p || W < 3 || H < 3 || sweeps < 1) {
+        msg = "fsb_pressure_sweeps_noalloc: null pointer, grid smaller than 3x3 or sweeps < 1";
+        return 2;
+    }
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kNaMaxDevices) {
+        msg = "fsb_pressure_sweeps_noalloc: no usable current CUDA device";
+        return e != cudaSuccess ? -(int)e : 2;
+    }
+    if (!g_na_addr[dev]) {
+        // first call on this device: translate the host-side symbol into this device's address
+        void *ptr = nullptr;
+        e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr) {
+            msg = std::string("fsb_pressure_sweeps_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e);
+            return -(int)e;
+        }
+        g_na_addr[dev] = ptr;
+        g_na_seq[dev] = 0;
+    }
+    unsigned long long *flags = reinterpret_cast<unsigned long long *>(g_na_addr[dev]);
+    float *rings = reinterpret_cast<float *>(static_cast<unsigned char *>(g_na_addr[dev]) + kNaFlagBytes);
+    const size_t ring_floats = kNaRingBytes / sizeof(float);
+
+    // The array keeps whatever the previous call left behind.  The progress words must not look "ahead" of
+    // this call: they are cleared here (the rings themselves are always written before they are read).
+    e = cudaMemsetAsync(flags, 0, kNaFlagBytes, st);
+    if (e != cudaSuccess) {
+        msg = std::string("fsb_pressure_sweeps_noalloc: clearing the progress words failed: ") + cudaGetErrorString(e);
+        return -(int)e;
+    }
+
+    int left = sweeps;
+    bool first = true;
+    while (left > 0) {
+        bool placed = false;
+        for (int lv : {10, 20, 5, 2, 1}) {
+            if (lv > left) continue;
+            int stg = left / lv;
+            if (stg > sweep_max_stages(lv)) stg = sweep_max_stages(lv);
+            for (; stg >= 1 && !placed; --stg) {
+                SweepLaunch L{};
+                L.nfields = 1;
+                L.fld[0] = SweepField{first ? nullptr : d_p, d_div, d_p, 1.0f, 1.0f};
+                L.W = W;
+                L.H = H;
+                L.mode = kGaussSeidel;
+                L.levels = lv;
+                L.stages = stg;
+                L.strips_per_cta = 0;
+                bool too_big = false;
+                g_na_seq[dev] += 1;
+                e = na_launch_levels(L, rings, ring_floats, flags, g_na_seq[dev], st, &too_big);
+                if (e == cudaErrorCooperativeLaunchTooLarge) {
+                    (void)cudaGetLastError();
+                    continue;   // fewer stages need fewer resident CTAs
+                }
+                if (e != cudaSuccess) {
+                    msg = std::string("fsb_pressure_sweeps_noalloc: launch failed: ") + cudaGetErrorString(e);
+                    return -(int)e;
+                }
+                if (too_big) {
+                    char buf[256];
+                    snprintf(buf, sizeof(buf),
+                             "fsb_pressure_sweeps_noalloc: a %d x %d grid with %d sweeps needs more than the %zu-byte "
+                             "built-in scratch (about 8000 columns at 40 sweeps fit); use fsb_step / fsb_op_project instead",
+                             W, H, sweeps, kNaRingBytes);
+                    msg = buf;
+                    return 1;
+                }
+                placed = true;
+                left -= lv * stg;
+            }
+            if (placed) break;
+        }
+        if (!placed) {
+            msg = "fsb_pressure_sweeps_noalloc: no launchable pipeline configuration for this grid";
+            return 1;
+        }
+        // walls and corners of p after the pass (setBoundary(0, p), src/fluid_sim.cpp:330)
+        BndJob job{d_p, 0, 0};
+        e = launch_set_boundary(&job, 1, W, H, st);
+        if (e != cudaSuccess) {
+            msg = std::string("fsb_pressure_sweeps_noalloc: boundary kernel failed: ") + cudaGetErrorString(e);
+            return -(int)e;
+        }
+        first = false;
+    }
+    return 0;
 }
 
 static cudaError_t sweep_dispatch(const SweepLaunch &L, SweepScratch &scr, cudaStream_t st, bool query_only)

@@ -160,6 +160,33 @@ enum {
 int fsb_profile_enable(fsb_sim *s, int on);
 int fsb_profile_read(fsb_sim *s, double *ms, uint64_t *counts, int reset);
 
+/* No counterpart in the reference.
+ *
+ * The pressure relaxation of project() (src/fluid_sim.cpp:313-331: p = 0, then `sweeps` lexicographic
+ * Gauss-Seidel sweeps, each followed by setBoundary(0, p)) on buffers the CALLER owns, without a single
+ * allocation.  It exists for hosts that cannot let this library allocate: an engine that reserved the
+ * whole GPU for its own pools at start-up (a later cudaMalloc simply fails there), or a frame / control
+ * loop that must never run into the device-wide synchronisation and unbounded latency that cudaMalloc and
+ * cudaFree imply.  fsb_create / fsb_step size their inter-CTA boundary rings with cudaMalloc on first use;
+ * this entry point keeps the same rings and progress words in one fixed 8.25 MiB array that is part of
+ * the library image (every GPU that loads the library holds it until the process exits) and calls no
+ * cudaMalloc, cudaFree or any other allocating routine.
+ *
+ *   d_divergence  device pointer, width*height floats (only interior cells are read)
+ *   d_pressure    device pointer, width*height floats, fully overwritten; must not alias d_divergence
+ *   stream        cudaStream_t of the caller (NULL = default stream); the work is queued, not waited for
+ *
+ * The result is bit-identical to what fsb_op_project leaves in FSB_PREV_VEL_X for the same divergence.
+ * Limits and rules:
+ *   - the rings must fit the fixed array: about 8000 columns at 40 sweeps; larger requests return FSB_ELIMIT
+ *     with a message and launch nothing;
+ *   - the first call on a device looks up the array's device address (once per device, with that device
+ *     current): make that first call outside any stream capture;
+ *   - every call on a device uses the same array: calls whose GPU work overlaps (different streams, or a
+ *     second thread) race with each other - serialise them; calls on one stream are safe back to back. */
+int fsb_pressure_sweeps_noalloc(const float *d_divergence, float *d_pressure, int width, int height, int sweeps,
+                                void *stream);
+
 /* Number of kernels this library has launched on behalf of `s` so far. */
 int fsb_launch_count(const fsb_sim *s, uint64_t *count);
 
