@@ -44,6 +44,12 @@ namespace {
 constexpr int kToff = 32;        // time offset: lane g sits on row t - kToff - g at level 0
 constexpr int kTileRows = 64;    // rows of an HBM staging ring (input tiles, result tile)
 constexpr int kTileFloats = kTileRows * 32;
+// Result rows are written back by the last-stage warp itself (0) or by the export helper warp (1).
+// Measured on B200 at 8192^2: the helper variant loses about 8 % (it competes for issue slots with the
+// compute warps of its scheduler), so the default is 0.
+#ifndef WF_FLUSH_OFFLOAD
+#define WF_FLUSH_OFFLOAD 0
+#endif
 #ifndef WF_GROUP
 #define WF_GROUP 4
 #endif
@@ -118,13 +124,24 @@ __device__ __forceinline__ void st_release_u64(unsigned long long *p, unsigned l
 __device__ __forceinline__ int ld_acquire_cta_s32(const int *p)
 {
     int v;
+#ifdef WF_STRICT_FENCES
     asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+#else
+    // Shared-memory accesses of an SM are performed in issue order, so a volatile flag access is enough
+    // here: the producer's data stores are issued (after __syncwarp) before its flag store, and this
+    // warp's data loads are issued after the flag load.  Avoids one MEMBAR per poll.
+    asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+#endif
     return v;
 }
 
 __device__ __forceinline__ void st_release_cta_s32(int *p, int v)
 {
+#ifdef WF_STRICT_FENCES
     asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+#else
+    asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+#endif
 }
 
 __device__ __forceinline__ void cp_async_f32(float *smem_dst, const float *gsrc, bool valid)
@@ -149,9 +166,20 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // state buffer (lane 31: in the ring read by the next strip instead) and reads lane g-1's state of the
 // previous steps from there (lane 0: from the ring written by the previous strip).  U receives lane
 // g-1's x of step t-1; Up is the U of the step before (centre value of SOR, first-sweep walls).
-template <int S, int MODE>
+// FIX: kStepFast no wall in reach; kStepLeft / kStepRight the strip contains the j == 0 / j == H-1 wall and all
+// rows are interior (the common case for the first and last strips: one compare + select per level);
+// kStepFull anything (first / last rows of the grid, tiny grids).
+enum { kStepFast = 0, kStepLeft = 1, kStepRight = 2, kStepFull = 3 };
+
+__device__ __forceinline__ float bit_select(float keep, float take, unsigned mask)
+{
+    return __uint_as_float((__float_as_uint(keep) & ~mask) | (__float_as_uint(take) & mask));
+}
+
+template <int S, int MODE, int FIX>
 __device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], const float (&Up)[S + 1], const int t,
-                                        const int lane, const int gp, const int fix, const WfWarp &cx)
+                                        const int lane, const int gp, const int fix, const unsigned (&wmask)[S + 1],
+                                        const WfWarp &cx)
 {
     using L = WfLayout<S>;
     float Dc[S + 1];
@@ -228,7 +256,23 @@ __device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], co
     // +-(the adjacent interior cell's sweep k-1 value) afterwards.  `fix` is warp-uniform and non-zero only
     // for the few batches / strips that touch a wall.  Cells outside the grid hold garbage that no cell
     // inside the grid ever reads.
-    if (fix) {
+    if (FIX == kStepLeft) {
+        // wmask[k] is all ones in the one lane that sits on column 0 at level k (loop-invariant registers:
+        // one LOP3 per level, no predicates).  Gauss-Seidel runs on the pressure only, whose wall sign is +1.
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wr = (MODE == kGaussSeidel) ? x[k - 1] : __fmul_rn(cx.sj, x[k - 1]);
+            const float wv = (k == 1 && cx.first) ? cold1 : wr;
+            acc[k] = bit_select(acc[k], wv, wmask[k]);
+        }
+    } else if (FIX == kStepRight) {
+        // wmask[k] is all ones in the one lane that sits on column H-1 at level k
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wv = (MODE == kGaussSeidel) ? U[k] : __fmul_rn(cx.sj, U[k]);
+            acc[k] = bit_select(acc[k], wv, wmask[k]);
+        }
+    } else if (FIX == kStepFull) {
         if (fix & kFixLeft) {
 #pragma unroll
             for (int k = 1; k <= S; ++k) {
@@ -311,14 +355,15 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     int *prog = reinterpret_cast<int *>(smem);                          // [NW] last step completed by a compute warp
     int *imp_steps = prog + 64;                                         // [NSTG] last step present in edge_in
     int *exp_steps = imp_steps + 16;                                    // [NSTG] last step moved out of edge_out
-    float *edge_in = smem + 96;                                         // [NSTG][kEdgeDepth * EXW]
+    int *flushed_steps = exp_steps + 16;                                // [NSTR] last result slot written back to HBM
+    float *edge_in = smem + 112;                                         // [NSTG][kEdgeDepth * EXW]
     float *edge_out = edge_in + NSTG * kEdgeDepth * L::EXW;             // [NSTG][kEdgeDepth * EXW]
     float *mid = edge_out + NSTG * kEdgeDepth * L::EXW;                 // [NSTR-1][NSTG][kMidDepth * EXW]
     float *tiles = mid + (NSTR - 1) * NSTG * kMidDepth * L::EXW;        // [NSTR][rhs | x0 | result]
     float *hand = tiles + NSTR * 3 * kTileFloats;                       // [NSTR][NSTG-1][x | rhs]
     float *state = hand + NSTR * (NSTG - 1) * 2 * L::kHandFloats;       // [NW][kStateFloats]
     {
-        const int total = 96 + 2 * NSTG * kEdgeDepth * L::EXW + (NSTR - 1) * NSTG * kMidDepth * L::EXW +
+        const int total = 112 + 2 * NSTG * kEdgeDepth * L::EXW + (NSTR - 1) * NSTG * kMidDepth * L::EXW +
                           NSTR * 3 * kTileFloats + NSTR * (NSTG - 1) * 2 * L::kHandFloats + NW * L::kStateFloats;
         for (int i = tid; i < total; i += nthreads) smem[i] = 0.0f;
     }
@@ -333,6 +378,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         imp_steps[tid] = first_step(warp_j0w(0, tid)) - 1;
         exp_steps[tid] = first_step(warp_j0w(NSTR - 1, tid)) - 1;
     }
+    if (tid < NSTR) flushed_steps[tid] = first_step(warp_j0w(tid, NSTG - 1)) - 48 - 1;
     __syncthreads();
 
     // =============================== comm warps ==================================================
@@ -342,11 +388,19 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     // cost of a round does not grow with the number of stages.
     if (w >= NW) {
         const bool is_exp = (w == NW + 1);
-        const int gi = lane;
-        const bool valid = (gi < NSTG) && (is_exp ? (c + 1 < P.ncta) : (c > 0));
-        int n = 0, n_end = -1, n_first_right = 0;
+        // lanes 0..15: one ring-transfer machine per stage; lanes 16..31 of the export warp: one result
+        // write-back machine per strip of the CTA (rows the last stage has finished, staged in its tile)
+        const bool is_flush = WF_FLUSH_OFFLOAD && is_exp && lane >= 16;
+        const int gi = lane & 15;
+        const bool valid = is_flush ? (gi < NSTR) : ((lane < 16) && (gi < NSTG) && (is_exp ? (c + 1 < P.ncta) : (c > 0)));
+        int n = 0, n_end = -1, n_first_right = 0, fl_tau_e = 0;
         if (valid) {
-            if (!is_exp) {
+            if (is_flush) {
+                const int jl = warp_j0w(gi, NSTG - 1);
+                n = (first_step(jl) - 48) >> 4;        // block n = result slots [16n, 16n+16)
+                fl_tau_e = last_step(jl);
+                n_end = fl_tau_e >> 4;
+            } else if (!is_exp) {
                 n = first_step(warp_j0w(0, gi)) >> 4;
                 n_end = last_needed(warp_j0w(0, gi) - 32) >> 4;           // last batch of the strip on the left
             } else {
@@ -358,12 +412,16 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         unsigned long long *fl = P.flags + ((size_t)fi * kMaxStages + (gi < kMaxStages ? gi : 0)) * kWfMaxCtas * 2;
         const volatile unsigned long long *poll_flag =
             is_exp ? fl + (size_t)c * 2 + 1 : fl + (size_t)(c > 0 ? c - 1 : 0) * 2;
-        const int *poll_prog = is_exp ? prog + (NSTR - 1) * NSTG + (gi < NSTG ? gi : 0) : prog + (gi < NSTG ? gi : 0);
+        const int *poll_prog = is_flush ? prog + (gi < NSTR ? gi : 0) * NSTG + (NSTG - 1)
+                                        : (is_exp ? prog + (NSTR - 1) * NSTG + (gi < NSTG ? gi : 0) : prog + (gi < NSTG ? gi : 0));
         bool done = !valid || n > n_end;
         while (!__all_sync(0xffffffffu, done)) {
             bool ready = false;
             if (!done) {
-                if (!is_exp) {
+                if (is_flush) {
+                    // every lane of the strip has written slot q once the warp has finished step q + 31
+                    ready = ld_acquire_cta_s32(poll_prog) >= min(16 * n + 15 + 32, fl_tau_e);
+                } else if (!is_exp) {
                     // batch n replaces batch n - kEdgeDepth/16 in edge_in, whose last slot is read one and two steps later
                     ready = ld_acquire_cta_s32(poll_prog) >= 16 * (n - kEdgeDepth / kWfBatch + 1) + 1 &&
                             *poll_flag >= P.seq_base + (unsigned long long)(n + kBatchBias + 1);
@@ -378,8 +436,8 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 __nanosleep(32);
                 continue;
             }
-            __threadfence();   // acquire side of the flags just observed
-            for (unsigned mm = m; mm; mm &= mm - 1) {
+            if (m & 0xffffu) __threadfence();   // acquire side of the global flags just observed
+            for (unsigned mm = m & 0xffffu; mm; mm &= mm - 1) {
                 const int src = __ffs(mm) - 1;
                 const int bn = __shfl_sync(0xffffffffu, n, src);
                 float *xg = P.xchg + ((size_t)fi * NSTG + src) * P.ncta * L::kBoundaryFloats;
@@ -399,10 +457,31 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                     for (int i = lane; i < kWfBatch * L::EXW / 4; i += 32) gdst[i] = ssrc[i];
                 }
             }
-            if (is_exp) __threadfence();
+            for (unsigned mm = m >> 16; mm; mm &= mm - 1) {
+                // write back result block bn of strip `strip` (lane = column inside the strip)
+                const int strip = __ffs(mm) - 1;
+                const int bn = __shfl_sync(0xffffffffu, n, 16 + strip);
+                const int jl = warp_j0w(strip, NSTG - 1);
+                const float *tile = tiles + strip * 3 * kTileFloats + 2 * kTileFloats;
+                const int col = jl + lane - S;
+                const bool colok = (col >= 1) && (col <= H - 2);
+                const int row0 = 16 * bn - kToff - S - jl;
+                float vals[kWfBatch];
+#pragma unroll
+                for (int it = 0; it < kWfBatch; ++it) vals[it] = tile[((16 * bn + it) & (kTileRows - 1)) * 32 + lane];
+                if (colok && row0 + kWfBatch - 1 >= 1 && row0 <= W - 2) {
+                    float *dst = F.out + ((long long)row0 * H + col);
+#pragma unroll
+                    for (int it = 0; it < kWfBatch; ++it)
+                        if (row0 + it >= 1 && row0 + it <= W - 2) dst[(long long)it * H] = vals[it];
+                }
+            }
+            if (is_exp && (m & 0xffffu)) __threadfence();
             __syncwarp();
             if (ready) {
-                if (!is_exp) {
+                if (is_flush) {
+                    st_release_cta_s32(flushed_steps + gi, 16 * n + 15);
+                } else if (!is_exp) {
                     st_release_cta_s32(imp_steps + gi, 16 * n + 15);
                     st_release_u64(fl + (size_t)(c - 1) * 2 + 1, P.seq_base + (unsigned long long)(n + kBatchBias + 1));
                 } else {
@@ -470,6 +549,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     // ---- what this warp waits for before a group of steps starting at t: counter >= min(t + add, clamp) ----
     //   lane 0: left neighbours present      lane 1: previous stage far enough ahead
     //   lane 2: right strip / export freed the slots we overwrite      lane 3: next stage freed its ring slots
+    //   lane 4: (last stage) the result tile slots we overwrite have been written back
     const int *wait_ptr = nullptr;
     int wait_add = 0, wait_clamp = 0x7fffffff;
     if (lane == 0) {
@@ -498,6 +578,10 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     } else if (lane == 3) {
         if (g < NSTG - 1) wait_ptr = prog + (w + 1);
         wait_add = kGroup - 1 - L::kHandRows - 2 * S;
+    } else if (lane == 4) {
+        // last stage: the result tile slot we are about to overwrite has been written back
+        if (WF_FLUSH_OFFLOAD && g == NSTG - 1) wait_ptr = flushed_steps + sidx;
+        wait_add = kGroup - 1 - kTileRows;
     }
 
     float x[S + 1], Ua[S + 1], Ub[S + 1];
@@ -511,18 +595,45 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     if (j0w - S <= 0 && j0w + 30 >= 0) fix_cols |= kFixLeft;
     if (j0w - S <= H - 1 && j0w + 30 >= H - 1) fix_cols |= kFixRight;
     int fix = fix_cols;
-
+    // lane masks of the column wall this strip contains (if exactly one); the empty asm keeps them in
+    // registers instead of letting the compiler recompute them inside the loop
+    unsigned wmask[S + 1];
+#pragma unroll
+    for (int k = 0; k <= S; ++k) {
+        const int col = gp - k;
+        wmask[k] = ((fix_cols == kFixLeft && col == 0) || (fix_cols == kFixRight && col == H - 1)) ? 0xffffffffu : 0u;
+        asm volatile("" : "+r"(wmask[k]));
+    }
+#ifdef WF_PROFILE
+    long long pf_wait = 0, pf_batch = 0, pf_step = 0, pf_first = 0;
+    int pf_groups = 0;
+    long long pf_spins = 0;
+    long long pf_mine = 0;   // spins in which this lane's own condition was the unmet one
+#endif
 #pragma unroll 1
     for (int t = tau_b; t <= tau_e; t += kGroup) {
+#ifdef WF_PROFILE
+        const long long pf0 = clock64();
+#endif
         // ---- wait for producers / consumers ------------------------------------------------------
         {
             const int need = min(t + wait_add, wait_clamp);
             for (;;) {
                 bool ok = true;
                 if (wait_ptr) ok = ld_acquire_cta_s32(wait_ptr) >= need;
+#ifdef WF_PROFILE
+                if (!ok) pf_mine++;
+#endif
                 if (__all_sync(0xffffffffu, ok)) break;
+#ifdef WF_PROFILE
+                pf_spins++;
+#endif
             }
         }
+#ifdef WF_PROFILE
+        const long long pf1 = clock64();
+        if (pf_groups == 0) pf_first = pf1 - pf0; else pf_wait += pf1 - pf0;
+#endif
         // ---- once per batch of 16 steps ----------------------------------------------------------
         if ((t & (kWfBatch - 1)) == 0) {
 #ifdef WF_EXP_NOFILL
@@ -561,11 +672,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 }
                 cp_async_commit();
             }
-#ifdef WF_EXP_NOFLUSH
-            if (false) {
-#else
-            if (g == NSTG - 1) {
-#endif
+            if (!WF_FLUSH_OFFLOAD && g == NSTG - 1) {
                 // write back the result rows that every lane has finished (all loads first, then all stores)
                 const int col = gp - S;
                 const bool colok = (col >= 1) && (col <= H - 2);
@@ -590,17 +697,58 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
             __syncwarp();
         }
         // ---- four time steps ----------------------------------------------------------------------
+#ifdef WF_PROFILE
+        const long long pf2 = clock64();
+        pf_batch += pf2 - pf1;
+#endif
+        // two step bodies (the U / Up roles alternate), kept small for the instruction cache; the wall
+        // fix-ups live in a second copy that only strips / batches near a wall execute
+        if (fix == 0) {
 #pragma unroll 1
-        for (int u4 = 0; u4 < kGroup; u4 += 4) {
-            wf_step<S, MODE>(x, Ua, Ub, t + u4, lane, gp, fix, cx);
-            wf_step<S, MODE>(x, Ub, Ua, t + u4 + 1, lane, gp, fix, cx);
-            wf_step<S, MODE>(x, Ua, Ub, t + u4 + 2, lane, gp, fix, cx);
-            wf_step<S, MODE>(x, Ub, Ua, t + u4 + 3, lane, gp, fix, cx);
+            for (int u2 = 0; u2 < kGroup; u2 += 2) {
+                wf_step<S, MODE, kStepFast>(x, Ua, Ub, t + u2, lane, gp, 0, wmask, cx);
+                wf_step<S, MODE, kStepFast>(x, Ub, Ua, t + u2 + 1, lane, gp, 0, wmask, cx);
+            }
+        } else if (fix == kFixLeft) {
+#pragma unroll 1
+            for (int u2 = 0; u2 < kGroup; u2 += 2) {
+                wf_step<S, MODE, kStepLeft>(x, Ua, Ub, t + u2, lane, gp, fix, wmask, cx);
+                wf_step<S, MODE, kStepLeft>(x, Ub, Ua, t + u2 + 1, lane, gp, fix, wmask, cx);
+            }
+        } else if (fix == kFixRight) {
+#pragma unroll 1
+            for (int u2 = 0; u2 < kGroup; u2 += 2) {
+                wf_step<S, MODE, kStepRight>(x, Ua, Ub, t + u2, lane, gp, fix, wmask, cx);
+                wf_step<S, MODE, kStepRight>(x, Ub, Ua, t + u2 + 1, lane, gp, fix, wmask, cx);
+            }
+        } else {
+#pragma unroll 1
+            for (int u2 = 0; u2 < kGroup; u2 += 2) {
+                wf_step<S, MODE, kStepFull>(x, Ua, Ub, t + u2, lane, gp, fix, wmask, cx);
+                wf_step<S, MODE, kStepFull>(x, Ub, Ua, t + u2 + 1, lane, gp, fix, wmask, cx);
+            }
         }
         if (lane == 0) st_release_cta_s32(prog + w, t + kGroup - 1);
+#ifdef WF_PROFILE
+        pf_step += clock64() - pf2;
+        pf_groups++;
+#endif
     }
+#ifdef WF_PROFILE
+    {
+        const long long m0 = __shfl_sync(0xffffffffu, pf_mine, 0), m1 = __shfl_sync(0xffffffffu, pf_mine, 1);
+        const long long m2 = __shfl_sync(0xffffffffu, pf_mine, 2), m3 = __shfl_sync(0xffffffffu, pf_mine, 3);
+        if (lane == 0 && fi == 0 && (c == P.ncta / 2 || c == 0 || c == P.ncta - 1 || c == P.ncta - 2))
+            printf("cta %d warp %d: unmet per group: left %.1f prev-stage %.1f right/export %.1f next-stage %.1f\n", c, w,
+                   (double)m0 / pf_groups, (double)m1 / pf_groups, (double)m2 / pf_groups, (double)m3 / pf_groups);
+    }
+    if (lane == 0 && fi == 0 && (c == P.ncta / 2 || c == 0 || c == P.ncta - 1 || c == P.ncta - 2))
+        printf("cta %d warp %d (strip %d stage %d): groups %d  first-wait %lld  per group: wait %lld batch %lld steps %lld  spins/group %.1f\n",
+               c, w, sidx, g, pf_groups, pf_first, pf_wait / pf_groups, pf_batch / pf_groups, pf_step / pf_groups,
+               (double)pf_spins / pf_groups);
+#endif
     cp_async_wait_all();
-    if (g == NSTG - 1) {
+    if (!WF_FLUSH_OFFLOAD && g == NSTG - 1) {
         // drain: rows finished during the last three batches
         __syncwarp();
         const int col = gp - S;
@@ -617,7 +765,7 @@ template <int S>
 size_t wf_smem_bytes(int nstr, int nstg)
 {
     using L = WfLayout<S>;
-    return sizeof(float) * ((size_t)96 + (size_t)2 * nstg * kEdgeDepth * L::EXW +
+    return sizeof(float) * ((size_t)112 + (size_t)2 * nstg * kEdgeDepth * L::EXW +
                             (size_t)(nstr - 1) * nstg * kMidDepth * L::EXW + (size_t)nstr * 3 * kTileFloats +
                             (size_t)nstr * (nstg - 1) * 2 * L::kHandFloats + (size_t)nstr * nstg * L::kStateFloats);
 }

@@ -13,3 +13,4 @@ for _ in range(3):
     sim.project()
 sim.sync()
 print("done")
+sim.close()
