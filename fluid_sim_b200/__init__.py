@@ -92,6 +92,16 @@ ABI = [
     ("fsb_get_stream", C.c_int, [_SIM, C.POINTER(C.c_void_p)]),
     ("fsb_profile_enable", C.c_int, [_SIM, C.c_int]),
     ("fsb_profile_read", C.c_int, [_SIM, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
+    ("fsb_create_block", C.c_int, [C.POINTER(Params), C.c_int, C.c_int, C.c_int, C.POINTER(_SIM)]),
+    ("fsb_block_info", C.c_int, [_SIM, _ip, _ip, _ip, _ip]),
+    ("fsb_link_handle", C.c_int, [_SIM, C.c_void_p]),
+    ("fsb_link_connect", C.c_int, [_SIM, C.c_void_p, C.c_void_p]),
+    ("fsb_blk_sweep", C.c_int, [_SIM, C.c_int, C.c_int, _ip, _ip, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_uint64]),
+    ("fsb_blk_set_boundary", C.c_int, [_SIM, C.c_int, _ip, _ip, _ip]),
+    ("fsb_blk_divergence", C.c_int, [_SIM]),
+    ("fsb_blk_gradient", C.c_int, [_SIM]),
+    ("fsb_blk_advect_velocity", C.c_int, [_SIM, C.c_float]),
+    ("fsb_blk_advect_density", C.c_int, [_SIM, C.c_float, C.c_int]),
     ("fsb_pressure_sweeps_noalloc", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     ("fsb_launch_count", C.c_int, [_SIM, C.POINTER(C.c_uint64)]),
     ("fsb_set_tuning", C.c_int, [_SIM, C.c_int, C.c_int, C.c_int]),

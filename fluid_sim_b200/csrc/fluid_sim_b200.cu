@@ -56,8 +56,9 @@ constexpr int kNumFields = 6;
 
 struct fsb_sim {
     fsb_params prm;
-    int W = 0, H = 0;
-    size_t ncells = 0;
+    int W = 0, H = 0;      // global grid
+    GridView G{};          // this process's view of it (the whole grid unless the simulation is a column block)
+    size_t ncells = 0;     // floats per local field (W * pitch)
     int device = 0;
     cudaStream_t stream = nullptr;
     float *f[kNumFields] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -77,6 +78,11 @@ struct fsb_sim {
     int tune_strips = 0;   // strips per CTA (0 = automatic)
     int tune_levels = 0;   // sweeps per warp (0 = automatic)
     int tune_stages = 0;   // cap on chained warps per strip (0 = automatic)
+    // column block of a multi-rank run (is_block == false: the whole grid)
+    bool is_block = false;
+    int strip_begin = 0, strip_end = -1;       // 32-column strips of the sweep chain this rank runs
+    unsigned char *link_buf = nullptr;          // [rings | in_prod | cons], shared with both neighbours through CUDA IPC
+    void *peer_left = nullptr, *peer_right = nullptr;   // the neighbours' link_buf mapped into this process
     // optional per-kernel-class timing (CUDA events on the simulation's stream)
     bool profiling = false;
     struct ProfRec { int cat; cudaEvent_t a, b; };
@@ -207,7 +213,7 @@ int set_noise_window(fsb_sim *s, uint32_t seed, uint64_t pos)
 int set_boundary(fsb_sim *s, const BndJob *jobs, int n)
 {
     ProfScope ps(s, FSB_PROF_BOUNDARY);
-    FSB_CUDA(launch_set_boundary(jobs, n, s->W, s->H, s->stream));
+    FSB_CUDA(launch_set_boundary(jobs, n, s->G, s->stream));
     s->launches += 1;
     return FSB_OK;
 }
@@ -321,7 +327,7 @@ int project(fsb_sim *s, float *u, float *v, float *p, float *div)
 {
     {
         ProfScope ps(s, FSB_PROF_DIVERGENCE);
-        FSB_CUDA(launch_divergence(u, v, div, s->W, s->H, s->stream));
+        FSB_CUDA(launch_divergence(u, v, div, s->G, s->stream));
     }
     s->launches += 1;
     const std::vector<SweepPlan> passes = plan_sweeps(s, s->prm.proj_iters, 1, kGaussSeidel);
@@ -349,7 +355,7 @@ int project(fsb_sim *s, float *u, float *v, float *p, float *div)
     }
     {
         ProfScope ps(s, FSB_PROF_GRADIENT);
-        FSB_CUDA(launch_gradient(u, v, p, s->W, s->H, s->stream));
+        FSB_CUDA(launch_gradient(u, v, p, s->G, s->stream));
     }
     s->launches += 1;
     BndJob jobs[2] = {BndJob{u, 1, 0}, BndJob{v, 2, 0}};
@@ -372,18 +378,18 @@ int advect_one(fsb_sim *s, int b, float *dst, const float *src, const float *u, 
     const int scheme = s->prm.advect_scheme;
     if (scheme == FSB_ADVECT_RK4) {
         ProfScope ps(s, FSB_PROF_ADVECT_SCALAR);
-        FSB_CUDA(launch_advect_rk4(dst, src, nullptr, nullptr, u, v, pz, s->W, s->H, dt, s->stream));
+        FSB_CUDA(launch_advect_rk4(dst, src, nullptr, nullptr, u, v, pz, s->G, dt, s->stream));
         s->launches += 1;
     } else if (scheme == FSB_ADVECT_SEMI_LAGRANGIAN) {
-        FSB_CUDA(launch_advect_sl(dst, src, u, v, pz, s->W, s->H, dt, -1.0f, s->stream));
+        FSB_CUDA(launch_advect_sl(dst, src, u, v, pz, s->G, dt, -1.0f, s->stream));
         s->launches += 1;
     } else {
         FSB_TRY(ensure_temps(s));
-        FSB_CUDA(launch_advect_sl(s->temp[0], src, u, v, pz, s->W, s->H, dt, -1.0f, s->stream));
+        FSB_CUDA(launch_advect_sl(s->temp[0], src, u, v, pz, s->G, dt, -1.0f, s->stream));
         FSB_TRY(set_boundary1(s, s->temp[0], b));
-        FSB_CUDA(launch_advect_sl(s->temp[1], s->temp[0], u, v, 0, s->W, s->H, dt, +1.0f, s->stream));
+        FSB_CUDA(launch_advect_sl(s->temp[1], s->temp[0], u, v, 0, s->G, dt, +1.0f, s->stream));
         FSB_TRY(set_boundary1(s, s->temp[1], b));
-        FSB_CUDA(launch_maccormack_combine(dst, src, s->temp[0], s->temp[1], pz, s->W, s->H, s->stream));
+        FSB_CUDA(launch_maccormack_combine(dst, src, s->temp[0], s->temp[1], pz, s->G, s->stream));
         s->launches += 3;
     }
     return set_boundary1(s, dst, b);
@@ -395,12 +401,15 @@ int add_noise(fsb_sim *s)
     std::memcpy(nw.w, s->noise_win, sizeof(nw.w));
     const int zero = s->prm.noise_mode == FSB_NOISE_ZERO;
     ProfScope ps(s, FSB_PROF_NOISE);
-    FSB_CUDA(launch_noise(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->ncells, nw, s->noise_tables, zero, s->stream));
+    if (s->is_block)
+        FSB_CUDA(launch_noise_block(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->G, nw, s->noise_tables, zero, s->stream));
+    else
+        FSB_CUDA(launch_noise(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->ncells, nw, s->noise_tables, zero, s->stream));
     s->launches += zero ? 2 : 1;
     // the reference consumes 2*W*H outputs per step in either case (the zero mode replaces rand() itself)
     if (!zero) {
         apply_jump(s->noise_step_jump, s->noise_win);
-        s->noise_pos += 2ull * s->ncells;
+        s->noise_pos += 2ull * (uint64_t)s->W * (uint64_t)s->H;
     }
     return FSB_OK;
 }
@@ -420,7 +429,7 @@ int velocity_step(fsb_sim *s, float dt)
     if (s->prm.advect_scheme == FSB_ADVECT_RK4) {
         {
             ProfScope ps(s, FSB_PROF_ADVECT_VELOCITY);
-            FSB_CUDA(launch_advect_rk4(nu, u, nv, v, u, v, 0, s->W, s->H, dt, s->stream));
+            FSB_CUDA(launch_advect_rk4(nu, u, nv, v, u, v, 0, s->G, dt, s->stream));
         }
         s->launches += 1;
         BndJob jobs[2] = {BndJob{nu, 1, 0}, BndJob{nv, 2, 0}};
@@ -450,6 +459,7 @@ void invalidate_mirror(fsb_sim *s) { s->mirror_valid[0] = s->mirror_valid[1] = s
 
 int refresh_mirror(fsb_sim *s, int field)
 {
+    if (s->is_block) return fail(FSB_EINVAL, "per-cell getters are not available on a column block; read the field instead");
     if (s->mirror_valid[field]) return FSB_OK;
     FSB_TRY(flush_sources(s));
     s->mirror[field].resize(s->ncells);
@@ -488,7 +498,31 @@ void fsb_default_params(fsb_params *p)
     p->device = -1;
 }
 
-int fsb_create(const fsb_params *p, fsb_sim **out)
+static int create_common(const fsb_params *p, const GridView *block, fsb_sim **out);
+
+int fsb_create(const fsb_params *p, fsb_sim **out) { return create_common(p, nullptr, out); }
+
+/* layout of the link buffer shared between neighbouring ranks */
+static const size_t kLinkRingBytes = (size_t)kMaxSweepFields * kLinkStages * kLinkRingFloats * sizeof(float);
+static const size_t kLinkFlagBytes = (size_t)kMaxSweepFields * kLinkStages * sizeof(unsigned long long);
+static const size_t kLinkBytes = kLinkRingBytes + 2 * kLinkFlagBytes;
+
+int fsb_create_block(const fsb_params *p, int col_begin, int col_end, int halo, fsb_sim **out)
+{
+    if (!p || !out) return fail(FSB_EINVAL, "fsb_create_block: null argument");
+    if (col_begin < 0 || col_end > p->height || col_begin >= col_end || halo < 0 || (halo & 31) || (col_begin & 31))
+        return fail(FSB_EINVAL, "fsb_create_block: columns must lie in the grid, col_begin and halo must be multiples of 32");
+    GridView G;
+    G.W = p->width;
+    G.H = p->height;
+    G.pitch = ((col_end - col_begin) + 2 * halo + 3) & ~3;
+    G.jbase = col_begin - halo;
+    G.j0 = col_begin;
+    G.j1 = col_end;
+    return create_common(p, &G, out);
+}
+
+static int create_common(const fsb_params *p, const GridView *block, fsb_sim **out)
 {
     if (!out) return fail(FSB_EINVAL, "fsb_create: out is null");
     *out = nullptr;
@@ -513,7 +547,13 @@ int fsb_create(const fsb_params *p, fsb_sim **out)
     s->prm = prm;
     s->W = prm.width;
     s->H = prm.height;
-    s->ncells = (size_t)prm.width * prm.height;
+    s->G = block ? *block : whole_grid(prm.width, prm.height);
+    s->is_block = block != nullptr;
+    s->ncells = (size_t)prm.width * s->G.pitch;
+    if (block) {
+        s->strip_begin = block->j0 / 32;
+        s->strip_end = (block->j1 >= prm.height) ? -1 : block->j1 / 32;
+    }
     s->device = dev;
     DeviceGuard guard(dev);
 
@@ -535,7 +575,12 @@ int fsb_create(const fsb_params *p, fsb_sim **out)
     FSB_CREATE_CUDA(cudaMalloc(&s->sweep.flags, sweep_flag_words() * sizeof(unsigned long long)));
     FSB_CREATE_CUDA(cudaMemsetAsync(s->sweep.flags, 0, sweep_flag_words() * sizeof(unsigned long long), s->stream));
     FSB_CREATE_CUDA(noise_tables_create(s->noise_tables));
-    s->noise_step_jump = jump_matrix(2ull * s->ncells);
+    if (block) {
+        FSB_CREATE_CUDA(noise_tables_create_pow2(s->noise_tables));
+        FSB_CREATE_CUDA(cudaMalloc(&s->link_buf, kLinkBytes));
+        FSB_CREATE_CUDA(cudaMemsetAsync(s->link_buf, 0, kLinkBytes, s->stream));
+    }
+    s->noise_step_jump = jump_matrix(2ull * (uint64_t)prm.width * (uint64_t)prm.height);
     set_noise_window(s, prm.noise_seed, prm.noise_pos);
     FSB_CREATE_CUDA(cudaStreamSynchronize(s->stream));
 #undef FSB_CREATE_CUDA
@@ -560,6 +605,9 @@ int fsb_destroy(fsb_sim *s)
         if (s->d_entries) cudaFree(s->d_entries);
         if (s->d_segs) cudaFree(s->d_segs);
         noise_tables_destroy(s->noise_tables);
+        if (s->peer_left) cudaIpcCloseMemHandle(s->peer_left);
+        if (s->peer_right) cudaIpcCloseMemHandle(s->peer_right);
+        if (s->link_buf) cudaFree(s->link_buf);
         for (auto &r : s->prof_open) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         for (auto &e : s->prof_free) cudaEventDestroy(e);
         if (s->stream) cudaStreamDestroy(s->stream);
@@ -604,7 +652,8 @@ int fsb_add_density(fsb_sim *s, int x, int y, float amount)
 {
     if (!s) return fail(FSB_EINVAL, "fsb_add_density: null handle");
     if (!in_range(s, x, y)) return FSB_OK;   // silently ignored, src/fluid_sim.cpp:426
-    const int cell = x * s->H + y;
+    if (y < s->G.j0 || y >= s->G.j1) return FSB_OK;   // another rank's column
+    const int cell = x * s->G.pitch + (y - s->G.jbase);
     s->pending.push_back(SourceEntry{cell, 0, amount});
     if (s->mirror_valid[0]) s->mirror[0][cell] += amount;
     return FSB_OK;
@@ -614,7 +663,8 @@ int fsb_add_velocity(fsb_sim *s, int x, int y, float ax, float ay)
 {
     if (!s) return fail(FSB_EINVAL, "fsb_add_velocity: null handle");
     if (!in_range(s, x, y)) return FSB_OK;   // src/fluid_sim.cpp:434
-    const int cell = x * s->H + y;
+    if (y < s->G.j0 || y >= s->G.j1) return FSB_OK;   // another rank's column
+    const int cell = x * s->G.pitch + (y - s->G.jbase);
     s->pending.push_back(SourceEntry{cell, 1, ax});
     s->pending.push_back(SourceEntry{cell, 2, ay});
     if (s->mirror_valid[1]) s->mirror[1][cell] += ax;
@@ -885,6 +935,173 @@ int fsb_profile_read(fsb_sim *s, double *ms, uint64_t *counts, int reset)
         if (counts) counts[c] = s->prof_n[c];
         if (reset) { s->prof_ms[c] = 0.0; s->prof_n[c] = 0; }
     }
+    return FSB_OK;
+}
+
+/* ---------------------------- column blocks of a multi-rank run ---------------------------- */
+
+int fsb_block_info(const fsb_sim *s, int *pitch, int *jbase, int *j0, int *j1)
+{
+    if (!s) return fail(FSB_EINVAL, "fsb_block_info: null handle");
+    if (pitch) *pitch = s->G.pitch;
+    if (jbase) *jbase = s->G.jbase;
+    if (j0) *j0 = s->G.j0;
+    if (j1) *j1 = s->G.j1;
+    return FSB_OK;
+}
+
+int fsb_link_handle(fsb_sim *s, void *handle64)
+{
+    if (!s || !handle64 || !s->link_buf) return fail(FSB_EINVAL, "fsb_link_handle: not a block simulation");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    DeviceGuard guard(s->device);
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    FSB_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t *>(handle64), s->link_buf));
+    return FSB_OK;
+}
+
+int fsb_link_connect(fsb_sim *s, const void *left_handle64, const void *right_handle64)
+{
+    if (!s || !s->link_buf) return fail(FSB_EINVAL, "fsb_link_connect: not a block simulation");
+    DeviceGuard guard(s->device);
+    if (left_handle64) {
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, left_handle64, sizeof(h));
+        FSB_CUDA(cudaIpcOpenMemHandle(&s->peer_left, h, cudaIpcMemLazyEnablePeerAccess));
+    }
+    if (right_handle64) {
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, right_handle64, sizeof(h));
+        FSB_CUDA(cudaIpcOpenMemHandle(&s->peer_right, h, cudaIpcMemLazyEnablePeerAccess));
+    }
+    return FSB_OK;
+}
+
+static SweepLink make_link(const fsb_sim *s, unsigned long long seq)
+{
+    SweepLink L;
+    L.has_left = s->peer_left != nullptr;
+    L.has_right = s->peer_right != nullptr;
+    L.in_rings = reinterpret_cast<const float *>(s->link_buf);
+    L.in_prod = reinterpret_cast<const unsigned long long *>(s->link_buf + kLinkRingBytes);
+    L.cons = reinterpret_cast<const unsigned long long *>(s->link_buf + kLinkRingBytes + kLinkFlagBytes);
+    if (s->peer_left)
+        L.left_cons = reinterpret_cast<unsigned long long *>(static_cast<unsigned char *>(s->peer_left) + kLinkRingBytes + kLinkFlagBytes);
+    if (s->peer_right) {
+        L.right_rings = reinterpret_cast<float *>(s->peer_right);
+        L.right_prod = reinterpret_cast<unsigned long long *>(static_cast<unsigned char *>(s->peer_right) + kLinkRingBytes);
+    }
+    L.seq = seq;
+    return L;
+}
+
+/* One launch of the sweep chain on this rank's strips.  mode 0: Gauss-Seidel of the pressure (rhs = divergence in
+ * FSB_PREV_VEL_Y, result in FSB_PREV_VEL_X, `first` = start from p == 0); mode 1: SOR diffusion of `nfields` fields in
+ * place.  `seq` must be the same, strictly increasing number on every rank.  The result columns that belong to the
+ * left neighbour land in this rank's left halo; the caller returns them and then applies the boundaries. */
+int fsb_blk_sweep(fsb_sim *s, int mode, int nfields, const int *fields, const int *bs, int levels, int stages, int first,
+                  float diff, float dt, unsigned long long seq)
+{
+    if (!s || !s->is_block || nfields < 1 || nfields > kMaxSweepFields) return fail(FSB_EINVAL, "fsb_blk_sweep: bad argument");
+    DeviceGuard guard(s->device);
+    SweepLaunch L{};
+    L.nfields = nfields;
+    L.W = s->W;
+    L.H = s->H;
+    L.levels = levels;
+    L.stages = stages;
+    L.strips_per_cta = s->tune_strips > 0 ? s->tune_strips : 2;
+    L.pitch = s->G.pitch;
+    L.jbase = s->G.jbase;
+    L.strip_begin = s->strip_begin;
+    L.strip_end = s->strip_end;
+    L.link = make_link(s, seq);
+    if (mode == 0) {
+        L.mode = kGaussSeidel;
+        L.fld[0] = SweepField{first ? nullptr : s->f[FSB_PREV_VEL_X], s->f[FSB_PREV_VEL_Y], s->f[FSB_PREV_VEL_X], 1.0f, 1.0f};
+        L.a = 0.0f; L.c_recip = 1.0f; L.omega = 1.0f;
+    } else {
+        if (!fields || !bs) return fail(FSB_EINVAL, "fsb_blk_sweep: fields missing");
+        L.mode = kSor;
+        const float a = dt * diff * (float)s->W * (float)s->H;
+        L.a = a;
+        L.c_recip = 1.0f / (1.0f + 4.0f * a);
+        L.omega = s->prm.omega;
+        for (int i = 0; i < nfields; ++i) {
+            if (!valid_field(fields[i])) return fail(FSB_EINVAL, "fsb_blk_sweep: bad field");
+            float *x = s->f[fields[i]];
+            L.fld[i] = SweepField{x, x, x, sign_i(bs[i]), sign_j(bs[i])};
+        }
+    }
+    int nl = 0;
+    {
+        ProfScope ps(s, mode == 0 ? FSB_PROF_GS : FSB_PROF_SOR);
+        FSB_CUDA(launch_sweep_pass(L, s->sweep, s->stream, &nl));
+    }
+    s->launches += nl;
+    return FSB_OK;
+}
+
+int fsb_blk_set_boundary(fsb_sim *s, int n, const int *fields, const int *bs, const int *plus_zero)
+{
+    if (!s || n < 1 || n > 4 || !fields || !bs) return fail(FSB_EINVAL, "fsb_blk_set_boundary: bad argument");
+    DeviceGuard guard(s->device);
+    BndJob jobs[4];
+    for (int i = 0; i < n; ++i) {
+        if (!valid_field(fields[i])) return fail(FSB_EINVAL, "fsb_blk_set_boundary: bad field");
+        jobs[i] = BndJob{s->f[fields[i]], bs[i], plus_zero ? plus_zero[i] : 0};
+    }
+    return set_boundary(s, jobs, n);
+}
+
+int fsb_blk_divergence(fsb_sim *s)
+{
+    if (!s) return fail(FSB_EINVAL, "null handle");
+    DeviceGuard guard(s->device);
+    ProfScope ps(s, FSB_PROF_DIVERGENCE);
+    FSB_CUDA(launch_divergence(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_Y], s->G, s->stream));
+    s->launches += 1;
+    return FSB_OK;
+}
+
+int fsb_blk_gradient(fsb_sim *s)
+{
+    if (!s) return fail(FSB_EINVAL, "null handle");
+    DeviceGuard guard(s->device);
+    ProfScope ps(s, FSB_PROF_GRADIENT);
+    FSB_CUDA(launch_gradient(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_X], s->G, s->stream));
+    s->launches += 1;
+    return FSB_OK;
+}
+
+/* RK4 advection of both velocity components (halo columns must hold the neighbours' values out to the trace
+ * radius); the fields swap roles with the prev* buffers, boundaries are left to the caller. */
+int fsb_blk_advect_velocity(fsb_sim *s, float dt)
+{
+    if (!s) return fail(FSB_EINVAL, "null handle");
+    DeviceGuard guard(s->device);
+    {
+        ProfScope ps(s, FSB_PROF_ADVECT_VELOCITY);
+        FSB_CUDA(launch_advect_rk4(s->f[FSB_PREV_VEL_X], s->f[FSB_VELOCITY_X], s->f[FSB_PREV_VEL_Y], s->f[FSB_VELOCITY_Y],
+                                   s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], 0, s->G, dt, s->stream));
+    }
+    s->launches += 1;
+    std::swap(s->f[FSB_VELOCITY_X], s->f[FSB_PREV_VEL_X]);
+    std::swap(s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_Y]);
+    return FSB_OK;
+}
+
+int fsb_blk_advect_density(fsb_sim *s, float dt, int plus_zero)
+{
+    if (!s) return fail(FSB_EINVAL, "null handle");
+    DeviceGuard guard(s->device);
+    {
+        ProfScope ps(s, FSB_PROF_ADVECT_SCALAR);
+        FSB_CUDA(launch_advect_rk4(s->f[FSB_PREV_DENSITY], s->f[FSB_DENSITY], nullptr, nullptr, s->f[FSB_VELOCITY_X],
+                                   s->f[FSB_VELOCITY_Y], plus_zero, s->G, dt, s->stream));
+    }
+    s->launches += 1;
+    std::swap(s->f[FSB_DENSITY], s->f[FSB_PREV_DENSITY]);
     return FSB_OK;
 }
 

@@ -9,6 +9,17 @@
 
 namespace fsb {
 
+// A rank's view of the global W x H grid: all rows of the global columns [j0, j1) ("owned"), stored with
+// `pitch` floats per row, local column 0 holding global column `jbase` (jbase <= j0: halo columns left and
+// right of the owned block).  Single GPU: pitch = H, jbase = 0, j0 = 0, j1 = H.
+struct GridView {
+    int W, H;
+    int pitch;
+    int jbase;
+    int j0, j1;
+};
+inline GridView whole_grid(int W, int H) { return GridView{W, H, H, 0, 0, H}; }
+
 // ------------------------------------------------------------------------------------
 // Strip-pipelined exact-order sweeps (wavefront.cu)
 // ------------------------------------------------------------------------------------
@@ -27,15 +38,35 @@ struct SweepField {
     float si, sj;       // sign applied on the i-walls / j-walls (setBoundary's b)
 };
 
+// Hand-over of the strip chain between two ranks that own adjacent column blocks (peer memory over
+// NVLink).  All pointers are device addresses valid on THIS rank; "peer" ones map the neighbour's memory.
+// Layout per field f and stage g: rings[(f * kLinkStages + g) * kLinkRingFloats], flags[(f * kLinkStages + g)].
+constexpr int kLinkStages = 16;
+constexpr int kLinkRingFloats = kWfSlots * kWfBatch * 44;   // 44 = floats per lane-step at 20 sweeps per warp
+struct SweepLink {
+    bool has_left = false, has_right = false;
+    const float *in_rings = nullptr;                 // local: written by the left rank
+    const unsigned long long *in_prod = nullptr;     // local: batches the left rank has published
+    unsigned long long *left_cons = nullptr;         // peer (left rank): batches this rank has consumed
+    float *right_rings = nullptr;                    // peer (right rank): its in_rings
+    unsigned long long *right_prod = nullptr;        // peer (right rank): its in_prod
+    const unsigned long long *cons = nullptr;        // local: batches the right rank has consumed
+    unsigned long long seq = 0;                      // pass number, identical on all ranks
+};
+
 struct SweepLaunch {
     SweepField fld[kMaxSweepFields];
     int nfields;
-    int W, H;
+    int W, H;           // global grid
     int mode;           // SweepMode
     int levels;         // sweeps per warp (1, 2, 5, 10 or 20)
     int stages;         // warps chained per strip; the launch applies levels * stages sweeps
     float a, c_recip, omega;   // SOR coefficients (src/fluid_sim.cpp:45-47)
     int strips_per_cta; // 0 = choose
+    // column block of a multi-rank run (defaults: the whole grid on one GPU)
+    int pitch = 0, jbase = 0;            // local row pitch / global column of local column 0 (pitch 0: = H)
+    int strip_begin = 0, strip_end = -1; // global 32-column strips this rank runs (-1: to the end)
+    SweepLink link;
 };
 
 struct SweepScratch {
@@ -59,17 +90,17 @@ int pressure_sweeps_noalloc(const float *d_div, float *d_p, int W, int H, int sw
 // ------------------------------------------------------------------------------------
 struct BndJob { float *x; int b; int plus_zero; };   // plus_zero: interior values are read as (v + 0.0f)
 
-cudaError_t launch_set_boundary(const BndJob *jobs, int njobs, int W, int H, cudaStream_t st);
-cudaError_t launch_divergence(const float *u, const float *v, float *div, int W, int H, cudaStream_t st);
-cudaError_t launch_gradient(float *u, float *v, const float *p, int W, int H, cudaStream_t st);
+cudaError_t launch_set_boundary(const BndJob *jobs, int njobs, const GridView &G, cudaStream_t st);
+cudaError_t launch_divergence(const float *u, const float *v, float *div, const GridView &G, cudaStream_t st);
+cudaError_t launch_gradient(float *u, float *v, const float *p, const GridView &G, cudaStream_t st);
 // RK4 back-trace of (src_a[, src_b]) through (u, v); dst_b/src_b may be null.
 cudaError_t launch_advect_rk4(float *dst_a, const float *src_a, float *dst_b, const float *src_b,
-                              const float *u, const float *v, int src_plus_zero, int W, int H, float dt,
+                              const float *u, const float *v, int src_plus_zero, const GridView &G, float dt,
                               cudaStream_t st);
 cudaError_t launch_advect_sl(float *dst, const float *src, const float *u, const float *v, int src_plus_zero,
-                             int W, int H, float dt, float sign, cudaStream_t st);
+                             const GridView &G, float dt, float sign, cudaStream_t st);
 cudaError_t launch_maccormack_combine(float *dst, const float *src, const float *fwd, const float *back,
-                                      int src_plus_zero, int W, int H, cudaStream_t st);
+                                      int src_plus_zero, const GridView &G, cudaStream_t st);
 cudaError_t launch_add_zero(float *x, size_t n, cudaStream_t st);
 cudaError_t launch_axpy_field(float *x, const float *y, size_t n, cudaStream_t st);
 
@@ -85,7 +116,8 @@ constexpr int kNoiseCellsPerWarp = 32 * kNoiseCellsPerLane;
 constexpr int kNoiseMaxLevels = 24;                              // warp-index bits covered by jump matrices
 
 struct NoiseTables {
-    uint32_t *dev = nullptr;   // [1 + kNoiseMaxLevels] transposed 31x31 matrices: lane jump, then warp jumps 2^b
+    uint32_t *dev = nullptr;        // [1 + kNoiseMaxLevels] transposed 31x31 matrices: lane jump, then warp jumps 2^b
+    uint32_t *dev_pow2 = nullptr;   // column-block runs: x^(2^b), b = 0..39
 };
 
 struct NoiseWindow { uint32_t w[kRandDeg]; };
@@ -94,5 +126,8 @@ cudaError_t noise_tables_create(NoiseTables &t);
 void noise_tables_destroy(NoiseTables &t);
 cudaError_t launch_noise(float *u, float *v, size_t ncells, const NoiseWindow &base, const NoiseTables &t,
                          int zero_mode, cudaStream_t st);
+cudaError_t noise_tables_create_pow2(NoiseTables &t);
+cudaError_t launch_noise_block(float *u, float *v, const GridView &G, const NoiseWindow &base, const NoiseTables &t,
+                               int zero_mode, cudaStream_t st);
 
 }  // namespace fsb

@@ -112,6 +112,61 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) noise_kernel(float *__res
     (void)lane_cell0;
 }
 
+// ---- column-block variant: any rank's block of the grid, addressed by stream position ---------------------
+// One warp per (row, 1024-cell piece of the owned columns).  The piece starts at stream position
+// 2 * (i * H + j): the warp reaches it from the step's base window through the binary decomposition of
+// that position (matrices x^(2^b)), lane windows are 64 outputs apart.
+constexpr int kNbCells = 1024;
+constexpr int kNbLevels = 40;
+constexpr int kNbPitch = 65;
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) noise_block_kernel(float *__restrict__ u, float *__restrict__ v,
+                                                                         const GridView G, const NoiseWindow base,
+                                                                         const uint32_t *__restrict__ pow2)
+{
+    __shared__ float s_stage[kWarpsPerBlock][32 * kNbPitch];   // also holds the lane windows before generation
+    const int lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5;
+    const int nown = G.j1 - G.j0;
+    const int pieces = (nown + kNbCells - 1) / kNbCells;
+    const long long wg = (long long)blockIdx.x * kWarpsPerBlock + wib;
+    if (wg >= (long long)G.W * pieces) return;
+    const int i = (int)(wg / pieces);
+    const int jstart = G.j0 + (int)(wg % pieces) * kNbCells;
+    const unsigned long long pos = 2ull * ((unsigned long long)i * G.H + jstart);
+
+    uint32_t win = (lane < kRandDeg) ? base.w[lane] : 0u;
+    for (int b = 0; b < kNbLevels; ++b)
+        if ((pos >> b) & 1ull) win = matvec(pow2 + (size_t)b * kMatStride, win, lane);
+    uint32_t *sw = reinterpret_cast<uint32_t *>(s_stage[wib]);
+    for (int r = 0; r < 32; ++r) {
+        if (lane < kRandDeg) sw[r * kWinPitch + lane] = win;
+        win = matvec(pow2 + (size_t)6 * kMatStride, win, lane);   // x^64: the next lane's 32 cells
+    }
+    __syncwarp();
+    uint32_t w[kRandDeg];
+#pragma unroll
+    for (int m = 0; m < kRandDeg; ++m) w[m] = sw[lane * kWinPitch + m];
+    __syncwarp();
+    float *stg = s_stage[wib];
+#pragma unroll
+    for (int n = 0; n < 64; ++n) {
+        const uint32_t nw = w[n % kRandDeg] + w[(n + 28) % kRandDeg];
+        w[n % kRandDeg] = nw;
+        stg[lane * kNbPitch + n] = noise_of(nw);
+    }
+    __syncwarp();
+#pragma unroll 4
+    for (int r = 0; r < 32; ++r) {
+        const int j = jstart + 32 * r + lane;
+        if (j < G.j1) {
+            const size_t c = (size_t)i * G.pitch + (j - G.jbase);
+            u[c] = __fadd_rn(u[c], stg[r * kNbPitch + 2 * lane]);
+            v[c] = __fadd_rn(v[c], stg[r * kNbPitch + 2 * lane + 1]);
+        }
+    }
+}
+
 }  // namespace
 
 cudaError_t noise_tables_create(NoiseTables &t)
@@ -133,10 +188,45 @@ cudaError_t noise_tables_create(NoiseTables &t)
     return cudaMemcpy(t.dev, host.data(), words * sizeof(uint32_t), cudaMemcpyHostToDevice);
 }
 
+cudaError_t noise_tables_create_pow2(NoiseTables &t)
+{
+    const size_t words = (size_t)kNbLevels * kMatStride;
+    std::vector<uint32_t> host(words, 0u);
+    RandPoly p = poly_x_pow(1);
+    for (int b = 0; b < kNbLevels; ++b) {
+        const RandJump J = jump_from_poly(p);
+        for (int m = 0; m < kRandDeg; ++m)
+            for (int j = 0; j < kRandDeg; ++j) host[(size_t)b * kMatStride + j * 32 + m] = J.m[m][j];
+        p = poly_mul(p, p);
+    }
+    cudaError_t e = cudaMalloc(&t.dev_pow2, words * sizeof(uint32_t));
+    if (e != cudaSuccess) return e;
+    return cudaMemcpy(t.dev_pow2, host.data(), words * sizeof(uint32_t), cudaMemcpyHostToDevice);
+}
+
 void noise_tables_destroy(NoiseTables &t)
 {
     if (t.dev) cudaFree(t.dev);
+    if (t.dev_pow2) cudaFree(t.dev_pow2);
     t.dev = nullptr;
+    t.dev_pow2 = nullptr;
+}
+
+cudaError_t launch_noise_block(float *u, float *v, const GridView &G, const NoiseWindow &base, const NoiseTables &t,
+                               int zero_mode, cudaStream_t st)
+{
+    if (zero_mode) {
+        // like the whole-grid path: the reference still adds +0.0f everywhere (halo columns are refreshed later)
+        cudaError_t e = launch_add_zero(u, (size_t)G.W * G.pitch, st);
+        if (e != cudaSuccess) return e;
+        return launch_add_zero(v, (size_t)G.W * G.pitch, st);
+    }
+    if (!t.dev_pow2) return cudaErrorInvalidValue;
+    const long long pieces = ((G.j1 - G.j0) + kNbCells - 1) / kNbCells;
+    const long long warps = (long long)G.W * pieces;
+    const unsigned blocks = (unsigned)((warps + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    noise_block_kernel<<<blocks, kWarpsPerBlock * 32, 0, st>>>(u, v, G, base, t.dev_pow2);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_noise(float *u, float *v, size_t ncells, const NoiseWindow &base, const NoiseTables &t,

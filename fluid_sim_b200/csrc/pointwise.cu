@@ -17,74 +17,82 @@ __device__ __forceinline__ float plusz(float v, int plus_zero) { return plus_zer
 // the interior, so there is no ordering between wall and corner threads.
 struct BndJobs { BndJob j[4]; int n; };
 
-__device__ __forceinline__ float wall_j(const float *x, int H, int i, int jin, int b, int pz)
+#define AT(G, i, j) ((size_t)(i) * (G).pitch + ((j) - (G).jbase))
+
+__device__ __forceinline__ float wall_j(const float *x, const GridView &G, int i, int jin, int b, int pz)
 {   // value setBoundary gives to (i, 0) or (i, H-1); jin = 1 or H-2
-    const float v = plusz(x[(size_t)i * H + jin], pz);
+    const float v = plusz(x[AT(G, i, jin)], pz);
     return b == 2 ? -v : v;
 }
-__device__ __forceinline__ float wall_i(const float *x, int H, int iin, int j, int b, int pz)
+__device__ __forceinline__ float wall_i(const float *x, const GridView &G, int iin, int j, int b, int pz)
 {   // value setBoundary gives to (0, j) or (W-1, j); iin = 1 or W-2
-    const float v = plusz(x[(size_t)iin * H + j], pz);
+    const float v = plusz(x[AT(G, iin, j)], pz);
     return b == 1 ? -v : v;
 }
 
-__global__ void set_boundary_kernel(const BndJobs jobs, int W, int H)
+// Only perimeter cells in owned columns [j0, j1) are written; perimeter cells in halo columns arrive with the
+// halo exchange from the rank that owns them.
+__global__ void set_boundary_kernel(const BndJobs jobs, const GridView G)
 {
     const BndJob J = jobs.j[blockIdx.y];
     float *x = J.x;
     const int b = J.b, pz = J.plus_zero;
-    const int per = 2 * W + 2 * H;
+    const int W = G.W, H = G.H;
+    const int nown = G.j1 - G.j0;
+    const int per = 2 * nown + 2 * W;
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < per; t += gridDim.x * blockDim.x) {
-        if (t < 2 * H) {
-            // rows i = 0 and i = W-1, all j
-            const int top = t < H;
-            const int j = top ? t : t - H;
+        if (t < 2 * nown) {
+            // rows i = 0 and i = W-1, owned columns
+            const int top = t < nown;
+            const int j = G.j0 + (top ? t : t - nown);
             const int i = top ? 0 : W - 1;
             const int iin = top ? 1 : W - 2;
             float v;
             if (j >= 1 && j <= H - 2) {
-                v = wall_i(x, H, iin, j, b, pz);
+                v = wall_i(x, G, iin, j, b, pz);
             } else {
                 // corner: 0.5f * (x[iin][jc] + x[i][jin]) with jc = j, jin = 1 or H-2 (:363-366)
                 const int jin = (j == 0) ? 1 : H - 2;
-                const float a = wall_j(x, H, iin, jin, b, pz);   // x[iin][j]  (a j-wall cell)
-                const float c = wall_i(x, H, iin, jin, b, pz);   // x[i][jin]  (an i-wall cell)
+                const float a = wall_j(x, G, iin, jin, b, pz);   // x[iin][j]  (a j-wall cell)
+                const float c = wall_i(x, G, iin, jin, b, pz);   // x[i][jin]  (an i-wall cell)
                 v = __fmul_rn(0.5f, __fadd_rn(a, c));
             }
-            x[(size_t)i * H + j] = v;
+            x[AT(G, i, j)] = v;
         } else {
-            const int s = t - 2 * H;
+            const int s = t - 2 * nown;
             const int left = s < W;
             const int i = left ? s : s - W;
             const int j = left ? 0 : H - 1;
             const int jin = left ? 1 : H - 2;
-            if (i >= 1 && i <= W - 2) x[(size_t)i * H + j] = wall_j(x, H, i, jin, b, pz);
+            if (j >= G.j0 && j < G.j1 && i >= 1 && i <= W - 2) x[AT(G, i, j)] = wall_j(x, G, i, jin, b, pz);
         }
     }
 }
 
 // ---- divergence (src/fluid_sim.cpp:307-314) -------------------------------------------------------
 __global__ void divergence_kernel(const float *__restrict__ u, const float *__restrict__ v, float *__restrict__ div,
-                                  int W, int H, float mhh)
+                                  const GridView G, float mhh)
 {
-    const int j = blockIdx.x * kBx + threadIdx.x;
+    const int W = G.W, H = G.H;
+    const int j = G.j0 + blockIdx.x * kBx + threadIdx.x;
     const int i = blockIdx.y * kBy + threadIdx.y;
-    if (i < 1 || i > W - 2 || j < 1 || j > H - 2) return;
-    const size_t c = (size_t)i * H + j;
-    const float du = __fsub_rn(u[c + H], u[c - H]);
+    if (i < 1 || i > W - 2 || j < 1 || j > H - 2 || j >= G.j1) return;
+    const size_t c = AT(G, i, j);
+    const float du = __fsub_rn(u[c + G.pitch], u[c - G.pitch]);
     const float s = __fsub_rn(__fadd_rn(du, v[c + 1]), v[c - 1]);
     div[c] = __fmul_rn(mhh, s);
 }
 
 // ---- pressure gradient (src/fluid_sim.cpp:334-341) ---------------------------------------------------
 __global__ void gradient_kernel(float *__restrict__ u, float *__restrict__ v, const float *__restrict__ p,
-                                int W, int H, float h)
+                                const GridView G, float h)
 {
-    const int j = blockIdx.x * kBx + threadIdx.x;
+    const int W = G.W, H = G.H;
+    const int j = G.j0 + blockIdx.x * kBx + threadIdx.x;
     const int i = blockIdx.y * kBy + threadIdx.y;
-    if (i < 1 || i > W - 2 || j < 1 || j > H - 2) return;
-    const size_t c = (size_t)i * H + j;
-    const float gx = __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(p[c + H], p[c - H])), h);
+    if (i < 1 || i > W - 2 || j < 1 || j > H - 2 || j >= G.j1) return;
+    const size_t c = AT(G, i, j);
+    const float gx = __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(p[c + G.pitch], p[c - G.pitch])), h);
     const float gy = __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(p[c + 1], p[c - 1])), h);
     u[c] = __fsub_rn(u[c], gx);
     v[c] = __fsub_rn(v[c], gy);
@@ -93,7 +101,7 @@ __global__ void gradient_kernel(float *__restrict__ u, float *__restrict__ v, co
 // ---- bilinear sample (src/fluid_sim.cpp:231-252) -------------------------------------------------------
 struct Taps { int i0, j0; float s0, s1, t0, t1; };
 
-__device__ __forceinline__ Taps make_taps(float x, float y, int H, float xm, float ym)
+__device__ __forceinline__ Taps make_taps(float x, float y, float xm, float ym)
 {
     x = (x < xm) ? x : xm;        // std::min(width - 1.5f, x)
     x = (0.5f < x) ? x : 0.5f;    // std::max(0.5f, .)
@@ -112,9 +120,10 @@ __device__ __forceinline__ Taps make_taps(float x, float y, int H, float xm, flo
 }
 
 template <bool PZ>
-__device__ __forceinline__ float tap_val(const float *__restrict__ f, int i, int j, int W, int H)
+__device__ __forceinline__ float tap_val(const float *__restrict__ f, int i, int j, const GridView &G)
 {
-    float v = __ldg(f + (size_t)i * H + j);
+    const int W = G.W, H = G.H;
+    float v = __ldg(f + AT(G, i, j));
     if (PZ) {
         // density only: the reference's diffuse pass with a == 0 rewrites every interior cell as
         // d + 1.5f * ((d + 0*nb) - d), i.e. d + 0.0f (src/fluid_sim.cpp:56-57); folded in here.
@@ -124,10 +133,10 @@ __device__ __forceinline__ float tap_val(const float *__restrict__ f, int i, int
 }
 
 template <bool PZ>
-__device__ __forceinline__ float sample(const float *__restrict__ f, const Taps &t, int W, int H)
+__device__ __forceinline__ float sample(const float *__restrict__ f, const Taps &t, const GridView &G)
 {
-    const float f00 = tap_val<PZ>(f, t.i0, t.j0, W, H), f01 = tap_val<PZ>(f, t.i0, t.j0 + 1, W, H);
-    const float f10 = tap_val<PZ>(f, t.i0 + 1, t.j0, W, H), f11 = tap_val<PZ>(f, t.i0 + 1, t.j0 + 1, W, H);
+    const float f00 = tap_val<PZ>(f, t.i0, t.j0, G), f01 = tap_val<PZ>(f, t.i0, t.j0 + 1, G);
+    const float f10 = tap_val<PZ>(f, t.i0 + 1, t.j0, G), f11 = tap_val<PZ>(f, t.i0 + 1, t.j0 + 1, G);
     const float a = __fadd_rn(__fmul_rn(t.t0, f00), __fmul_rn(t.t1, f01));
     const float b = __fadd_rn(__fmul_rn(t.t0, f10), __fmul_rn(t.t1, f11));
     return __fadd_rn(__fmul_rn(t.s0, a), __fmul_rn(t.s1, b));
@@ -139,65 +148,68 @@ __device__ __forceinline__ float sample(const float *__restrict__ f, const Taps 
 template <bool TWO, bool PZ>
 __global__ void advect_rk4_kernel(float *__restrict__ dst_a, const float *__restrict__ src_a,
                                   float *__restrict__ dst_b, const float *__restrict__ src_b,
-                                  const float *__restrict__ u, const float *__restrict__ v, int W, int H, float ndt0)
+                                  const float *__restrict__ u, const float *__restrict__ v, const GridView G, float ndt0)
 {
-    const int j = blockIdx.x * kBx + threadIdx.x;
+    const int W = G.W, H = G.H;
+    const int j = G.j0 + blockIdx.x * kBx + threadIdx.x;
     const int i = blockIdx.y * kBy + threadIdx.y;
-    if (i < 1 || i > W - 2 || j < 1 || j > H - 2) return;
+    if (i < 1 || i > W - 2 || j < 1 || j > H - 2 || j >= G.j1) return;
     const float xm = (float)W - 1.5f, ym = (float)H - 1.5f;
     const float x = (float)i, y = (float)j;
 
-    Taps t = make_taps(x, y, H, xm, ym);
-    const float k1x = __fmul_rn(sample<false>(u, t, W, H), ndt0);
-    const float k1y = __fmul_rn(sample<false>(v, t, W, H), ndt0);
+    Taps t = make_taps(x, y, xm, ym);
+    const float k1x = __fmul_rn(sample<false>(u, t, G), ndt0);
+    const float k1y = __fmul_rn(sample<false>(v, t, G), ndt0);
 
-    t = make_taps(__fadd_rn(x, __fmul_rn(k1x, 0.5f)), __fadd_rn(y, __fmul_rn(k1y, 0.5f)), H, xm, ym);
-    const float k2x = __fmul_rn(sample<false>(u, t, W, H), ndt0);
-    const float k2y = __fmul_rn(sample<false>(v, t, W, H), ndt0);
+    t = make_taps(__fadd_rn(x, __fmul_rn(k1x, 0.5f)), __fadd_rn(y, __fmul_rn(k1y, 0.5f)), xm, ym);
+    const float k2x = __fmul_rn(sample<false>(u, t, G), ndt0);
+    const float k2y = __fmul_rn(sample<false>(v, t, G), ndt0);
 
-    t = make_taps(__fadd_rn(x, __fmul_rn(k2x, 0.5f)), __fadd_rn(y, __fmul_rn(k2y, 0.5f)), H, xm, ym);
-    const float k3x = __fmul_rn(sample<false>(u, t, W, H), ndt0);
-    const float k3y = __fmul_rn(sample<false>(v, t, W, H), ndt0);
+    t = make_taps(__fadd_rn(x, __fmul_rn(k2x, 0.5f)), __fadd_rn(y, __fmul_rn(k2y, 0.5f)), xm, ym);
+    const float k3x = __fmul_rn(sample<false>(u, t, G), ndt0);
+    const float k3y = __fmul_rn(sample<false>(v, t, G), ndt0);
 
-    t = make_taps(__fadd_rn(x, k3x), __fadd_rn(y, k3y), H, xm, ym);
-    const float k4x = __fmul_rn(sample<false>(u, t, W, H), ndt0);
-    const float k4y = __fmul_rn(sample<false>(v, t, W, H), ndt0);
+    t = make_taps(__fadd_rn(x, k3x), __fadd_rn(y, k3y), xm, ym);
+    const float k4x = __fmul_rn(sample<false>(u, t, G), ndt0);
+    const float k4y = __fmul_rn(sample<false>(v, t, G), ndt0);
 
     const float dx = __fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(k1x, __fmul_rn(2.0f, k2x)), __fmul_rn(2.0f, k3x)), k4x), 6.0f);
     const float dy = __fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(k1y, __fmul_rn(2.0f, k2y)), __fmul_rn(2.0f, k3y)), k4y), 6.0f);
 
-    t = make_taps(__fadd_rn(x, dx), __fadd_rn(y, dy), H, xm, ym);
-    const size_t c = (size_t)i * H + j;
-    dst_a[c] = sample<PZ>(src_a, t, W, H);
-    if (TWO) dst_b[c] = sample<PZ>(src_b, t, W, H);
+    t = make_taps(__fadd_rn(x, dx), __fadd_rn(y, dy), xm, ym);
+    const size_t c = AT(G, i, j);
+    dst_a[c] = sample<PZ>(src_a, t, G);
+    if (TWO) dst_b[c] = sample<PZ>(src_b, t, G);
 }
 
 // ---- single semi-Lagrangian trace (src/fluid_sim.cpp:65-100 and the two halves of :103-168) ---------------------
 template <bool PZ>
 __global__ void advect_sl_kernel(float *__restrict__ dst, const float *__restrict__ src, const float *__restrict__ u,
-                                 const float *__restrict__ v, int W, int H, float dt0, int forward)
+                                 const float *__restrict__ v, const GridView G, float dt0, int forward)
 {
-    const int j = blockIdx.x * kBx + threadIdx.x;
+    const int W = G.W, H = G.H;
+    const int j = G.j0 + blockIdx.x * kBx + threadIdx.x;
     const int i = blockIdx.y * kBy + threadIdx.y;
-    if (i < 1 || i > W - 2 || j < 1 || j > H - 2) return;
-    const size_t c = (size_t)i * H + j;
+    if (i < 1 || i > W - 2 || j < 1 || j > H - 2 || j >= G.j1) return;
+    const size_t c = AT(G, i, j);
     const float du = __fmul_rn(dt0, u[c]), dv = __fmul_rn(dt0, v[c]);
     const float x = forward ? __fadd_rn((float)i, du) : __fsub_rn((float)i, du);
     const float y = forward ? __fadd_rn((float)j, dv) : __fsub_rn((float)j, dv);
-    const Taps t = make_taps(x, y, H, (float)W - 1.5f, (float)H - 1.5f);
-    dst[c] = sample<PZ>(src, t, W, H);
+    const Taps t = make_taps(x, y, (float)W - 1.5f, (float)H - 1.5f);
+    dst[c] = sample<PZ>(src, t, G);
 }
 
 // ---- MacCormack correction and clamp (src/fluid_sim.cpp:170-207) --------------------------------------------------
 template <bool PZ>
 __global__ void maccormack_combine_kernel(float *__restrict__ dst, const float *__restrict__ src,
-                                          const float *__restrict__ fwd, const float *__restrict__ back, int W, int H)
+                                          const float *__restrict__ fwd, const float *__restrict__ back, const GridView G)
 {
-    const int j = blockIdx.x * kBx + threadIdx.x;
+    const int W = G.W, H = G.H;
+    const int j = G.j0 + blockIdx.x * kBx + threadIdx.x;
     const int i = blockIdx.y * kBy + threadIdx.y;
-    if (i < 1 || i > W - 2 || j < 1 || j > H - 2) return;
-    const size_t c = (size_t)i * H + j;
-    const float s = tap_val<PZ>(src, i, j, W, H);
+    if (i < 1 || i > W - 2 || j < 1 || j > H - 2 || j >= G.j1) return;
+    const size_t c = AT(G, i, j);
+    const float s = tap_val<PZ>(src, i, j, G);
     const float err = __fsub_rn(s, back[c]);
     float r = __fadd_rn(fwd[c], __fmul_rn(0.5f, err));
     float lo = s, hi = s;
@@ -205,7 +217,7 @@ __global__ void maccormack_combine_kernel(float *__restrict__ dst, const float *
     for (int di = -1; di <= 1; ++di)
 #pragma unroll
         for (int dj = -1; dj <= 1; ++dj) {
-            const float q = tap_val<PZ>(src, i + di, j + dj, W, H);
+            const float q = tap_val<PZ>(src, i + di, j + dj, G);
             lo = (q < lo) ? q : lo;
             hi = (hi < q) ? q : hi;
         }
@@ -237,71 +249,71 @@ __global__ void apply_sources_kernel(float *d, float *u, float *v, const SourceE
     }
 }
 
-inline dim3 cell_grid(int W, int H) { return dim3((H + kBx - 1) / kBx, (W + kBy - 1) / kBy); }
+inline dim3 cell_grid(const GridView &G) { return dim3((G.j1 - G.j0 + kBx - 1) / kBx, (G.W + kBy - 1) / kBy); }
 
 }  // namespace
 
-cudaError_t launch_set_boundary(const BndJob *jobs, int njobs, int W, int H, cudaStream_t st)
+cudaError_t launch_set_boundary(const BndJob *jobs, int njobs, const GridView &G, cudaStream_t st)
 {
     if (njobs < 1 || njobs > 4) return cudaErrorInvalidValue;
     BndJobs J;
     J.n = njobs;
     for (int i = 0; i < 4; ++i) J.j[i] = jobs[i < njobs ? i : 0];
-    const int per = 2 * W + 2 * H;
+    const int per = 2 * G.W + 2 * (G.j1 - G.j0);
     int blocks = (per + 255) / 256;
     if (blocks > 1024) blocks = 1024;
-    set_boundary_kernel<<<dim3(blocks, njobs), 256, 0, st>>>(J, W, H);
+    set_boundary_kernel<<<dim3(blocks, njobs), 256, 0, st>>>(J, G);
     return cudaGetLastError();
 }
 
-cudaError_t launch_divergence(const float *u, const float *v, float *div, int W, int H, cudaStream_t st)
+cudaError_t launch_divergence(const float *u, const float *v, float *div, const GridView &G, cudaStream_t st)
 {
-    const float h = 1.0f / (float)W;        // src/fluid_sim.cpp:304
+    const float h = 1.0f / (float)G.W;      // src/fluid_sim.cpp:304
     const float mhh = -0.5f * h;            // -0.5f * h, evaluated first (:311)
-    divergence_kernel<<<cell_grid(W, H), dim3(kBx, kBy), 0, st>>>(u, v, div, W, H, mhh);
+    divergence_kernel<<<cell_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, div, G, mhh);
     return cudaGetLastError();
 }
 
-cudaError_t launch_gradient(float *u, float *v, const float *p, int W, int H, cudaStream_t st)
+cudaError_t launch_gradient(float *u, float *v, const float *p, const GridView &G, cudaStream_t st)
 {
-    const float h = 1.0f / (float)W;
-    gradient_kernel<<<cell_grid(W, H), dim3(kBx, kBy), 0, st>>>(u, v, p, W, H, h);
+    const float h = 1.0f / (float)G.W;
+    gradient_kernel<<<cell_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, p, G, h);
     return cudaGetLastError();
 }
 
 cudaError_t launch_advect_rk4(float *dst_a, const float *src_a, float *dst_b, const float *src_b, const float *u,
-                              const float *v, int src_plus_zero, int W, int H, float dt, cudaStream_t st)
+                              const float *v, int src_plus_zero, const GridView &G, float dt, cudaStream_t st)
 {
-    const float dt0 = dt * (float)W;        // src/fluid_sim.cpp:264
+    const float dt0 = dt * (float)G.W;      // src/fluid_sim.cpp:264
     const float ndt0 = -dt0;
-    const dim3 g = cell_grid(W, H), b(kBx, kBy);
+    const dim3 g = cell_grid(G), b(kBx, kBy);
     if (dst_b) {
-        if (src_plus_zero) advect_rk4_kernel<true, true><<<g, b, 0, st>>>(dst_a, src_a, dst_b, src_b, u, v, W, H, ndt0);
-        else advect_rk4_kernel<true, false><<<g, b, 0, st>>>(dst_a, src_a, dst_b, src_b, u, v, W, H, ndt0);
+        if (src_plus_zero) advect_rk4_kernel<true, true><<<g, b, 0, st>>>(dst_a, src_a, dst_b, src_b, u, v, G, ndt0);
+        else advect_rk4_kernel<true, false><<<g, b, 0, st>>>(dst_a, src_a, dst_b, src_b, u, v, G, ndt0);
     } else {
-        if (src_plus_zero) advect_rk4_kernel<false, true><<<g, b, 0, st>>>(dst_a, src_a, nullptr, nullptr, u, v, W, H, ndt0);
-        else advect_rk4_kernel<false, false><<<g, b, 0, st>>>(dst_a, src_a, nullptr, nullptr, u, v, W, H, ndt0);
+        if (src_plus_zero) advect_rk4_kernel<false, true><<<g, b, 0, st>>>(dst_a, src_a, nullptr, nullptr, u, v, G, ndt0);
+        else advect_rk4_kernel<false, false><<<g, b, 0, st>>>(dst_a, src_a, nullptr, nullptr, u, v, G, ndt0);
     }
     return cudaGetLastError();
 }
 
-cudaError_t launch_advect_sl(float *dst, const float *src, const float *u, const float *v, int src_plus_zero, int W,
-                             int H, float dt, float sign, cudaStream_t st)
+cudaError_t launch_advect_sl(float *dst, const float *src, const float *u, const float *v, int src_plus_zero,
+                             const GridView &G, float dt, float sign, cudaStream_t st)
 {
-    const float dt0 = dt * (float)W;
-    const dim3 g = cell_grid(W, H), b(kBx, kBy);
+    const float dt0 = dt * (float)G.W;
+    const dim3 g = cell_grid(G), b(kBx, kBy);
     const int fwd = sign > 0.0f;
-    if (src_plus_zero) advect_sl_kernel<true><<<g, b, 0, st>>>(dst, src, u, v, W, H, dt0, fwd);
-    else advect_sl_kernel<false><<<g, b, 0, st>>>(dst, src, u, v, W, H, dt0, fwd);
+    if (src_plus_zero) advect_sl_kernel<true><<<g, b, 0, st>>>(dst, src, u, v, G, dt0, fwd);
+    else advect_sl_kernel<false><<<g, b, 0, st>>>(dst, src, u, v, G, dt0, fwd);
     return cudaGetLastError();
 }
 
 cudaError_t launch_maccormack_combine(float *dst, const float *src, const float *fwd, const float *back,
-                                      int src_plus_zero, int W, int H, cudaStream_t st)
+                                      int src_plus_zero, const GridView &G, cudaStream_t st)
 {
-    const dim3 g = cell_grid(W, H), b(kBx, kBy);
-    if (src_plus_zero) maccormack_combine_kernel<true><<<g, b, 0, st>>>(dst, src, fwd, back, W, H);
-    else maccormack_combine_kernel<false><<<g, b, 0, st>>>(dst, src, fwd, back, W, H);
+    const dim3 g = cell_grid(G), b(kBx, kBy);
+    if (src_plus_zero) maccormack_combine_kernel<true><<<g, b, 0, st>>>(dst, src, fwd, back, G);
+    else maccormack_combine_kernel<false><<<g, b, 0, st>>>(dst, src, fwd, back, G);
     return cudaGetLastError();
 }
 

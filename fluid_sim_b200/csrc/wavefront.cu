@@ -80,12 +80,16 @@ struct WfLayout {
 
 struct WfKernelParams {
     SweepField fld[kMaxSweepFields];
-    int W, H;
-    int nstr, nstg, ncta;   // strips per CTA, stages per strip, CTAs per chain
+    int W, H;               // global grid
+    int pitch, jbase;       // local arrays: floats per row, global column of local column 0
+    int nstr, nstg, ncta;   // strips per CTA, stages per strip, CTAs of this launch (this rank's part of the chain)
+    int c_base;             // global index of this launch's first CTA
     float a, c_recip, omega;
     float *xchg;
     unsigned long long *flags;
     unsigned long long seq_base;
+    SweepLink link;         // chain hand-over to neighbouring ranks
+    unsigned long long link_seq_base;
 };
 
 // Per-warp wiring of the pipeline.
@@ -119,6 +123,11 @@ __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long
 __device__ __forceinline__ void st_release_u64(unsigned long long *p, unsigned long long v)
 {
     asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__device__ __forceinline__ void st_release_sys_u64(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
 __device__ __forceinline__ int ld_acquire_cta_s32(const int *p)
@@ -345,10 +354,16 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int w = tid >> 5;
-    const int c = blockIdx.x;
+    const int cl = blockIdx.x;                   // CTA index inside this launch
+    const int c = P.c_base + cl;                 // ... inside the global chain (geometry)
     const int fi = blockIdx.y;
     const SweepField F = P.fld[fi];
     const int W = P.W, H = P.H;
+    const int pitch = P.pitch, jbase = P.jbase;
+    const bool link_l = (cl == 0) && P.link.has_left;             // left neighbours come from another rank
+    const bool link_r = (cl == P.ncta - 1) && P.link.has_right;   // right edge goes to another rank
+    const bool has_left = (cl > 0) || link_l;
+    const bool has_right = (cl + 1 < P.ncta) || link_r;
     const int j0_first = 32 * NSTR * c;
 
     // ---- shared memory carve-up -------------------------------------------------------------
@@ -392,7 +407,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         // write-back machine per strip of the CTA (rows the last stage has finished, staged in its tile)
         const bool is_flush = WF_FLUSH_OFFLOAD && is_exp && lane >= 16;
         const int gi = lane & 15;
-        const bool valid = is_flush ? (gi < NSTR) : ((lane < 16) && (gi < NSTG) && (is_exp ? (c + 1 < P.ncta) : (c > 0)));
+        const bool valid = is_flush ? (gi < NSTR) : ((lane < 16) && (gi < NSTG) && (is_exp ? has_right : has_left));
         int n = 0, n_end = -1, n_first_right = 0, fl_tau_e = 0;
         if (valid) {
             if (is_flush) {
@@ -410,8 +425,12 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
             }
         }
         unsigned long long *fl = P.flags + ((size_t)fi * kMaxStages + (gi < kMaxStages ? gi : 0)) * kWfMaxCtas * 2;
+        const int lk = fi * kLinkStages + (gi < kLinkStages ? gi : 0);   // slot of (field, stage) in the rank links
+        const bool via_link = is_exp ? link_r : link_l;
+        const unsigned long long flag_base = via_link ? P.link_seq_base : P.seq_base;
         const volatile unsigned long long *poll_flag =
-            is_exp ? fl + (size_t)c * 2 + 1 : fl + (size_t)(c > 0 ? c - 1 : 0) * 2;
+            is_exp ? (link_r ? P.link.cons + lk : fl + (size_t)cl * 2 + 1)
+                   : (link_l ? P.link.in_prod + lk : fl + (size_t)(cl > 0 ? cl - 1 : 0) * 2);
         const int *poll_prog = is_flush ? prog + (gi < NSTR ? gi : 0) * NSTG + (NSTG - 1)
                                         : (is_exp ? prog + (NSTR - 1) * NSTG + (gi < NSTG ? gi : 0) : prog + (gi < NSTG ? gi : 0));
         bool done = !valid || n > n_end;
@@ -424,11 +443,11 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 } else if (!is_exp) {
                     // batch n replaces batch n - kEdgeDepth/16 in edge_in, whose last slot is read one and two steps later
                     ready = ld_acquire_cta_s32(poll_prog) >= 16 * (n - kEdgeDepth / kWfBatch + 1) + 1 &&
-                            *poll_flag >= P.seq_base + (unsigned long long)(n + kBatchBias + 1);
+                            *poll_flag >= flag_base + (unsigned long long)(n + kBatchBias + 1);
                 } else {
                     ready = ld_acquire_cta_s32(poll_prog) >= 16 * n + 15 &&
                             (n - kWfSlots < n_first_right ||
-                             *poll_flag >= P.seq_base + (unsigned long long)(n - kWfSlots + kBatchBias + 1));
+                             *poll_flag >= flag_base + (unsigned long long)(n - kWfSlots + kBatchBias + 1));
                 }
             }
             unsigned m = __ballot_sync(0xffffffffu, ready);
@@ -436,21 +455,27 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 __nanosleep(32);
                 continue;
             }
-            if (m & 0xffffu) __threadfence();   // acquire side of the global flags just observed
+            if (m & 0xffffu) {   // acquire side of the global flags just observed
+                if (via_link) __threadfence_system();
+                else __threadfence();
+            }
             for (unsigned mm = m & 0xffffu; mm; mm &= mm - 1) {
                 const int src = __ffs(mm) - 1;
                 const int bn = __shfl_sync(0xffffffffu, n, src);
                 float *xg = P.xchg + ((size_t)fi * NSTG + src) * P.ncta * L::kBoundaryFloats;
+                const size_t slot_off = (size_t)(bn & (kWfSlots - 1)) * kWfBatch * L::EXW;
+                const size_t lk_off = (size_t)(fi * kLinkStages + src) * kLinkRingFloats;
                 if (!is_exp) {
                     const float4 *gsrc = reinterpret_cast<const float4 *>(
-                        xg + (size_t)(c - 1) * L::kBoundaryFloats + (size_t)(bn & (kWfSlots - 1)) * kWfBatch * L::EXW);
+                        link_l ? P.link.in_rings + lk_off + slot_off
+                               : xg + (size_t)(cl - 1) * L::kBoundaryFloats + slot_off);
                     float4 *sdst = reinterpret_cast<float4 *>(edge_in + src * kEdgeDepth * L::EXW +
                                                               ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
 #pragma unroll 2
                     for (int i = lane; i < kWfBatch * L::EXW / 4; i += 32) sdst[i] = __ldcg(gsrc + i);
                 } else {
                     float4 *gdst = reinterpret_cast<float4 *>(
-                        xg + (size_t)c * L::kBoundaryFloats + (size_t)(bn & (kWfSlots - 1)) * kWfBatch * L::EXW);
+                        link_r ? P.link.right_rings + lk_off + slot_off : xg + (size_t)cl * L::kBoundaryFloats + slot_off);
                     const float4 *ssrc = reinterpret_cast<const float4 *>(edge_out + src * kEdgeDepth * L::EXW +
                                                                           ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
 #pragma unroll 2
@@ -470,22 +495,27 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
 #pragma unroll
                 for (int it = 0; it < kWfBatch; ++it) vals[it] = tile[((16 * bn + it) & (kTileRows - 1)) * 32 + lane];
                 if (colok && row0 + kWfBatch - 1 >= 1 && row0 <= W - 2) {
-                    float *dst = F.out + ((long long)row0 * H + col);
+                    float *dst = F.out + ((long long)row0 * pitch + (col - jbase));
 #pragma unroll
                     for (int it = 0; it < kWfBatch; ++it)
-                        if (row0 + it >= 1 && row0 + it <= W - 2) dst[(long long)it * H] = vals[it];
+                        if (row0 + it >= 1 && row0 + it <= W - 2) dst[(long long)it * pitch] = vals[it];
                 }
             }
-            if (is_exp && (m & 0xffffu)) __threadfence();
+            if (is_exp && (m & 0xffffu)) {
+                if (link_r) __threadfence_system();
+                else __threadfence();
+            }
             __syncwarp();
             if (ready) {
                 if (is_flush) {
                     st_release_cta_s32(flushed_steps + gi, 16 * n + 15);
                 } else if (!is_exp) {
                     st_release_cta_s32(imp_steps + gi, 16 * n + 15);
-                    st_release_u64(fl + (size_t)(c - 1) * 2 + 1, P.seq_base + (unsigned long long)(n + kBatchBias + 1));
+                    if (link_l) st_release_sys_u64(P.link.left_cons + lk, flag_base + (unsigned long long)(n + kBatchBias + 1));
+                    else st_release_u64(fl + (size_t)(cl - 1) * 2 + 1, flag_base + (unsigned long long)(n + kBatchBias + 1));
                 } else {
-                    st_release_u64(fl + (size_t)c * 2, P.seq_base + (unsigned long long)(n + kBatchBias + 1));
+                    if (link_r) st_release_sys_u64(P.link.right_prod + lk, flag_base + (unsigned long long)(n + kBatchBias + 1));
+                    else st_release_u64(fl + (size_t)cl * 2, flag_base + (unsigned long long)(n + kBatchBias + 1));
                     st_release_cta_s32(exp_steps + gi, 16 * n + 15);
                 }
                 n += 1;
@@ -556,7 +586,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         if (sidx > 0) {
             wait_ptr = prog + (w - NSTG);
             wait_clamp = last_step(j0w - 32);
-        } else if (c > 0) {
+        } else if (has_left) {
             wait_ptr = imp_steps + g;
             wait_clamp = 16 * (last_needed(j0w - 32) >> 4) + 15;
         }
@@ -571,7 +601,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         if (sidx < NSTR - 1) {
             wait_ptr = prog + (w + NSTG);
             wait_add = kGroup - 1 - (kMidDepth - 2);
-        } else if (c + 1 < P.ncta) {
+        } else if (has_right) {
             wait_ptr = exp_steps + g;
             wait_add = kGroup - 1 - kEdgeDepth;
         }
@@ -590,7 +620,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         x[k] = 0.0f; Ua[k] = 0.0f; Ub[k] = 0.0f;
     }
 
-    const bool vec_ok = ((H & 3) == 0);
+    const bool vec_ok = ((H & 3) == 0) && ((pitch & 3) == 0) && ((jbase & 3) == 0);
     int fix_cols = 0;
     if (j0w - S <= 0 && j0w + 30 >= 0) fix_cols |= kFixLeft;
     if (j0w - S <= H - 1 && j0w + 30 >= H - 1) fix_cols |= kFixRight;
@@ -652,7 +682,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                         const int row = q - kToff - j0;
                         const int col = j0 + cg * 4;
                         const bool ok = (row >= 0) && (row < W) && (col < H);
-                        const size_t off = ok ? ((size_t)row * H + col) : 0;
+                        const size_t off = ok ? ((size_t)row * pitch + (col - jbase)) : 0;
                         const int so = (q & (kTileRows - 1)) * 32 + cg * 4;
                         cp_async_f32x4(t_rhs + so, F.rhs + off, ok);
                         if (HAS_X0) cp_async_f32x4(t_x0 + so, F.x0 + off, ok);
@@ -664,7 +694,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                         const int row = q - kToff - j0;
                         const int col = j0 + lane;
                         const bool ok = (row >= 0) && (row < W) && (col < H);
-                        const size_t off = ok ? ((size_t)row * H + col) : 0;
+                        const size_t off = ok ? ((size_t)row * pitch + (col - jbase)) : 0;
                         const int so = (q & (kTileRows - 1)) * 32 + lane;
                         cp_async_f32(t_rhs + so, F.rhs + off, ok);
                         if (HAS_X0) cp_async_f32(t_x0 + so, F.x0 + off, ok);
@@ -681,10 +711,10 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
 #pragma unroll
                 for (int it = 0; it < kWfBatch; ++it) vals[it] = t_out[((t - 48 + it) & (kTileRows - 1)) * 32 + lane];
                 if (colok && row0 + kWfBatch - 1 >= 1 && row0 <= W - 2) {
-                    float *dst = F.out + ((long long)row0 * H + col);
+                    float *dst = F.out + ((long long)row0 * pitch + (col - jbase));
 #pragma unroll
                     for (int it = 0; it < kWfBatch; ++it) {
-                        if (row0 + it >= 1 && row0 + it <= W - 2) dst[(long long)it * H] = vals[it];
+                        if (row0 + it >= 1 && row0 + it <= W - 2) dst[(long long)it * pitch] = vals[it];
                     }
                 }
             }
@@ -756,7 +786,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         for (int q = tau_e + 1 - 48; q <= tau_e; ++q) {
             const int row = q - kToff - S - j0w;
             if (colok && row >= 1 && row <= W - 2)
-                F.out[(size_t)row * H + col] = t_out[(q & (kTileRows - 1)) * 32 + lane];
+                F.out[(size_t)row * pitch + (col - jbase)] = t_out[(q & (kTileRows - 1)) * 32 + lane];
         }
     }
 }
@@ -770,7 +800,7 @@ size_t wf_smem_bytes(int nstr, int nstg)
                             (size_t)nstr * (nstg - 1) * 2 * L::kHandFloats + (size_t)nstr * nstg * L::kStateFloats);
 }
 
-struct WfConfig { int nstr, ncta; size_t smem; };
+struct WfConfig { int nstr, ncta, c_base; size_t smem; };
 
 // Chooses strips per CTA so that every CTA of the launch is co-resident (cooperative launch).
 template <int S, int MODE, bool HAS_X0>
@@ -779,7 +809,11 @@ cudaError_t wf_configure(const SweepLaunch &Lc, WfConfig &cfg)
     using L = WfLayout<S>;
     auto kern = wf_kernel<S, MODE, HAS_X0>;
     const int nstg = Lc.stages;
-    const int NS = (Lc.H + S * nstg + 31) / 32;     // strips: the last stage's frame is shifted left by all earlier sweeps
+    const int NS_all = (Lc.H + S * nstg + 31) / 32;   // strips: the last stage's frame is shifted left by all earlier sweeps
+    const int s_begin = Lc.strip_begin;
+    const int s_end = (Lc.strip_end < 0 || Lc.strip_end > NS_all) ? NS_all : Lc.strip_end;
+    const int NS = s_end - s_begin;                   // strips this rank runs
+    if (NS < 1 || s_begin < 0) return cudaErrorInvalidValue;
     int dev = 0, nsm = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
@@ -790,8 +824,11 @@ cudaError_t wf_configure(const SweepLaunch &Lc, WfConfig &cfg)
     int nstr = Lc.strips_per_cta > 0 ? Lc.strips_per_cta : 1;
     while (nstr > 1 && nstr * nstg > max_compute_warps) nstr >>= 1;
     if (nstr > NS) nstr = NS;
+    const bool multi_rank = Lc.link.has_left || Lc.link.has_right || s_begin > 0;
     for (;;) {
+        if (s_begin % nstr != 0) return cudaErrorInvalidValue;   // rank boundaries must fall on CTA boundaries
         cfg.nstr = nstr;
+        cfg.c_base = s_begin / nstr;
         cfg.ncta = (NS + nstr - 1) / nstr;
         cfg.smem = wf_smem_bytes<S>(nstr, nstg);
         bool fits = cfg.smem <= 227 * 1024 && cfg.ncta <= kWfMaxCtas;
@@ -804,7 +841,8 @@ cudaError_t wf_configure(const SweepLaunch &Lc, WfConfig &cfg)
             fits = (long long)cfg.ncta * Lc.nfields <= (long long)per_sm * nsm;
         }
         if (fits) return cudaSuccess;
-        if ((nstr * 2) * nstg > max_compute_warps || wf_smem_bytes<S>(nstr * 2, nstg) > 227 * 1024 || nstr >= NS)
+        // every rank of a multi-rank chain must use the same strips-per-CTA: no silent adjustment there
+        if (multi_rank || (nstr * 2) * nstg > max_compute_warps || wf_smem_bytes<S>(nstr * 2, nstg) > 227 * 1024 || nstr >= NS)
             return cudaErrorCooperativeLaunchTooLarge;
         nstr *= 2;
     }
@@ -837,15 +875,21 @@ cudaError_t wf_launch_inst(const SweepLaunch &Lc, SweepScratch &scr, cudaStream_
     for (int i = 0; i < kMaxSweepFields; ++i) P.fld[i] = Lc.fld[i < Lc.nfields ? i : 0];
     P.W = Lc.W;
     P.H = Lc.H;
+    P.pitch = Lc.pitch > 0 ? Lc.pitch : Lc.H;
+    P.jbase = Lc.jbase;
     P.nstr = nstr;
     P.nstg = nstg;
     P.ncta = ncta;
+    P.c_base = cfg.c_base;
     P.a = Lc.a;
     P.c_recip = Lc.c_recip;
     P.omega = Lc.omega;
     P.xchg = scr.xchg;
     P.flags = scr.flags;
     P.seq_base = scr.seq << 32;
+    P.link = Lc.link;
+    P.link_seq_base = Lc.link.seq << 32;
+    if ((Lc.link.has_left || Lc.link.has_right) && (nstg > kLinkStages || L::EXW > 44)) return cudaErrorInvalidValue;
     void *args[] = {&P};
     return cudaLaunchCooperativeKernel((const void *)kern, dim3(ncta, Lc.nfields), dim3((nstr * nstg + 2) * 32), args,
                                        cfg.smem, st);
@@ -916,9 +960,14 @@ cudaError_t na_launch(const SweepLaunch &Lc, float *rings, size_t ring_floats, u
     for (int i = 0; i < kMaxSweepFields; ++i) P.fld[i] = Lc.fld[0];
     P.W = Lc.W;
     P.H = Lc.H;
+    P.pitch = Lc.H;
+    P.jbase = 0;
     P.nstr = cfg.nstr;
     P.nstg = Lc.stages;
     P.ncta = cfg.ncta;
+    P.c_base = 0;
+    P.link = SweepLink{};
+    P.link_seq_base = 0;
     P.a = 0.0f;
     P.c_recip = 1.0f;
     P.omega = 1.0f;
@@ -1031,7 +1080,7 @@ int pressure_sweeps_noalloc(const float *d_div, float *d_p, int W, int H, int sw
         }
         // walls and corners of p after the pass (setBoundary(0, p), src/fluid_sim.cpp:330)
         BndJob job{d_p, 0, 0};
-        e = launch_set_boundary(&job, 1, W, H, st);
+        e = launch_set_boundary(&job, 1, whole_grid(W, H), st);
         if (e != cudaSuccess) {
             msg = std::string("fsb_pressure_sweeps_noalloc: boundary kernel failed: ") + cudaGetErrorString(e);
             return -(int)e;

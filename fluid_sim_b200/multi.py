@@ -1,0 +1,273 @@
+"""One FluidSim::step sharded over the GPUs of a box: every rank owns all rows of a block of columns.
+
+The exact-order relaxations (diffuse / project, reference src/fluid_sim.cpp:50-61, :319-331) stay ONE chain of
+column strips across all ranks: inside the sweep kernel the last CTA of a rank hands the strip boundary to the
+first CTA of the next rank through peer memory (CUDA IPC over NVLink) with the same ring + progress-word protocol
+that links CTAs on one GPU.  Everything else needs halo columns only; this module moves them between passes with
+``torch.distributed`` (NCCL send/recv), which is plumbing: all arithmetic runs in libfluidsim_b200.so.
+
+The result is bit-identical to the single-GPU run (tests/mgpu_check.py).
+"""
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import (DENSITY, VELOCITY_X, VELOCITY_Y, PREV_DENSITY, PREV_VEL_X, PREV_VEL_Y, NOISE_GLIBC, NOISE_ZERO,
+               FsbError, Params, load_library, _SIM, _ip)
+
+__all__ = ["BlockFluidSim", "column_range", "plan_projection", "exchange_halo", "return_columns"]
+
+
+def column_range(height, rank, world, align=64):
+    """Columns [begin, end) owned by `rank`; blocks are equal and a multiple of `align` (CTA granularity)."""
+    if height % world:
+        raise ValueError("height must be divisible by the number of ranks")
+    hl = height // world
+    if hl % align:
+        raise ValueError(f"columns per rank ({hl}) must be a multiple of {align}")
+    return rank * hl, (rank + 1) * hl
+
+
+def plan_projection(sweeps, levels=10, max_stages=8):
+    """Launches (levels per warp, stages) covering `sweeps` pressure sweeps; the same on every rank."""
+    out, left = [], sweeps
+    while left >= levels:
+        st = min(left // levels, max_stages)
+        out.append((levels, st))
+        left -= levels * st
+    for lv in (5, 2, 1):
+        while left >= lv:
+            out.append((lv, 1))
+            left -= lv
+    return out
+
+
+# ---- halo movement on plain tensors (runs on CPU tensors with gloo as well: tests/test_multi_host.py) -------
+def _neighbours(rank, world):
+    return (rank - 1 if rank > 0 else None), (rank + 1 if rank < world - 1 else None)
+
+
+def exchange_halo(tensors, halo, ncols, width, rank, world, group=None):
+    """Fill `width` halo columns on both sides of every [rows, pitch] tensor from the neighbours' owned columns.
+    Owned columns are local [halo, halo + ncols)."""
+    if world == 1 or width == 0:
+        return
+    left, right = _neighbours(rank, world)
+    ops, recvs = [], []
+    for t in tensors:
+        if left is not None:
+            send = t[:, halo:halo + width].contiguous()
+            buf = torch.empty_like(send)
+            ops += [dist.P2POp(dist.isend, send, left, group), dist.P2POp(dist.irecv, buf, left, group)]
+            recvs.append((t, halo - width, buf))
+        if right is not None:
+            send = t[:, halo + ncols - width:halo + ncols].contiguous()
+            buf = torch.empty_like(send)
+            ops += [dist.P2POp(dist.isend, send, right, group), dist.P2POp(dist.irecv, buf, right, group)]
+            recvs.append((t, halo + ncols, buf))
+    for w in dist.batch_isend_irecv(ops):
+        w.wait()
+    for t, c0, buf in recvs:
+        t[:, c0:c0 + width] = buf
+
+
+def return_columns(tensors, halo, ncols, width, rank, world, group=None):
+    """After a sweep pass: the `width` result columns a rank computed for its LEFT neighbour (they sit in its left
+    halo) go back to that neighbour's last owned columns.  Interior rows only; walls are redone afterwards."""
+    if world == 1 or width == 0:
+        return
+    left, right = _neighbours(rank, world)
+    ops, recvs = [], []
+    for t in tensors:
+        if left is not None:
+            ops.append(dist.P2POp(dist.isend, t[1:-1, halo - width:halo].contiguous(), left, group))
+        if right is not None:
+            buf = torch.empty((t.shape[0] - 2, width), dtype=t.dtype, device=t.device)
+            ops.append(dist.P2POp(dist.irecv, buf, right, group))
+            recvs.append((t, buf))
+    for w in dist.batch_isend_irecv(ops):
+        w.wait()
+    for t, buf in recvs:
+        t[1:-1, halo + ncols - width:halo + ncols] = buf
+
+
+class _DevicePointer:
+    """Zero-copy view of library-owned device memory for torch (CUDA array interface)."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+class BlockFluidSim:
+    """This rank's column block of a width x height simulation spread over `dist.get_world_size()` GPUs."""
+
+    def __init__(self, width, height, proj_iters=20, diff_iters=5, viscosity=1e-4, diffusion=0.0, omega=1.5,
+                 noise="glibc", noise_seed=1, noise_pos=0, device=0, halo=128, levels=10, strips_per_cta=2, group=None):
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.group = group
+        self.width, self.height = width, height
+        self.P, self.D = proj_iters, diff_iters
+        self.visc, self.diff = viscosity, diffusion
+        self.halo, self.levels = halo, levels
+        if diffusion != 0.0:
+            raise FsbError("BlockFluidSim: density diffusion other than the reference's 0 is not sharded yet")
+        if diff_iters not in (0, 1, 2, 5, 10, 20):
+            raise FsbError("BlockFluidSim: diffusion sweeps must be 0, 1, 2, 5, 10 or 20 (one launch)")
+        self.j0, self.j1 = column_range(height, self.rank, self.world, 32 * strips_per_cta)
+        self.ncols = self.j1 - self.j0
+        self.plan = plan_projection(proj_iters, levels)
+        if max([lv * st for lv, st in self.plan] + [diff_iters]) > halo:
+            raise FsbError("BlockFluidSim: halo narrower than the sweeps fused into one launch")
+        self._lib = load_library()
+        p = Params()
+        self._lib.fsb_default_params(C.byref(p))
+        p.width, p.height, p.proj_iters, p.diff_iters = width, height, proj_iters, diff_iters
+        p.viscosity, p.diffusion, p.omega = viscosity, diffusion, omega
+        p.noise_mode = NOISE_GLIBC if noise == "glibc" else NOISE_ZERO
+        p.noise_seed, p.noise_pos, p.device = noise_seed, noise_pos, device
+        self._h = _SIM()
+        self._check(self._lib.fsb_create_block(C.byref(p), self.j0, self.j1, halo, C.byref(self._h)))
+        self._check(self._lib.fsb_set_tuning(self._h, strips_per_cta, levels, 0))
+        pitch, jbase = C.c_int(), C.c_int()
+        self._check(self._lib.fsb_block_info(self._h, C.byref(pitch), C.byref(jbase), None, None))
+        self.pitch, self.jbase = pitch.value, jbase.value
+        self.device = torch.device("cuda", device)
+        st = C.c_void_p()
+        self._check(self._lib.fsb_get_stream(self._h, C.byref(st)))
+        self.stream = torch.cuda.ExternalStream(st.value, device=self.device)
+        self.seq = 0
+        self._connect()
+
+    # -- plumbing ----------------------------------------------------------------------------------
+    def _check(self, rc):
+        if rc != 0:
+            raise FsbError(f"fluid_sim_b200 error {rc}: {self._lib.fsb_last_error().decode()}")
+
+    def _connect(self):
+        """Exchange the CUDA IPC handles of the link buffers and map the neighbours'."""
+        mine = (C.c_ubyte * 64)()
+        self._check(self._lib.fsb_link_handle(self._h, mine))
+        t = torch.tensor(list(mine), dtype=torch.uint8, device=self.device)
+        allh = [torch.empty_like(t) for _ in range(self.world)]
+        dist.all_gather(allh, t, group=self.group)
+        left, right = _neighbours(self.rank, self.world)
+        lh = (C.c_ubyte * 64)(*allh[left].cpu().tolist()) if left is not None else None
+        rh = (C.c_ubyte * 64)(*allh[right].cpu().tolist()) if right is not None else None
+        self._check(self._lib.fsb_link_connect(self._h, lh, rh))
+        dist.barrier(group=self.group)
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.fsb_destroy(self._h)
+            self._h = _SIM()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def tensor(self, field):
+        """The local [width, pitch] array of a field as a torch tensor (valid until the next advection swaps buffers)."""
+        ptr = C.c_void_p()
+        self._check(self._lib.fsb_device_field(self._h, field, C.byref(ptr)))
+        return torch.as_tensor(_DevicePointer(ptr.value, (self.width, self.pitch)), device=self.device)
+
+    def owned(self, field):
+        return self.tensor(field)[:, self.halo:self.halo + self.ncols]
+
+    def sync(self):
+        self._check(self._lib.fsb_sync(self._h))
+
+    def _ids(self, vals):
+        return (C.c_int * len(vals))(*vals)
+
+    def _bnd(self, fields, bs, pz=None):
+        self._check(self._lib.fsb_blk_set_boundary(self._h, len(fields), self._ids(fields), self._ids(bs),
+                                                   self._ids(pz) if pz else None))
+
+    def _halo(self, fields, width):
+        exchange_halo([self.tensor(f) for f in fields], self.halo, self.ncols, width, self.rank, self.world, self.group)
+
+    def _return(self, fields, width):
+        return_columns([self.tensor(f) for f in fields], self.halo, self.ncols, width, self.rank, self.world, self.group)
+
+    def _trace_radius(self, dt):
+        """Columns an RK4 back-trace can reach: every stage moves at most dt*width*max|velocity| cells."""
+        u, v = self.owned(VELOCITY_X), self.owned(VELOCITY_Y)
+        m = torch.maximum(u.abs().max(), v.abs().max()).reshape(1)
+        dist.all_reduce(m, op=dist.ReduceOp.MAX, group=self.group)
+        r = int(math.ceil(float(m.item()) * dt * self.width)) + 2
+        if r > self.halo:
+            raise FsbError(f"BlockFluidSim: advection reaches {r} columns, halo is {self.halo}")
+        return r
+
+    # -- inputs / outputs -----------------------------------------------------------------------------
+    def set_from_global(self, field, full):
+        """Load this rank's columns (and halos, where the grid has them) from a full [width, height] host array."""
+        loc = np.zeros((self.width, self.pitch), np.float32)
+        a, b = max(self.jbase, 0), min(self.jbase + self.pitch, self.height)
+        loc[:, a - self.jbase:b - self.jbase] = full[:, a:b]
+        self._check(self._lib.fsb_write_field(self._h, field, loc.ctypes.data))
+
+    def read_owned(self, field):
+        with torch.cuda.stream(self.stream):
+            out = self.owned(field).contiguous().cpu()
+        return out.numpy()
+
+    def gather(self, field, dst=0):
+        """Full [width, height] array on rank `dst` (None elsewhere)."""
+        with torch.cuda.stream(self.stream):
+            mine = self.owned(field).contiguous()
+            parts = [torch.empty_like(mine) for _ in range(self.world)] if self.rank == dst else None
+            dist.gather(mine, parts, dst=dst, group=self.group)
+            if self.rank != dst:
+                return None
+            return torch.cat(parts, dim=1).cpu().numpy()
+
+    def addDensity(self, x, y, amount):
+        self._check(self._lib.fsb_add_density(self._h, x, y, amount))   # ignored unless this rank owns column y
+
+    def addVelocity(self, x, y, ax, ay):
+        self._check(self._lib.fsb_add_velocity(self._h, x, y, ax, ay))
+
+    # -- the step (same order as velocityStep / densityStep, src/fluid_sim.cpp:370-422) ---------------------
+    def _project(self):
+        self._halo([VELOCITY_X, VELOCITY_Y], 1)
+        self._check(self._lib.fsb_blk_divergence(self._h))
+        for k, (lv, st) in enumerate(self.plan):
+            self.seq += 1
+            self._check(self._lib.fsb_blk_sweep(self._h, 0, 1, None, None, lv, st, 1 if k == 0 else 0, 0.0, 0.0, self.seq))
+            self._return([PREV_VEL_X], lv * st)
+            self._bnd([PREV_VEL_X], [0])
+        if not self.plan:
+            self.tensor(PREV_VEL_X).zero_()
+        self._halo([PREV_VEL_X], 1)
+        self._check(self._lib.fsb_blk_gradient(self._h))
+        self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
+
+    def step(self, dt=0.01):
+        with torch.cuda.stream(self.stream):
+            self._check(self._lib.fsb_op_add_noise(self._h))
+            if self.D > 0:
+                a = np.float32(np.float32(np.float32(dt) * np.float32(self.visc)) * np.float32(self.width)) * np.float32(self.height)
+                if a == 0:
+                    raise FsbError("BlockFluidSim: zero viscosity is not sharded yet")
+                self.seq += 1
+                self._check(self._lib.fsb_blk_sweep(self._h, 1, 2, self._ids([VELOCITY_X, VELOCITY_Y]), self._ids([1, 2]),
+                                                    self.D, 1, 0, self.visc, dt, self.seq))
+                self._return([VELOCITY_X, VELOCITY_Y], self.D)
+                self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
+            self._project()
+            self._halo([VELOCITY_X, VELOCITY_Y], self._trace_radius(dt))
+            self._check(self._lib.fsb_blk_advect_velocity(self._h, dt))
+            self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
+            self._project()
+            # density: diffusion 0 is the identity d + 0.0f plus the boundary update, folded into the gather
+            self._bnd([DENSITY], [0], [1])
+            self._halo([DENSITY, VELOCITY_X, VELOCITY_Y], self._trace_radius(dt))
+            self._check(self._lib.fsb_blk_advect_density(self._h, dt, 1))
+            self._bnd([DENSITY], [0])

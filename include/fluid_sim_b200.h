@@ -160,6 +160,25 @@ enum {
 int fsb_profile_enable(fsb_sim *s, int on);
 int fsb_profile_read(fsb_sim *s, double *ms, uint64_t *counts, int reset);
 
+/* ---- column blocks: one simulation per GPU, each owning all rows of a range of columns --------------------
+ * No counterpart in the reference (it is single-process); this is the sharded form of the same passes.
+ * A block stores global columns [col_begin - halo, col_end + halo) with `pitch` floats per row
+ * (fsb_block_info); fsb_read_field / fsb_write_field move the whole local array (width * pitch floats).
+ * The exact-order sweeps run as ONE chain across all ranks: neighbouring blocks hand the strip boundary over
+ * through a small buffer mapped with CUDA IPC (fsb_link_handle / fsb_link_connect), inside the kernels.
+ * Halo columns are exchanged by the caller between passes (fluid_sim_b200/multi.py does it with NCCL). */
+int fsb_create_block(const fsb_params *p, int col_begin, int col_end, int halo, fsb_sim **out);
+int fsb_block_info(const fsb_sim *s, int *pitch, int *jbase, int *j0, int *j1);
+int fsb_link_handle(fsb_sim *s, void *handle64);                                   /* 64-byte cudaIpcMemHandle_t */
+int fsb_link_connect(fsb_sim *s, const void *left_handle64, const void *right_handle64);   /* NULL = no neighbour */
+int fsb_blk_sweep(fsb_sim *s, int mode, int nfields, const int *fields, const int *bs, int levels, int stages,
+                  int first, float diff, float dt, unsigned long long seq);
+int fsb_blk_set_boundary(fsb_sim *s, int n, const int *fields, const int *bs, const int *plus_zero);
+int fsb_blk_divergence(fsb_sim *s);
+int fsb_blk_gradient(fsb_sim *s);
+int fsb_blk_advect_velocity(fsb_sim *s, float dt);
+int fsb_blk_advect_density(fsb_sim *s, float dt, int plus_zero);
+
 /* No counterpart in the reference.
  *
  * The pressure relaxation of project() (src/fluid_sim.cpp:313-331: p = 0, then `sweeps` lexicographic
