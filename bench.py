@@ -168,8 +168,8 @@ def workload_for(n_gpus, args):
         return args.width, args.height, args.proj or 40, "custom"
     if n_gpus == 1:
         return 8192, 8192, args.proj or 40, "config3: 8192x8192 grid, 40 projection sweeps, 1xB200"
-    # config 5 of BASELINE.json, weak-scaled: 4096 rows x 32768 columns per GPU, P = 100
-    return 4096, 32768, args.proj or 100, "config5: 32768-column grid, 4096 rows per GPU, 100 projection sweeps"
+    # config 5 of BASELINE.json, weak-scaled: 32768 rows x 4096 columns per GPU (32768^2 at 8 GPUs), P = 100
+    return 32768, 4096 * n_gpus, args.proj or 100, "config5: 32768-row grid, 4096 columns per GPU (32768^2 at 8 GPUs), 100 projection sweeps"
 
 
 def main():
@@ -229,16 +229,45 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    sim = fsb.FluidSim(W, H, P, 5, device=local_rank, strips_per_cta=args.strips_per_cta, sweeps_per_warp=args.sweeps_per_warp, max_stages=args.max_stages)
-    stream = torch.cuda.ExternalStream(sim.stream(), device=torch.device("cuda", local_rank))
+    multi = world > 1
+    if multi:
+        from fluid_sim_b200.multi import BlockFluidSim
+        from tests.util import vortex_lattice_block
+        sim = BlockFluidSim(W, H, P, 5, device=local_rank)
+        a0, a1 = sim.jbase, sim.jbase + sim.pitch
+        d, u, v = vortex_lattice_block(W, H, a0, a1)
+        for fid, arr in ((fsb.DENSITY, d), (fsb.VELOCITY_X, u), (fsb.VELOCITY_Y, v)):
+            sim._check(sim._lib.fsb_write_field(sim._h, fid, np.ascontiguousarray(arr).ctypes.data))
+        del d, u, v
+        stream = sim.stream
+        lib_sim = sim
 
-    # synthetic input, built on the host in page-locked memory and injected through the C ABI
-    d, u, v = vortex_lattice(W, H)
-    buf = sim.pinned_array()
-    for fid, arr in ((fsb.DENSITY, d), (fsb.VELOCITY_X, u), (fsb.VELOCITY_Y, v)):
-        buf[...] = arr
-        sim.add_field(fid, buf)
-    del d, u, v
+        class _Shim:   # the few calls the timing code below makes, on the block simulation
+            def step(self, dt): lib_sim.step(dt)
+            def sync(self): lib_sim.sync()
+            def profile_enable(self, on): lib_sim._check(lib_sim._lib.fsb_profile_enable(lib_sim._h, 1 if on else 0))
+            def profile_read(self, reset=True):
+                import ctypes as C
+                names = fsb.FluidSim.PROF_NAMES
+                ms = (C.c_double * len(names))(); cnt = (C.c_uint64 * len(names))()
+                lib_sim._check(lib_sim._lib.fsb_profile_read(lib_sim._h, ms, cnt, 1 if reset else 0))
+                return {n: (ms[i], cnt[i]) for i, n in enumerate(names)}
+            def launch_count(self):
+                import ctypes as C
+                v_ = C.c_uint64(); lib_sim._check(lib_sim._lib.fsb_launch_count(lib_sim._h, C.byref(v_))); return v_.value
+        sim = _Shim()
+    else:
+        sim = fsb.FluidSim(W, H, P, 5, device=local_rank, strips_per_cta=args.strips_per_cta,
+                           sweeps_per_warp=args.sweeps_per_warp, max_stages=args.max_stages)
+        stream = torch.cuda.ExternalStream(sim.stream(), device=torch.device("cuda", local_rank))
+
+        # synthetic input, built on the host in page-locked memory and injected through the C ABI
+        d, u, v = vortex_lattice(W, H)
+        buf = sim.pinned_array()
+        for fid, arr in ((fsb.DENSITY, d), (fsb.VELOCITY_X, u), (fsb.VELOCITY_Y, v)):
+            buf[...] = arr
+            sim.add_field(fid, buf)
+        del d, u, v
 
     for _ in range(max(Wm, 3) if K > 0 else 0):
         sim.step(0.01)
@@ -268,7 +297,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
     ms_per_step = ms_total / K
-    cells_total = W * H * world
+    cells_total = W * H            # H is the global column count at N > 1
     value = cells_total * K / (ms_total * 1e-3)
 
     # -------- e2e: the reference's frame loop with host buffers (inject patch, step, read density back)
@@ -279,17 +308,31 @@ def main():
     dx = np.full(len(patch), 0.05, np.float32)
     dy = np.full(len(patch), -0.02, np.float32)
     h2d = xs.nbytes * 2 + ys.nbytes * 2 + ones.nbytes + dx.nbytes + dy.nbytes
-    d2h = W * H * 4
+    if multi:
+        host_d = torch.empty((W, lib_sim.ncols), dtype=torch.float32).pin_memory()
+        d2h = W * lib_sim.ncols * 4
+
+        def frame():
+            for x_, y_, o_, a_, b_ in zip(xs, ys, ones, dx, dy):
+                lib_sim.addDensity(int(x_), int(y_), float(o_)); lib_sim.addVelocity(int(x_), int(y_), float(a_), float(b_))
+            lib_sim.step(0.01)
+            with torch.cuda.stream(stream):
+                host_d.copy_(lib_sim.owned(fsb.DENSITY), non_blocking=True)
+            lib_sim.sync()
+        checksum_of = lambda: float(host_d.double().sum())
+    else:
+        d2h = W * H * 4
+
+        def frame():
+            sim.addDensityN(xs, ys, ones); sim.addVelocityN(xs, ys, dx, dy); sim.step(0.01); sim.read(fsb.DENSITY, buf)
+        checksum_of = lambda: float(buf.astype(np.float64).sum())
     for _ in range(2):
-        sim.addDensityN(xs, ys, ones); sim.addVelocityN(xs, ys, dx, dy); sim.step(0.01); sim.read(fsb.DENSITY, buf)
+        frame()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record(stream)
     for _ in range(K):
-        sim.addDensityN(xs, ys, ones)
-        sim.addVelocityN(xs, ys, dx, dy)
-        sim.step(0.01)
-        sim.read(fsb.DENSITY, buf)
+        frame()
     e1.record(stream)
     sim.sync()
     barrier()
@@ -298,8 +341,9 @@ def main():
         t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
+        d2h *= world
     e2e_value = cells_total * K / (e2e_ms * 1e-3)
-    checksum = float(buf.astype(np.float64).sum())
+    checksum = checksum_of()
 
     if rank != 0:
         if world > 1:
@@ -310,7 +354,7 @@ def main():
     peak, peak_src = measured_peak_gbs()
     gs_ms, gs_n = prof["gs"]
     gs_launch_ms = gs_ms / max(gs_n, 1)
-    cells = W * H
+    cells = W * (H // world)                                  # cells of one rank's block
     launches_per_proj = max(1.0, gs_n / (2.0 * K))          # two projections per step
     levels = P / launches_per_proj                            # sweeps fused into one launch
     algo_bytes = 12.0 * levels * cells                        # reference pass structure: 12 B per cell per sweep
@@ -350,11 +394,12 @@ def main():
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(Wm, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload, "grid_per_gpu": [W, H], "proj_iters": P, "diff_iters": 5, "dt": 0.01,
+            "config": {"workload": workload, "grid": [W, H], "grid_per_gpu": [W, H // world], "proj_iters": P, "diff_iters": 5, "dt": 0.01,
                        "input": "vortex lattice (SURVEY.md 8(d) I3) + glibc rand() noise",
                        "l2": "fields are larger than L2 (no flush needed)" if cells * 4 > 126e6 else "fields fit in L2",
                        "decomposition": "single GPU" if world == 1 else
-                       "independent 4096-row slabs, one per GPU (slab coupling across GPUs is not implemented yet)"},
+                       "column blocks, one per GPU: the exact-order sweep chain crosses GPUs through CUDA-IPC peer rings "
+                       "inside the kernel, halo columns move with NCCL send/recv between passes"},
             "roofline": roofline, "step_roofline": step_roofline, "kernel_ms_per_step": shares,
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),

@@ -31,7 +31,7 @@ def column_range(height, rank, world, align=64):
     return rank * hl, (rank + 1) * hl
 
 
-def plan_projection(sweeps, levels=10, max_stages=8):
+def plan_projection(sweeps, levels=10, max_stages=4):
     """Launches (levels per warp, stages) covering `sweeps` pressure sweeps; the same on every rank."""
     out, left = [], sweeps
     while left >= levels:

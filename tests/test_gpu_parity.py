@@ -293,3 +293,19 @@ def test_cpp_dropin_headless_main():
     lines = out.stdout.strip().splitlines()
     assert lines[0] == want, (lines[0], want)
     assert lines[1] == "after reset d[100][110] 0"
+
+
+@pytest.mark.parametrize("args", ["256 512 20 5 2", "200 1024 40 5 1"])
+def test_multi_gpu_matches_single_gpu(args):
+    """Column blocks on 2 GPUs (sweep chain handed over through peer memory, NCCL halos) give the single-GPU bits."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    from tests.util import ROOT
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", os.path.join(ROOT, "tests", "mgpu_check.py")] + args.split()
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert "MGPU-PARITY PASS" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]

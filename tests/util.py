@@ -74,3 +74,17 @@ def vortex_lattice(w, h, dt=0.01, k=8):
     v = (-A * cx * sy).astype(np.float32)
     d = (0.5 * (1 + sx * sy)).astype(np.float32)
     return d, u, v
+
+
+def vortex_lattice_block(w, h, a, b, dt=0.01, k=8):
+    """Columns [a, b) of vortex_lattice(w, h) (columns outside the grid are zero)."""
+    i = np.arange(w, dtype=np.float64)[:, None]
+    j = np.arange(a, b, dtype=np.float64)[None, :]
+    A = 4.0 / (dt * w)
+    sx, cx = np.sin(2 * np.pi * k * i / w), np.cos(2 * np.pi * k * i / w)
+    sy, cy = np.sin(2 * np.pi * k * j / h), np.cos(2 * np.pi * k * j / h)
+    inside = ((j >= 0) & (j < h)).astype(np.float64)
+    u = (A * sx * cy * inside).astype(np.float32)
+    v = (-A * cx * sy * inside).astype(np.float32)
+    d = (0.5 * (1 + sx * sy) * inside).astype(np.float32)
+    return d, u, v
