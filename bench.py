@@ -166,7 +166,7 @@ def cpu_reference(H, P, nsteps, warmup, budget_s):
 def workload_for(n_gpus, args):
     if args.width and args.height:
         return args.width, args.height, args.proj or 40, "custom"
-    if n_gpus == 1:
+    if n_gpus == 1 and args.workload != "config5":
         return 8192, 8192, args.proj or 40, "config3: 8192x8192 grid, 40 projection sweeps, 1xB200"
     # config 5 of BASELINE.json, weak-scaled: 32768 rows x 4096 columns per GPU (32768^2 at 8 GPUs), P = 100
     return 32768, 4096 * n_gpus, args.proj or 100, "config5: 32768-row grid, 4096 columns per GPU (32768^2 at 8 GPUs), 100 projection sweeps"
@@ -182,6 +182,7 @@ def main():
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--proj", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="", help="config5: run the weak-scaling per-GPU workload at N=1 too")
     ap.add_argument("--strips-per-cta", type=int, default=0)
     ap.add_argument("--sweeps-per-warp", type=int, default=0)
     ap.add_argument("--max-stages", type=int, default=0)
