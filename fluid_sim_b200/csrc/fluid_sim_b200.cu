@@ -83,6 +83,9 @@ struct fsb_sim {
     int strip_begin = 0, strip_end = -1;       // 32-column strips of the sweep chain this rank runs
     unsigned char *link_buf = nullptr;          // [rings | in_prod | cons], shared with both neighbours through CUDA IPC
     void *peer_left = nullptr, *peer_right = nullptr;   // the neighbours' link_buf mapped into this process
+    float *peer_left_f[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // left rank's fields (same roles)
+    void *peer_left_base[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; // as opened (for closing)
+    int left_ncols = 0;                                  // columns owned by the left rank
     // optional per-kernel-class timing (CUDA events on the simulation's stream)
     bool profiling = false;
     struct ProfRec { int cat; cudaEvent_t a, b; };
@@ -505,7 +508,8 @@ int fsb_create(const fsb_params *p, fsb_sim **out) { return create_common(p, nul
 /* layout of the link buffer shared between neighbouring ranks */
 static const size_t kLinkRingBytes = (size_t)kMaxSweepFields * kLinkStages * kLinkRingFloats * sizeof(float);
 static const size_t kLinkFlagBytes = (size_t)kMaxSweepFields * kLinkStages * sizeof(unsigned long long);
-static const size_t kLinkBytes = kLinkRingBytes + 2 * kLinkFlagBytes;
+static const size_t kLinkRetBytes = 64;   // completion counters of the columns stored here by the right rank
+static const size_t kLinkBytes = kLinkRingBytes + 2 * kLinkFlagBytes + kLinkRetBytes;
 
 int fsb_create_block(const fsb_params *p, int col_begin, int col_end, int halo, fsb_sim **out)
 {
@@ -605,6 +609,8 @@ int fsb_destroy(fsb_sim *s)
         if (s->d_entries) cudaFree(s->d_entries);
         if (s->d_segs) cudaFree(s->d_segs);
         noise_tables_destroy(s->noise_tables);
+        for (int k = 0; k < 6; ++k)
+            if (s->peer_left_base[k]) cudaIpcCloseMemHandle(s->peer_left_base[k]);
         if (s->peer_left) cudaIpcCloseMemHandle(s->peer_left);
         if (s->peer_right) cudaIpcCloseMemHandle(s->peer_right);
         if (s->link_buf) cudaFree(s->link_buf);
@@ -977,6 +983,44 @@ int fsb_link_connect(fsb_sim *s, const void *left_handle64, const void *right_ha
     return FSB_OK;
 }
 
+/* CUDA IPC handles of the six field buffers, in role order (6 x 64 bytes): the rank on the RIGHT maps them so that
+ * its sweep kernels can store the result columns that belong to this rank straight into these arrays. */
+int fsb_field_handles(fsb_sim *s, void *handles6x64)
+{
+    if (!s || !handles6x64 || !s->is_block) return fail(FSB_EINVAL, "fsb_field_handles: not a block simulation");
+    DeviceGuard guard(s->device);
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    for (int k = 0; k < 6; ++k)
+        FSB_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t *>(static_cast<unsigned char *>(handles6x64) + 64 * k), s->f[k]));
+    return FSB_OK;
+}
+
+int fsb_link_connect_fields(fsb_sim *s, const void *left_handles6x64, int left_ncols)
+{
+    if (!s || !left_handles6x64 || !s->is_block) return fail(FSB_EINVAL, "fsb_link_connect_fields: bad argument");
+    DeviceGuard guard(s->device);
+    for (int k = 0; k < 6; ++k) {
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, static_cast<const unsigned char *>(left_handles6x64) + 64 * k, sizeof(h));
+        FSB_CUDA(cudaIpcOpenMemHandle(&s->peer_left_base[k], h, cudaIpcMemLazyEnablePeerAccess));
+        s->peer_left_f[k] = static_cast<float *>(s->peer_left_base[k]);
+    }
+    s->left_ncols = left_ncols;
+    return FSB_OK;
+}
+
+/* Holds this simulation's stream until the rank on the right has stored `expected` strips' worth of result columns
+ * of sweep-field slot `slot` into this rank's arrays (counted since creation). */
+int fsb_blk_wait_returns(fsb_sim *s, int slot, unsigned long long expected)
+{
+    if (!s || !s->link_buf || slot < 0 || slot >= kMaxSweepFields) return fail(FSB_EINVAL, "fsb_blk_wait_returns: bad argument");
+    DeviceGuard guard(s->device);
+    const unsigned long long *c = reinterpret_cast<const unsigned long long *>(s->link_buf + kLinkRingBytes + 2 * kLinkFlagBytes) + slot;
+    FSB_CUDA(launch_wait_counter(c, expected, s->stream));
+    s->launches += 1;
+    return FSB_OK;
+}
+
 static SweepLink make_link(const fsb_sim *s, unsigned long long seq)
 {
     SweepLink L;
@@ -990,6 +1034,11 @@ static SweepLink make_link(const fsb_sim *s, unsigned long long seq)
     if (s->peer_right) {
         L.right_rings = reinterpret_cast<float *>(s->peer_right);
         L.right_prod = reinterpret_cast<unsigned long long *>(static_cast<unsigned char *>(s->peer_right) + kLinkRingBytes);
+    }
+    if (s->peer_left && s->peer_left_f[0]) {
+        L.left_ret = reinterpret_cast<unsigned long long *>(static_cast<unsigned char *>(s->peer_left) + kLinkRingBytes + 2 * kLinkFlagBytes);
+        L.peer_jbase = s->G.jbase - s->left_ncols;     // same halo width and pitch on every rank
+        L.peer_hi = s->G.j0 + 1;                        // the left rank's last owned columns and its first halo column
     }
     L.seq = seq;
     return L;
@@ -1019,6 +1068,7 @@ int fsb_blk_sweep(fsb_sim *s, int mode, int nfields, const int *fields, const in
     if (mode == 0) {
         L.mode = kGaussSeidel;
         L.fld[0] = SweepField{first ? nullptr : s->f[FSB_PREV_VEL_X], s->f[FSB_PREV_VEL_Y], s->f[FSB_PREV_VEL_X], 1.0f, 1.0f};
+        if (L.link.left_ret) L.fld[0].out_peer = s->peer_left_f[FSB_PREV_VEL_X];
         L.a = 0.0f; L.c_recip = 1.0f; L.omega = 1.0f;
     } else {
         if (!fields || !bs) return fail(FSB_EINVAL, "fsb_blk_sweep: fields missing");
@@ -1031,6 +1081,7 @@ int fsb_blk_sweep(fsb_sim *s, int mode, int nfields, const int *fields, const in
             if (!valid_field(fields[i])) return fail(FSB_EINVAL, "fsb_blk_sweep: bad field");
             float *x = s->f[fields[i]];
             L.fld[i] = SweepField{x, x, x, sign_i(bs[i]), sign_j(bs[i])};
+            if (L.link.left_ret) L.fld[i].out_peer = s->peer_left_f[fields[i]];
         }
     }
     int nl = 0;
@@ -1088,6 +1139,8 @@ int fsb_blk_advect_velocity(fsb_sim *s, float dt)
     s->launches += 1;
     std::swap(s->f[FSB_VELOCITY_X], s->f[FSB_PREV_VEL_X]);
     std::swap(s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_Y]);
+    std::swap(s->peer_left_f[FSB_VELOCITY_X], s->peer_left_f[FSB_PREV_VEL_X]);   // every rank swaps the same roles
+    std::swap(s->peer_left_f[FSB_VELOCITY_Y], s->peer_left_f[FSB_PREV_VEL_Y]);
     return FSB_OK;
 }
 
@@ -1102,6 +1155,7 @@ int fsb_blk_advect_density(fsb_sim *s, float dt, int plus_zero)
     }
     s->launches += 1;
     std::swap(s->f[FSB_DENSITY], s->f[FSB_PREV_DENSITY]);
+    std::swap(s->peer_left_f[FSB_DENSITY], s->peer_left_f[FSB_PREV_DENSITY]);
     return FSB_OK;
 }
 

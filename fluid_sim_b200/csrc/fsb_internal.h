@@ -36,6 +36,7 @@ struct SweepField {
     const float *rhs;   // divergence (GS) or source field (SOR)
     float *out;         // result (interior cells only; may alias x0)
     float si, sj;       // sign applied on the i-walls / j-walls (setBoundary's b)
+    float *out_peer = nullptr;   // multi-rank: the same field of the rank on the LEFT (peer memory), or nullptr
 };
 
 // Hand-over of the strip chain between two ranks that own adjacent column blocks (peer memory over
@@ -52,6 +53,11 @@ struct SweepLink {
     unsigned long long *right_prod = nullptr;        // peer (right rank): its in_prod
     const unsigned long long *cons = nullptr;        // local: batches the right rank has consumed
     unsigned long long seq = 0;                      // pass number, identical on all ranks
+    // result columns that belong to the left rank (its last owned columns and its first halo column) are
+    // stored straight into its arrays; every strip that wrote some adds 1 to left_ret[field] when it is done
+    unsigned long long *left_ret = nullptr;          // peer (left rank): completion counters
+    int peer_jbase = 0;                              // global column of the left rank's local column 0
+    int peer_hi = 0;                                 // columns < peer_hi go to the left rank as well
 };
 
 struct SweepLaunch {
@@ -103,6 +109,7 @@ cudaError_t launch_maccormack_combine(float *dst, const float *src, const float 
                                       int src_plus_zero, const GridView &G, cudaStream_t st);
 cudaError_t launch_add_zero(float *x, size_t n, cudaStream_t st);
 cudaError_t launch_axpy_field(float *x, const float *y, size_t n, cudaStream_t st);
+cudaError_t launch_wait_counter(const unsigned long long *counter, unsigned long long expected, cudaStream_t st);
 
 struct SourceEntry { int cell; int field; float amount; };   // field: 0 d, 1 u, 2 v
 cudaError_t launch_apply_sources(float *d, float *u, float *v, const SourceEntry *entries, const int *seg_start,

@@ -232,6 +232,15 @@ __global__ void add_zero_kernel(float *x, size_t n)
         x[i] = __fadd_rn(x[i], 0.0f);
 }
 
+// Holds the stream until a counter in this GPU's memory, incremented by kernels of the neighbouring GPU through
+// peer memory, reaches `expected`.
+__global__ void wait_counter_kernel(const unsigned long long *counter, unsigned long long expected)
+{
+    const volatile unsigned long long *c = counter;
+    while (*c < expected) __nanosleep(200);
+    __threadfence_system();
+}
+
 __global__ void axpy_field_kernel(float *x, const float *y, size_t n)
 {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
@@ -330,6 +339,12 @@ cudaError_t launch_axpy_field(float *x, const float *y, size_t n, cudaStream_t s
     size_t blocks = (n + 255) / 256;
     if (blocks > 148 * 16) blocks = 148 * 16;
     axpy_field_kernel<<<(unsigned)blocks, 256, 0, st>>>(x, y, n);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wait_counter(const unsigned long long *counter, unsigned long long expected, cudaStream_t st)
+{
+    wait_counter_kernel<<<1, 1, 0, st>>>(counter, expected);
     return cudaGetLastError();
 }
 

@@ -575,6 +575,8 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     const int gp = j0w + lane;
     const int tau_b = first_step(j0w);
     const int tau_e = last_step(j0w);
+    // last stage of a strip whose result columns reach into the block of the rank on the left
+    const bool to_peer = (g == NSTG - 1) && (F.out_peer != nullptr) && (j0w - S < P.link.peer_hi);
 
     // ---- what this warp waits for before a group of steps starting at t: counter >= min(t + add, clamp) ----
     //   lane 0: left neighbours present      lane 1: previous stage far enough ahead
@@ -716,6 +718,14 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                     for (int it = 0; it < kWfBatch; ++it) {
                         if (row0 + it >= 1 && row0 + it <= W - 2) dst[(long long)it * pitch] = vals[it];
                     }
+                    if (to_peer && col < P.link.peer_hi) {
+                        // these columns belong to (or border) the block of the rank on the left: store them there too
+                        float *pd = F.out_peer + ((long long)row0 * pitch + (col - P.link.peer_jbase));
+#pragma unroll
+                        for (int it = 0; it < kWfBatch; ++it) {
+                            if (row0 + it >= 1 && row0 + it <= W - 2) pd[(long long)it * pitch] = vals[it];
+                        }
+                    }
                 }
             }
             // which walls the (lane, level) cells of this batch can touch
@@ -785,8 +795,17 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         const bool colok = (col >= 1) && (col <= H - 2);
         for (int q = tau_e + 1 - 48; q <= tau_e; ++q) {
             const int row = q - kToff - S - j0w;
-            if (colok && row >= 1 && row <= W - 2)
-                F.out[(size_t)row * pitch + (col - jbase)] = t_out[(q & (kTileRows - 1)) * 32 + lane];
+            if (colok && row >= 1 && row <= W - 2) {
+                const float val = t_out[(q & (kTileRows - 1)) * 32 + lane];
+                F.out[(size_t)row * pitch + (col - jbase)] = val;
+                if (to_peer && col < P.link.peer_hi) F.out_peer[(size_t)row * pitch + (col - P.link.peer_jbase)] = val;
+            }
+        }
+        if (to_peer) {
+            // all result columns this strip owes the left rank are stored: tell it
+            __threadfence_system();
+            __syncwarp();
+            if (lane == 0) atomicAdd_system(P.link.left_ret + fi, 1ull);
         }
     }
 }

@@ -139,6 +139,8 @@ class BlockFluidSim:
         self._check(self._lib.fsb_get_stream(self._h, C.byref(st)))
         self.stream = torch.cuda.ExternalStream(st.value, device=self.device)
         self.seq = 0
+        self.trace = None      # set to {} to collect GPU time per phase (CUDA events on the simulation's stream)
+        self._ev = []
         self._connect()
 
     # -- plumbing ----------------------------------------------------------------------------------
@@ -157,6 +159,16 @@ class BlockFluidSim:
         lh = (C.c_ubyte * 64)(*allh[left].cpu().tolist()) if left is not None else None
         rh = (C.c_ubyte * 64)(*allh[right].cpu().tolist()) if right is not None else None
         self._check(self._lib.fsb_link_connect(self._h, lh, rh))
+        # the rank on the right stores the result columns it owes this rank straight into these field buffers
+        fh = (C.c_ubyte * 384)()
+        self._check(self._lib.fsb_field_handles(self._h, fh))
+        t = torch.tensor(list(fh), dtype=torch.uint8, device=self.device)
+        allf = [torch.empty_like(t) for _ in range(self.world)]
+        dist.all_gather(allf, t, group=self.group)
+        if left is not None:
+            lf = (C.c_ubyte * 384)(*allf[left].cpu().tolist())
+            self._check(self._lib.fsb_link_connect_fields(self._h, lf, self.ncols))
+        self.returned = [0, 0, 0]    # strips' worth of columns the right rank has stored here so far, per sweep slot
         dist.barrier(group=self.group)
 
     def close(self):
@@ -182,6 +194,22 @@ class BlockFluidSim:
     def sync(self):
         self._check(self._lib.fsb_sync(self._h))
 
+    def _mark(self, name):
+        if self.trace is None:
+            return
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(self.stream)
+        self._ev.append((name, e))
+
+    def trace_report(self):
+        """ms per phase since the last report (synchronises)."""
+        self.sync()
+        out = {}
+        for (n0, e0), (n1, e1) in zip(self._ev, self._ev[1:]):
+            out[n1] = out.get(n1, 0.0) + e0.elapsed_time(e1)
+        self._ev = []
+        return out
+
     def _ids(self, vals):
         return (C.c_int * len(vals))(*vals)
 
@@ -194,6 +222,15 @@ class BlockFluidSim:
 
     def _return(self, fields, width):
         return_columns([self.tensor(f) for f in fields], self.halo, self.ncols, width, self.rank, self.world, self.group)
+
+    def _await_returns(self, nfields, sweeps):
+        """Hold the stream until the rank on the right has stored this rank's last `sweeps` columns (and its first
+        halo column) of every field of the launch; no host wait, no collective."""
+        if self.rank == self.world - 1:
+            return
+        for slot in range(nfields):
+            self.returned[slot] += sweeps // 32 + 1
+            self._check(self._lib.fsb_blk_wait_returns(self._h, slot, self.returned[slot]))
 
     def _trace_radius(self, dt):
         """Columns an RK4 back-trace can reach: every stage moves at most dt*width*max|velocity| cells."""
@@ -235,23 +272,32 @@ class BlockFluidSim:
         self._check(self._lib.fsb_add_velocity(self._h, x, y, ax, ay))
 
     # -- the step (same order as velocityStep / densityStep, src/fluid_sim.cpp:370-422) ---------------------
-    def _project(self):
-        self._halo([VELOCITY_X, VELOCITY_Y], 1)
+    def _project(self, fresh_halo):
+        if not fresh_halo:
+            self._halo([VELOCITY_X, VELOCITY_Y], 1)
+        self._mark("halo1")
         self._check(self._lib.fsb_blk_divergence(self._h))
+        self._mark("pointwise")
         for k, (lv, st) in enumerate(self.plan):
             self.seq += 1
             self._check(self._lib.fsb_blk_sweep(self._h, 0, 1, None, None, lv, st, 1 if k == 0 else 0, 0.0, 0.0, self.seq))
-            self._return([PREV_VEL_X], lv * st)
+            self._mark("sweep")
+            self._await_returns(1, lv * st)
+            self._mark("return")
             self._bnd([PREV_VEL_X], [0])
         if not self.plan:
             self.tensor(PREV_VEL_X).zero_()
-        self._halo([PREV_VEL_X], 1)
+            self._halo([PREV_VEL_X], 1)
+        self._mark("halo1")
         self._check(self._lib.fsb_blk_gradient(self._h))
         self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
+        self._mark("pointwise")
 
     def step(self, dt=0.01):
         with torch.cuda.stream(self.stream):
+            self._mark("start")
             self._check(self._lib.fsb_op_add_noise(self._h))
+            self._mark("pointwise")
             if self.D > 0:
                 a = np.float32(np.float32(np.float32(dt) * np.float32(self.visc)) * np.float32(self.width)) * np.float32(self.height)
                 if a == 0:
@@ -259,15 +305,25 @@ class BlockFluidSim:
                 self.seq += 1
                 self._check(self._lib.fsb_blk_sweep(self._h, 1, 2, self._ids([VELOCITY_X, VELOCITY_Y]), self._ids([1, 2]),
                                                     self.D, 1, 0, self.visc, dt, self.seq))
-                self._return([VELOCITY_X, VELOCITY_Y], self.D)
+                self._mark("sweep")
+                self._await_returns(2, self.D)
+                self._mark("return")
                 self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
-            self._project()
-            self._halo([VELOCITY_X, VELOCITY_Y], self._trace_radius(dt))
+            self._project(fresh_halo=self.D > 0)
+            r = self._trace_radius(dt)
+            self._mark("allreduce")
+            self._halo([VELOCITY_X, VELOCITY_Y], r)
+            self._mark("haloR")
             self._check(self._lib.fsb_blk_advect_velocity(self._h, dt))
             self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
-            self._project()
+            self._mark("pointwise")
+            self._project(fresh_halo=False)
             # density: diffusion 0 is the identity d + 0.0f plus the boundary update, folded into the gather
             self._bnd([DENSITY], [0], [1])
-            self._halo([DENSITY, VELOCITY_X, VELOCITY_Y], self._trace_radius(dt))
+            r = self._trace_radius(dt)
+            self._mark("allreduce")
+            self._halo([DENSITY, VELOCITY_X, VELOCITY_Y], r)
+            self._mark("haloR")
             self._check(self._lib.fsb_blk_advect_density(self._h, dt, 1))
             self._bnd([DENSITY], [0])
+            self._mark("pointwise")

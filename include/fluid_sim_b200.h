@@ -171,6 +171,9 @@ int fsb_create_block(const fsb_params *p, int col_begin, int col_end, int halo, 
 int fsb_block_info(const fsb_sim *s, int *pitch, int *jbase, int *j0, int *j1);
 int fsb_link_handle(fsb_sim *s, void *handle64);                                   /* 64-byte cudaIpcMemHandle_t */
 int fsb_link_connect(fsb_sim *s, const void *left_handle64, const void *right_handle64);   /* NULL = no neighbour */
+int fsb_field_handles(fsb_sim *s, void *handles6x64);                             /* 6 IPC handles, role order */
+int fsb_link_connect_fields(fsb_sim *s, const void *left_handles6x64, int left_ncols);
+int fsb_blk_wait_returns(fsb_sim *s, int slot, unsigned long long expected);
 int fsb_blk_sweep(fsb_sim *s, int mode, int nfields, const int *fields, const int *bs, int levels, int stages,
                   int first, float diff, float dt, unsigned long long seq);
 int fsb_blk_set_boundary(fsb_sim *s, int n, const int *fields, const int *bs, const int *plus_zero);
