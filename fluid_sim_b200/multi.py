@@ -31,7 +31,7 @@ def column_range(height, rank, world, align=64):
     return rank * hl, (rank + 1) * hl
 
 
-def plan_projection(sweeps, levels=10, max_stages=4):
+def plan_projection(sweeps, levels=10, max_stages=5):
     """Launches (levels per warp, stages) covering `sweeps` pressure sweeps; the same on every rank."""
     out, left = [], sweeps
     while left >= levels:
@@ -105,7 +105,7 @@ class BlockFluidSim:
     """This rank's column block of a width x height simulation spread over `dist.get_world_size()` GPUs."""
 
     def __init__(self, width, height, proj_iters=20, diff_iters=5, viscosity=1e-4, diffusion=0.0, omega=1.5,
-                 noise="glibc", noise_seed=1, noise_pos=0, device=0, halo=128, levels=10, strips_per_cta=2, group=None):
+                 noise="glibc", noise_seed=1, noise_pos=0, device=0, halo=128, levels=10, strips_per_cta=1, group=None):
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.group = group
         self.width, self.height = width, height

@@ -27,9 +27,9 @@ def test_projection_plan_covers_all_sweeps():
     for p in (0, 1, 7, 20, 40, 100, 133):
         plan = plan_projection(p)
         assert sum(lv * st for lv, st in plan) == p
-        assert all(lv in (1, 2, 5, 10) and 1 <= st <= 4 for lv, st in plan)
+        assert all(lv in (1, 2, 5, 10) and 1 <= st <= 5 for lv, st in plan)
     assert plan_projection(40) == [(10, 4)]
-    assert plan_projection(100) == [(10, 4), (10, 4), (10, 2)]
+    assert plan_projection(100) == [(10, 5), (10, 5)]
 
 
 def _free_port():
