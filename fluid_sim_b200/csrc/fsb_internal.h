@@ -43,11 +43,12 @@ struct SweepField {
 // NVLink).  All pointers are device addresses valid on THIS rank; "peer" ones map the neighbour's memory.
 // Layout per field f and stage g: rings[(f * kLinkStages + g) * kLinkRingFloats], flags[(f * kLinkStages + g)].
 constexpr int kLinkStages = 16;
-constexpr int kLinkRingFloats = kWfSlots * kWfBatch * 44;   // 44 = floats per lane-step at 20 sweeps per warp
+// 44 = floats per lane-step at 20 sweeps per warp; x2: every float travels with a 4-byte tag (flag-in-data)
+constexpr int kLinkRingFloats = kWfSlots * kWfBatch * 44 * 2;
 struct SweepLink {
     bool has_left = false, has_right = false;
-    const float *in_rings = nullptr;                 // local: written by the left rank
-    const unsigned long long *in_prod = nullptr;     // local: batches the left rank has published
+    const float *in_rings = nullptr;                 // local: written by the left rank (tagged 16-byte words)
+    const unsigned long long *in_prod = nullptr;     // unused since the rings carry their own tags
     unsigned long long *left_cons = nullptr;         // peer (left rank): batches this rank has consumed
     float *right_rings = nullptr;                    // peer (right rank): its in_rings
     unsigned long long *right_prod = nullptr;        // peer (right rank): its in_prod

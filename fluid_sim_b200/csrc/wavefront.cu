@@ -130,6 +130,27 @@ __device__ __forceinline__ void st_release_sys_u64(unsigned long long *p, unsign
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// Rank-to-rank rings carry the flag inside the data: every 16-byte store holds two floats and two copies of
+// a tag unique to (pass, batch), and the reader retries until all tags of a batch match.  A 16-byte access is
+// performed as a unit (8-byte halves at worst, each with its own tag), so neither side needs a fence and the
+// writer never waits for NVLink acknowledgements.
+__device__ __forceinline__ void st_volatile_v4(uint4 *p, uint4 v)
+{
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+__device__ __forceinline__ uint4 ld_volatile_v4(const uint4 *p)
+{
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void st_volatile_u64(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 __device__ __forceinline__ int ld_acquire_cta_s32(const int *p)
 {
     int v;
@@ -427,6 +448,9 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         unsigned long long *fl = P.flags + ((size_t)fi * kMaxStages + (gi < kMaxStages ? gi : 0)) * kWfMaxCtas * 2;
         const int lk = fi * kLinkStages + (gi < kLinkStages ? gi : 0);   // slot of (field, stage) in the rank links
         const bool via_link = is_exp ? link_r : link_l;
+        const float *ll_in = P.link.in_rings;
+        const unsigned ll_seq = (unsigned)(P.link_seq_base >> 32) << 20;
+        auto ll_tag = [ll_seq](int batch) { return ll_seq + (unsigned)(batch + kBatchBias + 1); };
         const unsigned long long flag_base = via_link ? P.link_seq_base : P.seq_base;
         const volatile unsigned long long *poll_flag =
             is_exp ? (link_r ? P.link.cons + lk : fl + (size_t)cl * 2 + 1)
@@ -442,8 +466,15 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                     ready = ld_acquire_cta_s32(poll_prog) >= min(16 * n + 15 + 32, fl_tau_e);
                 } else if (!is_exp) {
                     // batch n replaces batch n - kEdgeDepth/16 in edge_in, whose last slot is read one and two steps later
-                    ready = ld_acquire_cta_s32(poll_prog) >= 16 * (n - kEdgeDepth / kWfBatch + 1) + 1 &&
-                            *poll_flag >= flag_base + (unsigned long long)(n + kBatchBias + 1);
+                    ready = ld_acquire_cta_s32(poll_prog) >= 16 * (n - kEdgeDepth / kWfBatch + 1) + 1;
+                    if (ready) {
+                        if (link_l)   // hint only: the tag of the batch's last store (the copy below checks all of them)
+                            ready = *reinterpret_cast<const volatile unsigned *>(
+                                        ll_in + (size_t)lk * kLinkRingFloats + 2 * (size_t)(n & (kWfSlots - 1)) * kWfBatch * L::EXW +
+                                        2 * kWfBatch * L::EXW - 1) == ll_tag(n);
+                        else
+                            ready = *poll_flag >= flag_base + (unsigned long long)(n + kBatchBias + 1);
+                    }
                 } else {
                     ready = ld_acquire_cta_s32(poll_prog) >= 16 * n + 15 &&
                             (n - kWfSlots < n_first_right ||
@@ -455,27 +486,57 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 __nanosleep(32);
                 continue;
             }
-            if (m & 0xffffu) {   // acquire side of the global flags just observed
-                if (via_link) __threadfence_system();
-                else __threadfence();
-            }
+            if ((m & 0xffffu) && !via_link) __threadfence();   // acquire side of the global flags just observed
             for (unsigned mm = m & 0xffffu; mm; mm &= mm - 1) {
                 const int src = __ffs(mm) - 1;
                 const int bn = __shfl_sync(0xffffffffu, n, src);
                 float *xg = P.xchg + ((size_t)fi * NSTG + src) * P.ncta * L::kBoundaryFloats;
                 const size_t slot_off = (size_t)(bn & (kWfSlots - 1)) * kWfBatch * L::EXW;
                 const size_t lk_off = (size_t)(fi * kLinkStages + src) * kLinkRingFloats;
-                if (!is_exp) {
-                    const float4 *gsrc = reinterpret_cast<const float4 *>(
-                        link_l ? P.link.in_rings + lk_off + slot_off
-                               : xg + (size_t)(cl - 1) * L::kBoundaryFloats + slot_off);
+                constexpr int kPairs = kWfBatch * L::EXW / 2;           // float pairs per batch
+                constexpr int kPairsPerLane = (kPairs + 31) / 32;
+                if (!is_exp && link_l) {
+                    const uint4 *gsrc = reinterpret_cast<const uint4 *>(ll_in + lk_off + 2 * slot_off);
+                    float2 *sdst = reinterpret_cast<float2 *>(edge_in + src * kEdgeDepth * L::EXW +
+                                                              ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
+                    const unsigned tag = ll_tag(bn);
+                    uint4 v[kPairsPerLane];
+                    bool ok = true;
+#pragma unroll
+                    for (int k = 0; k < kPairsPerLane; ++k) {
+                        const int i = lane + 32 * k;
+                        if (i < kPairs) {
+                            v[k] = ld_volatile_v4(gsrc + i);
+                            ok = ok && v[k].y == tag && v[k].w == tag;
+                        }
+                    }
+                    if (__all_sync(0xffffffffu, ok)) {
+#pragma unroll
+                        for (int k = 0; k < kPairsPerLane; ++k) {
+                            const int i = lane + 32 * k;
+                            if (i < kPairs) sdst[i] = make_float2(__uint_as_float(v[k].x), __uint_as_float(v[k].z));
+                        }
+                    } else if (lane == src) {
+                        ready = false;    // part of the batch is still in flight: try again next round
+                    }
+                } else if (!is_exp) {
+                    const float4 *gsrc = reinterpret_cast<const float4 *>(xg + (size_t)(cl - 1) * L::kBoundaryFloats + slot_off);
                     float4 *sdst = reinterpret_cast<float4 *>(edge_in + src * kEdgeDepth * L::EXW +
                                                               ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
 #pragma unroll 2
                     for (int i = lane; i < kWfBatch * L::EXW / 4; i += 32) sdst[i] = __ldcg(gsrc + i);
+                } else if (link_r) {
+                    uint4 *gdst = reinterpret_cast<uint4 *>(P.link.right_rings + lk_off + 2 * slot_off);
+                    const float2 *ssrc = reinterpret_cast<const float2 *>(edge_out + src * kEdgeDepth * L::EXW +
+                                                                          ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
+                    const unsigned tag = ll_tag(bn);
+#pragma unroll 2
+                    for (int i = lane; i < kPairs; i += 32) {
+                        const float2 d = ssrc[i];
+                        st_volatile_v4(gdst + i, make_uint4(__float_as_uint(d.x), tag, __float_as_uint(d.y), tag));
+                    }
                 } else {
-                    float4 *gdst = reinterpret_cast<float4 *>(
-                        link_r ? P.link.right_rings + lk_off + slot_off : xg + (size_t)cl * L::kBoundaryFloats + slot_off);
+                    float4 *gdst = reinterpret_cast<float4 *>(xg + (size_t)cl * L::kBoundaryFloats + slot_off);
                     const float4 *ssrc = reinterpret_cast<const float4 *>(edge_out + src * kEdgeDepth * L::EXW +
                                                                           ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
 #pragma unroll 2
@@ -501,21 +562,18 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                         if (row0 + it >= 1 && row0 + it <= W - 2) dst[(long long)it * pitch] = vals[it];
                 }
             }
-            if (is_exp && (m & 0xffffu)) {
-                if (link_r) __threadfence_system();
-                else __threadfence();
-            }
+            if (is_exp && (m & 0xffffu) && !link_r) __threadfence();
             __syncwarp();
             if (ready) {
                 if (is_flush) {
                     st_release_cta_s32(flushed_steps + gi, 16 * n + 15);
                 } else if (!is_exp) {
                     st_release_cta_s32(imp_steps + gi, 16 * n + 15);
-                    if (link_l) st_release_sys_u64(P.link.left_cons + lk, flag_base + (unsigned long long)(n + kBatchBias + 1));
+                    // the batch has been read (its tags were checked), so the credit needs no ordering
+                    if (link_l) st_volatile_u64(P.link.left_cons + lk, flag_base + (unsigned long long)(n + kBatchBias + 1));
                     else st_release_u64(fl + (size_t)(cl - 1) * 2 + 1, flag_base + (unsigned long long)(n + kBatchBias + 1));
                 } else {
-                    if (link_r) st_release_sys_u64(P.link.right_prod + lk, flag_base + (unsigned long long)(n + kBatchBias + 1));
-                    else st_release_u64(fl + (size_t)cl * 2, flag_base + (unsigned long long)(n + kBatchBias + 1));
+                    if (!link_r) st_release_u64(fl + (size_t)cl * 2, flag_base + (unsigned long long)(n + kBatchBias + 1));
                     st_release_cta_s32(exp_steps + gi, 16 * n + 15);
                 }
                 n += 1;

@@ -56,22 +56,22 @@ def exchange_halo(tensors, halo, ncols, width, rank, world, group=None):
     if world == 1 or width == 0:
         return
     left, right = _neighbours(rank, world)
-    ops, recvs = [], []
-    for t in tensors:
-        if left is not None:
-            send = t[:, halo:halo + width].contiguous()
+    # Two separate send/recv groups, the left neighbour's first: the pair (r, r+1) is then r's second group and
+    # r+1's first, so a rank waits only for the neighbour it really depends on.  One group holding both neighbours
+    # would chain every rank to the slowest one (the sweep chain leaves the ranks staggered in time).
+    for peer, send0, recv0 in ((left, halo, halo - width), (right, halo + ncols - width, halo + ncols)):
+        if peer is None:
+            continue
+        ops, recvs = [], []
+        for t in tensors:
+            send = t[:, send0:send0 + width].contiguous()
             buf = torch.empty_like(send)
-            ops += [dist.P2POp(dist.isend, send, left, group), dist.P2POp(dist.irecv, buf, left, group)]
-            recvs.append((t, halo - width, buf))
-        if right is not None:
-            send = t[:, halo + ncols - width:halo + ncols].contiguous()
-            buf = torch.empty_like(send)
-            ops += [dist.P2POp(dist.isend, send, right, group), dist.P2POp(dist.irecv, buf, right, group)]
-            recvs.append((t, halo + ncols, buf))
-    for w in dist.batch_isend_irecv(ops):
-        w.wait()
-    for t, c0, buf in recvs:
-        t[:, c0:c0 + width] = buf
+            ops += [dist.P2POp(dist.isend, send, peer, group), dist.P2POp(dist.irecv, buf, peer, group)]
+            recvs.append((t, buf))
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+        for t, buf in recvs:
+            t[:, recv0:recv0 + width] = buf
 
 
 def return_columns(tensors, halo, ncols, width, rank, world, group=None):
@@ -105,7 +105,7 @@ class BlockFluidSim:
     """This rank's column block of a width x height simulation spread over `dist.get_world_size()` GPUs."""
 
     def __init__(self, width, height, proj_iters=20, diff_iters=5, viscosity=1e-4, diffusion=0.0, omega=1.5,
-                 noise="glibc", noise_seed=1, noise_pos=0, device=0, halo=128, levels=10, strips_per_cta=1, group=None):
+                 noise="glibc", noise_seed=1, noise_pos=0, device=0, halo=128, levels=10, strips_per_cta=1, reach=None, group=None):
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.group = group
         self.width, self.height = width, height
@@ -139,6 +139,12 @@ class BlockFluidSim:
         self._check(self._lib.fsb_get_stream(self._h, C.byref(st)))
         self.stream = torch.cuda.ExternalStream(st.value, device=self.device)
         self.seq = 0
+        # columns exchanged before every advection: a neighbour can only supply columns it owns
+        narrowest = min(b - a for a, b in (column_range(height, r, self.world, 32 * strips_per_cta) for r in range(self.world)))
+        self.reach = min(halo, narrowest) if reach is None else reach
+        if not 3 <= self.reach <= min(halo, narrowest):
+            raise FsbError("BlockFluidSim: reach must be between 3 and min(halo, narrowest column block)")
+        self._overshoot = torch.zeros((), dtype=torch.float32, device=self.device)
         self.trace = None      # set to {} to collect GPU time per phase (CUDA events on the simulation's stream)
         self._ev = []
         self._connect()
@@ -193,6 +199,10 @@ class BlockFluidSim:
 
     def sync(self):
         self._check(self._lib.fsb_sync(self._h))
+        over = float(self._overshoot.item())
+        if over > 0:
+            raise FsbError(f"BlockFluidSim: an advection reached {int(over)} columns past the {self.reach} exchanged; "
+                           "results since the last sync() are invalid (raise `reach`/`halo` or lower dt)")
 
     def _mark(self, name):
         if self.trace is None:
@@ -200,6 +210,11 @@ class BlockFluidSim:
         e = torch.cuda.Event(enable_timing=True)
         e.record(self.stream)
         self._ev.append((name, e))
+
+    def trace_timeline(self):
+        """[(phase, ms since the first mark)] since the last report (synchronises); leaves the marks in place."""
+        self.sync()
+        return [(n, self._ev[0][1].elapsed_time(e)) for n, e in self._ev]
 
     def trace_report(self):
         """ms per phase since the last report (synchronises)."""
@@ -232,15 +247,17 @@ class BlockFluidSim:
             self.returned[slot] += sweeps // 32 + 1
             self._check(self._lib.fsb_blk_wait_returns(self._h, slot, self.returned[slot]))
 
-    def _trace_radius(self, dt):
-        """Columns an RK4 back-trace can reach: every stage moves at most dt*width*max|velocity| cells."""
-        u, v = self.owned(VELOCITY_X), self.owned(VELOCITY_Y)
-        m = torch.maximum(u.abs().max(), v.abs().max()).reshape(1)
-        dist.all_reduce(m, op=dist.ReduceOp.MAX, group=self.group)
-        r = int(math.ceil(float(m.item()) * dt * self.width)) + 2
-        if r > self.halo:
-            raise FsbError(f"BlockFluidSim: advection reaches {r} columns, halo is {self.halo}")
-        return r
+    def _check_reach(self, dt, width):
+        """Columns an RK4 back-trace can reach: every stage moves at most dt*width*max|velocity| cells.  The halo
+        exchange before an advection always moves `width` columns; this records, on the device and without a host
+        wait or a collective, by how much the velocities now in [owned - width, owned + width) overshoot that.
+        The positions a trace samples stay inside that window whenever the bound computed from the window's own
+        maximum fits, so the local test is sufficient.  `sync()` raises if any step overshot."""
+        lo, hi = self.halo - width, self.halo + self.ncols + width
+        u, v = self.tensor(VELOCITY_X)[:, lo:hi], self.tensor(VELOCITY_Y)[:, lo:hi]
+        m = torch.maximum(u.abs().max(), v.abs().max())
+        need = torch.ceil(m * (dt * self.width)) + 2.0
+        self._overshoot = torch.maximum(self._overshoot, need - float(width))
 
     # -- inputs / outputs -----------------------------------------------------------------------------
     def set_from_global(self, field, full):
@@ -310,9 +327,8 @@ class BlockFluidSim:
                 self._mark("return")
                 self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
             self._project(fresh_halo=self.D > 0)
-            r = self._trace_radius(dt)
-            self._mark("allreduce")
-            self._halo([VELOCITY_X, VELOCITY_Y], r)
+            self._halo([VELOCITY_X, VELOCITY_Y], self.reach)
+            self._check_reach(dt, self.reach)
             self._mark("haloR")
             self._check(self._lib.fsb_blk_advect_velocity(self._h, dt))
             self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
@@ -320,9 +336,8 @@ class BlockFluidSim:
             self._project(fresh_halo=False)
             # density: diffusion 0 is the identity d + 0.0f plus the boundary update, folded into the gather
             self._bnd([DENSITY], [0], [1])
-            r = self._trace_radius(dt)
-            self._mark("allreduce")
-            self._halo([DENSITY, VELOCITY_X, VELOCITY_Y], r)
+            self._halo([DENSITY, VELOCITY_X, VELOCITY_Y], self.reach)
+            self._check_reach(dt, self.reach)
             self._mark("haloR")
             self._check(self._lib.fsb_blk_advect_density(self._h, dt, 1))
             self._bnd([DENSITY], [0])

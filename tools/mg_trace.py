@@ -9,7 +9,7 @@ rank = int(os.environ["RANK"]); local = int(os.environ["LOCAL_RANK"]); world = i
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 W, P = 32768, 100
-H = 4096 * world
+H = int(os.environ.get("MG_COLS", "4096")) * world
 sim = BlockFluidSim(W, H, P, 5, device=local)
 d, u, v = vortex_lattice_block(W, H, sim.jbase, sim.jbase + sim.pitch)
 for fid, arr in ((fsb.DENSITY, d), (fsb.VELOCITY_X, u), (fsb.VELOCITY_Y, v)):
@@ -19,6 +19,20 @@ sim.trace = {}
 steps = 2
 for _ in range(steps):
     sim.step(0.01)
+if os.environ.get("MG_TIMELINE"):
+    # one more step, started from a barrier, as a timeline (device clocks differ; the barrier aligns them to ~10 us)
+    sim.sync(); sim._ev = []
+    with torch.cuda.stream(sim.stream):
+        dist.barrier()
+    sim.step(0.01)
+    tl = sim.trace_timeline()
+    for r in range(world):
+        dist.barrier()
+        if r == rank:
+            print(f"timeline rank {rank}: " + " ".join(f"{n}@{t:.1f}" for n, t in tl), flush=True)
+    sim._ev = []
+    for _ in range(steps):
+        sim.step(0.01)
 rep = sim.trace_report()
 tot = sum(rep.values())
 for r in range(world):
