@@ -1060,6 +1060,8 @@ int fsb_blk_sweep(fsb_sim *s, int mode, int nfields, const int *fields, const in
     L.levels = levels;
     L.stages = stages;
     L.strips_per_cta = s->tune_strips > 0 ? s->tune_strips : 2;
+    // diffusion runs one stage per strip: four strips per CTA where every rank's block allows it (same choice on all ranks)
+    if (mode == 1 && stages == 1 && s->strip_begin % 4 == 0 && (s->G.j1 - s->G.j0) % 128 == 0) L.strips_per_cta = 4;
     L.pitch = s->G.pitch;
     L.jbase = s->G.jbase;
     L.strip_begin = s->strip_begin;

@@ -34,6 +34,7 @@
 //
 // All arithmetic uses explicit round-to-nearest intrinsics: no FMA contraction (F7).
 #include "fsb_internal.h"
+#include <cstdlib>
 
 #include <cstdio>
 
@@ -52,6 +53,15 @@ constexpr int kTileFloats = kTileRows * 32;
 #endif
 #ifndef WF_GROUP
 #define WF_GROUP 4
+#endif
+#ifndef WF_BACKOFF
+#define WF_BACKOFF 0        // > 0: failed polls of a wait before the warp starts sleeping between polls
+#endif
+#ifndef WF_TOP_PATH
+#define WF_TOP_PATH 1       // dedicated step body for batches that touch only the top wall row
+#endif
+#ifndef WF_CLUSTER_MODE
+#define WF_CLUSTER_MODE 0   // 0: no cluster code, 1: cluster barriers only, 2: hand-over through distributed shared memory
 #endif
 constexpr int kGroup = WF_GROUP;  // steps a warp runs between two progress checks (4, 8 or 16)
 constexpr int kEdgeDepth = 64;   // steps held by the CTA-edge rings (four batches)
@@ -74,8 +84,10 @@ struct WfLayout {
     static constexpr int kHandRows = (2 * S + 2 * kGroup + 2 <= 16) ? 16 : ((2 * S + 2 * kGroup + 2 <= 32) ? 32 : 64);
     static constexpr int kHandFloats = kHandRows * 32;
     static constexpr int kMaxStagesS = (S <= 2) ? 16 : 8;
-    static constexpr int kMaxThreads = (kMaxStagesS + 2) * 32;   // compute warps + the two comm warps
-    static constexpr int kMinBlocks = (S == 5) ? 2 : 1;
+    // compute warps per CTA: bounded by the register file (S >= 10 needs ~168 registers per thread)
+    static constexpr int kMaxComputeWarps = (S <= 5) ? 16 : 8;
+    static constexpr int kMaxThreads = (kMaxComputeWarps + 2) * 32;   // + the two comm warps
+    static constexpr int kMinBlocks = 1;
 };
 
 struct WfKernelParams {
@@ -151,6 +163,54 @@ __device__ __forceinline__ void st_volatile_u64(unsigned long long *p, unsigned 
     asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// ---- thread-block cluster helpers: neighbouring CTAs of a cluster hand the strip chain over through
+// distributed shared memory instead of global rings ----
+__device__ __forceinline__ unsigned cluster_ctarank()
+{
+    unsigned r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+
+__device__ __forceinline__ unsigned cluster_nctarank()
+{
+    unsigned r;
+    asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+    return r;
+}
+
+__device__ __forceinline__ void cluster_barrier()
+{
+#if WF_CLUSTER_MODE >= 1
+    asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;" ::: "memory");
+#endif
+}
+
+// shared::cluster address of `p` (a pointer into this CTA's shared memory) in CTA `rank` of the cluster
+__device__ __forceinline__ unsigned cluster_map(const void *p, unsigned rank)
+{
+    unsigned a = (unsigned)__cvta_generic_to_shared(p), r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(rank));
+    return r;
+}
+
+__device__ __forceinline__ void st_cluster_f32x4(unsigned addr, float4 v)
+{
+    asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__device__ __forceinline__ void st_release_cluster_s32(unsigned addr, int v)
+{
+    asm volatile("st.release.cluster.shared::cluster.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+__device__ __forceinline__ int ld_acquire_cluster_s32(const int *p)
+{
+    int v;
+    asm volatile("ld.acquire.cluster.shared::cta.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+    return v;
+}
+
 __device__ __forceinline__ int ld_acquire_cta_s32(const int *p)
 {
     int v;
@@ -199,7 +259,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // FIX: kStepFast no wall in reach; kStepLeft / kStepRight the strip contains the j == 0 / j == H-1 wall and all
 // rows are interior (the common case for the first and last strips: one compare + select per level);
 // kStepFull anything (first / last rows of the grid, tiny grids).
-enum { kStepFast = 0, kStepLeft = 1, kStepRight = 2, kStepFull = 3 };
+enum { kStepFast = 0, kStepLeft = 1, kStepRight = 2, kStepFull = 3, kStepTop = 4 };
 
 __device__ __forceinline__ float bit_select(float keep, float take, unsigned mask)
 {
@@ -302,6 +362,16 @@ __device__ __forceinline__ void wf_step(float (&x)[S + 1], float (&U)[S + 1], co
             const float wv = (MODE == kGaussSeidel) ? U[k] : __fmul_rn(cx.sj, U[k]);
             acc[k] = bit_select(acc[k], wv, wmask[k]);
         }
+    } else if (FIX == kStepTop) {
+        // only the top wall row is in reach (the start of every strip, which the hand-over chain runs through):
+        // the wall cell of level k carries +-(row 1, sweep k-1)
+        const int ib = t - kToff - gp;   // row of level 0
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wr = (MODE == kGaussSeidel) ? U[k - 1] : __fmul_rn(cx.si, U[k - 1]);
+            const float wv = (k == 1 && cx.first) ? cold1 : wr;
+            acc[k] = (ib == k) ? wv : acc[k];
+        }
     } else if (FIX == kStepFull) {
         if (fix & kFixLeft) {
 #pragma unroll
@@ -385,6 +455,16 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     const bool link_r = (cl == P.ncta - 1) && P.link.has_right;   // right edge goes to another rank
     const bool has_left = (cl > 0) || link_l;
     const bool has_right = (cl + 1 < P.ncta) || link_r;
+    // CTAs of one cluster are consecutive in the chain: inside a cluster the right edge of a CTA goes straight
+    // into the next CTA's edge_in ring (distributed shared memory), without the comm warps and global rings
+#if WF_CLUSTER_MODE >= 2
+    const unsigned crank = cluster_ctarank(), csize = cluster_nctarank();
+    const bool dsm_l = (crank > 0) && (cl > 0) && (cl < P.ncta);
+    const bool dsm_r = (crank + 1 < csize) && (cl + 1 < P.ncta);
+#else
+    const unsigned crank = 0;
+    const bool dsm_l = false, dsm_r = false;
+#endif
     const int j0_first = 32 * NSTR * c;
 
     // ---- shared memory carve-up -------------------------------------------------------------
@@ -416,6 +496,11 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     }
     if (tid < NSTR) flushed_steps[tid] = first_step(warp_j0w(tid, NSTG - 1)) - 48 - 1;
     __syncthreads();
+    cluster_barrier();     // every CTA of the cluster has initialised its rings and counters
+    if (cl >= P.ncta) {    // padding CTA (the grid is a whole number of clusters)
+        cluster_barrier();
+        return;
+    }
 
     // =============================== comm warps ==================================================
     // Warp NW moves the left neighbours in (global ring written by the CTA on the left -> edge_in), warp
@@ -428,7 +513,8 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         // write-back machine per strip of the CTA (rows the last stage has finished, staged in its tile)
         const bool is_flush = WF_FLUSH_OFFLOAD && is_exp && lane >= 16;
         const int gi = lane & 15;
-        const bool valid = is_flush ? (gi < NSTR) : ((lane < 16) && (gi < NSTG) && (is_exp ? has_right : has_left));
+        const bool valid = is_flush ? (gi < NSTR)
+                                    : ((lane < 16) && (gi < NSTG) && (is_exp ? (has_right && !dsm_r) : (has_left && !dsm_l)));
         int n = 0, n_end = -1, n_first_right = 0, fl_tau_e = 0;
         if (valid) {
             if (is_flush) {
@@ -580,6 +666,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 done = n > n_end;
             }
         }
+        cluster_barrier();   // nobody leaves while a neighbour may still write into this CTA's shared memory
         return;
     }
 
@@ -640,6 +727,14 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     //   lane 0: left neighbours present      lane 1: previous stage far enough ahead
     //   lane 2: right strip / export freed the slots we overwrite      lane 3: next stage freed its ring slots
     //   lane 4: (last stage) the result tile slots we overwrite have been written back
+    // hand-over inside a cluster: this warp pushes its right-edge rows into the next CTA's edge_in ring and
+    // publishes its progress there (push_r); the first strip tells the previous CTA how far it has read (cred_l)
+    const bool push_r = dsm_r && (sidx == NSTR - 1);
+    const bool cred_l = dsm_l && (sidx == 0);
+    const unsigned r_edge = push_r ? cluster_map(edge_in + g * kEdgeDepth * L::EXW, crank + 1) : 0u;
+    const unsigned r_imp = push_r ? cluster_map(imp_steps + g, crank + 1) : 0u;
+    const unsigned l_exp = cred_l ? cluster_map(exp_steps + g, crank - 1) : 0u;
+    const bool cluster_waits = push_r || cred_l;   // some counter this warp polls is written by another CTA of the cluster
     const int *wait_ptr = nullptr;
     int wait_add = 0, wait_clamp = 0x7fffffff;
     if (lane == 0) {
@@ -664,6 +759,9 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         } else if (has_right) {
             wait_ptr = exp_steps + g;
             wait_add = kGroup - 1 - kEdgeDepth;
+            if (dsm_r) {   // exp_steps[g] is the progress of the reader in the next CTA; its ring has kEdgeDepth rows
+                wait_add = kGroup - 1 - (kEdgeDepth - 2);
+            }
         }
     } else if (lane == 3) {
         if (g < NSTG - 1) wait_ptr = prog + (w + 1);
@@ -699,6 +797,8 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     int pf_groups = 0;
     long long pf_spins = 0;
     long long pf_mine = 0;   // spins in which this lane's own condition was the unmet one
+    long long pf_top = 0, pf_early = 0;
+    int pf_top_n = 0;
 #endif
 #pragma unroll 1
     for (int t = tau_b; t <= tau_e; t += kGroup) {
@@ -708,6 +808,9 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         // ---- wait for producers / consumers ------------------------------------------------------
         {
             const int need = min(t + wait_add, wait_clamp);
+#if WF_BACKOFF
+            int misses = 0;
+#endif
             for (;;) {
                 bool ok = true;
                 if (wait_ptr) ok = ld_acquire_cta_s32(wait_ptr) >= need;
@@ -718,7 +821,13 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
 #ifdef WF_PROFILE
                 pf_spins++;
 #endif
+#if WF_BACKOFF
+                // a warp that keeps missing is far from its turn (pipeline fill): stop competing for issue slots
+                if (++misses > WF_BACKOFF) __nanosleep(64);
+#endif
             }
+            // counters written by another CTA of the cluster were polled with plain loads: order the data after them
+            if (cluster_waits) asm volatile("fence.acq_rel.cluster;" ::: "memory");
         }
 #ifdef WF_PROFILE
         const long long pf1 = clock64();
@@ -819,6 +928,14 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 wf_step<S, MODE, kStepRight>(x, Ua, Ub, t + u2, lane, gp, fix, wmask, cx);
                 wf_step<S, MODE, kStepRight>(x, Ub, Ua, t + u2 + 1, lane, gp, fix, wmask, cx);
             }
+#if WF_TOP_PATH
+        } else if (fix == kFixTop) {
+#pragma unroll 1
+            for (int u2 = 0; u2 < kGroup; u2 += 2) {
+                wf_step<S, MODE, kStepTop>(x, Ua, Ub, t + u2, lane, gp, fix, wmask, cx);
+                wf_step<S, MODE, kStepTop>(x, Ub, Ua, t + u2 + 1, lane, gp, fix, wmask, cx);
+            }
+#endif
         } else {
 #pragma unroll 1
             for (int u2 = 0; u2 < kGroup; u2 += 2) {
@@ -827,8 +944,20 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
             }
         }
         if (lane == 0) st_release_cta_s32(prog + w, t + kGroup - 1);
+        if (push_r) {
+            // rows t .. t+kGroup-1 of the local right-edge ring -> the same rows of the next CTA's edge_in
+            const int row_off = (t & (kEdgeDepth - 1)) * L::EXW;
+            const float4 *src = reinterpret_cast<const float4 *>(cx.exp + row_off);
+#pragma unroll
+            for (int i = lane; i < kGroup * L::EXW / 4; i += 32) st_cluster_f32x4(r_edge + 4u * (unsigned)row_off + 16u * (unsigned)i, src[i]);
+            __syncwarp();
+            if (lane == 0) st_release_cluster_s32(r_imp, t + kGroup - 1);
+        }
+        if (cred_l && lane == 0) st_release_cluster_s32(l_exp, t + kGroup - 1);
 #ifdef WF_PROFILE
         pf_step += clock64() - pf2;
+        if (fix & kFixTop) { pf_top += clock64() - pf0; pf_top_n++; }
+        if (pf_groups >= 1 && pf_groups <= 9) pf_early += clock64() - pf0;
         pf_groups++;
 #endif
     }
@@ -844,6 +973,9 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         printf("cta %d warp %d (strip %d stage %d): groups %d  first-wait %lld  per group: wait %lld batch %lld steps %lld  spins/group %.1f\n",
                c, w, sidx, g, pf_groups, pf_first, pf_wait / pf_groups, pf_batch / pf_groups, pf_step / pf_groups,
                (double)pf_spins / pf_groups);
+    if (lane == 0 && fi == 0 && (c == P.ncta / 2 || c == 0))
+        printf("cta %d warp %d: top-wall groups %d, %lld cycles each; groups 1..9 after the first wait: %lld cycles each\n", c, w,
+               pf_top_n, pf_top / max(pf_top_n, 1), pf_early / 9);
 #endif
     cp_async_wait_all();
     if (!WF_FLUSH_OFFLOAD && g == NSTG - 1) {
@@ -866,6 +998,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
             if (lane == 0) atomicAdd_system(P.link.left_ret + fi, 1ull);
         }
     }
+    cluster_barrier();
 }
 
 template <int S>
@@ -877,7 +1010,7 @@ size_t wf_smem_bytes(int nstr, int nstg)
                             (size_t)nstr * (nstg - 1) * 2 * L::kHandFloats + (size_t)nstr * nstg * L::kStateFloats);
 }
 
-struct WfConfig { int nstr, ncta, c_base; size_t smem; };
+struct WfConfig { int nstr, ncta, c_base; size_t smem; int cluster; };
 
 // Chooses strips per CTA so that every CTA of the launch is co-resident (cooperative launch).
 template <int S, int MODE, bool HAS_X0>
@@ -898,8 +1031,12 @@ cudaError_t wf_configure(const SweepLaunch &Lc, WfConfig &cfg)
     if (e != cudaSuccess) return e;
     if (nstg < 1 || nstg > L::kMaxStagesS) return cudaErrorInvalidValue;
     const int max_compute_warps = L::kMaxThreads / 32 - 2;
-    int nstr = Lc.strips_per_cta > 0 ? Lc.strips_per_cta : 1;
+    // default: as many strips per CTA as fit (up to 4) -- a hand-over inside a CTA costs one group of steps, one
+    // through the global rings about five, and the chain of hand-overs along the top row is what a launch waits for
+    int nstr = Lc.strips_per_cta > 0 ? Lc.strips_per_cta : 4;
     while (nstr > 1 && nstr * nstg > max_compute_warps) nstr >>= 1;
+    if (Lc.strips_per_cta <= 0)
+        while (nstr > 1 && (wf_smem_bytes<S>(nstr, nstg) > 227 * 1024 || nstr > NS || s_begin % nstr != 0)) nstr >>= 1;
     if (nstr > NS) nstr = NS;
     const bool multi_rank = Lc.link.has_left || Lc.link.has_right || s_begin > 0;
     for (;;) {
@@ -917,7 +1054,41 @@ cudaError_t wf_configure(const SweepLaunch &Lc, WfConfig &cfg)
             if (e != cudaSuccess) return e;
             fits = (long long)cfg.ncta * Lc.nfields <= (long long)per_sm * nsm;
         }
-        if (fits) return cudaSuccess;
+        if (fits) {
+            // Largest cluster size (CTAs that hand over through distributed shared memory) for which the whole
+            // grid, padded to full clusters, is still co-resident.  FSB_CLUSTER caps it (1 = no clusters).
+            static const int cap = [] {
+                const char *e = std::getenv("FSB_CLUSTER");
+                const int v = e ? std::atoi(e) : 8;
+                return (WF_CLUSTER_MODE < 2 || v < 1) ? 1 : (v > 8 ? 8 : v);
+            }();
+            cfg.cluster = 1;
+            for (int cs = 8; cs >= 2; cs >>= 1) {
+                if (cs > cap || cfg.ncta < 2) continue;
+                const int gx = (cfg.ncta + cs - 1) / cs * cs;
+                cudaLaunchConfig_t lc{};
+                lc.gridDim = dim3(gx, Lc.nfields);
+                lc.blockDim = dim3((nstr * nstg + 2) * 32);
+                lc.dynamicSmemBytes = cfg.smem;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = cs;
+                at[0].val.clusterDim.y = 1;
+                at[0].val.clusterDim.z = 1;
+                lc.attrs = at;
+                lc.numAttrs = 1;
+                int nclusters = 0;
+                if (cudaOccupancyMaxActiveClusters(&nclusters, kern, &lc) != cudaSuccess) {
+                    (void)cudaGetLastError();
+                    continue;
+                }
+                if ((long long)nclusters >= (long long)(gx / cs) * Lc.nfields) {
+                    cfg.cluster = cs;
+                    break;
+                }
+            }
+            return cudaSuccess;
+        }
         // every rank of a multi-rank chain must use the same strips-per-CTA: no silent adjustment there
         if (multi_rank || (nstr * 2) * nstg > max_compute_warps || wf_smem_bytes<S>(nstr * 2, nstg) > 227 * 1024 || nstr >= NS)
             return cudaErrorCooperativeLaunchTooLarge;
@@ -968,8 +1139,22 @@ cudaError_t wf_launch_inst(const SweepLaunch &Lc, SweepScratch &scr, cudaStream_
     P.link_seq_base = Lc.link.seq << 32;
     if ((Lc.link.has_left || Lc.link.has_right) && (nstg > kLinkStages || L::EXW > 44)) return cudaErrorInvalidValue;
     void *args[] = {&P};
-    return cudaLaunchCooperativeKernel((const void *)kern, dim3(ncta, Lc.nfields), dim3((nstr * nstg + 2) * 32), args,
-                                       cfg.smem, st);
+    const int cs = cfg.cluster;
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3((ncta + cs - 1) / cs * cs, Lc.nfields);   // padding CTAs leave at once
+    lc.blockDim = dim3((nstr * nstg + 2) * 32);
+    lc.dynamicSmemBytes = cfg.smem;
+    lc.stream = st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeCooperative;      // every CTA resident: the chain spins on its neighbours
+    at[0].val.cooperative = 1;
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = cs;
+    at[1].val.clusterDim.y = 1;
+    at[1].val.clusterDim.z = 1;
+    lc.attrs = at;
+    lc.numAttrs = cs > 1 ? 2 : 1;
+    return cudaLaunchKernelExC(&lc, (const void *)kern, args);
 }
 
 template <int S>
