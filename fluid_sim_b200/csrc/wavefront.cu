@@ -54,6 +54,9 @@ constexpr int kTileFloats = kTileRows * 32;
 #ifndef WF_GROUP
 #define WF_GROUP 4
 #endif
+#ifndef WF_XFER
+#define WF_XFER 8           // steps per ring hand-over between CTAs (4, 8 or 16)
+#endif
 #ifndef WF_BACKOFF
 #define WF_BACKOFF 0        // > 0: failed polls of a wait before the warp starts sleeping between polls
 #endif
@@ -74,7 +77,7 @@ struct WfLayout {
     static constexpr int XW = (S + 1 + 3) & ~3;   // x[0..S], padded to float4
     static constexpr int DW = (S + 3) & ~3;       // rhs levels 0..S-1
     static constexpr int EXW = XW + DW;           // floats one lane hands to the next strip per step
-    static constexpr int kBoundaryFloats = kWfSlots * kWfBatch * EXW;
+    static constexpr int kBoundaryFloats = kWfSlots * kWfBatch * EXW * 2;   // x2: every float travels with a tag
     // per-lane strides of a warp's own state buffers: an odd number of 16-byte chunks keeps the
     // 128-bit shared-memory accesses of a quarter warp on distinct banks
     static constexpr int XP = ((XW / 4) & 1) ? XW : XW + 4;
@@ -515,6 +518,17 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         const int gi = lane & 15;
         const bool valid = is_flush ? (gi < NSTR)
                                     : ((lane < 16) && (gi < NSTG) && (is_exp ? (has_right && !dsm_r) : (has_left && !dsm_l)));
+        // Ring hand-overs move units of kXfer steps.  Every 16-byte word of a ring (global memory on this GPU, or
+        // the neighbouring rank's memory) holds two floats and two copies of a tag unique to (launch, unit): the
+        // reader polls the data itself and retries until all tags of a unit match, so neither side executes a
+        // fence or waits for a flag round trip.  Only the credit (units consumed) travels back as a counter.
+        constexpr int kXfer = WF_XFER;
+        constexpr int kXferLog = (kXfer == 4) ? 2 : ((kXfer == 8) ? 3 : 4);
+        static_assert(kXfer % kGroup == 0 && kXfer <= 16, "hand-over unit: a whole number of groups, at most a batch");
+        constexpr int kRingUnits = kWfSlots * kWfBatch / kXfer;
+        constexpr int kUnitFloats = kXfer * L::EXW;
+        constexpr int kWords = kUnitFloats / 2;
+        constexpr int kWordsPerLane = (kWords + 31) / 32;
         int n = 0, n_end = -1, n_first_right = 0, fl_tau_e = 0;
         if (valid) {
             if (is_flush) {
@@ -523,24 +537,31 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 fl_tau_e = last_step(jl);
                 n_end = fl_tau_e >> 4;
             } else if (!is_exp) {
-                n = first_step(warp_j0w(0, gi)) >> 4;
-                n_end = last_needed(warp_j0w(0, gi) - 32) >> 4;           // last batch of the strip on the left
+                n = first_step(warp_j0w(0, gi)) >> kXferLog;
+                n_end = last_needed(warp_j0w(0, gi) - 32) >> kXferLog;    // last unit of the strip on the left
             } else {
-                n = first_step(warp_j0w(NSTR - 1, gi)) >> 4;
-                n_end = last_needed(warp_j0w(NSTR - 1, gi)) >> 4;
-                n_first_right = first_step(warp_j0w(NSTR, gi)) >> 4;
+                n = first_step(warp_j0w(NSTR - 1, gi)) >> kXferLog;
+                n_end = last_needed(warp_j0w(NSTR - 1, gi)) >> kXferLog;
+                n_first_right = first_step(warp_j0w(NSTR, gi)) >> kXferLog;   // first unit the reader takes
             }
         }
         unsigned long long *fl = P.flags + ((size_t)fi * kMaxStages + (gi < kMaxStages ? gi : 0)) * kWfMaxCtas * 2;
         const int lk = fi * kLinkStages + (gi < kLinkStages ? gi : 0);   // slot of (field, stage) in the rank links
         const bool via_link = is_exp ? link_r : link_l;
-        const float *ll_in = P.link.in_rings;
-        const unsigned ll_seq = (unsigned)(P.link_seq_base >> 32) << 20;
-        auto ll_tag = [ll_seq](int batch) { return ll_seq + (unsigned)(batch + kBatchBias + 1); };
         const unsigned long long flag_base = via_link ? P.link_seq_base : P.seq_base;
-        const volatile unsigned long long *poll_flag =
-            is_exp ? (link_r ? P.link.cons + lk : fl + (size_t)cl * 2 + 1)
-                   : (link_l ? P.link.in_prod + lk : fl + (size_t)(cl > 0 ? cl - 1 : 0) * 2);
+        const unsigned tag_seq = (unsigned)(flag_base >> 32) << 18;
+        auto unit_tag = [tag_seq](int unit) { return tag_seq + (unsigned)(unit + kBatchBias + 1); };
+        // ring of (stage st) this warp reads (import) or writes (export), as floats
+        auto ring_of = [&](int st) -> float * {
+            if (via_link)
+                return (is_exp ? P.link.right_rings : const_cast<float *>(P.link.in_rings)) +
+                       (size_t)(fi * kLinkStages + st) * kLinkRingFloats;
+            return P.xchg + (((size_t)fi * NSTG + st) * P.ncta + (is_exp ? cl : cl - 1)) * L::kBoundaryFloats;
+        };
+        const float *my_ring = ring_of(gi < NSTG ? gi : 0);
+        // credits: units the reader has consumed
+        const volatile unsigned long long *credit_in = link_r ? P.link.cons + lk : fl + (size_t)cl * 2 + 1;
+        unsigned long long *credit_out = link_l ? P.link.left_cons + lk : fl + (size_t)(cl > 0 ? cl - 1 : 0) * 2 + 1;
         const int *poll_prog = is_flush ? prog + (gi < NSTR ? gi : 0) * NSTG + (NSTG - 1)
                                         : (is_exp ? prog + (NSTR - 1) * NSTG + (gi < NSTG ? gi : 0) : prog + (gi < NSTG ? gi : 0));
         bool done = !valid || n > n_end;
@@ -551,20 +572,15 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                     // every lane of the strip has written slot q once the warp has finished step q + 31
                     ready = ld_acquire_cta_s32(poll_prog) >= min(16 * n + 15 + 32, fl_tau_e);
                 } else if (!is_exp) {
-                    // batch n replaces batch n - kEdgeDepth/16 in edge_in, whose last slot is read one and two steps later
-                    ready = ld_acquire_cta_s32(poll_prog) >= 16 * (n - kEdgeDepth / kWfBatch + 1) + 1;
-                    if (ready) {
-                        if (link_l)   // hint only: the tag of the batch's last store (the copy below checks all of them)
-                            ready = *reinterpret_cast<const volatile unsigned *>(
-                                        ll_in + (size_t)lk * kLinkRingFloats + 2 * (size_t)(n & (kWfSlots - 1)) * kWfBatch * L::EXW +
-                                        2 * kWfBatch * L::EXW - 1) == ll_tag(n);
-                        else
-                            ready = *poll_flag >= flag_base + (unsigned long long)(n + kBatchBias + 1);
-                    }
+                    // unit n replaces unit n - kEdgeDepth/kXfer in edge_in, whose last slot is read one and two steps later
+                    ready = ld_acquire_cta_s32(poll_prog) >= kXfer * (n - kEdgeDepth / kXfer + 1) + 1;
+                    if (ready)   // hint only: the tag of the unit's last word (the copy below checks all of them)
+                        ready = *reinterpret_cast<const volatile unsigned *>(
+                                    my_ring + 2 * (size_t)(n & (kRingUnits - 1)) * kUnitFloats + 2 * kUnitFloats - 1) == unit_tag(n);
                 } else {
-                    ready = ld_acquire_cta_s32(poll_prog) >= 16 * n + 15 &&
-                            (n - kWfSlots < n_first_right ||
-                             *poll_flag >= flag_base + (unsigned long long)(n - kWfSlots + kBatchBias + 1));
+                    ready = ld_acquire_cta_s32(poll_prog) >= kXfer * n + kXfer - 1 &&
+                            (n - kRingUnits < n_first_right ||
+                             *credit_in >= flag_base + (unsigned long long)(n - kRingUnits + kBatchBias + 1));
                 }
             }
             unsigned m = __ballot_sync(0xffffffffu, ready);
@@ -572,61 +588,69 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 __nanosleep(32);
                 continue;
             }
-            if ((m & 0xffffu) && !via_link) __threadfence();   // acquire side of the global flags just observed
-            for (unsigned mm = m & 0xffffu; mm; mm &= mm - 1) {
-                const int src = __ffs(mm) - 1;
-                const int bn = __shfl_sync(0xffffffffu, n, src);
-                float *xg = P.xchg + ((size_t)fi * NSTG + src) * P.ncta * L::kBoundaryFloats;
-                const size_t slot_off = (size_t)(bn & (kWfSlots - 1)) * kWfBatch * L::EXW;
-                const size_t lk_off = (size_t)(fi * kLinkStages + src) * kLinkRingFloats;
-                constexpr int kPairs = kWfBatch * L::EXW / 2;           // float pairs per batch
-                constexpr int kPairsPerLane = (kPairs + 31) / 32;
-                if (!is_exp && link_l) {
-                    const uint4 *gsrc = reinterpret_cast<const uint4 *>(ll_in + lk_off + 2 * slot_off);
-                    float2 *sdst = reinterpret_cast<float2 *>(edge_in + src * kEdgeDepth * L::EXW +
-                                                              ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
-                    const unsigned tag = ll_tag(bn);
-                    uint4 v[kPairsPerLane];
-                    bool ok = true;
+            if (!is_exp) {
+                // the loads of several stages' units are in flight together (one L2 round trip per burst, not per stage)
+                constexpr int kBurst = (kWordsPerLane <= 1) ? 8 : ((kWordsPerLane == 2) ? 4 : 2);
+                unsigned mm = m & 0xffffu;
+                while (mm) {
+                    int srcs[kBurst], bns[kBurst];
+                    uint4 v[kBurst][kWordsPerLane];
 #pragma unroll
-                    for (int k = 0; k < kPairsPerLane; ++k) {
-                        const int i = lane + 32 * k;
-                        if (i < kPairs) {
-                            v[k] = ld_volatile_v4(gsrc + i);
-                            ok = ok && v[k].y == tag && v[k].w == tag;
+                    for (int b = 0; b < kBurst; ++b) {
+                        srcs[b] = -1;
+                        bns[b] = 0;
+                        if (mm) {
+                            srcs[b] = __ffs(mm) - 1;
+                            mm &= mm - 1;
+                            bns[b] = __shfl_sync(0xffffffffu, n, srcs[b]);
+                            const uint4 *gring = reinterpret_cast<const uint4 *>(
+                                ring_of(srcs[b]) + 2 * (size_t)(bns[b] & (kRingUnits - 1)) * kUnitFloats);
+#pragma unroll
+                            for (int k = 0; k < kWordsPerLane; ++k) {
+                                const int i = lane + 32 * k;
+                                if (i < kWords) v[b][k] = ld_volatile_v4(gring + i);
+                            }
                         }
                     }
-                    if (__all_sync(0xffffffffu, ok)) {
 #pragma unroll
-                        for (int k = 0; k < kPairsPerLane; ++k) {
+                    for (int b = 0; b < kBurst; ++b) {
+                        if (srcs[b] < 0) continue;
+                        const unsigned tag = unit_tag(bns[b]);
+                        bool ok = true;
+#pragma unroll
+                        for (int k = 0; k < kWordsPerLane; ++k) {
                             const int i = lane + 32 * k;
-                            if (i < kPairs) sdst[i] = make_float2(__uint_as_float(v[k].x), __uint_as_float(v[k].z));
+                            if (i < kWords) ok = ok && v[b][k].y == tag && v[b][k].w == tag;
                         }
-                    } else if (lane == src) {
-                        ready = false;    // part of the batch is still in flight: try again next round
+                        if (__all_sync(0xffffffffu, ok)) {
+                            float2 *sring = reinterpret_cast<float2 *>(edge_in + srcs[b] * kEdgeDepth * L::EXW +
+                                                                       ((kXfer * bns[b]) & (kEdgeDepth - 1)) * L::EXW);
+#pragma unroll
+                            for (int k = 0; k < kWordsPerLane; ++k) {
+                                const int i = lane + 32 * k;
+                                if (i < kWords) sring[i] = make_float2(__uint_as_float(v[b][k].x), __uint_as_float(v[b][k].z));
+                            }
+                        } else if (lane == srcs[b]) {
+                            ready = false;    // part of the unit is still in flight: try again next round
+                        }
                     }
-                } else if (!is_exp) {
-                    const float4 *gsrc = reinterpret_cast<const float4 *>(xg + (size_t)(cl - 1) * L::kBoundaryFloats + slot_off);
-                    float4 *sdst = reinterpret_cast<float4 *>(edge_in + src * kEdgeDepth * L::EXW +
-                                                              ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
-#pragma unroll 2
-                    for (int i = lane; i < kWfBatch * L::EXW / 4; i += 32) sdst[i] = __ldcg(gsrc + i);
-                } else if (link_r) {
-                    uint4 *gdst = reinterpret_cast<uint4 *>(P.link.right_rings + lk_off + 2 * slot_off);
-                    const float2 *ssrc = reinterpret_cast<const float2 *>(edge_out + src * kEdgeDepth * L::EXW +
-                                                                          ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
-                    const unsigned tag = ll_tag(bn);
-#pragma unroll 2
-                    for (int i = lane; i < kPairs; i += 32) {
-                        const float2 d = ssrc[i];
-                        st_volatile_v4(gdst + i, make_uint4(__float_as_uint(d.x), tag, __float_as_uint(d.y), tag));
+                }
+            } else {
+                for (unsigned mm = m & 0xffffu; mm; mm &= mm - 1) {
+                    const int src = __ffs(mm) - 1;
+                    const int bn = __shfl_sync(0xffffffffu, n, src);
+                    uint4 *gring = reinterpret_cast<uint4 *>(ring_of(src) + 2 * (size_t)(bn & (kRingUnits - 1)) * kUnitFloats);
+                    const float2 *sring = reinterpret_cast<const float2 *>(edge_out + src * kEdgeDepth * L::EXW +
+                                                                           ((kXfer * bn) & (kEdgeDepth - 1)) * L::EXW);
+                    const unsigned tag = unit_tag(bn);
+#pragma unroll
+                    for (int k = 0; k < kWordsPerLane; ++k) {
+                        const int i = lane + 32 * k;
+                        if (i < kWords) {
+                            const float2 d = sring[i];
+                            st_volatile_v4(gring + i, make_uint4(__float_as_uint(d.x), tag, __float_as_uint(d.y), tag));
+                        }
                     }
-                } else {
-                    float4 *gdst = reinterpret_cast<float4 *>(xg + (size_t)cl * L::kBoundaryFloats + slot_off);
-                    const float4 *ssrc = reinterpret_cast<const float4 *>(edge_out + src * kEdgeDepth * L::EXW +
-                                                                          ((16 * bn) & (kEdgeDepth - 1)) * L::EXW);
-#pragma unroll 2
-                    for (int i = lane; i < kWfBatch * L::EXW / 4; i += 32) gdst[i] = ssrc[i];
                 }
             }
             for (unsigned mm = m >> 16; mm; mm &= mm - 1) {
@@ -648,19 +672,16 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                         if (row0 + it >= 1 && row0 + it <= W - 2) dst[(long long)it * pitch] = vals[it];
                 }
             }
-            if (is_exp && (m & 0xffffu) && !link_r) __threadfence();
             __syncwarp();
             if (ready) {
                 if (is_flush) {
                     st_release_cta_s32(flushed_steps + gi, 16 * n + 15);
                 } else if (!is_exp) {
-                    st_release_cta_s32(imp_steps + gi, 16 * n + 15);
-                    // the batch has been read (its tags were checked), so the credit needs no ordering
-                    if (link_l) st_volatile_u64(P.link.left_cons + lk, flag_base + (unsigned long long)(n + kBatchBias + 1));
-                    else st_release_u64(fl + (size_t)(cl - 1) * 2 + 1, flag_base + (unsigned long long)(n + kBatchBias + 1));
+                    st_release_cta_s32(imp_steps + gi, kXfer * n + kXfer - 1);
+                    // the unit has been read (its tags were checked), so the credit needs no ordering
+                    st_volatile_u64(credit_out, flag_base + (unsigned long long)(n + kBatchBias + 1));
                 } else {
-                    if (!link_r) st_release_u64(fl + (size_t)cl * 2, flag_base + (unsigned long long)(n + kBatchBias + 1));
-                    st_release_cta_s32(exp_steps + gi, 16 * n + 15);
+                    st_release_cta_s32(exp_steps + gi, kXfer * n + kXfer - 1);
                 }
                 n += 1;
                 done = n > n_end;
@@ -743,7 +764,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
             wait_clamp = last_step(j0w - 32);
         } else if (has_left) {
             wait_ptr = imp_steps + g;
-            wait_clamp = 16 * (last_needed(j0w - 32) >> 4) + 15;
+            wait_clamp = WF_XFER * (last_needed(j0w - 32) / WF_XFER) + WF_XFER - 1;   // end of the last unit handed over
         }
         wait_add = kGroup - 2;
     } else if (lane == 1) {
@@ -1114,6 +1135,8 @@ cudaError_t wf_launch_inst(const SweepLaunch &Lc, SweepScratch &scr, cudaStream_
         scr.xchg = nullptr;
         scr.xchg_floats = 0;
         e = cudaMalloc(&scr.xchg, need * sizeof(float));
+        if (e != cudaSuccess) return e;
+        e = cudaMemsetAsync(scr.xchg, 0, need * sizeof(float), st);   // tag 0 is never used
         if (e != cudaSuccess) return e;
         scr.xchg_floats = need;
     }
