@@ -98,6 +98,100 @@ __global__ void gradient_kernel(float *__restrict__ u, float *__restrict__ v, co
     v[c] = __fsub_rn(v[c], gy);
 }
 
+// ---- the same two stencils, four columns and kRows rows per thread -------------------------------------------------
+// Used when every row starts 16-byte aligned (pitch, jbase and j0 multiples of 4).  A thread walks down kRows rows
+// with the rows above / below kept in registers, so each value of the i-stencil is loaded once per thread; the two
+// j-neighbours outside the quad are scalar loads that hit the lines the neighbouring lanes load anyway.  Quads that
+// contain a wall column (or the end of the owned block) store per component.
+constexpr int kRows = 4;
+
+__device__ __forceinline__ float4 ld4(const float *p) { return *reinterpret_cast<const float4 *>(p); }
+
+__device__ __forceinline__ void store_quad(float *dst, float4 r, int j, int jlo, int jhi)
+{   // dst = &x[i][j]; only columns in [jlo, jhi] are written
+    if (j >= jlo && j + 3 <= jhi) {
+        *reinterpret_cast<float4 *>(dst) = r;
+    } else {
+        if (j >= jlo && j <= jhi) dst[0] = r.x;
+        if (j + 1 >= jlo && j + 1 <= jhi) dst[1] = r.y;
+        if (j + 2 >= jlo && j + 2 <= jhi) dst[2] = r.z;
+        if (j + 3 >= jlo && j + 3 <= jhi) dst[3] = r.w;
+    }
+}
+
+__global__ void __launch_bounds__(256) divergence_vec_kernel(const float *__restrict__ u, const float *__restrict__ v,
+                                                             float *__restrict__ div, const GridView G, float mhh)
+{
+    const int W = G.W, H = G.H;
+    const int j = G.j0 + 4 * (blockIdx.x * kBx + threadIdx.x);
+    const int i0 = 1 + kRows * (blockIdx.y * kBy + threadIdx.y);
+    if (j >= G.j1 || i0 > W - 2) return;
+    const int jlo = max(1, G.j0), jhi = min(H - 2, G.j1 - 1);
+    const int jmax = G.jbase + G.pitch - 1;                 // last column the local array holds
+    size_t c = AT(G, i0, j);
+    float4 um = ld4(u + c - G.pitch), uc = ld4(u + c);
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+        const int i = i0 + r;
+        if (i > W - 2) break;
+        const float4 up = ld4(u + c + G.pitch);
+        const float4 vc = ld4(v + c);
+        const float vl = (j - 1 >= G.jbase) ? v[c - 1] : 0.0f;
+        const float vr = (j + 4 <= jmax) ? v[c + 4] : 0.0f;
+        float4 d;
+        d.x = __fmul_rn(mhh, __fsub_rn(__fadd_rn(__fsub_rn(up.x, um.x), vc.y), vl));
+        d.y = __fmul_rn(mhh, __fsub_rn(__fadd_rn(__fsub_rn(up.y, um.y), vc.z), vc.x));
+        d.z = __fmul_rn(mhh, __fsub_rn(__fadd_rn(__fsub_rn(up.z, um.z), vc.w), vc.y));
+        d.w = __fmul_rn(mhh, __fsub_rn(__fadd_rn(__fsub_rn(up.w, um.w), vr), vc.z));
+        store_quad(div + c, d, j, jlo, jhi);
+        um = uc;
+        uc = up;
+        c += G.pitch;
+    }
+}
+
+__global__ void __launch_bounds__(256) gradient_vec_kernel(float *__restrict__ u, float *__restrict__ v,
+                                                           const float *__restrict__ p, const GridView G, float h)
+{
+    const int W = G.W, H = G.H;
+    const int j = G.j0 + 4 * (blockIdx.x * kBx + threadIdx.x);
+    const int i0 = 1 + kRows * (blockIdx.y * kBy + threadIdx.y);
+    if (j >= G.j1 || i0 > W - 2) return;
+    const int jlo = max(1, G.j0), jhi = min(H - 2, G.j1 - 1);
+    const int jmax = G.jbase + G.pitch - 1;
+    size_t c = AT(G, i0, j);
+    float4 pm = ld4(p + c - G.pitch), pc = ld4(p + c);
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+        const int i = i0 + r;
+        if (i > W - 2) break;
+        const float4 pp = ld4(p + c + G.pitch);
+        const float pl = (j - 1 >= G.jbase) ? p[c - 1] : 0.0f;
+        const float pr = (j + 4 <= jmax) ? p[c + 4] : 0.0f;
+        float4 uu = ld4(u + c), vv = ld4(v + c);
+        uu.x = __fsub_rn(uu.x, __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(pp.x, pm.x)), h));
+        uu.y = __fsub_rn(uu.y, __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(pp.y, pm.y)), h));
+        uu.z = __fsub_rn(uu.z, __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(pp.z, pm.z)), h));
+        uu.w = __fsub_rn(uu.w, __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(pp.w, pm.w)), h));
+        vv.x = __fsub_rn(vv.x, __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(pc.y, pl)), h));
+        vv.y = __fsub_rn(vv.y, __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(pc.z, pc.x)), h));
+        vv.z = __fsub_rn(vv.z, __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(pc.w, pc.y)), h));
+        vv.w = __fsub_rn(vv.w, __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(pr, pc.z)), h));
+        store_quad(u + c, uu, j, jlo, jhi);
+        store_quad(v + c, vv, j, jlo, jhi);
+        pm = pc;
+        pc = pp;
+        c += G.pitch;
+    }
+}
+
+inline bool quad_aligned(const GridView &G) { return (G.pitch % 4 == 0) && (G.jbase % 4 == 0) && (G.j0 % 4 == 0); }
+inline dim3 quad_grid(const GridView &G)
+{
+    const int quads = (G.j1 - G.j0 + 3) / 4, rows = (G.W - 2 + kRows - 1) / kRows;
+    return dim3((quads + kBx - 1) / kBx, (rows + kBy - 1) / kBy);
+}
+
 // ---- bilinear sample (src/fluid_sim.cpp:231-252) -------------------------------------------------------
 struct Taps { int i0, j0; float s0, s1, t0, t1; };
 
@@ -279,14 +373,16 @@ cudaError_t launch_divergence(const float *u, const float *v, float *div, const 
 {
     const float h = 1.0f / (float)G.W;      // src/fluid_sim.cpp:304
     const float mhh = -0.5f * h;            // -0.5f * h, evaluated first (:311)
-    divergence_kernel<<<cell_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, div, G, mhh);
+    if (quad_aligned(G)) divergence_vec_kernel<<<quad_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, div, G, mhh);
+    else divergence_kernel<<<cell_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, div, G, mhh);
     return cudaGetLastError();
 }
 
 cudaError_t launch_gradient(float *u, float *v, const float *p, const GridView &G, cudaStream_t st)
 {
     const float h = 1.0f / (float)G.W;
-    gradient_kernel<<<cell_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, p, G, h);
+    if (quad_aligned(G)) gradient_vec_kernel<<<quad_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, p, G, h);
+    else gradient_kernel<<<cell_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, p, G, h);
     return cudaGetLastError();
 }
 
