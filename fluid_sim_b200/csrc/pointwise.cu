@@ -226,11 +226,24 @@ __device__ __forceinline__ float tap_val(const float *__restrict__ f, int i, int
     return v;
 }
 
-template <bool PZ>
+// Idx: int when the local array has fewer than 2^31 elements (one 32-bit multiply-add per tap row instead of 64-bit
+// address arithmetic per tap), long long otherwise.
+template <bool PZ, typename Idx>
 __device__ __forceinline__ float sample(const float *__restrict__ f, const Taps &t, const GridView &G)
 {
-    const float f00 = tap_val<PZ>(f, t.i0, t.j0, G), f01 = tap_val<PZ>(f, t.i0, t.j0 + 1, G);
-    const float f10 = tap_val<PZ>(f, t.i0 + 1, t.j0, G), f11 = tap_val<PZ>(f, t.i0 + 1, t.j0 + 1, G);
+    const float *r0 = f + ((Idx)t.i0 * (Idx)G.pitch + (Idx)(t.j0 - G.jbase));
+    const float *r1 = r0 + G.pitch;
+    float f00 = __ldg(r0), f01 = __ldg(r0 + 1), f10 = __ldg(r1), f11 = __ldg(r1 + 1);
+    if (PZ) {
+        // density only: the reference's diffuse pass with a == 0 rewrites every interior cell as
+        // d + 1.5f * ((d + 0*nb) - d), i.e. d + 0.0f (src/fluid_sim.cpp:56-57); folded in here.
+        const bool i0in = t.i0 >= 1 && t.i0 <= G.W - 2, i1in = t.i0 + 1 >= 1 && t.i0 + 1 <= G.W - 2;
+        const bool j0in = t.j0 >= 1 && t.j0 <= G.H - 2, j1in = t.j0 + 1 >= 1 && t.j0 + 1 <= G.H - 2;
+        if (i0in && j0in) f00 = __fadd_rn(f00, 0.0f);
+        if (i0in && j1in) f01 = __fadd_rn(f01, 0.0f);
+        if (i1in && j0in) f10 = __fadd_rn(f10, 0.0f);
+        if (i1in && j1in) f11 = __fadd_rn(f11, 0.0f);
+    }
     const float a = __fadd_rn(__fmul_rn(t.t0, f00), __fmul_rn(t.t1, f01));
     const float b = __fadd_rn(__fmul_rn(t.t0, f10), __fmul_rn(t.t1, f11));
     return __fadd_rn(__fmul_rn(t.s0, a), __fmul_rn(t.s1, b));
@@ -239,7 +252,7 @@ __device__ __forceinline__ float sample(const float *__restrict__ f, const Taps 
 // ---- RK4 back-trace (src/fluid_sim.cpp:261-298) ------------------------------------------------------------
 // dst_a = src_a sampled at the traced position; dst_b likewise (the two velocity components share
 // one trace because both advect() calls of velocityStep use prevVelocityX/Y, :401-402).
-template <bool TWO, bool PZ>
+template <bool TWO, bool PZ, typename Idx>
 __global__ void advect_rk4_kernel(float *__restrict__ dst_a, const float *__restrict__ src_a,
                                   float *__restrict__ dst_b, const float *__restrict__ src_b,
                                   const float *__restrict__ u, const float *__restrict__ v, const GridView G, float ndt0)
@@ -252,32 +265,32 @@ __global__ void advect_rk4_kernel(float *__restrict__ dst_a, const float *__rest
     const float x = (float)i, y = (float)j;
 
     Taps t = make_taps(x, y, xm, ym);
-    const float k1x = __fmul_rn(sample<false>(u, t, G), ndt0);
-    const float k1y = __fmul_rn(sample<false>(v, t, G), ndt0);
+    const float k1x = __fmul_rn(sample<false, Idx>(u, t, G), ndt0);
+    const float k1y = __fmul_rn(sample<false, Idx>(v, t, G), ndt0);
 
     t = make_taps(__fadd_rn(x, __fmul_rn(k1x, 0.5f)), __fadd_rn(y, __fmul_rn(k1y, 0.5f)), xm, ym);
-    const float k2x = __fmul_rn(sample<false>(u, t, G), ndt0);
-    const float k2y = __fmul_rn(sample<false>(v, t, G), ndt0);
+    const float k2x = __fmul_rn(sample<false, Idx>(u, t, G), ndt0);
+    const float k2y = __fmul_rn(sample<false, Idx>(v, t, G), ndt0);
 
     t = make_taps(__fadd_rn(x, __fmul_rn(k2x, 0.5f)), __fadd_rn(y, __fmul_rn(k2y, 0.5f)), xm, ym);
-    const float k3x = __fmul_rn(sample<false>(u, t, G), ndt0);
-    const float k3y = __fmul_rn(sample<false>(v, t, G), ndt0);
+    const float k3x = __fmul_rn(sample<false, Idx>(u, t, G), ndt0);
+    const float k3y = __fmul_rn(sample<false, Idx>(v, t, G), ndt0);
 
     t = make_taps(__fadd_rn(x, k3x), __fadd_rn(y, k3y), xm, ym);
-    const float k4x = __fmul_rn(sample<false>(u, t, G), ndt0);
-    const float k4y = __fmul_rn(sample<false>(v, t, G), ndt0);
+    const float k4x = __fmul_rn(sample<false, Idx>(u, t, G), ndt0);
+    const float k4y = __fmul_rn(sample<false, Idx>(v, t, G), ndt0);
 
     const float dx = __fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(k1x, __fmul_rn(2.0f, k2x)), __fmul_rn(2.0f, k3x)), k4x), 6.0f);
     const float dy = __fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(k1y, __fmul_rn(2.0f, k2y)), __fmul_rn(2.0f, k3y)), k4y), 6.0f);
 
     t = make_taps(__fadd_rn(x, dx), __fadd_rn(y, dy), xm, ym);
     const size_t c = AT(G, i, j);
-    dst_a[c] = sample<PZ>(src_a, t, G);
-    if (TWO) dst_b[c] = sample<PZ>(src_b, t, G);
+    dst_a[c] = sample<PZ, Idx>(src_a, t, G);
+    if (TWO) dst_b[c] = sample<PZ, Idx>(src_b, t, G);
 }
 
 // ---- single semi-Lagrangian trace (src/fluid_sim.cpp:65-100 and the two halves of :103-168) ---------------------
-template <bool PZ>
+template <bool PZ, typename Idx>
 __global__ void advect_sl_kernel(float *__restrict__ dst, const float *__restrict__ src, const float *__restrict__ u,
                                  const float *__restrict__ v, const GridView G, float dt0, int forward)
 {
@@ -290,7 +303,7 @@ __global__ void advect_sl_kernel(float *__restrict__ dst, const float *__restric
     const float x = forward ? __fadd_rn((float)i, du) : __fsub_rn((float)i, du);
     const float y = forward ? __fadd_rn((float)j, dv) : __fsub_rn((float)j, dv);
     const Taps t = make_taps(x, y, (float)W - 1.5f, (float)H - 1.5f);
-    dst[c] = sample<PZ>(src, t, G);
+    dst[c] = sample<PZ, Idx>(src, t, G);
 }
 
 // ---- MacCormack correction and clamp (src/fluid_sim.cpp:170-207) --------------------------------------------------
@@ -392,13 +405,20 @@ cudaError_t launch_advect_rk4(float *dst_a, const float *src_a, float *dst_b, co
     const float dt0 = dt * (float)G.W;      // src/fluid_sim.cpp:264
     const float ndt0 = -dt0;
     const dim3 g = cell_grid(G), b(kBx, kBy);
+    const bool small = (size_t)G.W * (size_t)G.pitch < ((size_t)1 << 31);
+#define FSB_RK4(TWO_, PZ_)                                                                                         \
+    do {                                                                                                           \
+        if (small) advect_rk4_kernel<TWO_, PZ_, int><<<g, b, 0, st>>>(dst_a, src_a, dst_b, src_b, u, v, G, ndt0);  \
+        else advect_rk4_kernel<TWO_, PZ_, long long><<<g, b, 0, st>>>(dst_a, src_a, dst_b, src_b, u, v, G, ndt0);  \
+    } while (0)
     if (dst_b) {
-        if (src_plus_zero) advect_rk4_kernel<true, true><<<g, b, 0, st>>>(dst_a, src_a, dst_b, src_b, u, v, G, ndt0);
-        else advect_rk4_kernel<true, false><<<g, b, 0, st>>>(dst_a, src_a, dst_b, src_b, u, v, G, ndt0);
+        if (src_plus_zero) FSB_RK4(true, true);
+        else FSB_RK4(true, false);
     } else {
-        if (src_plus_zero) advect_rk4_kernel<false, true><<<g, b, 0, st>>>(dst_a, src_a, nullptr, nullptr, u, v, G, ndt0);
-        else advect_rk4_kernel<false, false><<<g, b, 0, st>>>(dst_a, src_a, nullptr, nullptr, u, v, G, ndt0);
+        if (src_plus_zero) FSB_RK4(false, true);
+        else FSB_RK4(false, false);
     }
+#undef FSB_RK4
     return cudaGetLastError();
 }
 
@@ -408,8 +428,14 @@ cudaError_t launch_advect_sl(float *dst, const float *src, const float *u, const
     const float dt0 = dt * (float)G.W;
     const dim3 g = cell_grid(G), b(kBx, kBy);
     const int fwd = sign > 0.0f;
-    if (src_plus_zero) advect_sl_kernel<true><<<g, b, 0, st>>>(dst, src, u, v, G, dt0, fwd);
-    else advect_sl_kernel<false><<<g, b, 0, st>>>(dst, src, u, v, G, dt0, fwd);
+    const bool small = (size_t)G.W * (size_t)G.pitch < ((size_t)1 << 31);
+    if (src_plus_zero) {
+        if (small) advect_sl_kernel<true, int><<<g, b, 0, st>>>(dst, src, u, v, G, dt0, fwd);
+        else advect_sl_kernel<true, long long><<<g, b, 0, st>>>(dst, src, u, v, G, dt0, fwd);
+    } else {
+        if (small) advect_sl_kernel<false, int><<<g, b, 0, st>>>(dst, src, u, v, G, dt0, fwd);
+        else advect_sl_kernel<false, long long><<<g, b, 0, st>>>(dst, src, u, v, G, dt0, fwd);
+    }
     return cudaGetLastError();
 }
 

@@ -813,6 +813,35 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         wmask[k] = ((fix_cols == kFixLeft && col == 0) || (fix_cols == kFixRight && col == H - 1)) ? 0xffffffffu : 0u;
         asm volatile("" : "+r"(wmask[k]));
     }
+    // stage 0: copy the 16 array rows the strip reaches during steps [q0, q0+16) into the input tiles (cp.async)
+    auto stage_tile_rows = [&](const int q0) {
+        if (vec_ok) {
+            const int rr = lane >> 3, cg = lane & 7;
+#pragma unroll
+            for (int it = 0; it < kWfBatch / 4; ++it) {
+                const int q = q0 + it * 4 + rr;
+                const int row = q - kToff - j0;
+                const int col = j0 + cg * 4;
+                const bool ok = (row >= 0) && (row < W) && (col < H);
+                const size_t off = ok ? ((size_t)row * pitch + (col - jbase)) : 0;
+                const int so = (q & (kTileRows - 1)) * 32 + cg * 4;
+                cp_async_f32x4(t_rhs + so, F.rhs + off, ok);
+                if (HAS_X0) cp_async_f32x4(t_x0 + so, F.x0 + off, ok);
+            }
+        } else {
+#pragma unroll 4
+            for (int it = 0; it < kWfBatch; ++it) {
+                const int q = q0 + it;
+                const int row = q - kToff - j0;
+                const int col = j0 + lane;
+                const bool ok = (row >= 0) && (row < W) && (col < H);
+                const size_t off = ok ? ((size_t)row * pitch + (col - jbase)) : 0;
+                const int so = (q & (kTileRows - 1)) * 32 + lane;
+                cp_async_f32(t_rhs + so, F.rhs + off, ok);
+                if (HAS_X0) cp_async_f32(t_x0 + so, F.x0 + off, ok);
+            }
+        }
+    };
 #ifdef WF_PROFILE
     long long pf_wait = 0, pf_batch = 0, pf_step = 0, pf_first = 0;
     int pf_groups = 0;
@@ -863,33 +892,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
 #endif
                 // stage the rows this strip reaches during the next batch
                 cp_async_wait_all();
-                const int q0 = t + kWfBatch;
-                if (vec_ok) {
-                    const int rr = lane >> 3, cg = lane & 7;
-#pragma unroll
-                    for (int it = 0; it < kWfBatch / 4; ++it) {
-                        const int q = q0 + it * 4 + rr;
-                        const int row = q - kToff - j0;
-                        const int col = j0 + cg * 4;
-                        const bool ok = (row >= 0) && (row < W) && (col < H);
-                        const size_t off = ok ? ((size_t)row * pitch + (col - jbase)) : 0;
-                        const int so = (q & (kTileRows - 1)) * 32 + cg * 4;
-                        cp_async_f32x4(t_rhs + so, F.rhs + off, ok);
-                        if (HAS_X0) cp_async_f32x4(t_x0 + so, F.x0 + off, ok);
-                    }
-                } else {
-#pragma unroll 4
-                    for (int it = 0; it < kWfBatch; ++it) {
-                        const int q = q0 + it;
-                        const int row = q - kToff - j0;
-                        const int col = j0 + lane;
-                        const bool ok = (row >= 0) && (row < W) && (col < H);
-                        const size_t off = ok ? ((size_t)row * pitch + (col - jbase)) : 0;
-                        const int so = (q & (kTileRows - 1)) * 32 + lane;
-                        cp_async_f32(t_rhs + so, F.rhs + off, ok);
-                        if (HAS_X0) cp_async_f32(t_x0 + so, F.x0 + off, ok);
-                    }
-                }
+                stage_tile_rows(t + kWfBatch);
                 cp_async_commit();
             }
             if (!WF_FLUSH_OFFLOAD && g == NSTG - 1) {
