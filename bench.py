@@ -346,6 +346,36 @@ def main():
     e2e_value = cells_total * K / (e2e_ms * 1e-3)
     checksum = checksum_of()
 
+    # -------- the same per-GPU workload on ONE GPU (rank 0, the other ranks idle): the N = 1 point of the weak-scaling
+    # series.  `bench.py --gpus 1` measures the 8192^2, P=40 headline instead, whose steps cost 2.5x less per cell.
+    base = None
+    if multi:
+        barrier()
+        if rank == 0:
+            one = fsb.FluidSim(W, H // world, P, 5, device=local_rank)
+            d, u, v = vortex_lattice(W, H // world)
+            buf1 = one.pinned_array()
+            for fid, arr in ((fsb.DENSITY, d), (fsb.VELOCITY_X, u), (fsb.VELOCITY_Y, v)):
+                buf1[...] = arr
+                one.add_field(fid, buf1)
+            del d, u, v
+            st1 = torch.cuda.ExternalStream(one.stream(), device=torch.device("cuda", local_rank))
+            for _ in range(3):
+                one.step(0.01)
+            one.sync()
+            b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            b0.record(st1)
+            for _ in range(K):
+                one.step(0.01)
+            b1.record(st1)
+            one.sync()
+            base_ms = b0.elapsed_time(b1) / K
+            base = {"n_gpus": 1, "grid": [W, H // world], "proj_iters": P, "ms_per_step": base_ms,
+                    "value": W * (H // world) / (base_ms * 1e-3), "unit": UNIT,
+                    "command": "python bench.py --gpus 1 --workload config5"}
+            one.close()
+        barrier()
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -406,6 +436,8 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": e2e_ms / K, "density_checksum": checksum},
             "gpu_launches": int(launches), "clocks": clocks}
+    if base is not None:
+        line["weak_scaling_base"] = base
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
