@@ -75,6 +75,8 @@ ABI = [
     ("fsb_get_width", C.c_int, [_SIM]),
     ("fsb_get_height", C.c_int, [_SIM]),
     ("fsb_read_field", C.c_int, [_SIM, C.c_int, C.c_void_p]),
+    ("fsb_view_density", C.c_int, [_SIM, C.c_int, C.c_int, C.c_void_p]),
+    ("fsb_view_density_device", C.c_int, [_SIM, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
     ("fsb_write_field", C.c_int, [_SIM, C.c_int, C.c_void_p]),
     ("fsb_add_field", C.c_int, [_SIM, C.c_int, C.c_void_p]),
     ("fsb_host_alloc", C.c_void_p, [C.c_size_t]),
@@ -249,6 +251,15 @@ class FluidSim:
         arr = np.ascontiguousarray(arr, np.float32)
         assert arr.size == self.width * self.height
         self._check(self._lib.fsb_add_field(self._h, field, arr.ctypes.data))
+
+    def view_density(self, px_w=800, px_h=600, out=None):
+        """The reference viewer's density image (src/main.cpp:388-427 + density shader) as [px_h, px_w, 4] uint8,
+        row 0 = bottom window row."""
+        if out is None:
+            out = np.empty((px_h, px_w, 4), np.uint8)
+        assert out.dtype == np.uint8 and out.size == px_w * px_h * 4 and out.flags.c_contiguous
+        self._check(self._lib.fsb_view_density(self._h, px_w, px_h, out.ctypes.data))
+        return out
 
     def fields(self):
         return self.read(DENSITY), self.read(VELOCITY_X), self.read(VELOCITY_Y)

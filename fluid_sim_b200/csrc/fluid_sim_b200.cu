@@ -81,6 +81,8 @@ struct fsb_sim {
     // column block of a multi-rank run (is_block == false: the whole grid)
     bool is_block = false;
     int strip_begin = 0, strip_end = -1;       // 32-column strips of the sweep chain this rank runs
+    unsigned char *view_buf = nullptr;          // RGBA8 image of the last fsb_view_density* call
+    size_t view_bytes = 0;
     unsigned char *link_buf = nullptr;          // [rings | in_prod | cons], shared with both neighbours through CUDA IPC
     void *peer_left = nullptr, *peer_right = nullptr;   // the neighbours' link_buf mapped into this process
     float *peer_left_f[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // left rank's fields (same roles)
@@ -614,6 +616,7 @@ int fsb_destroy(fsb_sim *s)
         if (s->peer_left) cudaIpcCloseMemHandle(s->peer_left);
         if (s->peer_right) cudaIpcCloseMemHandle(s->peer_right);
         if (s->link_buf) cudaFree(s->link_buf);
+        if (s->view_buf) cudaFree(s->view_buf);
         for (auto &r : s->prof_open) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         for (auto &e : s->prof_free) cudaEventDestroy(e);
         if (s->stream) cudaStreamDestroy(s->stream);
@@ -1158,6 +1161,46 @@ int fsb_blk_advect_density(fsb_sim *s, float dt, int plus_zero)
     s->launches += 1;
     std::swap(s->f[FSB_DENSITY], s->f[FSB_PREV_DENSITY]);
     std::swap(s->peer_left_f[FSB_DENSITY], s->peer_left_f[FSB_PREV_DENSITY]);
+    return FSB_OK;
+}
+
+/* ---------------------------- headless density view ---------------------------- */
+
+static int render_density(fsb_sim *s, int px_w, int px_h)
+{
+    if (px_w < 1 || px_h < 1 || (size_t)px_w * px_h > ((size_t)1 << 28)) return fail(FSB_EINVAL, "fsb_view_density: bad image size");
+    if (s->is_block) return fail(FSB_EINVAL, "fsb_view_density: not available on a column block (gather the density first)");
+    FSB_TRY(flush_sources(s));
+    const size_t need = (size_t)px_w * px_h * 4;
+    if (need > s->view_bytes) {
+        FSB_CUDA(cudaStreamSynchronize(s->stream));
+        if (s->view_buf) cudaFree(s->view_buf);
+        s->view_buf = nullptr;
+        s->view_bytes = 0;
+        FSB_CUDA(cudaMalloc(&s->view_buf, need));
+        s->view_bytes = need;
+    }
+    FSB_CUDA(launch_view_density(s->f[FSB_DENSITY], s->G, px_w, px_h, s->view_buf, s->stream));
+    s->launches += 1;
+    return FSB_OK;
+}
+
+int fsb_view_density_device(fsb_sim *s, int px_w, int px_h, void **d_rgba)
+{
+    if (!s || !d_rgba) return fail(FSB_EINVAL, "fsb_view_density_device: bad argument");
+    DeviceGuard guard(s->device);
+    FSB_TRY(render_density(s, px_w, px_h));
+    *d_rgba = s->view_buf;
+    return FSB_OK;
+}
+
+int fsb_view_density(fsb_sim *s, int px_w, int px_h, unsigned char *host_rgba)
+{
+    if (!s || !host_rgba) return fail(FSB_EINVAL, "fsb_view_density: bad argument");
+    DeviceGuard guard(s->device);
+    FSB_TRY(render_density(s, px_w, px_h));
+    FSB_CUDA(cudaMemcpyAsync(host_rgba, s->view_buf, (size_t)px_w * px_h * 4, cudaMemcpyDeviceToHost, s->stream));
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
     return FSB_OK;
 }
 

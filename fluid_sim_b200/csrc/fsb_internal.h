@@ -117,6 +117,12 @@ cudaError_t launch_apply_sources(float *d, float *u, float *v, const SourceEntry
                                  int nseg, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------
+// Headless density view (view.cu): the reference viewer's quads + density shader per pixel, RGBA8, row 0 = bottom
+// ------------------------------------------------------------------------------------
+cudaError_t launch_view_density(const float *d, const GridView &G, int px_w, int px_h, unsigned char *rgba,
+                                cudaStream_t st);
+
+// ------------------------------------------------------------------------------------
 // Noise (noise.cu): u, v += ((float)rand()/RAND_MAX - 0.5f) * 1e-4f over the full grid
 // ------------------------------------------------------------------------------------
 constexpr int kNoiseCellsPerLane = 256;                          // contiguous cells generated by one lane

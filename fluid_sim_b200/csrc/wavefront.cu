@@ -1218,7 +1218,7 @@ int sweep_max_stages(int levels)
 namespace {
 
 constexpr size_t kNaFlagBytes = (size_t)kMaxStages * kWfMaxCtas * 2 * sizeof(unsigned long long);   // 256 KiB
-constexpr size_t kNaRingBytes = (size_t)8 << 20;                                                      // 8 MiB
+constexpr size_t kNaRingBytes = (size_t)16 << 20;                                                     // 16 MiB (the rings carry a tag with every float)
 constexpr size_t kNaScratchBytes = kNaFlagBytes + kNaRingBytes;
 
 // Resident on every GPU that loads the library, until the process exits.  The name below is only a

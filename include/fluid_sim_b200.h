@@ -190,7 +190,7 @@ int fsb_blk_advect_density(fsb_sim *s, float dt, int plus_zero);
  * whole GPU for its own pools at start-up (a later cudaMalloc simply fails there), or a frame / control
  * loop that must never run into the device-wide synchronisation and unbounded latency that cudaMalloc and
  * cudaFree imply.  fsb_create / fsb_step size their inter-CTA boundary rings with cudaMalloc on first use;
- * this entry point keeps the same rings and progress words in one fixed 8.25 MiB array that is part of
+ * this entry point keeps the same rings and progress words in one fixed 16.25 MiB array that is part of
  * the library image (every GPU that loads the library holds it until the process exits) and calls no
  * cudaMalloc, cudaFree or any other allocating routine.
  *
@@ -208,6 +208,19 @@ int fsb_blk_advect_density(fsb_sim *s, float dt, int plus_zero);
  *     second thread) race with each other - serialise them; calls on one stream are safe back to back. */
 int fsb_pressure_sweeps_noalloc(const float *d_divergence, float *d_pressure, int width, int height, int sweeps,
                                 void *stream);
+
+/* Headless density view: what the reference viewer draws for the density field
+ * (src/main.cpp:388-427 quads, :32-41 fragment shader, :376-377 blending, :345 clear colour), evaluated per pixel
+ * by a CUDA kernel with no graphics API.  px_w x px_h RGBA8 pixels, 4 bytes each, row 0 = bottom window row (GL
+ * convention); the reference's window is 800 x 600 (src/main.cpp:9-10).  Pixel = cleared black (0,0,0,255) unless
+ * its centre lies in the quad of a cell with density >= 0.01: then rgb = (d, 0, 1-d) * a, a = min(2d, 0.8),
+ * alpha = a*a + (1-a), everything clamped to [0,1] and rounded to 8 bits.
+ *   fsb_view_density         renders and copies the image to host_rgba (px_w*px_h*4 bytes); synchronises.
+ *   fsb_view_density_device  renders into a library-owned device buffer (valid until the next view call or
+ *                            fsb_destroy) and returns its address; queued on the simulation's stream, not waited for.
+ * Not available on column blocks (gather the density first). */
+int fsb_view_density(fsb_sim *s, int px_w, int px_h, unsigned char *host_rgba);
+int fsb_view_density_device(fsb_sim *s, int px_w, int px_h, void **d_rgba);
 
 /* Number of kernels this library has launched on behalf of `s` so far. */
 int fsb_launch_count(const fsb_sim *s, uint64_t *count);

@@ -20,11 +20,22 @@ _lib = None
 
 
 def build(force=False):
-    src = os.path.join(HERE, "fluid_oracle.c")
-    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(src):
+    srcs = [os.path.join(HERE, "fluid_oracle.c"), os.path.join(HERE, "view_oracle.c")]
+    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(f) for f in srcs):
         subprocess.run(["gcc", "-std=c11", "-O2", "-ffp-contract=off", "-fPIC", "-shared",
-                        src, "-o", LIB, "-lm"], check=True)
+                        *srcs, "-o", LIB, "-lm"], check=True)
     return LIB
+
+
+def view_density(d, px_w=800, px_h=600):
+    """oracle/view_oracle.c: the reference viewer's density image of a [W, H] float32 array, [px_h, px_w, 4] uint8."""
+    L = lib()
+    d = np.ascontiguousarray(d, np.float32)
+    out = np.empty((px_h, px_w, 4), np.uint8)
+    L.ora_view_density.argtypes = [_fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    L.ora_view_density.restype = None
+    L.ora_view_density(d.ctypes.data_as(_fp), d.shape[0], d.shape[1], px_w, px_h, out.ctypes.data)
+    return out
 
 
 def lib():

@@ -1,0 +1,71 @@
+"""Headless density view: the CUDA kernel behind fsb_view_density against the CPU restatement
+of the reference viewer's quads + density shader (oracle/view_oracle.c; parity unpinned: the reference draws through
+OpenGL, which is unavailable on this box)."""
+import numpy as np
+import pytest
+
+from oracle import orasim
+
+
+def _density(w, h, seed):
+    rng = np.random.default_rng(seed)
+    d = rng.random((w, h), dtype=np.float32) * np.float32(1.6) - np.float32(0.2)   # below 0.01, inside (0,1), above 1
+    d[rng.random((w, h)) < 0.3] = 0.0
+    d[0, 0] = np.float32(0.01)        # exactly the skip threshold: drawn
+    d[1, 0] = np.float32(0.0099999)   # just below: skipped
+    d[2, 0] = np.float32(0.4)         # alpha reaches the 0.8 cap exactly at 0.4
+    return d
+
+
+def test_oracle_view_known_pixels():
+    """Hand-checked pixels of the restatement itself: one cell per pixel."""
+    d = np.zeros((4, 3), np.float32)
+    d[1, 2] = 0.25      # rgb = (0.25, 0, 0.75) * 0.5, alpha = 0.25 + 0.5
+    d[3, 0] = 2.0       # clamps: rgb = (1, 0, 0) * 0.8, alpha = 0.64 + 0.2
+    img = orasim.view_density(d, 4, 3)
+    assert img.shape == (3, 4, 4)
+    assert tuple(img[2, 1]) == (32, 0, 96, 191)      # 0.125*255 = 31.875 -> 32, 0.375*255 = 95.6 -> 96, 0.75*255 = 191.25
+    assert tuple(img[0, 3]) == (204, 0, 0, 214)      # 0.8*255 = 204, 0.84*255 = 214.2
+    assert tuple(img[0, 0]) == (0, 0, 0, 255)        # cleared
+    # several pixels per cell / several cells per pixel keep the image piecewise constant / point sampled
+    big = orasim.view_density(d, 8, 6)
+    assert (big[4:6, 2:4] == img[2, 1]).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h,pw,ph", [(200, 200, 800, 600), (48, 40, 97, 53), (257, 131, 800, 600),
+                                       (2048, 2048, 800, 600), (64, 96, 64, 96), (640, 512, 1920, 1080)])
+def test_view_density_matches_restatement(w, h, pw, ph):
+    import fluid_sim_b200 as fsb
+    d = _density(w, h, seed=w * 7 + h)
+    with fsb.FluidSim(w, h, noise="zero") as sim:
+        sim.write(fsb.DENSITY, d)
+        got = sim.view_density(pw, ph)
+        again = sim.view_density(pw, ph)
+    want = orasim.view_density(d, pw, ph)
+    assert np.array_equal(got, again)
+    bad = np.argwhere((got != want).any(axis=2))
+    assert bad.size == 0, f"{len(bad)} pixels differ, first at (row, col) = {tuple(bad[0])}: {got[tuple(bad[0])]} vs {want[tuple(bad[0])]}"
+    assert (got[..., 1] == 0).all()                       # the shader has no green
+    assert got[..., 3].min() >= 191                       # alpha = a*a + 1 - a has its minimum 0.75 at a = 0.5
+
+
+@pytest.mark.gpu
+def test_view_density_after_steps_and_bad_arguments():
+    import ctypes as C
+    import fluid_sim_b200 as fsb
+    from tests.util import demo_injection
+    with fsb.FluidSim(200, 200) as sim:
+        demo_injection(sim, 200, 200)
+        for _ in range(3):
+            sim.step(0.01)
+        img = sim.view_density()                          # the reference's 800 x 600 window
+        want = orasim.view_density(sim.read(fsb.DENSITY), 800, 600)
+        assert np.array_equal(img, want)
+        assert (img[..., 0] > 0).any()                    # something was drawn
+        with pytest.raises(fsb.FsbError):
+            sim.view_density(0, 600, out=np.empty(0, np.uint8))
+        ptr = C.c_void_p()
+        sim._check(sim._lib.fsb_view_density_device(sim._h, 320, 200, C.byref(ptr)))
+        assert ptr.value
+        sim.sync()
