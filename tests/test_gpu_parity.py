@@ -197,6 +197,22 @@ def test_step_with_diffusion_and_zero_noise():
         assert_bits(a, b, f"field {n}")
 
 
+def test_many_launches_ring_tags_wrap():
+    """The rings between CTAs carry a tag made of the launch number (14 bits) and the hand-over unit: more than 2^14
+    launches on one simulation must stay exact.  One strip per CTA, so every strip boundary crosses a ring."""
+    w, h = 40, 100
+    gpu, ora = make_pair(w, h, 10, 5, noise="zero", strips_per_cta=1)
+    d, u, v = vortex_lattice(w, h)
+    for s, ids in ((gpu, (fsb.DENSITY, fsb.VELOCITY_X, fsb.VELOCITY_Y)), (ora, (0, 1, 2))):
+        s.write(ids[0], d); s.write(ids[1], u); s.write(ids[2], v)
+    steps = 5600                                   # 3 sweep launches per step: 16800 launches
+    for _ in range(steps):
+        gpu.step(0.01); ora.step(0.01)
+    assert gpu.launch_count() > 3 * steps
+    for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+        assert_bits(a, b, f"field {n} after {steps} steps")
+
+
 def test_step_2048_config2():
     """Config 2 (2048^2, P=20): two steps of the vortex lattice against the oracle."""
     w = h = 2048
