@@ -324,20 +324,39 @@ def main():
     else:
         d2h = W * H * 4
 
+        # every step's density goes to pinned host memory, as the reference's loop reads every cell after every step;
+        # the copy of step k (fsb_read_field_async, second stream) overlaps with the velocity half of step k+1
+        bufs = [buf, sim.pinned_array()]
+        nframe = [0]
+
         def frame():
-            sim.addDensityN(xs, ys, ones); sim.addVelocityN(xs, ys, dx, dy); sim.step(0.01); sim.read(fsb.DENSITY, buf)
-        checksum_of = lambda: float(buf.astype(np.float64).sum())
+            sim.addDensityN(xs, ys, ones); sim.addVelocityN(xs, ys, dx, dy); sim.step(0.01)
+            sim.read_wait()                                   # the previous step's image is complete on the host
+            sim.read_async(fsb.DENSITY, bufs[nframe[0] % 2])
+            nframe[0] += 1
+
+        def checksum_of():
+            sim.read_wait()
+            return float(bufs[(nframe[0] - 1) % 2].astype(np.float64).sum())
     for _ in range(2):
         frame()
+    if not multi:
+        sim.read_wait()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record(stream)
+    t_host0 = time.perf_counter()
     for _ in range(K):
         frame()
+    if not multi:
+        sim.read_wait()                                       # the last image has arrived: end of the timed region
     e1.record(stream)
     sim.sync()
+    e2e_host_ms = (time.perf_counter() - t_host0) * 1e3
     barrier()
     e2e_ms = e0.elapsed_time(e1)
+    if not multi:
+        e2e_ms = max(e2e_ms, e2e_host_ms)                     # the copies run on a second stream: take the host clock too
     if world > 1:
         t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -75,6 +75,8 @@ ABI = [
     ("fsb_get_width", C.c_int, [_SIM]),
     ("fsb_get_height", C.c_int, [_SIM]),
     ("fsb_read_field", C.c_int, [_SIM, C.c_int, C.c_void_p]),
+    ("fsb_read_field_async", C.c_int, [_SIM, C.c_int, C.c_void_p]),
+    ("fsb_read_wait", C.c_int, [_SIM]),
     ("fsb_view_density", C.c_int, [_SIM, C.c_int, C.c_int, C.c_void_p]),
     ("fsb_view_density_device", C.c_int, [_SIM, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
     ("fsb_write_field", C.c_int, [_SIM, C.c_int, C.c_void_p]),
@@ -251,6 +253,14 @@ class FluidSim:
         arr = np.ascontiguousarray(arr, np.float32)
         assert arr.size == self.width * self.height
         self._check(self._lib.fsb_add_field(self._h, field, arr.ctypes.data))
+
+    def read_async(self, field, out):
+        """Queue the device-to-host copy of a field into `out` (a pinned_array()); later steps overlap with it."""
+        assert out.dtype == np.float32 and out.size == self.width * self.height and out.flags.c_contiguous
+        self._check(self._lib.fsb_read_field_async(self._h, field, out.ctypes.data))
+
+    def read_wait(self):
+        self._check(self._lib.fsb_read_wait(self._h))
 
     def view_density(self, px_w=800, px_h=600, out=None):
         """The reference viewer's density image (src/main.cpp:388-427 + density shader) as [px_h, px_w, 4] uint8,

@@ -81,6 +81,11 @@ struct fsb_sim {
     // column block of a multi-rank run (is_block == false: the whole grid)
     bool is_block = false;
     int strip_begin = 0, strip_end = -1;       // 32-column strips of the sweep chain this rank runs
+    // fsb_read_field_async: a device-to-host copy on its own stream, ordered against later writers of that buffer
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_ready = nullptr, ev_copied = nullptr;
+    bool copy_pending = false;
+    const float *copy_src = nullptr;
     unsigned char *view_buf = nullptr;          // RGBA8 image of the last fsb_view_density* call
     size_t view_bytes = 0;
     unsigned char *link_buf = nullptr;          // [rings | in_prod | cons], shared with both neighbours through CUDA IPC
@@ -229,9 +234,32 @@ int set_boundary1(fsb_sim *s, float *x, int b, int plus_zero = 0)
     return set_boundary(s, &j, 1);
 }
 
-int flush_sources(fsb_sim *s)
+// Later work on the simulation's stream must not overwrite a buffer an asynchronous read is still copying.
+int order_after_copy(fsb_sim *s)
 {
+    if (s->copy_pending) FSB_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied, 0));
+    return FSB_OK;
+}
+
+enum SourceSel { kAllSources = 0, kVelocitySources = 1, kDensitySources = 2 };
+
+int flush_sources(fsb_sim *s, SourceSel sel = kAllSources)
+{
+    if (sel == kAllSources) FSB_TRY(order_after_copy(s));      // every entry point but fsb_step comes through here
     if (s->pending.empty()) return FSB_OK;
+    std::vector<SourceEntry> chosen, rest;
+    if (sel != kAllSources) {
+        for (const SourceEntry &q : s->pending) ((sel == kDensitySources) == (q.field == 0) ? chosen : rest).push_back(q);
+        s->pending.swap(chosen);                                  // flushed now; `rest` is restored below
+        if (s->pending.empty()) {
+            s->pending.swap(rest);
+            return FSB_OK;
+        }
+    }
+    struct Restore {
+        std::vector<SourceEntry> &dst, &src;
+        ~Restore() { dst.insert(dst.end(), src.begin(), src.end()); }
+    } restore{s->pending, rest};
     // group by (field, cell) keeping call order inside a group: `+=` is applied in the order of the calls
     std::vector<SourceEntry> &e = s->pending;
     std::stable_sort(e.begin(), e.end(), [](const SourceEntry &a, const SourceEntry &b) {
@@ -619,6 +647,9 @@ int fsb_destroy(fsb_sim *s)
         if (s->view_buf) cudaFree(s->view_buf);
         for (auto &r : s->prof_open) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         for (auto &e : s->prof_free) cudaEventDestroy(e);
+        if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+        if (s->ev_ready) cudaEventDestroy(s->ev_ready);
+        if (s->ev_copied) cudaEventDestroy(s->ev_copied);
         if (s->stream) cudaStreamDestroy(s->stream);
         (void)cudaGetLastError();
     }
@@ -631,6 +662,7 @@ int fsb_reset(fsb_sim *s)
     if (!s) return fail(FSB_EINVAL, "fsb_reset: null handle");
     DeviceGuard guard(s->device);
     s->pending.clear();
+    FSB_TRY(order_after_copy(s));
     for (int k = 0; k < kNumFields; ++k) FSB_CUDA(cudaMemsetAsync(s->f[k], 0, s->ncells * sizeof(float), s->stream));
     for (int k = 0; k < 2; ++k)
         if (s->temp[k]) FSB_CUDA(cudaMemsetAsync(s->temp[k], 0, s->ncells * sizeof(float), s->stream));
@@ -642,9 +674,15 @@ int fsb_step(fsb_sim *s, float dt)
 {
     if (!s) return fail(FSB_EINVAL, "fsb_step: null handle");
     DeviceGuard guard(s->device);
-    FSB_TRY(flush_sources(s));
+    // An asynchronous read of the density (fsb_read_field_async) may still be copying: the velocity step does not
+    // touch the density, so only the density half of the step waits for it; density sources are applied there too.
+    const bool copy_density = s->copy_pending && s->copy_src == s->f[FSB_DENSITY];
+    if (!copy_density) FSB_TRY(order_after_copy(s));
+    FSB_TRY(flush_sources(s, kVelocitySources));
     invalidate_mirror(s);
     FSB_TRY(velocity_step(s, dt));   // src/fluid_sim.cpp:26
+    FSB_TRY(order_after_copy(s));
+    FSB_TRY(flush_sources(s, kDensitySources));
     FSB_TRY(density_step(s, dt));    // src/fluid_sim.cpp:27
     return FSB_OK;
 }
@@ -785,6 +823,40 @@ int fsb_write_field(fsb_sim *s, int field, const float *host_src)
     FSB_CUDA(cudaMemcpyAsync(s->f[field], host_src, s->ncells * sizeof(float), cudaMemcpyHostToDevice, s->stream));
     FSB_CUDA(cudaStreamSynchronize(s->stream));
     if (field < 3) s->mirror_valid[field] = false;
+    return FSB_OK;
+}
+
+/* Queues a device-to-host copy of a field as it is after all work queued so far, on a second stream: it overlaps
+ * with later fsb_step calls (the library orders later writers of that buffer after the copy).  One read at a time. */
+int fsb_read_field_async(fsb_sim *s, int field, float *host_dst)
+{
+    if (!s || !host_dst || !valid_field(field)) return fail(FSB_EINVAL, "fsb_read_field_async: bad argument");
+    if (s->is_block) return fail(FSB_EINVAL, "fsb_read_field_async: not available on a column block");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));               // also orders this read after a previous one
+    if (!s->copy_stream) {
+        FSB_CUDA(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+        FSB_CUDA(cudaEventCreateWithFlags(&s->ev_ready, cudaEventDisableTiming));
+        FSB_CUDA(cudaEventCreateWithFlags(&s->ev_copied, cudaEventDisableTiming));
+    }
+    FSB_CUDA(cudaEventRecord(s->ev_ready, s->stream));
+    FSB_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_ready, 0));
+    FSB_CUDA(cudaMemcpyAsync(host_dst, s->f[field], s->ncells * sizeof(float), cudaMemcpyDeviceToHost, s->copy_stream));
+    FSB_CUDA(cudaEventRecord(s->ev_copied, s->copy_stream));
+    s->copy_pending = true;
+    s->copy_src = s->f[field];
+    return FSB_OK;
+}
+
+/* Blocks the host until the copy queued by fsb_read_field_async has arrived (no-op if there is none). */
+int fsb_read_wait(fsb_sim *s)
+{
+    if (!s) return fail(FSB_EINVAL, "fsb_read_wait: null handle");
+    if (!s->copy_pending) return FSB_OK;
+    DeviceGuard guard(s->device);
+    FSB_CUDA(cudaEventSynchronize(s->ev_copied));
+    s->copy_pending = false;
+    s->copy_src = nullptr;
     return FSB_OK;
 }
 

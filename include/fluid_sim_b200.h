@@ -112,6 +112,14 @@ int fsb_get_height(const fsb_sim *s);
 /* Whole-field transfers with HOST buffers of width*height floats (the bulk form of the
  * per-cell getters the reference's render loop issues, src/main.cpp:388-396). */
 int fsb_read_field(fsb_sim *s, int field, float *host_dst);
+/* The same copy without stalling the frame loop (the reference's loop reads every cell after every step,
+ * src/main.cpp:388-396): fsb_read_field_async queues the device-to-host copy of the field as it is after all work
+ * queued so far on a second stream and returns; later fsb_step calls overlap with it (the library orders whatever
+ * overwrites that buffer after the copy: for the density that is only the density half of the next step).
+ * fsb_read_wait blocks until the data is in host_dst.  One outstanding read per simulation; host_dst should be
+ * page-locked (fsb_host_alloc) or the copy will not overlap.  Not available on column blocks. */
+int fsb_read_field_async(fsb_sim *s, int field, float *host_dst);
+int fsb_read_wait(fsb_sim *s);
 int fsb_write_field(fsb_sim *s, int field, const float *host_src);
 /* density += host_src (one addDensity per cell); velocity likewise */
 int fsb_add_field(fsb_sim *s, int field, const float *host_src);

@@ -197,6 +197,32 @@ def test_step_with_diffusion_and_zero_noise():
         assert_bits(a, b, f"field {n}")
 
 
+def test_async_read_is_a_snapshot():
+    """fsb_read_field_async returns the field as of the call, even though the following steps (and source injections)
+    are queued while the copy is still in flight."""
+    w, h = 512, 384
+    gpu, ora = make_pair(w, h, 20, 5)
+    demo_injection(gpu, w, h); demo_injection(ora, w, h)
+    bufs = [gpu.pinned_array(), gpu.pinned_array()]
+    snaps = []
+    for k in range(4):
+        gpu.addDensity(w // 3 + k, h // 2, 2.5); ora.addDensity(w // 3 + k, h // 2, 2.5)
+        gpu.addVelocity(w // 3, h // 2 + k, 0.3, -0.2); ora.addVelocity(w // 3, h // 2 + k, 0.3, -0.2)
+        gpu.step(0.01); ora.step(0.01)
+        gpu.read_wait()                                  # the previous snapshot has arrived ...
+        if k:
+            assert_bits(bufs[(k - 1) % 2].reshape(w, h), snaps[-1], f"density snapshot of step {k - 1}")
+        gpu.read_async(fsb.DENSITY, bufs[k % 2])         # ... queue this one and go on
+        snaps.append(ora.read(0).copy())
+    gpu.read_wait()
+    assert_bits(bufs[3 % 2].reshape(w, h), snaps[-1], "density snapshot of the last step")
+    for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+        assert_bits(a, b, f"field {n}")
+    # velocity snapshots take the conservative path (the next step waits for the copy)
+    gpu.read_async(fsb.VELOCITY_X, bufs[0]); gpu.step(0.01); gpu.read_wait()
+    assert_bits(bufs[0].reshape(w, h), ora.read(1), "velocity snapshot")
+
+
 def test_many_launches_ring_tags_wrap():
     """The rings between CTAs carry a tag made of the launch number (14 bits) and the hand-over unit: more than 2^14
     launches on one simulation must stay exact.  One strip per CTA, so every strip boundary crosses a ring."""
