@@ -272,6 +272,30 @@ class BlockFluidSim:
             out = self.owned(field).contiguous().cpu()
         return out.numpy()
 
+    def read_owned_async(self, field, host):
+        """Queue the copy of this rank's owned columns of a field into `host` (a pinned [width, ncols] float32 tensor)
+        and return; the copy runs on a second stream from a staging buffer, so later steps overlap with it."""
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._staging = torch.empty((self.width, self.ncols), dtype=torch.float32, device=self.device)
+            self._copy_done = None
+        with torch.cuda.stream(self.stream):
+            if self._copy_done is not None:
+                self.stream.wait_event(self._copy_done)        # the staging buffer is free again
+            self._staging.copy_(self.owned(field))
+            ready = torch.cuda.Event()
+            ready.record(self.stream)
+        self._copy_stream.wait_event(ready)
+        with torch.cuda.stream(self._copy_stream):
+            host.copy_(self._staging, non_blocking=True)
+            self._copy_done = torch.cuda.Event()
+            self._copy_done.record(self._copy_stream)
+
+    def read_wait(self):
+        """Block until the copy queued by read_owned_async has arrived."""
+        if getattr(self, "_copy_done", None) is not None:
+            self._copy_done.synchronize()
+
     def gather(self, field, dst=0):
         """Full [width, height] array on rank `dst` (None elsewhere)."""
         with torch.cuda.stream(self.stream):
