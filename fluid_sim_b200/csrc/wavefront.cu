@@ -21,14 +21,16 @@
 //     stream to.  Stage 0 is fed from HBM through cp.async row tiles, the last stage writes the
 //     result rows back.  All sweeps of a pass therefore read and write each cell of HBM once.
 //   * strips: lane 0 takes its left neighbours from the previous strip of the same stage: through a
-//     shared-memory ring inside a CTA, through a global ring with acquire/release progress flags
-//     between CTAs (batches of 16 steps, moved by the comm warp).  The launch is cooperative so that every CTA of a chain
-//     is resident while its right neighbour waits for it.
+//     shared-memory ring inside a CTA, through a ring in global memory between CTAs (units of 8 steps,
+//     moved by two transfer warps; every 16-byte word carries its own tag, so there are no flags and no
+//     fences on that path), and through the same kind of ring in the neighbouring GPU's memory between
+//     ranks.  The launch is cooperative so that every CTA of a chain is resident while its right
+//     neighbour waits for it.
 //   * there is no CTA-wide barrier in the main loop: every compute warp publishes the last step it
 //     has completed in shared memory and, before each group of 4 steps, checks that its producers
 //     (left strip, previous stage) are far enough ahead and its consumers (right strip, next stage)
-//     have freed the ring slots it is about to overwrite.  One extra "comm" warp per CTA moves the
-//     CTA-edge rings to and from global memory, so compute warps never wait on L2 latency.
+//     have freed the ring slots it is about to overwrite.  Two extra warps per CTA move the CTA-edge
+//     rings to and from global memory, so compute warps never wait on L2 latency.
 //   * wall cells are evaluated in the pipeline with the value setBoundary() would have left in the
 //     array at the moment the reference reads it (warp-uniform fix-ups, only near walls).
 //
@@ -45,6 +47,13 @@ namespace {
 constexpr int kToff = 32;        // time offset: lane g sits on row t - kToff - g at level 0
 constexpr int kTileRows = 64;    // rows of an HBM staging ring (input tiles, result tile)
 constexpr int kTileFloats = kTileRows * 32;
+// Compile-time switches (defaults are what ships; the others are kept as measured experiments):
+//   WF_GROUP (4)          steps a warp runs between two progress checks
+//   WF_XFER (8)           steps per ring hand-over between CTAs: 4 saturates the transfer warps, 16 adds latency
+//   WF_FLUSH_OFFLOAD (0)  result write-back by the export warp instead of the last-stage warp: 8 % slower
+//   WF_CLUSTER_MODE (0)   2 = hand-over through distributed shared memory inside thread-block clusters: slower
+//   WF_PROFILE            in-kernel cycle counters printed per warp (development builds only)
+//   WF_STRICT_FENCES      acquire/release instructions instead of volatile accesses on the shared-memory counters
 // Result rows are written back by the last-stage warp itself (0) or by the export helper warp (1).
 // Measured on B200 at 8192^2: the helper variant loses about 8 % (it competes for issue slots with the
 // compute warps of its scheduler), so the default is 0.
@@ -56,12 +65,6 @@ constexpr int kTileFloats = kTileRows * 32;
 #endif
 #ifndef WF_XFER
 #define WF_XFER 8           // steps per ring hand-over between CTAs (4, 8 or 16)
-#endif
-#ifndef WF_BACKOFF
-#define WF_BACKOFF 0        // > 0: failed polls of a wait before the warp starts sleeping between polls
-#endif
-#ifndef WF_TOP_PATH
-#define WF_TOP_PATH 1       // dedicated step body for batches that touch only the top wall row
 #endif
 #ifndef WF_CLUSTER_MODE
 #define WF_CLUSTER_MODE 0   // 0: no cluster code, 1: cluster barriers only, 2: hand-over through distributed shared memory
@@ -508,8 +511,8 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
     // =============================== comm warps ==================================================
     // Warp NW moves the left neighbours in (global ring written by the CTA on the left -> edge_in), warp
     // NW+1 moves the right edge out (edge_out -> global ring read by the CTA on the right); lane gi serves
-    // stage gi.  Every round handles all transfers that are ready, with one fence for all of them, so the
-    // cost of a round does not grow with the number of stages.
+    // stage gi.  Every round handles all transfers that are ready; the import loads of several stages are in
+    // flight together, so the cost of a round hardly grows with the number of stages.
     if (w >= NW) {
         const bool is_exp = (w == NW + 1);
         // lanes 0..15: one ring-transfer machine per stage; lanes 16..31 of the export warp: one result
@@ -858,9 +861,6 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
         // ---- wait for producers / consumers ------------------------------------------------------
         {
             const int need = min(t + wait_add, wait_clamp);
-#if WF_BACKOFF
-            int misses = 0;
-#endif
             for (;;) {
                 bool ok = true;
                 if (wait_ptr) ok = ld_acquire_cta_s32(wait_ptr) >= need;
@@ -870,10 +870,6 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 if (__all_sync(0xffffffffu, ok)) break;
 #ifdef WF_PROFILE
                 pf_spins++;
-#endif
-#if WF_BACKOFF
-                // a warp that keeps missing is far from its turn (pipeline fill): stop competing for issue slots
-                if (++misses > WF_BACKOFF) __nanosleep(64);
 #endif
             }
             // counters written by another CTA of the cluster were polled with plain loads: order the data after them
@@ -885,11 +881,7 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
 #endif
         // ---- once per batch of 16 steps ----------------------------------------------------------
         if ((t & (kWfBatch - 1)) == 0) {
-#ifdef WF_EXP_NOFILL
-            if (false) {
-#else
             if (g == 0) {
-#endif
                 // stage the rows this strip reaches during the next batch
                 cp_async_wait_all();
                 stage_tile_rows(t + kWfBatch);
@@ -952,14 +944,12 @@ __global__ void __launch_bounds__(WfLayout<S>::kMaxThreads, WfLayout<S>::kMinBlo
                 wf_step<S, MODE, kStepRight>(x, Ua, Ub, t + u2, lane, gp, fix, wmask, cx);
                 wf_step<S, MODE, kStepRight>(x, Ub, Ua, t + u2 + 1, lane, gp, fix, wmask, cx);
             }
-#if WF_TOP_PATH
         } else if (fix == kFixTop) {
 #pragma unroll 1
             for (int u2 = 0; u2 < kGroup; u2 += 2) {
                 wf_step<S, MODE, kStepTop>(x, Ua, Ub, t + u2, lane, gp, fix, wmask, cx);
                 wf_step<S, MODE, kStepTop>(x, Ub, Ua, t + u2 + 1, lane, gp, fix, wmask, cx);
             }
-#endif
         } else {
 #pragma unroll 1
             for (int u2 = 0; u2 < kGroup; u2 += 2) {
