@@ -1204,14 +1204,19 @@ int fsb_blk_gradient(fsb_sim *s)
 
 /* RK4 advection of both velocity components (halo columns must hold the neighbours' values out to the trace
  * radius); the fields swap roles with the prev* buffers, boundaries are left to the caller. */
-int fsb_blk_advect_velocity(fsb_sim *s, float dt)
+int fsb_blk_advect_velocity(fsb_sim *s, float dt, int extend_halo)
 {
     if (!s) return fail(FSB_EINVAL, "null handle");
     DeviceGuard guard(s->device);
+    GridView G = s->G;
+    if (extend_halo) {      // one more column towards every neighbouring rank (the grid's own walls stay excluded)
+        if (G.j0 > 0 && G.j0 - 1 >= G.jbase) G.j0 -= 1;
+        if (G.j1 < G.H && G.j1 + 1 <= G.jbase + G.pitch) G.j1 += 1;
+    }
     {
         ProfScope ps(s, FSB_PROF_ADVECT_VELOCITY);
         FSB_CUDA(launch_advect_rk4(s->f[FSB_PREV_VEL_X], s->f[FSB_VELOCITY_X], s->f[FSB_PREV_VEL_Y], s->f[FSB_VELOCITY_Y],
-                                   s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], 0, s->G, dt, s->stream));
+                                   s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], 0, G, dt, s->stream));
     }
     s->launches += 1;
     std::swap(s->f[FSB_VELOCITY_X], s->f[FSB_PREV_VEL_X]);

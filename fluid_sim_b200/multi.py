@@ -256,7 +256,7 @@ class BlockFluidSim:
         lo, hi = self.halo - width, self.halo + self.ncols + width
         u, v = self.tensor(VELOCITY_X)[:, lo:hi], self.tensor(VELOCITY_Y)[:, lo:hi]
         m = torch.maximum(u.abs().max(), v.abs().max())
-        need = torch.ceil(m * (dt * self.width)) + 2.0
+        need = torch.ceil(m * (dt * self.width)) + 3.0      # + bilinear tap + rounding + the extra advected halo column
         self._overshoot = torch.maximum(self._overshoot, need - float(width))
 
     # -- inputs / outputs -----------------------------------------------------------------------------
@@ -354,10 +354,12 @@ class BlockFluidSim:
             self._halo([VELOCITY_X, VELOCITY_Y], self.reach)
             self._check_reach(dt, self.reach)
             self._mark("haloR")
-            self._check(self._lib.fsb_blk_advect_velocity(self._h, dt))
+            # the first halo column on each side is advected here as well: the divergence of the second projection
+            # needs it, and the R-column halo just received covers its traces too (one exchange less per step)
+            self._check(self._lib.fsb_blk_advect_velocity(self._h, dt, 1))
             self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
             self._mark("pointwise")
-            self._project(fresh_halo=False)
+            self._project(fresh_halo=True)
             # density: diffusion 0 is the identity d + 0.0f plus the boundary update, folded into the gather
             self._bnd([DENSITY], [0], [1])
             self._halo([DENSITY, VELOCITY_X, VELOCITY_Y], self.reach)

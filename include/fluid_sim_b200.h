@@ -187,7 +187,9 @@ int fsb_blk_sweep(fsb_sim *s, int mode, int nfields, const int *fields, const in
 int fsb_blk_set_boundary(fsb_sim *s, int n, const int *fields, const int *bs, const int *plus_zero);
 int fsb_blk_divergence(fsb_sim *s);
 int fsb_blk_gradient(fsb_sim *s);
-int fsb_blk_advect_velocity(fsb_sim *s, float dt);
+/* extend_halo: also advect the first halo column on every side that has a neighbour (the divergence that follows needs
+ * it; computing it here saves a halo exchange -- the halo must then hold the neighbours' values one column further). */
+int fsb_blk_advect_velocity(fsb_sim *s, float dt, int extend_halo);
 int fsb_blk_advect_density(fsb_sim *s, float dt, int plus_zero);
 
 /* No counterpart in the reference.
