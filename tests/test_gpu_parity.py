@@ -252,6 +252,26 @@ def test_step_2048_config2():
         assert_bits(a, b, f"2048^2 field {n}")
 
 
+def test_step_8192_config3_full_size():
+    """Config 3 at its full size (8192^2, P=40, the bench workload): one step of the vortex lattice with glibc noise
+    against the real reference (about a minute on one host core), else against the C restatement."""
+    w = h = 8192
+    if refsim.available(w, h, 40, 5):
+        ref = refsim.RefSim(w, h, 40, 5, seed=1)
+    else:
+        ref = OracleSim(w, h, 40, 5)
+    gpu = fsb.FluidSim(w, h, 40, 5)
+    d, u, v = vortex_lattice(w, h)
+    for fid, f in ((0, d), (1, u), (2, v)):
+        ref.write(fid, f); gpu.write(fid, f)
+    del d, u, v
+    ref.step(0.01); gpu.step(0.01)
+    for fid, n in ((0, "d"), (1, "u"), (2, "v")):
+        a, b = gpu.read(fid), ref.read(fid)
+        assert_bits(a, b, f"8192^2 field {n}")
+        assert rel_max_abs(a, b) <= TOL
+
+
 def test_step_real_reference_wide():
     """A wide grid (35 strips, several CTAs in the chain) against the real reference, if prebuilt."""
     w, h, p, d = 96, 1100, 20, 5
