@@ -369,11 +369,15 @@ def main():
     # -------- the same per-GPU workload on ONE GPU (rank 0, the other ranks idle): the N = 1 point of the weak-scaling
     # series.  `bench.py --gpus 1` measures the 8192^2, P=40 headline instead, whose steps cost 2.5x less per cell.
     base = None
-    if multi:
+    c5 = (32768, 4096, 100)
+    if multi or (args.workload != "config5" and not (args.width and args.height)):
         barrier()
         if rank == 0:
-            one = fsb.FluidSim(W, H // world, P, 5, device=local_rank)
-            d, u, v = vortex_lattice(W, H // world)
+            bw, bh, bp = (W, H // world, P) if multi else c5
+            if not multi:
+                sim.close()                                       # free the headline workload's fields first
+            one = fsb.FluidSim(bw, bh, bp, 5, device=local_rank)
+            d, u, v = vortex_lattice(bw, bh)
             buf1 = one.pinned_array()
             for fid, arr in ((fsb.DENSITY, d), (fsb.VELOCITY_X, u), (fsb.VELOCITY_Y, v)):
                 buf1[...] = arr
@@ -390,9 +394,12 @@ def main():
             b1.record(st1)
             one.sync()
             base_ms = b0.elapsed_time(b1) / K
-            base = {"n_gpus": 1, "grid": [W, H // world], "proj_iters": P, "ms_per_step": base_ms,
-                    "value": W * (H // world) / (base_ms * 1e-3), "unit": UNIT,
-                    "command": "python bench.py --gpus 1 --workload config5"}
+            base = {"n_gpus": 1, "grid": [bw, bh], "proj_iters": bp, "ms_per_step": base_ms,
+                    "value": bw * bh / (base_ms * 1e-3), "unit": UNIT,
+                    "command": "python bench.py --gpus 1 --workload config5",
+                    "note": "N = 1 point of the weak-scaling series that `--gpus N` runs (config 5: 32768 rows x 4096 "
+                            "columns per GPU, P = 100); the headline `value` of a 1-GPU run is config 3 (8192^2, P = 40), "
+                            "whose steps cost 2.5x less per cell"}
             one.close()
         barrier()
 
