@@ -182,6 +182,7 @@ def main():
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--proj", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-scaling-base", action="store_true", help="skip the extra single-GPU run of the weak-scaling workload")
     ap.add_argument("--workload", default="", help="config5: run the weak-scaling per-GPU workload at N=1 too")
     ap.add_argument("--strips-per-cta", type=int, default=0)
     ap.add_argument("--sweeps-per-warp", type=int, default=0)
@@ -370,7 +371,7 @@ def main():
     # series.  `bench.py --gpus 1` measures the 8192^2, P=40 headline instead, whose steps cost 2.5x less per cell.
     base = None
     c5 = (32768, 4096, 100)
-    if multi or (args.workload != "config5" and not (args.width and args.height)):
+    if not args.no_scaling_base and (multi or (args.workload != "config5" and not (args.width and args.height))):
         barrier()
         if rank == 0:
             bw, bh, bp = (W, H // world, P) if multi else c5
