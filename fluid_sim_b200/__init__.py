@@ -79,6 +79,7 @@ ABI = [
     ("fsb_read_wait", C.c_int, [_SIM]),
     ("fsb_view_density", C.c_int, [_SIM, C.c_int, C.c_int, C.c_void_p]),
     ("fsb_view_density_device", C.c_int, [_SIM, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    ("fsb_view_velocity", C.c_int, [_SIM, C.c_int, C.c_int, C.c_void_p]),
     ("fsb_write_field", C.c_int, [_SIM, C.c_int, C.c_void_p]),
     ("fsb_add_field", C.c_int, [_SIM, C.c_int, C.c_void_p]),
     ("fsb_host_alloc", C.c_void_p, [C.c_size_t]),
@@ -269,6 +270,14 @@ class FluidSim:
             out = np.empty((px_h, px_w, 4), np.uint8)
         assert out.dtype == np.uint8 and out.size == px_w * px_h * 4 and out.flags.c_contiguous
         self._check(self._lib.fsb_view_density(self._h, px_w, px_h, out.ctypes.data))
+        return out
+
+    def view_velocity(self, px_w=800, px_h=600, out=None):
+        """The viewer's image with velocity vectors on (src/main.cpp:452-514): density image + glyph lines."""
+        if out is None:
+            out = np.empty((px_h, px_w, 4), np.uint8)
+        assert out.dtype == np.uint8 and out.size == px_w * px_h * 4 and out.flags.c_contiguous
+        self._check(self._lib.fsb_view_velocity(self._h, px_w, px_h, out.ctypes.data))
         return out
 
     def fields(self):

@@ -1262,6 +1262,20 @@ static int render_density(fsb_sim *s, int px_w, int px_h)
     return FSB_OK;
 }
 
+/* What the reference draws with the velocity vectors switched on (src/main.cpp:452-514): the density image, then one
+ * line per sampled cell. */
+int fsb_view_velocity(fsb_sim *s, int px_w, int px_h, unsigned char *host_rgba)
+{
+    if (!s || !host_rgba) return fail(FSB_EINVAL, "fsb_view_velocity: bad argument");
+    DeviceGuard guard(s->device);
+    FSB_TRY(render_density(s, px_w, px_h));
+    FSB_CUDA(launch_view_glyphs(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->G, px_w, px_h, s->view_buf, s->stream));
+    s->launches += 1;
+    FSB_CUDA(cudaMemcpyAsync(host_rgba, s->view_buf, (size_t)px_w * px_h * 4, cudaMemcpyDeviceToHost, s->stream));
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    return FSB_OK;
+}
+
 int fsb_view_density_device(fsb_sim *s, int px_w, int px_h, void **d_rgba)
 {
     if (!s || !d_rgba) return fail(FSB_EINVAL, "fsb_view_density_device: bad argument");

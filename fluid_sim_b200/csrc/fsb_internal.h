@@ -121,6 +121,9 @@ cudaError_t launch_apply_sources(float *d, float *u, float *v, const SourceEntry
 // ------------------------------------------------------------------------------------
 cudaError_t launch_view_density(const float *d, const GridView &G, int px_w, int px_h, unsigned char *rgba,
                                 cudaStream_t st);
+// velocity glyph lines (every second cell, |v| >= 0.1) blended over the image already in `rgba`
+cudaError_t launch_view_glyphs(const float *u, const float *v, const GridView &G, int px_w, int px_h, unsigned char *rgba,
+                               cudaStream_t st);
 
 // ------------------------------------------------------------------------------------
 // Noise (noise.cu): u, v += ((float)rand()/RAND_MAX - 0.5f) * 1e-4f over the full grid

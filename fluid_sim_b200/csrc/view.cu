@@ -1,5 +1,6 @@
-// Headless density view: the reference viewer's per-cell quads and its density shader,
-// evaluated per pixel by a CUDA kernel into an RGBA8 device buffer.  No graphics API is involved.
+// Headless views: the reference viewer's per-cell density quads with its density shader,
+// and its velocity glyph lines, evaluated per pixel by CUDA kernels into an RGBA8 device buffer.  No graphics API is
+// involved.
 //
 // What the reference draws (src/main.cpp):
 //   * clear colour (0, 0, 0, 1)                                                        :345
@@ -86,7 +87,103 @@ __global__ void view_density_kernel(const float *__restrict__ d, const GridView 
     out[(size_t)py * pw + px] = make_uchar4((unsigned char)v[0], (unsigned char)v[1], (unsigned char)v[2], (unsigned char)v[3]);
 }
 
+// ---- velocity glyphs (src/main.cpp:452-514, colour ramp src/fluid_sim.cpp:482-519) ---------------
+// Every second cell in i and j with |v| >= 0.1 draws a line from the cell centre, 0.05 NDC long, in the direction of the
+// velocity, ramp colour, alpha 0.8, glLineWidth(2).  GL leaves the exact pixels of a wide non-antialiased line to the
+// implementation; here a pixel belongs to a line when its centre lies in the half-open span [start, end) along the
+// major axis and within [-1, 1) pixels of the line along the minor axis (two pixels per column / row).  Lines are
+// blended in the reference's draw order (i outer, j inner) over the density image.
+struct Glyph { float ax, ay, bx, by, r, g, b; bool on; };
+
+__device__ __forceinline__ Glyph make_glyph(float vx, float vy, int i, int j, float fw, float fh, float pw, float ph)
+{
+    Glyph q;
+    const float mag = sqrtf(__fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy)));      // glm::length
+    q.on = !(mag < 0.1f);
+    float nx = 0.0f, ny = 0.0f;
+    if (mag > 0.001f) {
+        nx = __fdiv_rn(vx, mag);
+        ny = __fdiv_rn(vy, mag);
+    }
+    const float ns = fminf(__fdiv_rn(mag, 10.0f), 1.0f);
+    if (ns < 0.25f) {
+        q.r = 0.0f; q.g = __fdiv_rn(ns, 0.25f); q.b = 1.0f;
+    } else if (ns < 0.5f) {
+        q.r = 0.0f; q.g = 1.0f; q.b = __fsub_rn(1.0f, __fdiv_rn(__fsub_rn(ns, 0.25f), 0.25f));
+    } else if (ns < 0.75f) {
+        q.r = __fdiv_rn(__fsub_rn(ns, 0.5f), 0.25f); q.g = 1.0f; q.b = 0.0f;
+    } else {
+        q.r = 1.0f; q.g = __fsub_rn(1.0f, __fdiv_rn(__fsub_rn(ns, 0.75f), 0.25f)); q.b = 0.0f;
+    }
+    const float cx = __fadd_rn(__fsub_rn(__fmul_rn(__fdiv_rn((float)i, fw), 2.0f), 1.0f), __fdiv_rn(1.0f, fw));
+    const float cy = __fadd_rn(__fsub_rn(__fmul_rn(__fdiv_rn((float)j, fh), 2.0f), 1.0f), __fdiv_rn(1.0f, fh));
+    const float ex = __fadd_rn(cx, __fmul_rn(nx, 0.05f));
+    const float ey = __fadd_rn(cy, __fmul_rn(ny, 0.05f));
+    // viewport transform to window coordinates
+    q.ax = __fmul_rn(__fmul_rn(__fadd_rn(cx, 1.0f), 0.5f), pw);
+    q.ay = __fmul_rn(__fmul_rn(__fadd_rn(cy, 1.0f), 0.5f), ph);
+    q.bx = __fmul_rn(__fmul_rn(__fadd_rn(ex, 1.0f), 0.5f), pw);
+    q.by = __fmul_rn(__fmul_rn(__fadd_rn(ey, 1.0f), 0.5f), ph);
+    return q;
+}
+
+__device__ __forceinline__ bool glyph_covers(const Glyph &q, float pcx, float pcy)
+{
+    const float dx = __fsub_rn(q.bx, q.ax), dy = __fsub_rn(q.by, q.ay);
+    const bool xmajor = fabsf(dx) >= fabsf(dy);
+    const float a0 = xmajor ? q.ax : q.ay, a1 = xmajor ? q.bx : q.by;      // major axis
+    const float m0 = xmajor ? q.ay : q.ax;                                  // minor axis at the start
+    const float dmaj = xmajor ? dx : dy, dmin = xmajor ? dy : dx;
+    const float pc = xmajor ? pcx : pcy, pm = xmajor ? pcy : pcx;
+    if (dmaj == 0.0f) return false;
+    const float lo = fminf(a0, a1), hi = fmaxf(a0, a1);
+    if (!(pc >= lo && pc < hi)) return false;
+    const float at = __fadd_rn(m0, __fmul_rn(__fsub_rn(pc, a0), __fdiv_rn(dmin, dmaj)));
+    const float off = __fsub_rn(pm, at);
+    return off >= -1.0f && off < 1.0f;
+}
+
+__global__ void view_glyphs_kernel(const float *__restrict__ u, const float *__restrict__ v, const GridView G, int pw, int ph,
+                                   uchar4 *__restrict__ img)
+{
+    const int px = blockIdx.x * blockDim.x + threadIdx.x;
+    const int py = blockIdx.y * blockDim.y + threadIdx.y;
+    if (px >= pw || py >= ph) return;
+    const float fw = (float)G.W, fh = (float)G.H, fpw = (float)pw, fph = (float)ph;
+    const float pcx = __fadd_rn((float)px, 0.5f), pcy = __fadd_rn((float)py, 0.5f);
+    // sampled cells whose line can reach this pixel: centre within 0.05 NDC (+ 2 pixels) of it, generously rounded
+    const float rx = 0.05f * 0.5f * fw + 2.0f * fw / fpw + 2.0f, ry = 0.05f * 0.5f * fh + 2.0f * fh / fph + 2.0f;
+    const float ci = pcx / fpw * fw, cj = pcy / fph * fh;          // the pixel in cell units
+    int i0 = max(0, (int)floorf(ci - rx)), i1 = min(G.W - 1, (int)ceilf(ci + rx));
+    int j0 = max(0, (int)floorf(cj - ry)), j1 = min(G.H - 1, (int)ceilf(cj + ry));
+    i0 += i0 & 1;
+    j0 += j0 & 1;
+    const uchar4 in = img[(size_t)py * pw + px];
+    int c[4] = {in.x, in.y, in.z, in.w};
+    const float sa = 0.8f, ia = __fsub_rn(1.0f, 0.8f);
+    for (int i = i0; i <= i1; i += 2)
+        for (int j = j0; j <= j1; j += 2) {
+            const size_t o = (size_t)i * G.pitch + (j - G.jbase);
+            const Glyph q = make_glyph(u[o], v[o], i, j, fw, fh, fpw, fph);
+            if (!q.on || !glyph_covers(q, pcx, pcy)) continue;
+            const float src[4] = {clamp01(q.r), clamp01(q.g), clamp01(q.b), sa};
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                c[k] = to_unorm8(__fadd_rn(__fmul_rn(src[k], sa), __fmul_rn(__fdiv_rn((float)c[k], 255.0f), ia)));
+        }
+    img[(size_t)py * pw + px] = make_uchar4((unsigned char)c[0], (unsigned char)c[1], (unsigned char)c[2], (unsigned char)c[3]);
+}
+
 }  // namespace
+
+cudaError_t launch_view_glyphs(const float *u, const float *v, const GridView &G, int pw, int ph, unsigned char *rgba,
+                               cudaStream_t st)
+{
+    if (pw < 1 || ph < 1) return cudaErrorInvalidValue;
+    const dim3 b(32, 8), g((pw + 31) / 32, (ph + 7) / 8);
+    view_glyphs_kernel<<<g, b, 0, st>>>(u, v, G, pw, ph, reinterpret_cast<uchar4 *>(rgba));
+    return cudaGetLastError();
+}
 
 cudaError_t launch_view_density(const float *d, const GridView &G, int pw, int ph, unsigned char *rgba, cudaStream_t st)
 {

@@ -231,6 +231,12 @@ int fsb_pressure_sweeps_noalloc(const float *d_divergence, float *d_pressure, in
  * Not available on column blocks (gather the density first). */
 int fsb_view_density(fsb_sim *s, int px_w, int px_h, unsigned char *host_rgba);
 int fsb_view_density_device(fsb_sim *s, int px_w, int px_h, void **d_rgba);
+/* The viewer's image with the velocity vectors switched on (src/main.cpp:452-514, toggle :17): the density image,
+ * then for every second cell in x and y with |v| >= 0.1 a line from the cell centre, 0.05 NDC long along the
+ * normalised velocity (getNormalizedVelocity), in getVelocityColor's ramp colour with alpha 0.8, line width 2.
+ * GL leaves the exact pixels of such a line to the implementation; this library's rule: a pixel belongs to a line
+ * when its centre lies in [start, end) along the major axis and within [-1, 1) pixels of it along the minor axis. */
+int fsb_view_velocity(fsb_sim *s, int px_w, int px_h, unsigned char *host_rgba);
 
 /* Number of kernels this library has launched on behalf of `s` so far. */
 int fsb_launch_count(const fsb_sim *s, uint64_t *count);

@@ -38,6 +38,18 @@ def view_density(d, px_w=800, px_h=600):
     return out
 
 
+def view_velocity(d, u, v, px_w=800, px_h=600):
+    """oracle/view_oracle.c: the viewer's image with velocity vectors on (density image, then the glyph lines)."""
+    L = lib()
+    img = view_density(d, px_w, px_h)
+    u = np.ascontiguousarray(u, np.float32)
+    v = np.ascontiguousarray(v, np.float32)
+    L.ora_view_glyphs.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    L.ora_view_glyphs.restype = None
+    L.ora_view_glyphs(u.ctypes.data_as(_fp), v.ctypes.data_as(_fp), u.shape[0], u.shape[1], px_w, px_h, img.ctypes.data)
+    return img
+
+
 def lib():
     global _lib
     if _lib is not None:

@@ -61,3 +61,66 @@ void ora_view_density(const float *d, int W, int H, int pw, int ph, unsigned cha
         }
     }
 }
+
+/* ---- velocity glyphs: src/main.cpp:452-514, colour ramp src/fluid_sim.cpp:482-519 ----
+ * Literal: walk the sampled cells in draw order, build the line, blend it over every pixel it covers.  The
+ * coverage rule (GL leaves wide non-antialiased lines to the implementation) is the one stated in
+ * include/fluid_sim_b200.h: pixel centre in [start, end) along the major axis, within [-1, 1) pixels of the line
+ * along the minor axis. */
+static int line_covers(float ax, float ay, float bx, float by, float pcx, float pcy)
+{
+    const float dx = bx - ax, dy = by - ay;
+    const int xmajor = fabsf(dx) >= fabsf(dy);
+    const float a0 = xmajor ? ax : ay, a1 = xmajor ? bx : by;
+    const float m0 = xmajor ? ay : ax;
+    const float dmaj = xmajor ? dx : dy, dmin = xmajor ? dy : dx;
+    const float pc = xmajor ? pcx : pcy, pm = xmajor ? pcy : pcx;
+    if (dmaj == 0.0f) return 0;
+    const float lo = fminf(a0, a1), hi = fmaxf(a0, a1);
+    if (!(pc >= lo && pc < hi)) return 0;
+    const float at = m0 + (pc - a0) * (dmin / dmaj);
+    const float off = pm - at;
+    return off >= -1.0f && off < 1.0f;
+}
+
+/* u, v: W x H floats; img: ph x pw x 4 bytes already holding the density image (ora_view_density) */
+void ora_view_glyphs(const float *u, const float *v, int W, int H, int pw, int ph, unsigned char *img)
+{
+    const float fw = (float)W, fh = (float)H, fpw = (float)pw, fph = (float)ph;
+    for (int i = 0; i < W; i += 2) {
+        for (int j = 0; j < H; j += 2) {
+            const float vx = u[(long)i * H + j], vy = v[(long)i * H + j];
+            const float magnitude = sqrtf(vx * vx + vy * vy);          /* glm::length */
+            float nx = 0.0f, ny = 0.0f;
+            if (magnitude > 0.001f) { nx = vx / magnitude; ny = vy / magnitude; }
+            if (magnitude < 0.1f) continue;
+            /* getVelocityColor */
+            const float ns = fminf(magnitude / 10.0f, 1.0f);
+            float r, g, b;
+            if (ns < 0.25f) { r = 0.0f; g = ns / 0.25f; b = 1.0f; }
+            else if (ns < 0.5f) { r = 0.0f; g = 1.0f; b = 1.0f - (ns - 0.25f) / 0.25f; }
+            else if (ns < 0.75f) { r = (ns - 0.5f) / 0.25f; g = 1.0f; b = 0.0f; }
+            else { r = 1.0f; g = 1.0f - (ns - 0.75f) / 0.25f; b = 0.0f; }
+            const float centerX = (float)i / fw * 2.0f - 1.0f + (1.0f / fw);
+            const float centerY = (float)j / fh * 2.0f - 1.0f + (1.0f / fh);
+            const float endX = centerX + nx * 0.05f, endY = centerY + ny * 0.05f;
+            const float ax = (centerX + 1.0f) * 0.5f * fpw, ay = (centerY + 1.0f) * 0.5f * fph;
+            const float bx = (endX + 1.0f) * 0.5f * fpw, by = (endY + 1.0f) * 0.5f * fph;
+            int x0 = (int)floorf(fminf(ax, bx)) - 2, x1 = (int)ceilf(fmaxf(ax, bx)) + 2;
+            int y0 = (int)floorf(fminf(ay, by)) - 2, y1 = (int)ceilf(fmaxf(ay, by)) + 2;
+            if (x0 < 0) x0 = 0;
+            if (y0 < 0) y0 = 0;
+            if (x1 > pw - 1) x1 = pw - 1;
+            if (y1 > ph - 1) y1 = ph - 1;
+            const float sa = 0.8f, ia = 1.0f - 0.8f;
+            const float src[4] = {clamp01(r), clamp01(g), clamp01(b), sa};
+            for (int py = y0; py <= y1; ++py)
+                for (int px = x0; px <= x1; ++px) {
+                    if (!line_covers(ax, ay, bx, by, (float)px + 0.5f, (float)py + 0.5f)) continue;
+                    unsigned char *q = img + 4 * ((long)py * pw + px);
+                    for (int c = 0; c < 4; ++c)
+                        q[c] = (unsigned char)to_unorm8(src[c] * sa + ((float)q[c] / 255.0f) * ia);
+                }
+        }
+    }
+}

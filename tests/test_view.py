@@ -69,3 +69,38 @@ def test_view_density_after_steps_and_bad_arguments():
         sim._check(sim._lib.fsb_view_density_device(sim._h, 320, 200, C.byref(ptr)))
         assert ptr.value
         sim.sync()
+
+
+def test_oracle_glyph_known_pixels():
+    """One horizontal glyph: 64 x 64 cells on 64 x 64 pixels, velocity (5, 0) at cell (10, 20)."""
+    w = h = 64
+    d = np.zeros((w, h), np.float32)
+    u = np.zeros((w, h), np.float32); v = np.zeros((w, h), np.float32)
+    u[10, 20] = 5.0                                  # |v| = 5: ramp at 0.5 -> (0, 1, 0) exactly at the green corner
+    img = orasim.view_velocity(d, u, v, 64, 64)
+    # start (10.5, 20.5) px, 0.05 NDC = 1.6 px long: column 10 (centre 10.5) is the only centre in [10.5, 12.1) besides 11
+    lit = np.argwhere(img[..., 1] > 0)
+    assert {tuple(p) for p in lit} == {(19, 10), (20, 10), (19, 11), (20, 11)}      # two rows per column: [-1, 1) around y
+    assert tuple(img[20, 10]) == (0, 204, 0, 214)    # green * 0.8 = 204; alpha 0.64 + 0.2 -> 214.2
+    u[11, 20] = 5.0                                  # odd cell: not sampled
+    assert np.array_equal(orasim.view_velocity(d, u, v, 64, 64), img)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h,pw,ph", [(200, 200, 800, 600), (48, 40, 97, 53), (257, 131, 640, 480), (64, 96, 64, 96)])
+def test_view_velocity_matches_restatement(w, h, pw, ph):
+    import fluid_sim_b200 as fsb
+    rng = np.random.default_rng(w + h)
+    d = _density(w, h, seed=w)
+    u = (rng.standard_normal((w, h)) * 3).astype(np.float32)
+    v = (rng.standard_normal((w, h)) * 3).astype(np.float32)
+    u[rng.random((w, h)) < 0.4] = 0.0; v[u == 0.0] = np.float32(0.05)       # below the 0.1 threshold: no line
+    u[0, 0], v[0, 0] = 30.0, -40.0                   # speed above the ramp's end
+    with fsb.FluidSim(w, h, noise="zero") as sim:
+        sim.write(fsb.DENSITY, d); sim.write(fsb.VELOCITY_X, u); sim.write(fsb.VELOCITY_Y, v)
+        got = sim.view_velocity(pw, ph)
+        dens = sim.view_density(pw, ph)
+    want = orasim.view_velocity(d, u, v, pw, ph)
+    bad = np.argwhere((got != want).any(axis=2))
+    assert bad.size == 0, f"{len(bad)} pixels differ, first at (row, col) = {tuple(bad[0])}: {got[tuple(bad[0])]} vs {want[tuple(bad[0])]}"
+    assert (got != dens).any()                       # lines were drawn over the density image
