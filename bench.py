@@ -166,6 +166,9 @@ def cpu_reference(H, P, nsteps, warmup, budget_s):
 def workload_for(n_gpus, args):
     if args.width and args.height:
         return args.width, args.height, args.proj or 40, "custom"
+    if args.workload == "config4":
+        # config 4 of BASELINE.json: one fixed 16384^2 grid, P = 20, cut into column blocks (strong scaling)
+        return 16384, 16384, args.proj or 20, "config4: 16384x16384 grid, 20 projection sweeps, strong-scaled"
     if n_gpus == 1 and args.workload != "config5":
         return 8192, 8192, args.proj or 40, "config3: 8192x8192 grid, 40 projection sweeps, 1xB200"
     # config 5 of BASELINE.json, weak-scaled: 32768 rows x 4096 columns per GPU (32768^2 at 8 GPUs), P = 100
@@ -183,7 +186,7 @@ def main():
     ap.add_argument("--proj", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-scaling-base", action="store_true", help="skip the extra single-GPU run of the weak-scaling workload")
-    ap.add_argument("--workload", default="", help="config5: run the weak-scaling per-GPU workload at N=1 too")
+    ap.add_argument("--workload", default="", help="config5: run the weak-scaling per-GPU workload at N=1 too; config4: 16384^2, P=20, strong scaling")
     ap.add_argument("--strips-per-cta", type=int, default=0)
     ap.add_argument("--sweeps-per-warp", type=int, default=0)
     ap.add_argument("--max-stages", type=int, default=0)
@@ -235,7 +238,8 @@ def main():
     if multi:
         from fluid_sim_b200.multi import BlockFluidSim
         from tests.util import vortex_lattice_block
-        sim = BlockFluidSim(W, H, P, 5, device=local_rank)
+        # (10, 2) passes leave room for two strips per CTA; the (10, 5) passes of config 5 need one strip per CTA
+        sim = BlockFluidSim(W, H, P, 5, device=local_rank, strips_per_cta=2 if P <= 20 else 1)
         a0, a1 = sim.jbase, sim.jbase + sim.pitch
         d, u, v = vortex_lattice_block(W, H, a0, a1)
         for fid, arr in ((fsb.DENSITY, d), (fsb.VELOCITY_X, u), (fsb.VELOCITY_Y, v)):
@@ -371,7 +375,7 @@ def main():
     # series.  `bench.py --gpus 1` measures the 8192^2, P=40 headline instead, whose steps cost 2.5x less per cell.
     base = None
     c5 = (32768, 4096, 100)
-    if not args.no_scaling_base and (multi or (args.workload != "config5" and not (args.width and args.height))):
+    if not args.no_scaling_base and args.workload != "config4" and (multi or (args.workload != "config5" and not (args.width and args.height))):
         barrier()
         if rank == 0:
             bw, bh, bp = (W, H // world, P) if multi else c5
@@ -451,7 +455,8 @@ def main():
                "host_cores_visible": os.cpu_count()}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(Wm, 3),
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "strong" if args.workload == "config4" else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload, "grid": [W, H], "grid_per_gpu": [W, H // world], "proj_iters": P, "diff_iters": 5, "dt": 0.01,
                        "input": "vortex lattice (SURVEY.md 8(d) I3) + glibc rand() noise",
