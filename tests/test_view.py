@@ -104,3 +104,29 @@ def test_view_velocity_matches_restatement(w, h, pw, ph):
     bad = np.argwhere((got != want).any(axis=2))
     assert bad.size == 0, f"{len(bad)} pixels differ, first at (row, col) = {tuple(bad[0])}: {got[tuple(bad[0])]} vs {want[tuple(bad[0])]}"
     assert (got != dens).any()                       # lines were drawn over the density image
+
+
+@pytest.mark.gpu
+def test_headless_view_example_writes_the_reference_frame(tmp_path):
+    """examples/headless_view.cpp (drop-in class + C ABI): 3 frames of the demo, image equal to the restatement's."""
+    import os
+    import subprocess
+    import fluid_sim_b200 as fsb
+    from tests.util import ROOT, demo_injection
+    exe = os.path.join(ROOT, "examples", "headless_view")
+    if not os.path.exists(exe):
+        pytest.skip("examples/headless_view not built")
+    ppm = tmp_path / "f.ppm"
+    out = subprocess.run([exe, "3", str(ppm), "1", "320", "240"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    raw = ppm.read_bytes()
+    head = b"P6\n320 240\n255\n"
+    assert raw.startswith(head) and len(raw) == len(head) + 320 * 240 * 3
+    got = np.frombuffer(raw[len(head):], np.uint8).reshape(240, 320, 3)[::-1]      # back to bottom-up rows
+    with fsb.FluidSim(200, 200) as sim:
+        demo_injection(sim, 200, 200)
+        for _ in range(3):
+            sim.step(0.01)
+        d, u, v = sim.read(fsb.DENSITY), sim.read(fsb.VELOCITY_X), sim.read(fsb.VELOCITY_Y)
+    want = orasim.view_velocity(d, u, v, 320, 240)[..., :3]
+    assert np.array_equal(got, want)
