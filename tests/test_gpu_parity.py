@@ -223,6 +223,26 @@ def test_async_read_is_a_snapshot():
     assert_bits(bufs[0].reshape(w, h), ora.read(1), "velocity snapshot")
 
 
+@pytest.mark.parametrize("seed", range(40))
+def test_random_configurations(seed):
+    """Random small grids, sweep counts, coefficients and tuning: two whole steps against the C restatement.  Covers
+    the planner's mixed plans (sweep counts that are not multiples of 10), odd sizes and every strips-per-CTA choice."""
+    rng = np.random.default_rng(1000 + seed)
+    w, h = int(rng.integers(3, 140)), int(rng.integers(3, 400))
+    p, d = int(rng.integers(0, 46)), int(rng.integers(0, 13))
+    kw = dict(viscosity=float(rng.choice([0.0, 1e-4, 3e-3])), diffusion=float(rng.choice([0.0, 0.0, 2e-4])),
+              noise=str(rng.choice(["glibc", "zero"])), strips_per_cta=int(rng.choice([0, 1, 2, 4])))
+    gpu, ora = make_pair(w, h, p, d, **kw)
+    seed_state(gpu, ora, rng, w, h, scale=2.0)
+    for k in range(2):
+        x, y = int(rng.integers(0, w)), int(rng.integers(0, h))
+        gpu.addDensity(x, y, 3.0); ora.addDensity(x, y, 3.0)
+        gpu.addVelocity(x, y, -1.5, 0.75); ora.addVelocity(x, y, -1.5, 0.75)
+        gpu.step(0.01); ora.step(0.01)
+    for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+        assert_bits(a, b, f"{w}x{h} P={p} D={d} {kw}: field {n}")
+
+
 def test_many_launches_ring_tags_wrap():
     """The rings between CTAs carry a tag made of the launch number (14 bits) and the hand-over unit: more than 2^14
     launches on one simulation must stay exact.  One strip per CTA, so every strip boundary crosses a ring."""
