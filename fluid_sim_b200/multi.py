@@ -360,11 +360,14 @@ class BlockFluidSim:
             self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
             self._mark("pointwise")
             self._project(fresh_halo=True)
-            # density: diffusion 0 is the identity d + 0.0f plus the boundary update, folded into the gather
-            self._bnd([DENSITY], [0], [1])
+            # density: diffusion 0 is the identity d + 0.0f plus the boundary update, folded into the gather; with no
+            # diffusion sweeps at all (D == 0) the reference's loop body, boundary update included, never runs
+            fold = 1 if self.D > 0 else 0
+            if fold:
+                self._bnd([DENSITY], [0], [1])
             self._halo([DENSITY, VELOCITY_X, VELOCITY_Y], self.reach)
             self._check_reach(dt, self.reach)
             self._mark("haloR")
-            self._check(self._lib.fsb_blk_advect_density(self._h, dt, 1))
+            self._check(self._lib.fsb_blk_advect_density(self._h, dt, fold))
             self._bnd([DENSITY], [0])
             self._mark("pointwise")

@@ -377,7 +377,7 @@ def test_cpp_dropin_headless_main():
     assert lines[1] == "after reset d[100][110] 0"
 
 
-@pytest.mark.parametrize("args", ["256 512 20 5 2", "200 1024 40 5 1"])
+@pytest.mark.parametrize("args", ["256 512 20 5 2", "200 1024 40 5 1", "300 256 33 0 2", "130 512 100 5 1"])
 def test_multi_gpu_matches_single_gpu(args):
     """Column blocks on 2 GPUs (sweep chain handed over through peer memory, NCCL halos) give the single-GPU bits."""
     import os
