@@ -427,6 +427,7 @@ def main():
                 "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "peak_source": peak_src, "launch_ms": gs_launch_ms, "launches_timed": gs_n,
                 "algorithmic_bytes_per_launch": algo_bytes,
+                "sweep_cell_updates_per_sec": levels * cells / (gs_launch_ms * 1e-3) if gs_launch_ms > 0 else 0.0,
                 "compulsory_bytes_per_launch": compulsory,
                 "compulsory_gbs": compulsory / (gs_launch_ms * 1e-3) / 1e9 if gs_launch_ms > 0 else 0.0,
                 "note": "achieved = EFFECTIVE GB/s at the reference's pass structure (12 B per cell per sweep); the sweeps "
