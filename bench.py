@@ -446,6 +446,14 @@ def main():
     step_gbs = Bp * cells / (ms_per_step * 1e-3) / 1e9
     step_roofline = {"bytes_per_cell": Bp, "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak}
     shares = {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items()}
+    # per kernel class: effective GB/s at SURVEY.md 8(d)'s algorithmic bytes per cell and launch
+    per_launch_bytes = {"noise": 16.0, "divergence": 16.0, "gradient": 20.0, "advect_velocity": 16.0, "advect_scalar": 16.0,
+                        "sor": 12.0 * 5 * 2, "gs": 12.0 * levels}
+    for k, bpc in per_launch_bytes.items():
+        if k in shares and prof[k][1] > 0 and prof[k][0] > 0:
+            gbs = bpc * cells / (prof[k][0] / prof[k][1] * 1e-3) / 1e9
+            shares[k]["effective_gbs"] = gbs
+            shares[k]["frac_of_peak"] = gbs / peak
 
     # -------- CPU baseline: the real reference on this host, bounded sample
     if args.no_cpu_baseline or world > 1:
