@@ -1,0 +1,554 @@
+// Development prototype (NOT part of the library): cost of one pipeline step with two columns per lane (S levels,
+// 2 * S cell updates) against the shipped one-column step body (2 * S levels, as many cell updates), both on dummy
+// data in shared memory, no inter-warp protocol.  Answers the question DESIGN.md section 9 item 1 depends on: does the
+// two-column step cost about the same number of cycles?  The wiring itself is verified in tools/wavefront_emu.py.
+//   build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -fmad=false -I../../fluid_sim_b200/csrc \
+//               -I../../include step2_microbench.cu -o step2_microbench
+//   run:   ./step2_microbench [warps per CTA = 8] [steps = 4096]
+#include "../../fluid_sim_b200/csrc/wavefront.cu"
+
+namespace fsb {
+namespace {
+
+// the shipped step body without the travelling right-hand side (no loads / stores of it): how much of a step is
+// shared-memory traffic?
+template <int S, int MODE, int FIX>
+__device__ __forceinline__ void wf_step_nod(float (&x)[S + 1], float (&U)[S + 1], const float (&Up)[S + 1], const int t,
+                                        const int lane, const int gp, const int fix, const unsigned (&wmask)[S + 1],
+                                        const WfWarp &cx)
+{
+    using L = WfLayout<S>;
+    float Dc[S + 1];
+    {
+        const float *px = (lane == 0) ? cx.imp + ((t - 1) & cx.imp_mask) * L::EXW
+                                      : cx.bx + (((t - 1) & 1) * 32 + (lane - 1)) * L::XP;
+        const float *pd = (lane == 0) ? cx.imp + ((t - 2) & cx.imp_mask) * L::EXW + L::XW
+                                      : cx.bd + (((t - 2) & 3) * 32 + (lane - 1)) * L::DP;
+        const float4 *ix = reinterpret_cast<const float4 *>(px);
+        const float4 *id = reinterpret_cast<const float4 *>(pd);
+#pragma unroll
+        for (int q = 0; q < L::XW / 4; ++q) {
+            const float4 v = ix[q];
+            if (4 * q + 0 <= S) U[(4 * q + 0 <= S) ? 4 * q + 0 : 0] = v.x;
+            if (4 * q + 1 <= S) U[(4 * q + 1 <= S) ? 4 * q + 1 : 0] = v.y;
+            if (4 * q + 2 <= S) U[(4 * q + 2 <= S) ? 4 * q + 2 : 0] = v.z;
+            if (4 * q + 3 <= S) U[(4 * q + 3 <= S) ? 4 * q + 3 : 0] = v.w;
+        }
+#pragma unroll
+        for (int k = 1; k <= S; ++k) Dc[k] = 0.5f;
+        (void)id;
+    }
+    const int islot = ((t + cx.in_off - lane) & cx.in_mask) * 32 + lane;
+    const float nx0 = cx.has_in_x ? cx.in_x[islot] : 0.0f;
+    Dc[0] = cx.in_d[islot];
+    const float cold1 = Up[0];
+    // The S updates of a step are independent of each other (they read only values of step t-1), so
+    // they are written stage by stage across all levels: consecutive instructions belong to different
+    // dependency chains.
+    //   down = U[k-1] (i+1, j) sweep k-1      up    = x[k]   (i-1, j) sweep k
+    //   left = U[k]   (i, j-1) sweep k        right = x[k-1] (i, j+1) sweep k-1     centre = Up[k-1]
+    float acc[S + 1];
+    acc[0] = 0.0f;
+    if (MODE == kGaussSeidel) {
+        // src/fluid_sim.cpp:325-327: ((((div + down) + up) + right) + left) / 4
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Dc[k], U[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], U[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(acc[k], 0.25f);
+    } else {
+        // src/fluid_sim.cpp:56-57: nv = (src + a*(((down + up) + right) + left)) * cRecip; x += omega*(nv - x)
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(U[k - 1], x[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], U[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(cx.a, acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Dc[k], acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(acc[k], cx.c_recip);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fsub_rn(acc[k], Up[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(cx.omega, acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Up[k - 1], acc[k]);
+    }
+    // Cells on a wall carry what setBoundary() (src/fluid_sim.cpp:347-361) left in the array at the moment
+    // the reference reads them during sweep k: the array's own value before the first sweep of the pass,
+    // +-(the adjacent interior cell's sweep k-1 value) afterwards.  `fix` is warp-uniform and non-zero only
+    // for the few batches / strips that touch a wall.  Cells outside the grid hold garbage that no cell
+    // inside the grid ever reads.
+    if (FIX == kStepLeft) {
+        // wmask[k] is all ones in the one lane that sits on column 0 at level k (loop-invariant registers:
+        // one LOP3 per level, no predicates).  Gauss-Seidel runs on the pressure only, whose wall sign is +1.
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wr = (MODE == kGaussSeidel) ? x[k - 1] : __fmul_rn(cx.sj, x[k - 1]);
+            const float wv = (k == 1 && cx.first) ? cold1 : wr;
+            acc[k] = bit_select(acc[k], wv, wmask[k]);
+        }
+    } else if (FIX == kStepRight) {
+        // wmask[k] is all ones in the one lane that sits on column H-1 at level k
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wv = (MODE == kGaussSeidel) ? U[k] : __fmul_rn(cx.sj, U[k]);
+            acc[k] = bit_select(acc[k], wv, wmask[k]);
+        }
+    } else if (FIX == kStepTop) {
+        // only the top wall row is in reach (the start of every strip, which the hand-over chain runs through):
+        // the wall cell of level k carries +-(row 1, sweep k-1)
+        const int ib = t - kToff - gp;   // row of level 0
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wr = (MODE == kGaussSeidel) ? U[k - 1] : __fmul_rn(cx.si, U[k - 1]);
+            const float wv = (k == 1 && cx.first) ? cold1 : wr;
+            acc[k] = (ib == k) ? wv : acc[k];
+        }
+    } else if (FIX == kStepFull) {
+        if (fix & kFixLeft) {
+#pragma unroll
+            for (int k = 1; k <= S; ++k) {
+                const float wv = (k == 1 && cx.first) ? cold1 : __fmul_rn(cx.sj, x[k - 1]);
+                acc[k] = (gp == k) ? wv : acc[k];
+            }
+        }
+        if (fix & kFixRight) {
+            const int gw = gp - (cx.H - 1);
+#pragma unroll
+            for (int k = 1; k <= S; ++k) acc[k] = (gw == k) ? __fmul_rn(cx.sj, U[k]) : acc[k];
+        }
+        if (fix & kFixTop) {
+            const int ib = t - kToff - gp;   // row of level 0
+#pragma unroll
+            for (int k = 1; k <= S; ++k) {
+                const float wv = (k == 1 && cx.first) ? cold1 : __fmul_rn(cx.si, U[k - 1]);
+                acc[k] = (ib == k) ? wv : acc[k];
+            }
+        }
+        if (fix & kFixBottom) {
+            const int ibw = t - kToff - gp - (cx.W - 1);
+#pragma unroll
+            for (int k = 1; k <= S; ++k) acc[k] = (ibw == k) ? __fmul_rn(cx.si, x[k]) : acc[k];
+        }
+    }
+#pragma unroll
+    for (int k = 1; k <= S; ++k) x[k] = acc[k];
+    x[0] = nx0;
+    {
+        float *wx = (lane == 31) ? cx.exp + (t & cx.exp_mask) * L::EXW : cx.bx + ((t & 1) * 32 + lane) * L::XP;
+        float *wd = (lane == 31) ? cx.exp + (t & cx.exp_mask) * L::EXW + L::XW : cx.bd + ((t & 3) * 32 + lane) * L::DP;
+        float4 *ex = reinterpret_cast<float4 *>(wx);
+#pragma unroll
+        for (int q = 0; q < L::XW / 4; ++q) {
+            float4 v;
+            v.x = x[(4 * q + 0 <= S) ? 4 * q + 0 : 0];
+            v.y = x[(4 * q + 1 <= S) ? 4 * q + 1 : 0];
+            v.z = x[(4 * q + 2 <= S) ? 4 * q + 2 : 0];
+            v.w = x[(4 * q + 3 <= S) ? 4 * q + 3 : 0];
+            ex[q] = v;
+        }
+        (void)wd;
+    }
+    const int oslot = ((t - lane) & cx.out_mask) * 32 + lane;
+    cx.out_x[oslot] = x[S];
+    if (cx.out_d) cx.out_d[oslot] = Dc[S];
+    __syncwarp();
+}
+
+
+// the shipped step body with the right-hand side read from a 72-column, 128-row tile instead of travelling through the lanes
+template <int S, int MODE, int FIX>
+__device__ __forceinline__ void wf_step_tile(float (&x)[S + 1], float (&U)[S + 1], const float (&Up)[S + 1], const int t,
+                                        const int lane, const int gp, const int fix, const unsigned (&wmask)[S + 1],
+                                        const WfWarp &cx)
+{
+    using L = WfLayout<S>;
+    float Dc[S + 1];
+    {
+        const float *px = (lane == 0) ? cx.imp + ((t - 1) & cx.imp_mask) * L::EXW
+                                      : cx.bx + (((t - 1) & 1) * 32 + (lane - 1)) * L::XP;
+        const float *pd = (lane == 0) ? cx.imp + ((t - 2) & cx.imp_mask) * L::EXW + L::XW
+                                      : cx.bd + (((t - 2) & 3) * 32 + (lane - 1)) * L::DP;
+        const float4 *ix = reinterpret_cast<const float4 *>(px);
+        const float4 *id = reinterpret_cast<const float4 *>(pd);
+#pragma unroll
+        for (int q = 0; q < L::XW / 4; ++q) {
+            const float4 v = ix[q];
+            if (4 * q + 0 <= S) U[(4 * q + 0 <= S) ? 4 * q + 0 : 0] = v.x;
+            if (4 * q + 1 <= S) U[(4 * q + 1 <= S) ? 4 * q + 1 : 0] = v.y;
+            if (4 * q + 2 <= S) U[(4 * q + 2 <= S) ? 4 * q + 2 : 0] = v.z;
+            if (4 * q + 3 <= S) U[(4 * q + 3 <= S) ? 4 * q + 3 : 0] = v.w;
+        }
+#pragma unroll
+        {   // right-hand side straight from a wide, deep tile: level k sits one row and one column before level k-1
+            const float *rt = cx.in_d + ((t - lane) & 127) * 72 + lane + 1024;
+#pragma unroll
+            for (int k = 1; k <= S; ++k) Dc[k] = rt[-73 * k];
+        }
+        __syncwarp();   // keeps the ten loads together in front of the arithmetic (ptxas otherwise pairs each with its add)
+        (void)id;
+    }
+    const int islot = ((t + cx.in_off - lane) & cx.in_mask) * 32 + lane;
+    const float nx0 = cx.has_in_x ? cx.in_x[islot] : 0.0f;
+    Dc[0] = cx.in_d[islot];
+    const float cold1 = Up[0];
+    // The S updates of a step are independent of each other (they read only values of step t-1), so
+    // they are written stage by stage across all levels: consecutive instructions belong to different
+    // dependency chains.
+    //   down = U[k-1] (i+1, j) sweep k-1      up    = x[k]   (i-1, j) sweep k
+    //   left = U[k]   (i, j-1) sweep k        right = x[k-1] (i, j+1) sweep k-1     centre = Up[k-1]
+    float acc[S + 1];
+    acc[0] = 0.0f;
+    if (MODE == kGaussSeidel) {
+        // src/fluid_sim.cpp:325-327: ((((div + down) + up) + right) + left) / 4
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Dc[k], U[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], U[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(acc[k], 0.25f);
+    } else {
+        // src/fluid_sim.cpp:56-57: nv = (src + a*(((down + up) + right) + left)) * cRecip; x += omega*(nv - x)
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(U[k - 1], x[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], U[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(cx.a, acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Dc[k], acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(acc[k], cx.c_recip);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fsub_rn(acc[k], Up[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(cx.omega, acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Up[k - 1], acc[k]);
+    }
+    // Cells on a wall carry what setBoundary() (src/fluid_sim.cpp:347-361) left in the array at the moment
+    // the reference reads them during sweep k: the array's own value before the first sweep of the pass,
+    // +-(the adjacent interior cell's sweep k-1 value) afterwards.  `fix` is warp-uniform and non-zero only
+    // for the few batches / strips that touch a wall.  Cells outside the grid hold garbage that no cell
+    // inside the grid ever reads.
+    if (FIX == kStepLeft) {
+        // wmask[k] is all ones in the one lane that sits on column 0 at level k (loop-invariant registers:
+        // one LOP3 per level, no predicates).  Gauss-Seidel runs on the pressure only, whose wall sign is +1.
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wr = (MODE == kGaussSeidel) ? x[k - 1] : __fmul_rn(cx.sj, x[k - 1]);
+            const float wv = (k == 1 && cx.first) ? cold1 : wr;
+            acc[k] = bit_select(acc[k], wv, wmask[k]);
+        }
+    } else if (FIX == kStepRight) {
+        // wmask[k] is all ones in the one lane that sits on column H-1 at level k
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wv = (MODE == kGaussSeidel) ? U[k] : __fmul_rn(cx.sj, U[k]);
+            acc[k] = bit_select(acc[k], wv, wmask[k]);
+        }
+    } else if (FIX == kStepTop) {
+        // only the top wall row is in reach (the start of every strip, which the hand-over chain runs through):
+        // the wall cell of level k carries +-(row 1, sweep k-1)
+        const int ib = t - kToff - gp;   // row of level 0
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wr = (MODE == kGaussSeidel) ? U[k - 1] : __fmul_rn(cx.si, U[k - 1]);
+            const float wv = (k == 1 && cx.first) ? cold1 : wr;
+            acc[k] = (ib == k) ? wv : acc[k];
+        }
+    } else if (FIX == kStepFull) {
+        if (fix & kFixLeft) {
+#pragma unroll
+            for (int k = 1; k <= S; ++k) {
+                const float wv = (k == 1 && cx.first) ? cold1 : __fmul_rn(cx.sj, x[k - 1]);
+                acc[k] = (gp == k) ? wv : acc[k];
+            }
+        }
+        if (fix & kFixRight) {
+            const int gw = gp - (cx.H - 1);
+#pragma unroll
+            for (int k = 1; k <= S; ++k) acc[k] = (gw == k) ? __fmul_rn(cx.sj, U[k]) : acc[k];
+        }
+        if (fix & kFixTop) {
+            const int ib = t - kToff - gp;   // row of level 0
+#pragma unroll
+            for (int k = 1; k <= S; ++k) {
+                const float wv = (k == 1 && cx.first) ? cold1 : __fmul_rn(cx.si, U[k - 1]);
+                acc[k] = (ib == k) ? wv : acc[k];
+            }
+        }
+        if (fix & kFixBottom) {
+            const int ibw = t - kToff - gp - (cx.W - 1);
+#pragma unroll
+            for (int k = 1; k <= S; ++k) acc[k] = (ibw == k) ? __fmul_rn(cx.si, x[k]) : acc[k];
+        }
+    }
+#pragma unroll
+    for (int k = 1; k <= S; ++k) x[k] = acc[k];
+    x[0] = nx0;
+    {
+        float *wx = (lane == 31) ? cx.exp + (t & cx.exp_mask) * L::EXW : cx.bx + ((t & 1) * 32 + lane) * L::XP;
+        float *wd = (lane == 31) ? cx.exp + (t & cx.exp_mask) * L::EXW + L::XW : cx.bd + ((t & 3) * 32 + lane) * L::DP;
+        float4 *ex = reinterpret_cast<float4 *>(wx);
+#pragma unroll
+        for (int q = 0; q < L::XW / 4; ++q) {
+            float4 v;
+            v.x = x[(4 * q + 0 <= S) ? 4 * q + 0 : 0];
+            v.y = x[(4 * q + 1 <= S) ? 4 * q + 1 : 0];
+            v.z = x[(4 * q + 2 <= S) ? 4 * q + 2 : 0];
+            v.w = x[(4 * q + 3 <= S) ? 4 * q + 3 : 0];
+            ex[q] = v;
+        }
+        (void)wd;
+    }
+    const int oslot = ((t - lane) & cx.out_mask) * 32 + lane;
+    cx.out_x[oslot] = x[S];
+    if (cx.out_d) cx.out_d[oslot] = Dc[S];
+    __syncwarp();
+}
+
+
+
+template <int S>
+struct Layout2 {
+    static constexpr int XW = (2 * (S + 1) + 3) & ~3;      // A0..AS, B0..BS
+    static constexpr int DW = (2 * S + 3) & ~3;            // dA0..dA(S-1), dB0..dB(S-1)
+    static constexpr int EXW = XW + DW;
+    static constexpr int XP = ((XW / 4) & 1) ? XW : XW + 4;
+    static constexpr int DP = ((DW / 4) & 1) ? DW : DW + 4;
+};
+
+// Two columns per lane: lane g, level k owns columns A = 2J, B = 2J + 1 of the pair J = g - k on row t - k - g.
+template <int S, int MODE>
+__device__ __forceinline__ void wf_step2(float (&xA)[S + 1], float (&xB)[S + 1], float (&U)[2 * (S + 1)],
+                                         const float (&Up)[2 * (S + 1)], const int t, const int lane, const WfWarp &cx)
+{
+    using L = Layout2<S>;
+    float DA[S + 1], DB[S + 1];
+    {
+        const float *px = (lane == 0) ? cx.imp + ((t - 1) & cx.imp_mask) * L::EXW
+                                      : cx.bx + (((t - 1) & 1) * 32 + (lane - 1)) * L::XP;
+        const float *pd = (lane == 0) ? cx.imp + ((t - 2) & cx.imp_mask) * L::EXW + L::XW
+                                      : cx.bd + (((t - 2) & 3) * 32 + (lane - 1)) * L::DP;
+        const float4 *ix = reinterpret_cast<const float4 *>(px);
+        const float4 *id = reinterpret_cast<const float4 *>(pd);
+        float tmp[L::XW], tmd[L::DW];
+#pragma unroll
+        for (int q = 0; q < L::XW / 4; ++q) {
+            const float4 v = ix[q];
+            tmp[4 * q] = v.x; tmp[4 * q + 1] = v.y; tmp[4 * q + 2] = v.z; tmp[4 * q + 3] = v.w;
+        }
+#pragma unroll
+        for (int q = 0; q < L::DW / 4; ++q) {
+            const float4 v = id[q];
+            tmd[4 * q] = v.x; tmd[4 * q + 1] = v.y; tmd[4 * q + 2] = v.z; tmd[4 * q + 3] = v.w;
+        }
+#pragma unroll
+        for (int k = 0; k < 2 * (S + 1); ++k) U[k] = tmp[k];
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            DA[k] = tmd[k - 1];
+            DB[k] = tmd[S + k - 1];
+        }
+    }
+    const int islot = (((t + cx.in_off - lane) & cx.in_mask) * 32 + lane) * 2;
+    const float2 n0 = cx.has_in_x ? *reinterpret_cast<const float2 *>(cx.in_x + islot) : make_float2(0.0f, 0.0f);
+    const float2 d0 = *reinterpret_cast<const float2 *>(cx.in_d + islot);
+    DA[0] = d0.x;
+    DB[0] = d0.y;
+    // U[k] = lane g-1's A of level k, U[S+1+k] = its B; Up = the same one step earlier
+    float nA[S + 1], nB[S + 1];
+    if (MODE == kGaussSeidel) {
+#pragma unroll
+        for (int k = 1; k <= S; ++k) nA[k] = __fadd_rn(DA[k], U[k - 1]);                 // + down
+#pragma unroll
+        for (int k = 1; k <= S; ++k) nA[k] = __fadd_rn(nA[k], xA[k]);                    // + up
+#pragma unroll
+        for (int k = 1; k <= S; ++k) nA[k] = __fadd_rn(nA[k], Up[S + 1 + k - 1]);        // + right: B of level k-1, t-2
+#pragma unroll
+        for (int k = 1; k <= S; ++k) nA[k] = __fadd_rn(nA[k], U[S + 1 + k]);             // + left: B of level k
+#pragma unroll
+        for (int k = 1; k <= S; ++k) nA[k] = __fmul_rn(nA[k], 0.25f);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) nB[k] = __fadd_rn(DB[k], U[S + 1 + k - 1]);         // + down
+#pragma unroll
+        for (int k = 1; k <= S; ++k) nB[k] = __fadd_rn(nB[k], xB[k]);                    // + up
+#pragma unroll
+        for (int k = 1; k <= S; ++k) nB[k] = __fadd_rn(nB[k], xA[k - 1]);                // + right: own old A of level k-1
+#pragma unroll
+        for (int k = 1; k <= S; ++k) nB[k] = __fadd_rn(nB[k], nA[k]);                    // + left: the A just computed
+#pragma unroll
+        for (int k = 1; k <= S; ++k) nB[k] = __fmul_rn(nB[k], 0.25f);
+    } else {
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            float v = __fadd_rn(__fadd_rn(__fadd_rn(U[k - 1], xA[k]), Up[S + 1 + k - 1]), U[S + 1 + k]);
+            v = __fmul_rn(__fadd_rn(DA[k], __fmul_rn(cx.a, v)), cx.c_recip);
+            nA[k] = __fadd_rn(Up[k - 1], __fmul_rn(cx.omega, __fsub_rn(v, Up[k - 1])));
+        }
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            float v = __fadd_rn(__fadd_rn(__fadd_rn(U[S + 1 + k - 1], xB[k]), xA[k - 1]), nA[k]);
+            v = __fmul_rn(__fadd_rn(DB[k], __fmul_rn(cx.a, v)), cx.c_recip);
+            nB[k] = __fadd_rn(Up[S + 1 + k - 1], __fmul_rn(cx.omega, __fsub_rn(v, Up[S + 1 + k - 1])));
+        }
+    }
+#pragma unroll
+    for (int k = 1; k <= S; ++k) {
+        xA[k] = nA[k];
+        xB[k] = nB[k];
+    }
+    xA[0] = n0.x;
+    xB[0] = n0.y;
+    {
+        float *wx = (lane == 31) ? cx.exp + (t & cx.exp_mask) * L::EXW : cx.bx + ((t & 1) * 32 + lane) * L::XP;
+        float *wd = (lane == 31) ? cx.exp + (t & cx.exp_mask) * L::EXW + L::XW : cx.bd + ((t & 3) * 32 + lane) * L::DP;
+        float sx[L::XW], sd[L::DW];
+#pragma unroll
+        for (int k = 0; k < L::XW; ++k) sx[k] = 0.0f;
+#pragma unroll
+        for (int k = 0; k < L::DW; ++k) sd[k] = 0.0f;
+#pragma unroll
+        for (int k = 0; k <= S; ++k) {
+            sx[k] = xA[k];
+            sx[S + 1 + k] = xB[k];
+        }
+#pragma unroll
+        for (int k = 0; k < S; ++k) {
+            sd[k] = DA[k];
+            sd[S + k] = DB[k];
+        }
+#pragma unroll
+        for (int q = 0; q < L::XW / 4; ++q)
+            reinterpret_cast<float4 *>(wx)[q] = make_float4(sx[4 * q], sx[4 * q + 1], sx[4 * q + 2], sx[4 * q + 3]);
+#pragma unroll
+        for (int q = 0; q < L::DW / 4; ++q)
+            reinterpret_cast<float4 *>(wd)[q] = make_float4(sd[4 * q], sd[4 * q + 1], sd[4 * q + 2], sd[4 * q + 3]);
+    }
+    const int oslot = (((t - lane) & cx.out_mask) * 32 + lane) * 2;
+    *reinterpret_cast<float2 *>(cx.out_x + oslot) = make_float2(xA[S], xB[S]);
+    if (cx.out_d) *reinterpret_cast<float2 *>(cx.out_d + oslot) = make_float2(DA[S], DB[S]);
+    __syncwarp();
+}
+
+// mode 0: shipped one-column body, S = 10; mode 1: two-column body, S = 5.  Same cell updates per step (10 per lane).
+template <int VARIANT>
+__global__ void __launch_bounds__(320) bench_kernel(int steps, long long *cycles, float *sink)
+{
+    extern __shared__ float4 smem4[];
+    float *smem = reinterpret_cast<float *>(smem4);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    constexpr int kState = 2 * 32 * 12 + 4 * 32 * 12;
+    float *rings = smem;                          // imp | exp, shared by all warps (only lanes 0 / 31 touch them)
+    float *tiles = rings + 2 * 64 * 24;           // in_x | in_d | out_x | out_d, 64 rows x 64 floats each, shared
+    float *state = tiles + 4 * 64 * 64 + w * kState;
+    for (int i = threadIdx.x; i < 2 * 64 * 24 + 4 * 64 * 64 + nw * kState; i += blockDim.x) smem[i] = 1e-3f * (float)(i % 97);
+    __syncthreads();
+    WfWarp cx;
+    cx.imp = rings; cx.exp = rings + 64 * 24; cx.imp_mask = cx.exp_mask = 63;
+    cx.in_x = tiles; cx.in_d = tiles + 64 * 64; cx.in_mask = 63; cx.in_off = 0; cx.has_in_x = true;
+    cx.out_x = tiles + 2 * 64 * 64; cx.out_d = tiles + 3 * 64 * 64; cx.out_mask = 63;
+    cx.bx = state; cx.bd = state + 2 * 32 * 12; cx.first = false;
+    cx.W = 1 << 20; cx.H = 1 << 20; cx.si = cx.sj = 1.0f; cx.a = 0.3f; cx.c_recip = 0.45f; cx.omega = 1.5f;
+    long long t0 = 0, t1 = 0;
+    float acc = 0.0f;
+    if (VARIANT == 0) {
+        constexpr int S = 10;
+        float x[S + 1], Ua[S + 1], Ub[S + 1];
+        unsigned wmask[S + 1];
+        for (int k = 0; k <= S; ++k) { x[k] = 0.01f * k; Ua[k] = Ub[k] = 0.0f; wmask[k] = 0u; }
+        t0 = clock64();
+#pragma unroll 1
+        for (int t = 64; t < 64 + steps; t += 2) {
+            wf_step<S, kGaussSeidel, kStepFast>(x, Ua, Ub, t, lane, lane + 1000, 0, wmask, cx);
+            wf_step<S, kGaussSeidel, kStepFast>(x, Ub, Ua, t + 1, lane, lane + 1000, 0, wmask, cx);
+        }
+        t1 = clock64();
+        for (int k = 0; k <= S; ++k) acc += x[k];
+    } else if (VARIANT == 3) {
+        constexpr int S = 10;
+        float x[S + 1], Ua[S + 1], Ub[S + 1];
+        unsigned wmask[S + 1];
+        for (int k = 0; k <= S; ++k) { x[k] = 0.01f * k; Ua[k] = Ub[k] = 0.0f; wmask[k] = 0u; }
+        t0 = clock64();
+#pragma unroll 1
+        for (int t = 64; t < 64 + steps; t += 2) {
+            wf_step_tile<S, kGaussSeidel, kStepFast>(x, Ua, Ub, t, lane, lane + 1000, 0, wmask, cx);
+            wf_step_tile<S, kGaussSeidel, kStepFast>(x, Ub, Ua, t + 1, lane, lane + 1000, 0, wmask, cx);
+        }
+        t1 = clock64();
+        for (int k = 0; k <= S; ++k) acc += x[k];
+    } else if (VARIANT == 2) {
+        constexpr int S = 10;
+        float x[S + 1], Ua[S + 1], Ub[S + 1];
+        unsigned wmask[S + 1];
+        for (int k = 0; k <= S; ++k) { x[k] = 0.01f * k; Ua[k] = Ub[k] = 0.0f; wmask[k] = 0u; }
+        t0 = clock64();
+#pragma unroll 1
+        for (int t = 64; t < 64 + steps; t += 2) {
+            wf_step_nod<S, kGaussSeidel, kStepFast>(x, Ua, Ub, t, lane, lane + 1000, 0, wmask, cx);
+            wf_step_nod<S, kGaussSeidel, kStepFast>(x, Ub, Ua, t + 1, lane, lane + 1000, 0, wmask, cx);
+        }
+        t1 = clock64();
+        for (int k = 0; k <= S; ++k) acc += x[k];
+    } else {
+        constexpr int S = 5;
+        float xA[S + 1], xB[S + 1], Ua[2 * (S + 1)], Ub[2 * (S + 1)];
+        for (int k = 0; k <= S; ++k) { xA[k] = 0.01f * k; xB[k] = 0.02f * k; }
+        for (int k = 0; k < 2 * (S + 1); ++k) Ua[k] = Ub[k] = 0.0f;
+        t0 = clock64();
+#pragma unroll 1
+        for (int t = 64; t < 64 + steps; t += 2) {
+            wf_step2<S, kGaussSeidel>(xA, xB, Ua, Ub, t, lane, cx);
+            wf_step2<S, kGaussSeidel>(xA, xB, Ub, Ua, t + 1, lane, cx);
+        }
+        t1 = clock64();
+        for (int k = 0; k <= S; ++k) acc += xA[k] + xB[k];
+    }
+    if (lane == 0) cycles[blockIdx.x * nw + w] = t1 - t0;
+    if (acc == 123.456f) sink[0] = acc;
+}
+
+}  // namespace
+}  // namespace fsb
+
+int main(int argc, char **argv)
+{
+    const int nw = argc > 1 ? atoi(argv[1]) : 8, steps = argc > 2 ? atoi(argv[2]) : 4096;
+    const int nblk = 148;
+    long long *d_cyc, *h = new long long[nblk * nw];
+    float *d_sink;
+    cudaMalloc(&d_cyc, sizeof(long long) * nblk * nw);
+    cudaMalloc(&d_sink, 4);
+    const size_t smem = sizeof(float) * (2 * 64 * 24 + 4 * 64 * 64 + nw * (2 * 32 * 12 + 4 * 32 * 12));
+    for (int variant = 0; variant < 4; ++variant) {
+        auto kern = variant == 0 ? fsb::bench_kernel<0> : (variant == 1 ? fsb::bench_kernel<1> : (variant == 2 ? fsb::bench_kernel<2> : fsb::bench_kernel<3>));
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        for (int rep = 0; rep < 2; ++rep) kern<<<nblk, nw * 32, smem>>>(steps, d_cyc, d_sink);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("variant %d: %s\n", variant, cudaGetErrorString(e)); return 1; }
+        cudaMemcpy(h, d_cyc, sizeof(long long) * nblk * nw, cudaMemcpyDeviceToHost);
+        double sum = 0; long long mx = 0;
+        for (int i = 0; i < nblk * nw; ++i) { sum += h[i]; if (h[i] > mx) mx = h[i]; }
+        printf("%s, %d warps per SM: %.0f cycles per step (mean), %.0f (slowest warp); 10 cell updates per lane and step\n",
+               variant == 0 ? "one column per lane, S=10" : (variant == 1 ? "two columns per lane, S=5" : (variant == 2 ? "one column, S=10, no right-hand-side traffic" : "one column, S=10, right-hand side read from a wide tile")), nw, sum / (nblk * nw) / steps,
+               (double)mx / steps);
+    }
+    return 0;
+}
