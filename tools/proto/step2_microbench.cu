@@ -165,6 +165,166 @@ __device__ __forceinline__ void wf_step_nod(float (&x)[S + 1], float (&U)[S + 1]
 }
 
 
+// the shipped step body with the right-hand side prefetched from a wide tile two steps ahead (one register array per parity)
+template <int S, int MODE, int FIX>
+__device__ __forceinline__ void wf_step_pref(float (&Dn)[S + 1], float (&x)[S + 1], float (&U)[S + 1], const float (&Up)[S + 1], const int t,
+                                        const int lane, const int gp, const int fix, const unsigned (&wmask)[S + 1],
+                                        const WfWarp &cx)
+{
+    using L = WfLayout<S>;
+    float Dc[S + 1];
+    {
+        const float *px = (lane == 0) ? cx.imp + ((t - 1) & cx.imp_mask) * L::EXW
+                                      : cx.bx + (((t - 1) & 1) * 32 + (lane - 1)) * L::XP;
+        const float *pd = (lane == 0) ? cx.imp + ((t - 2) & cx.imp_mask) * L::EXW + L::XW
+                                      : cx.bd + (((t - 2) & 3) * 32 + (lane - 1)) * L::DP;
+        const float4 *ix = reinterpret_cast<const float4 *>(px);
+        const float4 *id = reinterpret_cast<const float4 *>(pd);
+#pragma unroll
+        for (int q = 0; q < L::XW / 4; ++q) {
+            const float4 v = ix[q];
+            if (4 * q + 0 <= S) U[(4 * q + 0 <= S) ? 4 * q + 0 : 0] = v.x;
+            if (4 * q + 1 <= S) U[(4 * q + 1 <= S) ? 4 * q + 1 : 0] = v.y;
+            if (4 * q + 2 <= S) U[(4 * q + 2 <= S) ? 4 * q + 2 : 0] = v.z;
+            if (4 * q + 3 <= S) U[(4 * q + 3 <= S) ? 4 * q + 3 : 0] = v.w;
+        }
+#pragma unroll
+        for (int k = 1; k <= S; ++k) Dc[k] = Dn[k];
+        (void)id;
+    }
+    const int islot = ((t + cx.in_off - lane) & cx.in_mask) * 32 + lane;
+    const float nx0 = cx.has_in_x ? cx.in_x[islot] : 0.0f;
+    Dc[0] = cx.in_d[islot];
+    const float cold1 = Up[0];
+    // The S updates of a step are independent of each other (they read only values of step t-1), so
+    // they are written stage by stage across all levels: consecutive instructions belong to different
+    // dependency chains.
+    //   down = U[k-1] (i+1, j) sweep k-1      up    = x[k]   (i-1, j) sweep k
+    //   left = U[k]   (i, j-1) sweep k        right = x[k-1] (i, j+1) sweep k-1     centre = Up[k-1]
+    float acc[S + 1];
+    acc[0] = 0.0f;
+    if (MODE == kGaussSeidel) {
+        // src/fluid_sim.cpp:325-327: ((((div + down) + up) + right) + left) / 4
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Dc[k], U[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], U[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(acc[k], 0.25f);
+    } else {
+        // src/fluid_sim.cpp:56-57: nv = (src + a*(((down + up) + right) + left)) * cRecip; x += omega*(nv - x)
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(U[k - 1], x[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], x[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(acc[k], U[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(cx.a, acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Dc[k], acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(acc[k], cx.c_recip);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fsub_rn(acc[k], Up[k - 1]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fmul_rn(cx.omega, acc[k]);
+#pragma unroll
+        for (int k = 1; k <= S; ++k) acc[k] = __fadd_rn(Up[k - 1], acc[k]);
+    }
+    // Cells on a wall carry what setBoundary() (src/fluid_sim.cpp:347-361) left in the array at the moment
+    // the reference reads them during sweep k: the array's own value before the first sweep of the pass,
+    // +-(the adjacent interior cell's sweep k-1 value) afterwards.  `fix` is warp-uniform and non-zero only
+    // for the few batches / strips that touch a wall.  Cells outside the grid hold garbage that no cell
+    // inside the grid ever reads.
+    if (FIX == kStepLeft) {
+        // wmask[k] is all ones in the one lane that sits on column 0 at level k (loop-invariant registers:
+        // one LOP3 per level, no predicates).  Gauss-Seidel runs on the pressure only, whose wall sign is +1.
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wr = (MODE == kGaussSeidel) ? x[k - 1] : __fmul_rn(cx.sj, x[k - 1]);
+            const float wv = (k == 1 && cx.first) ? cold1 : wr;
+            acc[k] = bit_select(acc[k], wv, wmask[k]);
+        }
+    } else if (FIX == kStepRight) {
+        // wmask[k] is all ones in the one lane that sits on column H-1 at level k
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wv = (MODE == kGaussSeidel) ? U[k] : __fmul_rn(cx.sj, U[k]);
+            acc[k] = bit_select(acc[k], wv, wmask[k]);
+        }
+    } else if (FIX == kStepTop) {
+        // only the top wall row is in reach (the start of every strip, which the hand-over chain runs through):
+        // the wall cell of level k carries +-(row 1, sweep k-1)
+        const int ib = t - kToff - gp;   // row of level 0
+#pragma unroll
+        for (int k = 1; k <= S; ++k) {
+            const float wr = (MODE == kGaussSeidel) ? U[k - 1] : __fmul_rn(cx.si, U[k - 1]);
+            const float wv = (k == 1 && cx.first) ? cold1 : wr;
+            acc[k] = (ib == k) ? wv : acc[k];
+        }
+    } else if (FIX == kStepFull) {
+        if (fix & kFixLeft) {
+#pragma unroll
+            for (int k = 1; k <= S; ++k) {
+                const float wv = (k == 1 && cx.first) ? cold1 : __fmul_rn(cx.sj, x[k - 1]);
+                acc[k] = (gp == k) ? wv : acc[k];
+            }
+        }
+        if (fix & kFixRight) {
+            const int gw = gp - (cx.H - 1);
+#pragma unroll
+            for (int k = 1; k <= S; ++k) acc[k] = (gw == k) ? __fmul_rn(cx.sj, U[k]) : acc[k];
+        }
+        if (fix & kFixTop) {
+            const int ib = t - kToff - gp;   // row of level 0
+#pragma unroll
+            for (int k = 1; k <= S; ++k) {
+                const float wv = (k == 1 && cx.first) ? cold1 : __fmul_rn(cx.si, U[k - 1]);
+                acc[k] = (ib == k) ? wv : acc[k];
+            }
+        }
+        if (fix & kFixBottom) {
+            const int ibw = t - kToff - gp - (cx.W - 1);
+#pragma unroll
+            for (int k = 1; k <= S; ++k) acc[k] = (ibw == k) ? __fmul_rn(cx.si, x[k]) : acc[k];
+        }
+    }
+#pragma unroll
+    for (int k = 1; k <= S; ++k) x[k] = acc[k];
+    x[0] = nx0;
+    {
+        float *wx = (lane == 31) ? cx.exp + (t & cx.exp_mask) * L::EXW : cx.bx + ((t & 1) * 32 + lane) * L::XP;
+        float *wd = (lane == 31) ? cx.exp + (t & cx.exp_mask) * L::EXW + L::XW : cx.bd + ((t & 3) * 32 + lane) * L::DP;
+        float4 *ex = reinterpret_cast<float4 *>(wx);
+#pragma unroll
+        for (int q = 0; q < L::XW / 4; ++q) {
+            float4 v;
+            v.x = x[(4 * q + 0 <= S) ? 4 * q + 0 : 0];
+            v.y = x[(4 * q + 1 <= S) ? 4 * q + 1 : 0];
+            v.z = x[(4 * q + 2 <= S) ? 4 * q + 2 : 0];
+            v.w = x[(4 * q + 3 <= S) ? 4 * q + 3 : 0];
+            ex[q] = v;
+        }
+        (void)wd;
+    }
+    const int oslot = ((t - lane) & cx.out_mask) * 32 + lane;
+    cx.out_x[oslot] = x[S];
+    if (cx.out_d) cx.out_d[oslot] = Dc[S];
+    {   // right-hand side of step t + 2 (same parity, same registers), straight from the wide tile: a full step of slack
+        const float *rt = cx.in_d + ((t + 2 - lane) & 127) * 72 + lane + 1024;
+#pragma unroll
+        for (int k = 1; k <= S; ++k) Dn[k] = rt[-73 * k];
+    }
+    __syncwarp();
+}
+
+
+
 // the shipped step body with the right-hand side moved by warp shuffles (two steps of history in registers)
 template <int S, int MODE, int FIX>
 __device__ __forceinline__ void wf_step_shfl(float (&H1)[S + 1], float (&H2)[S + 1], float (&x)[S + 1], float (&U)[S + 1], const float (&Up)[S + 1], const int t,
@@ -641,6 +801,19 @@ __global__ void __launch_bounds__(320) bench_kernel(int steps, long long *cycles
         }
         t1 = clock64();
         for (int k = 0; k <= S; ++k) acc += x[k];
+    } else if (VARIANT == 5) {
+        constexpr int S = 10;
+        float x[S + 1], Ua[S + 1], Ub[S + 1], De[S + 1], Do[S + 1];
+        unsigned wmask[S + 1];
+        for (int k = 0; k <= S; ++k) { x[k] = 0.01f * k; Ua[k] = Ub[k] = 0.0f; De[k] = Do[k] = 0.1f; wmask[k] = 0u; }
+        t0 = clock64();
+#pragma unroll 1
+        for (int t = 64; t < 64 + steps; t += 2) {
+            wf_step_pref<S, kGaussSeidel, kStepFast>(De, x, Ua, Ub, t, lane, lane + 1000, 0, wmask, cx);
+            wf_step_pref<S, kGaussSeidel, kStepFast>(Do, x, Ub, Ua, t + 1, lane, lane + 1000, 0, wmask, cx);
+        }
+        t1 = clock64();
+        for (int k = 0; k <= S; ++k) acc += x[k] + De[k] + Do[k];
     } else if (VARIANT == 4) {
         constexpr int S = 10;
         float x[S + 1], Ua[S + 1], Ub[S + 1], H1[S + 1], H2[S + 1];
@@ -710,8 +883,8 @@ int main(int argc, char **argv)
     cudaMalloc(&d_cyc, sizeof(long long) * nblk * nw);
     cudaMalloc(&d_sink, 4);
     const size_t smem = sizeof(float) * (2 * 64 * 24 + 4 * 64 * 64 + nw * (2 * 32 * 12 + 4 * 32 * 12));
-    for (int variant = 0; variant < 5; ++variant) {
-        auto kern = variant == 0 ? fsb::bench_kernel<0> : (variant == 1 ? fsb::bench_kernel<1> : (variant == 2 ? fsb::bench_kernel<2> : (variant == 3 ? fsb::bench_kernel<3> : fsb::bench_kernel<4>)));
+    for (int variant = 0; variant < 6; ++variant) {
+        auto kern = variant == 0 ? fsb::bench_kernel<0> : (variant == 1 ? fsb::bench_kernel<1> : (variant == 2 ? fsb::bench_kernel<2> : (variant == 3 ? fsb::bench_kernel<3> : (variant == 4 ? fsb::bench_kernel<4> : fsb::bench_kernel<5>))));
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         for (int rep = 0; rep < 2; ++rep) kern<<<nblk, nw * 32, smem>>>(steps, d_cyc, d_sink);
         cudaError_t e = cudaDeviceSynchronize();
@@ -720,7 +893,7 @@ int main(int argc, char **argv)
         double sum = 0; long long mx = 0;
         for (int i = 0; i < nblk * nw; ++i) { sum += h[i]; if (h[i] > mx) mx = h[i]; }
         printf("%s, %d warps per SM: %.0f cycles per step (mean), %.0f (slowest warp); 10 cell updates per lane and step\n",
-               variant == 0 ? "one column per lane, S=10" : (variant == 1 ? "two columns per lane, S=5" : (variant == 2 ? "one column, S=10, no right-hand-side traffic" : (variant == 3 ? "one column, S=10, right-hand side read from a wide tile" : "one column, S=10, right-hand side by warp shuffles"))), nw, sum / (nblk * nw) / steps,
+               variant == 0 ? "one column per lane, S=10" : (variant == 1 ? "two columns per lane, S=5" : (variant == 2 ? "one column, S=10, no right-hand-side traffic" : (variant == 3 ? "one column, S=10, right-hand side read from a wide tile" : (variant == 4 ? "one column, S=10, right-hand side by warp shuffles" : "one column, S=10, right-hand side prefetched from a wide tile")))), nw, sum / (nblk * nw) / steps,
                (double)mx / steps);
     }
     return 0;
