@@ -35,7 +35,8 @@ class Params(C.Structure):
     _fields_ = [("width", C.c_int), ("height", C.c_int), ("proj_iters", C.c_int), ("diff_iters", C.c_int),
                 ("viscosity", C.c_float), ("diffusion", C.c_float), ("omega", C.c_float),
                 ("advect_scheme", C.c_int), ("noise_mode", C.c_int), ("noise_seed", C.c_uint32),
-                ("noise_pos", C.c_uint64), ("device", C.c_int), ("reserved", C.c_int * 7)]
+                ("noise_pos", C.c_uint64), ("device", C.c_int), ("noise_process_stream", C.c_int),
+                ("reserved", C.c_int * 6)]
 
 
 def library_path():
@@ -141,7 +142,7 @@ class FluidSim:
 
     def __init__(self, width=200, height=200, proj_iters=20, diff_iters=5, viscosity=1e-4, diffusion=0.0,
                  omega=1.5, advect_scheme=ADVECT_RK4, noise="glibc", noise_seed=1, noise_pos=0, device=-1,
-                 strips_per_cta=0, sweeps_per_warp=0, max_stages=0):
+                 strips_per_cta=0, sweeps_per_warp=0, max_stages=0, process_stream=False):
         self._lib = load_library()
         p = Params()
         self._lib.fsb_default_params(C.byref(p))
@@ -150,6 +151,7 @@ class FluidSim:
         p.advect_scheme = advect_scheme
         p.noise_mode = NOISE_GLIBC if noise == "glibc" else NOISE_ZERO
         p.noise_seed, p.noise_pos, p.device = noise_seed, noise_pos, device
+        p.noise_process_stream = 1 if process_stream else 0
         self._h = _SIM()
         self.width, self.height = width, height
         self._check(self._lib.fsb_create(C.byref(p), C.byref(self._h)))

@@ -16,6 +16,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 
 #include "fsb_internal.h"
@@ -51,6 +52,11 @@ int fail_cuda(cudaError_t e, const char *what)
     } while (0)
 
 constexpr int kNumFields = 6;
+
+// Position of the process-wide rand() stream (fsb_params.noise_process_stream): outputs consumed so far by all
+// simulations that share it.  The reference's generator is libc's, one per process (src/fluid_sim.cpp:378-379).
+std::mutex g_proc_noise_mu;
+uint64_t g_proc_noise_pos = 0;
 
 }  // namespace
 
@@ -430,6 +436,17 @@ int advect_one(fsb_sim *s, int b, float *dst, const float *src, const float *u, 
 
 int add_noise(fsb_sim *s)
 {
+    const bool shared = s->prm.noise_process_stream && s->prm.noise_mode == FSB_NOISE_GLIBC && !s->is_block;
+    std::unique_lock<std::mutex> lock(g_proc_noise_mu, std::defer_lock);
+    if (shared) {
+        // another simulation of the process may have drawn from the stream since this one's last step
+        lock.lock();
+        if (s->noise_pos != g_proc_noise_pos) set_noise_window(s, s->prm.noise_seed, g_proc_noise_pos);
+    }
+    struct Publish {
+        fsb_sim *s; bool on;
+        ~Publish() { if (on) g_proc_noise_pos = s->noise_pos; }
+    } publish{s, shared};
     NoiseWindow nw;
     std::memcpy(nw.w, s->noise_win, sizeof(nw.w));
     const int zero = s->prm.noise_mode == FSB_NOISE_ZERO;
@@ -885,7 +902,12 @@ int fsb_device_field(fsb_sim *s, int field, void **dptr)
 int fsb_get_noise_pos(const fsb_sim *s, uint64_t *pos)
 {
     if (!s || !pos) return fail(FSB_EINVAL, "fsb_get_noise_pos: bad argument");
-    *pos = s->noise_pos;
+    if (s->prm.noise_process_stream && !s->is_block) {
+        std::lock_guard<std::mutex> lock(g_proc_noise_mu);
+        *pos = g_proc_noise_pos;
+    } else {
+        *pos = s->noise_pos;
+    }
     return FSB_OK;
 }
 
@@ -893,6 +915,10 @@ int fsb_set_noise(fsb_sim *s, int mode, uint32_t seed, uint64_t pos)
 {
     if (!s || (mode != FSB_NOISE_GLIBC && mode != FSB_NOISE_ZERO)) return fail(FSB_EINVAL, "fsb_set_noise: bad argument");
     s->prm.noise_mode = mode;
+    if (s->prm.noise_process_stream && !s->is_block) {     // repositions the stream for every simulation that shares it
+        std::lock_guard<std::mutex> lock(g_proc_noise_mu);
+        g_proc_noise_pos = pos;
+    }
     return set_noise_window(s, seed, pos);
 }
 

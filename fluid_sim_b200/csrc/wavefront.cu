@@ -1217,7 +1217,10 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaScratchBytes
 
 constexpr int kNaMaxDevices = 64;
 void *g_na_addr[kNaMaxDevices];                 // device address of g_noalloc_scratch, per device ordinal
-unsigned long long g_na_seq[kNaMaxDevices];     // launch sequence number carried by the progress words
+unsigned long long g_na_seq[kNaMaxDevices];     // launch sequence number carried by the ring tags
+// (width, height, sweeps) of the previous call per device: the ring layout inside the array depends on them
+struct NaShape { int W, H, sweeps; };
+NaShape g_na_shape[kNaMaxDevices];
 
 template <int S>
 cudaError_t na_launch(const SweepLaunch &Lc, float *rings, size_t ring_floats, unsigned long long *flags,
@@ -1302,12 +1305,18 @@ int pressure_sweeps_noalloc(const float *d_div, float *d_p, int W, int H, int sw
     const size_t ring_floats = kNaRingBytes / sizeof(float);
 
     // The array keeps whatever the previous call left behind.  The progress words must not look "ahead" of
-    // this call: they are cleared here (the rings themselves are always written before they are read).
-    e = cudaMemsetAsync(flags, 0, kNaFlagBytes, st);
+    // this call: they are cleared here.  Ring words are recognised by a tag made of (launch number mod 2^14,
+    // unit); a call with the same shape as the previous one rewrites every word it later reads, but another
+    // shape lays the rings out differently and could, 16384 launches later, meet a word of an older layout
+    // whose tag matches by accident.  So a change of shape clears the ring region as well (a memset on the
+    // caller's stream: still no allocation).  Tag 0 is never produced.
+    const bool reshaped = g_na_shape[dev].W != W || g_na_shape[dev].H != H || g_na_shape[dev].sweeps != sweeps;
+    e = cudaMemsetAsync(flags, 0, reshaped ? kNaScratchBytes : kNaFlagBytes, st);
     if (e != cudaSuccess) {
-        msg = std::string("fsb_pressure_sweeps_noalloc: clearing the progress words failed: ") + cudaGetErrorString(e);
+        msg = std::string("fsb_pressure_sweeps_noalloc: clearing the built-in scratch failed: ") + cudaGetErrorString(e);
         return -(int)e;
     }
+    g_na_shape[dev] = NaShape{W, H, sweeps};
 
     int left = sweeps;
     bool first = true;

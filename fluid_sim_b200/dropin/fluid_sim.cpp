@@ -41,6 +41,9 @@ void FluidSim::create()
     p.diff_iters = diffSweeps;
     p.viscosity = visc;
     p.diffusion = diff;
+    // rand() is process-global in the reference (src/fluid_sim.cpp:378-379, no srand anywhere): every FluidSim of
+    // the process draws from one stream, so copies, resets and objects stepped in turn continue it
+    p.noise_process_stream = 1;
     check(fsb_create(&p, &sim), "fsb_create");
 }
 
@@ -52,15 +55,12 @@ void FluidSim::destroy()
 
 void FluidSim::copyStateFrom(const FluidSim &o)
 {
-    // the rand() stream is process-global in the reference, so a copied / reset object continues it
-    uint64_t pos = 0;
-    check(fsb_get_noise_pos(o.sim, &pos), "fsb_get_noise_pos");
+    // the three live fields; the position in the rand() stream is shared by all objects (see create())
     std::vector<float> buf((size_t)width * height);
     for (int f = FSB_DENSITY; f <= FSB_VELOCITY_Y; ++f) {
         check(fsb_read_field(o.sim, f, buf.data()), "fsb_read_field");
         check(fsb_write_field(sim, f, buf.data()), "fsb_write_field");
     }
-    (void)pos;
 }
 
 FluidSim::FluidSim(const FluidSim &o)
@@ -79,7 +79,8 @@ FluidSim::FluidSim(FluidSim &&o) noexcept
 FluidSim &FluidSim::operator=(const FluidSim &o)
 {
     if (this == &o) return *this;
-    if (width != o.width || height != o.height || projSweeps != o.projSweeps || diffSweeps != o.diffSweeps) {
+    if (width != o.width || height != o.height || projSweeps != o.projSweeps || diffSweeps != o.diffSweeps ||
+        visc != o.visc || diff != o.diff) {
         destroy();
         width = o.width; height = o.height; projSweeps = o.projSweeps; diffSweeps = o.diffSweeps;
         visc = o.visc; diff = o.diff;
@@ -92,13 +93,8 @@ FluidSim &FluidSim::operator=(const FluidSim &o)
 FluidSim &FluidSim::operator=(FluidSim &&o) noexcept
 {
     if (this == &o) return *this;
-    // `sim = FluidSim();` (src/main.cpp:289): keep this object's position in the rand() stream, like the
-    // reference's process-global generator, and take the other object's (zero) fields
-    if (sim && o.sim && width == o.width && height == o.height && projSweeps == o.projSweeps && diffSweeps == o.diffSweeps) {
-        uint64_t pos = 0;
-        fsb_get_noise_pos(sim, &pos);
-        fsb_set_noise(o.sim, FSB_NOISE_GLIBC, 1, pos);
-    }
+    // `sim = FluidSim();` (src/main.cpp:289): take the other object's (zero) fields; the rand() stream is the
+    // process's, so it simply continues
     destroy();
     width = o.width; height = o.height; projSweeps = o.projSweeps; diffSweeps = o.diffSweeps;
     visc = o.visc; diff = o.diff;

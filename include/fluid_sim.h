@@ -7,7 +7,9 @@
 //
 // Differences a caller can observe:
 //   * copying a FluidSim copies the whole device state (the reference's `sim = FluidSim();` reset idiom,
-//     src/main.cpp:289, keeps working: assigning a fresh object clears the fields);
+//     src/main.cpp:289, keeps working: assigning a fresh object clears the fields); the velocity noise comes from one
+//     rand() stream per process, as in the reference, so copies and objects stepped in turn continue it
+//     (tests/dropin_vs_ref.cpp runs those cases side by side with the compiled reference);
 //   * step() returns before the GPU has finished; every getter synchronises;
 //   * an additional constructor takes run-time sizes and sweep counts (the reference's are literals).
 #ifndef FLUID_SIM_H

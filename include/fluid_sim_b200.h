@@ -69,7 +69,11 @@ typedef struct fsb_params {
     uint32_t noise_seed;   /* srand() seed of the emulated stream (1 = glibc default) */
     uint64_t noise_pos;    /* number of rand() outputs already consumed by the process */
     int device;            /* CUDA device ordinal, -1 = current device */
-    int reserved[7];
+    int noise_process_stream; /* 1: draw the noise from ONE stream shared by every simulation of the process that sets
+                              * this flag, like the reference, whose rand() is process-global (src/fluid_sim.cpp:378-379:
+                              * two FluidSim objects stepped alternately consume alternate stretches of it, a copy goes
+                              * on where the original stopped).  0 (default): the simulation owns its position. */
+    int reserved[6];
 } fsb_params;
 
 /* Fill *p with the reference's literals (200x200, 20/5 sweeps, ...). */
@@ -214,8 +218,21 @@ int fsb_blk_advect_density(fsb_sim *s, float dt, int plus_zero);
  *     with a message and launch nothing;
  *   - the first call on a device looks up the array's device address (once per device, with that device
  *     current): make that first call outside any stream capture;
+ *   - "part of the library image" does not mean "resident from dlopen": CUDA loads a module lazily by
+ *     default, so the array, and the code of each sweep-kernel variant, reach the GPU the first time they are
+ *     used.  The first call on a device (the array: 16.25 MiB) and the first call with a sweep count that
+ *     needs a kernel variant not used before (a few hundred KB of code) therefore make the DRIVER set device
+ *     memory aside and may synchronise the device, although this library still calls no allocator.  A host
+ *     that hands all GPU memory to its own pools must make one call per sweep count it will use BEFORE it
+ *     reserves that memory, and a latency-critical loop must make those calls before it starts; or run the
+ *     process with CUDA_MODULE_LOADING=EAGER, which moves all of it to library load.  After that warm-up a
+ *     call changes nothing in cudaMemGetInfo (tests/test_zz_no_alloc.py checks this);
  *   - every call on a device uses the same array: calls whose GPU work overlaps (different streams, or a
- *     second thread) race with each other - serialise them; calls on one stream are safe back to back. */
+ *     second thread) race with each other - serialise them; calls on one stream are safe back to back;
+ *   - the array keeps the previous call's contents.  Every call clears the progress words; a call whose
+ *     (width, height, sweeps) differ from the previous call's on that device also clears the ring region
+ *     (the rings of another shape sit elsewhere in the array, and their tags repeat every 16384 launches).
+ *     Both are memsets on `stream`, not allocations. */
 int fsb_pressure_sweeps_noalloc(const float *d_divergence, float *d_pressure, int width, int height, int sweeps,
                                 void *stream);
 

@@ -44,6 +44,12 @@ DEFAULT_VARIANTS = [
     (512, 8192, 40, 5),
     (1024, 8192, 40, 5),
     (8192, 8192, 40, 5),   # config 3 (one step costs about a minute of CPU)
+    # bounded samples of the multi-GPU workloads (same columns, few rows) for bench.py's reference arm at N > 1
+    (512, 4096, 100, 5),   # config 5 at 1 GPU (32768 x 4096)
+    (256, 8192, 100, 5),   # config 5 at 2 GPUs
+    (128, 16384, 100, 5),  # config 5 at 4 GPUs
+    (64, 32768, 100, 5),   # config 5 at 8 GPUs
+    (128, 16384, 20, 5),   # config 4 (16384^2, strong scaling)
 ]
 
 CXXFLAGS = ["-std=c++17", "-O2", "-fPIC"]

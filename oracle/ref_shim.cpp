@@ -78,6 +78,9 @@ void ref_reset(void *h)
     delete fresh;
 }
 
+// copy construction (`FluidSim b = a;`): a second object with the same fields; rand() stays process-global
+void *ref_copy(void *h) { return new FluidSim(*static_cast<FluidSim *>(h)); }
+
 void ref_srand(unsigned seed) { srand(seed); }
 void ref_noise_mode(int m) { g_noise_mode = m; }
 int ref_rand(void) { return rand(); }

@@ -377,6 +377,24 @@ def test_cpp_dropin_headless_main():
     assert lines[1] == "after reset d[100][110] 0"
 
 
+def test_cpp_dropin_object_semantics_against_reference(tmp_path):
+    """tests/dropin_vs_ref.cpp: the drop-in class and the compiled reference side by side in one process - copy
+    construction after three steps, two objects stepped alternately, the `sim = FluidSim()` reset idiom, copy
+    assignment: bit-identical fields throughout (the reference's rand() is process-global, src/fluid_sim.cpp:378-379)."""
+    import os
+    import subprocess
+    from oracle import refsim
+    from tests.util import ROOT
+    libdir = os.path.join(ROOT, "fluid_sim_b200")
+    if not os.path.exists(os.path.join(libdir, "libfluidsim_dropin.so")) or not refsim.available(200, 200, 20, 5):
+        pytest.skip("drop-in library or oracle/_ref/libref_200x200_p20_d5.so not built")
+    exe = str(tmp_path / "dropin_vs_ref")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "dropin_vs_ref.cpp"),
+                    "-o", exe, "-L", libdir, "-lfluidsim_dropin", "-lfluidsim_b200", "-ldl", f"-Wl,-rpath,{libdir}"], check=True)
+    out = subprocess.run([exe, refsim.lib_path(200, 200, 20, 5)], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "ALL IDENTICAL" in out.stdout, out.stdout + out.stderr
+
+
 @pytest.mark.parametrize("args", ["256 512 20 5 2", "200 1024 40 5 1", "300 256 33 0 2", "130 512 100 5 1"])
 def test_multi_gpu_matches_single_gpu(args):
     """Column blocks on 2 GPUs (sweep chain handed over through peer memory, NCCL halos) give the single-GPU bits."""
