@@ -318,7 +318,7 @@ class FluidSim:
         self._check(self._lib.fsb_get_stream(self._h, C.byref(p)))
         return p.value
 
-    PROF_NAMES = ("noise", "sor", "gs", "divergence", "gradient", "advect_velocity", "advect_scalar", "boundary")
+    PROF_NAMES = ("noise", "sor", "gs", "divergence", "gradient", "advect_velocity", "advect_scalar", "boundary", "chain")
 
     def profile_enable(self, on=True):
         self._check(self._lib.fsb_profile_enable(self._h, 1 if on else 0))

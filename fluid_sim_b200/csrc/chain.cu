@@ -1,0 +1,550 @@
+// Several passes of FluidSim::step chained inside ONE cooperative launch (sm_100a).
+//
+// Why: an exact-order sweep pass (wavefront.cuh) is a wave that crosses the grid's columns from left to right; the
+// CTA that owns the last columns starts when the wave arrives and finishes one full column walk later, so a
+// stand-alone launch spends more time filling and draining the pipeline than running it full.  Between two passes
+// of velocityStep (src/fluid_sim.cpp:370-406) nothing forces that drain: diffuse -> divergence -> pressure sweeps ->
+// gradient only ever need the previous pass's results a few columns to the right of the cell being worked on.  So
+// this kernel keeps every CTA resident across the passes ("phases") and lets each CTA go on to the next phase as
+// soon as the columns it needs are done, instead of waiting for the whole grid.  The stagger between CTAs is paid
+// once per launch, not once per pass.
+//
+//   * a phase is a list of work items, one per block of columns (all rows); item `i` of every phase is run by
+//     CTA `i mod gridDim.x`, phases in order.  Sweep phases (wf_pass) have at most gridDim.x items, which therefore
+//     run concurrently and hand the strip chain over exactly as the CTAs of a stand-alone launch do;
+//   * done[phase][item] holds the launch number once the item's results are in global memory (release store
+//     after a CTA barrier).  Before an item starts, its CTA waits (acquire loads) for the items of earlier phases
+//     whose results it reads (RAW) or whose inputs it is about to overwrite (WAR), found from column ranges;
+//   * the pointwise phases in between (divergence, gradient + boundaries) evaluate wall values on the fly from the
+//     adjacent interior cell, as setBoundary() (src/fluid_sim.cpp:347-361) defines them, so no separate boundary
+//     pass sits between two phases.  The final walls and corners of u and v are written by the gradient phase.
+//
+// Every wait loop carries a watchdog (global timer): a protocol error traps instead of hanging the GPU.
+// All arithmetic uses round-to-nearest intrinsics in the reference's association order (no FMA).
+#include "wavefront.cuh"
+
+#include <algorithm>
+
+namespace fsb {
+
+namespace {
+
+constexpr int kChainThreads = 320;      // 8 compute warps + 2 transfer warps: the widest sweep pass
+constexpr int kChainMaxPhases = 12;
+constexpr int kChainMaxItems = 1024;    // items per phase the done[] array is sized for
+constexpr int kChainMaxDeps = 4;
+constexpr int kChainMaxSweeps = 3;      // sweep phases per launch
+constexpr int kChainCols = 64;          // columns of a pointwise work item
+
+enum ChainKind { kPhSor = 1, kPhGs = 2, kPhDiv = 3, kPhGrad = 4 };
+
+// "wait until phase `phase` has finished every item whose result columns meet [b0 - lo, b1 + hi]", where [b0, b1]
+// are the waiting item's own columns: the ones it reads (from_out = 0) or the ones it writes (from_out = 1).
+struct ChainDep { int phase, from_out, lo, hi; };
+
+struct ChainPhase {
+    int kind;
+    int nitems;      // work items = ncl * nf
+    int ncl;         // column ranges
+    int nf;          // fields per column range (sweep passes over several fields: one item per field)
+    int cpv;         // columns per range
+    int shift;       // range c reads columns [c*cpv, (c+1)*cpv) and writes [c*cpv - shift, (c+1)*cpv - shift)
+    int wf;          // sweep phases: index into ChainParams::wf
+    int ndeps;
+    ChainDep dep[kChainMaxDeps];
+    float *u, *v;    // pointwise phases: velocity components
+    float *q;        // divergence (written) or pressure (read)
+    float c0;        // -0.5f * h (divergence) / h (gradient)
+};
+
+struct ChainParams {
+    int W, H, nphases;
+    unsigned epoch;                 // number of this launch (done[] words hold the epoch of their last completion)
+    unsigned *done;                 // [kChainMaxPhases][kChainMaxItems]
+    unsigned long long *err;        // watchdog report: (phase << 32 | item) + 1 of the first wait that timed out
+    unsigned long long timeout_ns;
+    ChainPhase ph[kChainMaxPhases];
+    WfKernelParams wf[kChainMaxSweeps];
+};
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v)
+{
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__device__ __forceinline__ unsigned long long global_timer_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+__device__ __forceinline__ int floor_div(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
+
+// Blocks the CTA until the dependencies of item (phase p, column range cl) are met.  Thread d polls dependency d.
+__device__ __forceinline__ void chain_wait(const ChainParams &C, const int p, const int cl)
+{
+    const ChainPhase &ph = C.ph[p];
+    const int d = threadIdx.x;
+    if (d < ph.ndeps) {
+        const ChainDep dep = ph.dep[d];
+        const ChainPhase &q = C.ph[dep.phase];
+        const int b0 = cl * ph.cpv - (dep.from_out ? ph.shift : 0);
+        const int b1 = b0 + ph.cpv - 1;
+        int a = floor_div(b0 - dep.lo + q.shift, q.cpv), b = floor_div(b1 + dep.hi + q.shift, q.cpv);
+        a = max(a, 0);
+        b = min(b, q.ncl - 1);
+        const unsigned *flags = C.done + (size_t)dep.phase * kChainMaxItems;
+        unsigned long long t0 = 0;
+        for (int x = a * q.nf; x < (b + 1) * q.nf; ++x) {
+            unsigned spins = 0;
+            while ((int)(ld_acquire_u32(flags + x) - C.epoch) < 0) {
+                __nanosleep(64);
+                if ((++spins & 0x3ffu) == 0) {
+                    const unsigned long long now = global_timer_ns();
+                    if (t0 == 0) t0 = now;
+                    else if (now - t0 > C.timeout_ns) {
+                        atomicCAS(C.err, 0ull, (((unsigned long long)p << 32) | (unsigned)cl) + 1ull);
+                        __threadfence_system();
+                        __trap();
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+// ---- divergence (src/fluid_sim.cpp:307-314) on the columns [c0, c0 + 64) ---------------------------------------------
+// A warp walks a run of rows with the rows above / below kept in registers; every lane owns two columns (c0 + lane,
+// c0 + 32 + lane), the j-neighbours come from the neighbouring lanes (two edge loads per row for the columns outside
+// the block).  Wall cells are read as setBoundary(1, u) / setBoundary(2, v) would have left them:
+//   u[0][j] = -u[1][j], u[W-1][j] = -u[W-2][j], v[i][0] = -v[i][1], v[i][H-1] = -v[i][H-2]   (:350-360)
+constexpr int kPwRun = 64;   // rows per warp run
+constexpr int kPwBatch = 4;  // rows whose loads are in flight together
+
+__device__ __forceinline__ void chain_divergence(const ChainPhase &ph, const int W, const int H, const int cl)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int c0 = cl * kChainCols;
+    const float *u = ph.u, *v = ph.v;
+    float *div = ph.q;
+    const float mhh = ph.c0;
+    const int ja = c0 + lane, jb = c0 + 32 + lane;
+    const bool ina = ja >= 1 && ja <= H - 2, inb = jb >= 1 && jb <= H - 2;
+    const bool edge_l = (lane == 0) && (c0 - 1 >= 1), edge_r = (lane == 31) && (c0 + 64 <= H - 2);
+    const int je = (lane == 0) ? c0 - 1 : c0 + 64;
+    for (int r0 = 1 + kPwRun * w; r0 <= W - 2; r0 += kPwRun * nw) {
+        const int r1 = min(r0 + kPwRun, W - 1);   // rows [r0, r1)
+        const size_t row0 = (size_t)r0 * H;
+        float uca = ina ? __ldcg(u + row0 + ja) : 0.0f, ucb = inb ? __ldcg(u + row0 + jb) : 0.0f;
+        float uma, umb;
+        if (r0 == 1) {
+            uma = -uca;
+            umb = -ucb;
+        } else {
+            uma = ina ? __ldcg(u + row0 - H + ja) : 0.0f;
+            umb = inb ? __ldcg(u + row0 - H + jb) : 0.0f;
+        }
+        for (int i0 = r0; i0 < r1; i0 += kPwBatch) {
+            float upa[kPwBatch], upb[kPwBatch], vca[kPwBatch], vcb[kPwBatch], ve[kPwBatch];
+#pragma unroll
+            for (int k = 0; k < kPwBatch; ++k) {
+                const int i = i0 + k;
+                const size_t row = (size_t)i * H;
+                const bool rv = i < r1;
+                const bool nx = rv && (i + 1 <= W - 2);
+                upa[k] = (nx && ina) ? __ldcg(u + row + H + ja) : 0.0f;
+                upb[k] = (nx && inb) ? __ldcg(u + row + H + jb) : 0.0f;
+                vca[k] = (rv && ina) ? __ldcg(v + row + ja) : 0.0f;
+                vcb[k] = (rv && inb) ? __ldcg(v + row + jb) : 0.0f;
+                ve[k] = (rv && (edge_l || edge_r)) ? __ldcg(v + row + je) : 0.0f;
+            }
+#pragma unroll
+            for (int k = 0; k < kPwBatch; ++k) {
+                const int i = i0 + k;
+                if (i >= r1) break;                       // warp-uniform
+                const size_t row = (size_t)i * H;
+                const float nua = (i + 1 == W - 1) ? -uca : upa[k];
+                const float nub = (i + 1 == W - 1) ? -ucb : upb[k];
+                // j-neighbours from the neighbouring lanes
+                float la = __shfl_up_sync(0xffffffffu, vca[k], 1), ra = __shfl_down_sync(0xffffffffu, vca[k], 1);
+                float lb = __shfl_up_sync(0xffffffffu, vcb[k], 1), rb = __shfl_down_sync(0xffffffffu, vcb[k], 1);
+                const float b_first = __shfl_sync(0xffffffffu, vcb[k], 0), a_last = __shfl_sync(0xffffffffu, vca[k], 31);
+                if (lane == 0) { la = ve[k]; lb = a_last; }
+                if (lane == 31) { ra = b_first; rb = ve[k]; }
+                if (ja - 1 == 0) la = -vca[k];
+                if (ja + 1 == H - 1) ra = -vca[k];
+                if (jb - 1 == 0) lb = -vcb[k];
+                if (jb + 1 == H - 1) rb = -vcb[k];
+                // (-0.5f*h) * (((u[i+1][j] - u[i-1][j]) + v[i][j+1]) - v[i][j-1])
+                if (ina) div[row + ja] = __fmul_rn(mhh, __fsub_rn(__fadd_rn(__fsub_rn(nua, uma), ra), la));
+                if (inb) div[row + jb] = __fmul_rn(mhh, __fsub_rn(__fadd_rn(__fsub_rn(nub, umb), rb), lb));
+                uma = uca; umb = ucb;
+                uca = nua; ucb = nub;
+            }
+        }
+    }
+}
+
+// ---- pressure gradient (src/fluid_sim.cpp:334-341) on the columns [c0, c0 + 64), then setBoundary(1, u) and
+// setBoundary(2, v) (:342-343) for those columns.  Pressure walls are read as setBoundary(0, p) defines them
+// (p[0][j] = p[1][j], p[i][0] = p[i][1], ...), so the pressure array's own wall cells are never touched.
+__device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W, const int H, const int cl)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int c0 = cl * kChainCols;
+    float *u = ph.u, *v = ph.v;
+    const float *p = ph.q;
+    const float h = ph.c0;
+    const int ja = c0 + lane, jb = c0 + 32 + lane;
+    const bool ina = ja >= 1 && ja <= H - 2, inb = jb >= 1 && jb <= H - 2;
+    const bool edge_l = (lane == 0) && (c0 - 1 >= 1), edge_r = (lane == 31) && (c0 + 64 <= H - 2);
+    const int je = (lane == 0) ? c0 - 1 : c0 + 64;
+    for (int r0 = 1 + kPwRun * w; r0 <= W - 2; r0 += kPwRun * nw) {
+        const int r1 = min(r0 + kPwRun, W - 1);
+        const size_t row0 = (size_t)r0 * H;
+        float pca = ina ? __ldcg(p + row0 + ja) : 0.0f, pcb = inb ? __ldcg(p + row0 + jb) : 0.0f;
+        float pma, pmb;
+        if (r0 == 1) {
+            pma = pca;
+            pmb = pcb;
+        } else {
+            pma = ina ? __ldcg(p + row0 - H + ja) : 0.0f;
+            pmb = inb ? __ldcg(p + row0 - H + jb) : 0.0f;
+        }
+        float pe = (edge_l || edge_r) ? __ldcg(p + row0 + je) : 0.0f;   // this row's pressure just outside the block
+        for (int i0 = r0; i0 < r1; i0 += kPwBatch) {
+            float ppa[kPwBatch], ppb[kPwBatch], pen[kPwBatch], ua[kPwBatch], ub[kPwBatch], va[kPwBatch], vb[kPwBatch];
+#pragma unroll
+            for (int k = 0; k < kPwBatch; ++k) {
+                const int i = i0 + k;
+                const size_t row = (size_t)i * H;
+                const bool rv = i < r1;
+                const bool nx = rv && (i + 1 <= W - 2);
+                ppa[k] = (nx && ina) ? __ldcg(p + row + H + ja) : 0.0f;
+                ppb[k] = (nx && inb) ? __ldcg(p + row + H + jb) : 0.0f;
+                pen[k] = (nx && (edge_l || edge_r)) ? __ldcg(p + row + H + je) : 0.0f;
+                ua[k] = (rv && ina) ? __ldcg(u + row + ja) : 0.0f;
+                ub[k] = (rv && inb) ? __ldcg(u + row + jb) : 0.0f;
+                va[k] = (rv && ina) ? __ldcg(v + row + ja) : 0.0f;
+                vb[k] = (rv && inb) ? __ldcg(v + row + jb) : 0.0f;
+            }
+#pragma unroll
+            for (int k = 0; k < kPwBatch; ++k) {
+                const int i = i0 + k;
+                if (i >= r1) break;
+                const size_t row = (size_t)i * H;
+                const float npa = (i + 1 == W - 1) ? pca : ppa[k];
+                const float npb = (i + 1 == W - 1) ? pcb : ppb[k];
+                float la = __shfl_up_sync(0xffffffffu, pca, 1), ra = __shfl_down_sync(0xffffffffu, pca, 1);
+                float lb = __shfl_up_sync(0xffffffffu, pcb, 1), rb = __shfl_down_sync(0xffffffffu, pcb, 1);
+                const float b_first = __shfl_sync(0xffffffffu, pcb, 0), a_last = __shfl_sync(0xffffffffu, pca, 31);
+                if (lane == 0) { la = pe; lb = a_last; }
+                if (lane == 31) { ra = b_first; rb = pe; }
+                if (ja - 1 == 0) la = pca;
+                if (ja + 1 == H - 1) ra = pca;
+                if (jb - 1 == 0) lb = pcb;
+                if (jb + 1 == H - 1) rb = pcb;
+                // u -= (0.5f*(p[i+1][j] - p[i-1][j])) / h ; v -= (0.5f*(p[i][j+1] - p[i][j-1])) / h
+                if (ina) {
+                    u[row + ja] = __fsub_rn(ua[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(npa, pma)), h));
+                    v[row + ja] = __fsub_rn(va[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(ra, la)), h));
+                }
+                if (inb) {
+                    u[row + jb] = __fsub_rn(ub[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(npb, pmb)), h));
+                    v[row + jb] = __fsub_rn(vb[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(rb, lb)), h));
+                }
+                pma = pca; pmb = pcb;
+                pca = npa; pcb = npb;
+                pe = pen[k];
+            }
+        }
+    }
+    __syncthreads();   // every interior cell of the block carries its new velocity
+    // setBoundary(1, u), setBoundary(2, v) on this block's columns (src/fluid_sim.cpp:347-367)
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (int t = tid; t < 2 * kChainCols; t += nt) {
+        const int j = c0 + (t % kChainCols);
+        if (j < 1 || j > H - 2) continue;
+        const int i = (t < kChainCols) ? 0 : W - 1, iin = (t < kChainCols) ? 1 : W - 2;
+        u[(size_t)i * H + j] = -__ldcg(u + (size_t)iin * H + j);     // b == 1: negated on the i-walls (:357-358)
+        v[(size_t)i * H + j] = __ldcg(v + (size_t)iin * H + j);
+    }
+    for (int side = 0; side < 2; ++side) {
+        const int j = side ? H - 1 : 0, jin = side ? H - 2 : 1;
+        if (j < c0 || j >= c0 + kChainCols) continue;
+        for (int i = 1 + tid; i <= W - 2; i += nt) {
+            u[(size_t)i * H + j] = __ldcg(u + (size_t)i * H + jin);
+            v[(size_t)i * H + j] = -__ldcg(v + (size_t)i * H + jin);  // b == 2: negated on the j-walls (:351-352)
+        }
+        if (tid < 2) {
+            // corners: 0.5f * (x[iin][j] + x[i][jin]), both wall cells, rebuilt from the interior (:363-366)
+            const int i = tid ? W - 1 : 0, iin = tid ? W - 2 : 1;
+            const float ui = __ldcg(u + (size_t)iin * H + jin), vi = __ldcg(v + (size_t)iin * H + jin);
+            u[(size_t)i * H + j] = __fmul_rn(0.5f, __fadd_rn(ui, -ui));
+            v[(size_t)i * H + j] = __fmul_rn(0.5f, __fadd_rn(-vi, vi));
+        }
+    }
+}
+
+template <int SD, int SP>
+__global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_constant__ ChainParams C)
+{
+    extern __shared__ float4 smem4[];
+    float *smem = reinterpret_cast<float *>(smem4);
+    for (int p = 0; p < C.nphases; ++p) {
+        const ChainPhase &ph = C.ph[p];
+        for (int item = blockIdx.x; item < ph.nitems; item += gridDim.x) {
+            const int cl = item / ph.nf, fi = item - cl * ph.nf;
+            chain_wait(C, p, cl);
+            if (ph.kind == kPhSor) {
+                if constexpr (SD > 0) wf_pass<SD, kSor, true>(C.wf[ph.wf], cl, fi, smem);
+            } else if (ph.kind == kPhGs) {
+                wf_pass<SP, kGaussSeidel, false>(C.wf[ph.wf], cl, fi, smem);
+            } else if (ph.kind == kPhDiv) {
+                chain_divergence(ph, C.W, C.H, cl);
+            } else if (ph.kind == kPhGrad) {
+                chain_gradient(ph, C.W, C.H, cl);
+            }
+            __syncthreads();   // the item's results are written, its shared memory is free
+            if (threadIdx.x == 0) {
+                __threadfence();
+                st_release_u32(C.done + (size_t)p * kChainMaxItems + item, C.epoch);
+            }
+        }
+    }
+}
+
+// Strips per CTA of a sweep phase inside the chain kernel: as many as the 8 compute warps, shared memory and
+// the grid allow (a hand-over inside a CTA is far cheaper than one through the global rings).
+template <int S>
+bool chain_pick(int H, int nstg, int nfields, int max_ctas, int *nstr_out, int *ncta_out, size_t *smem_out)
+{
+    using L = WfLayout<S>;
+    if (nstg < 1 || nstg > L::kMaxStagesS) return false;
+    const int NS = (H + S * nstg + 31) / 32;
+    const int max_warps = kChainThreads / 32 - 2;
+    int nstr = 4;
+    while (nstr > 1 && (nstr * nstg > max_warps || wf_smem_bytes<S>(nstr, nstg) > 227 * 1024 || nstr > NS)) nstr >>= 1;
+    if (nstr * nstg > max_warps || wf_smem_bytes<S>(nstr, nstg) > 227 * 1024) return false;
+    const int ncta = (NS + nstr - 1) / nstr;
+    if ((long long)ncta * nfields > max_ctas || ncta > kWfMaxCtas) return false;
+    *nstr_out = nstr;
+    *ncta_out = ncta;
+    *smem_out = wf_smem_bytes<S>(nstr, nstg);
+    return true;
+}
+
+constexpr int kChainSD = 5, kChainSP = 10;   // sweeps per warp of the diffusion / pressure phases (the instantiated pair)
+
+struct ChainPlan {
+    bool ok = false;
+    int W = 0, H = 0, D = 0, P = 0;
+    int sor_nstr = 0, sor_ncta = 0, gs_nstr = 0, gs_ncta = 0, grid = 0;
+    size_t smem = 0;
+    size_t sor_ring_floats = 0, gs_ring_floats = 0;
+};
+
+}  // namespace
+
+struct ChainState {
+    ChainPlan plan_full, plan_proj;       // diffuse + project / project only
+    unsigned char *buf = nullptr;         // [done | err | flags sor | flags gs | rings sor | rings gs]
+    size_t bytes = 0;
+    unsigned epoch = 0;
+};
+
+namespace {
+
+// Can (D diffusion sweeps of u and v +) P pressure sweeps run as one chained launch on this grid?
+ChainPlan make_plan(int W, int H, int D, int P)
+{
+    ChainPlan pl;
+    pl.W = W; pl.H = H; pl.D = D; pl.P = P;
+    if (P < kChainSP || P % kChainSP != 0) return pl;
+    if (D != 0 && D % kChainSD != 0) return pl;
+    int dev = 0, nsm = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return pl;
+    if (cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return pl;
+    size_t smem_gs = 0, smem_sor = 0;
+    if (!chain_pick<kChainSP>(H, P / kChainSP, 1, nsm, &pl.gs_nstr, &pl.gs_ncta, &smem_gs)) return pl;
+    if (D > 0 && !chain_pick<kChainSD>(H, D / kChainSD, 2, nsm, &pl.sor_nstr, &pl.sor_ncta, &smem_sor)) return pl;
+    pl.smem = std::max(smem_gs, smem_sor);
+    const int nblk = (H + kChainCols - 1) / kChainCols;
+    pl.grid = std::max(std::max(pl.gs_ncta, 2 * pl.sor_ncta), std::min(nblk, nsm));
+    if (pl.grid > nsm || nblk > kChainMaxItems || pl.grid > kChainMaxItems) return pl;
+    auto kern = D > 0 ? chain_kernel<kChainSD, kChainSP> : chain_kernel<0, kChainSP>;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return pl;
+    }
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kChainThreads, pl.smem) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return pl;
+    }
+    if ((long long)per_sm * nsm < pl.grid) return pl;
+    pl.gs_ring_floats = (size_t)(P / kChainSP) * pl.gs_ncta * WfLayout<kChainSP>::kBoundaryFloats;
+    pl.sor_ring_floats = D > 0 ? (size_t)2 * (D / kChainSD) * pl.sor_ncta * WfLayout<kChainSD>::kBoundaryFloats : 0;
+    pl.ok = true;
+    return pl;
+}
+
+void fill_wf(WfKernelParams &P, int W, int H, int nstr, int nstg, int ncta, float a, float c_recip, float omega,
+             float *rings, unsigned long long *flags, unsigned long long seq)
+{
+    P.W = W;
+    P.H = H;
+    P.pitch = H;
+    P.jbase = 0;
+    P.nstr = nstr;
+    P.nstg = nstg;
+    P.ncta = ncta;
+    P.c_base = 0;
+    P.a = a;
+    P.c_recip = c_recip;
+    P.omega = omega;
+    P.xchg = rings;
+    P.flags = flags;
+    P.seq_base = seq << 32;
+    P.link = SweepLink{};
+    P.link_seq_base = 0;
+}
+
+}  // namespace
+
+void chain_state_destroy(ChainState *cs)
+{
+    if (!cs) return;
+    if (cs->buf) cudaFree(cs->buf);
+    delete cs;
+}
+
+// diffuse(u), diffuse(v) (when A.sor_sweeps > 0) and project(u, v, p, div) of velocityStep as one launch.
+// Returns cudaErrorNotSupported when this grid / sweep counts have no chained configuration (the caller then
+// runs the passes as separate launches).
+cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st,
+                                 bool query_only)
+{
+    if (!cs) cs = new ChainState();
+    ChainPlan &pl = A.sor_sweeps > 0 ? cs->plan_full : cs->plan_proj;
+    if (pl.W != A.W || pl.H != A.H || pl.D != A.sor_sweeps || pl.P != A.gs_sweeps) pl = make_plan(A.W, A.H, A.sor_sweeps, A.gs_sweeps);
+    if (!pl.ok) return cudaErrorNotSupported;
+    if (query_only) return cudaSuccess;
+
+    // scratch: done words, watchdog word, progress words and boundary rings of the two sweep phases
+    const size_t done_bytes = (size_t)kChainMaxPhases * kChainMaxItems * sizeof(unsigned);
+    const size_t flag_bytes = sweep_flag_words() * sizeof(unsigned long long);
+    const size_t sor_rings = std::max(cs->plan_full.sor_ring_floats, pl.sor_ring_floats) * sizeof(float);
+    const size_t gs_rings = std::max(std::max(cs->plan_full.gs_ring_floats, cs->plan_proj.gs_ring_floats), pl.gs_ring_floats) * sizeof(float);
+    const size_t need = done_bytes + 256 + 2 * flag_bytes + sor_rings + gs_rings;
+    if (need > cs->bytes) {
+        cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) return e;
+        if (cs->buf) cudaFree(cs->buf);
+        cs->buf = nullptr;
+        cs->bytes = 0;
+        e = cudaMalloc(&cs->buf, need);
+        if (e != cudaSuccess) return e;
+        e = cudaMemsetAsync(cs->buf, 0, need, st);   // done epoch 0 and ring tag 0 are never produced
+        if (e != cudaSuccess) return e;
+        cs->bytes = need;
+    }
+    unsigned char *b = cs->buf;
+    unsigned *done = reinterpret_cast<unsigned *>(b);
+    unsigned long long *err = reinterpret_cast<unsigned long long *>(b + done_bytes);
+    unsigned long long *flags_sor = reinterpret_cast<unsigned long long *>(b + done_bytes + 256);
+    unsigned long long *flags_gs = reinterpret_cast<unsigned long long *>(b + done_bytes + 256 + flag_bytes);
+    float *rings_sor = reinterpret_cast<float *>(b + done_bytes + 256 + 2 * flag_bytes);
+    float *rings_gs = reinterpret_cast<float *>(b + done_bytes + 256 + 2 * flag_bytes + sor_rings);
+
+    ChainParams C{};
+    C.W = A.W;
+    C.H = A.H;
+    C.epoch = ++cs->epoch;
+    C.done = done;
+    C.err = err;
+    C.timeout_ns = 20ull * 1000 * 1000 * 1000;
+    const int nblk = (A.H + kChainCols - 1) / kChainCols;
+    int np = 0, nwf = 0;
+    int ph_sor = -1;
+    if (A.sor_sweeps > 0) {
+        ChainPhase &ph = C.ph[np];
+        ph.kind = kPhSor;
+        ph.ncl = pl.sor_ncta;
+        ph.nf = 2;
+        ph.nitems = 2 * pl.sor_ncta;
+        ph.cpv = 32 * pl.sor_nstr;
+        ph.shift = A.sor_sweeps;
+        ph.wf = nwf;
+        ph.ndeps = 0;
+        WfKernelParams &P = C.wf[nwf++];
+        fill_wf(P, A.W, A.H, pl.sor_nstr, A.sor_sweeps / kChainSD, pl.sor_ncta, A.a, A.c_recip, A.omega, rings_sor, flags_sor, ++scr.seq);
+        P.fld[0] = SweepField{A.u, A.u, A.u, -1.0f, 1.0f};    // setBoundary(1, u): negated on the i-walls
+        P.fld[1] = SweepField{A.v, A.v, A.v, 1.0f, -1.0f};    // setBoundary(2, v): negated on the j-walls
+        P.fld[2] = P.fld[0];
+        ph_sor = np++;
+    }
+    const int ph_div = np;
+    {
+        ChainPhase &ph = C.ph[np++];
+        ph.kind = kPhDiv;
+        ph.ncl = ph.nitems = nblk;
+        ph.nf = 1;
+        ph.cpv = kChainCols;
+        ph.shift = 0;
+        ph.u = A.u;
+        ph.v = A.v;
+        ph.q = A.div;
+        const float h = 1.0f / (float)A.W;        // src/fluid_sim.cpp:304
+        ph.c0 = -0.5f * h;                        // evaluated first (:311)
+        ph.ndeps = 0;
+        if (ph_sor >= 0) ph.dep[ph.ndeps++] = ChainDep{ph_sor, 0, 1, 1};   // u, v of the block and one column either side
+    }
+    const int ph_gs = np;
+    {
+        ChainPhase &ph = C.ph[np++];
+        ph.kind = kPhGs;
+        ph.ncl = ph.nitems = pl.gs_ncta;
+        ph.nf = 1;
+        ph.cpv = 32 * pl.gs_nstr;
+        ph.shift = A.gs_sweeps;
+        ph.wf = nwf;
+        ph.ndeps = 0;
+        ph.dep[ph.ndeps++] = ChainDep{ph_div, 0, 0, 0};                    // the divergence of the columns it loads
+        WfKernelParams &P = C.wf[nwf++];
+        fill_wf(P, A.W, A.H, pl.gs_nstr, A.gs_sweeps / kChainSP, pl.gs_ncta, 0.0f, 1.0f, 1.0f, rings_gs, flags_gs, ++scr.seq);
+        P.fld[0] = SweepField{nullptr, A.div, A.p, 1.0f, 1.0f};           // p starts at 0 (:313, :316)
+        P.fld[1] = P.fld[2] = P.fld[0];
+    }
+    {
+        ChainPhase &ph = C.ph[np++];
+        ph.kind = kPhGrad;
+        ph.ncl = ph.nitems = nblk;
+        ph.nf = 1;
+        ph.cpv = kChainCols;
+        ph.shift = 0;
+        ph.u = A.u;
+        ph.v = A.v;
+        ph.q = A.p;
+        ph.c0 = 1.0f / (float)A.W;
+        ph.ndeps = 0;
+        ph.dep[ph.ndeps++] = ChainDep{ph_gs, 0, 1, 1};    // pressure of the block and one column either side
+        ph.dep[ph.ndeps++] = ChainDep{ph_div, 1, 1, 1};   // the divergence blocks that read the u, v about to change
+    }
+    C.nphases = np;
+
+    void *args[] = {&C};
+    const void *kern = A.sor_sweeps > 0 ? (const void *)chain_kernel<kChainSD, kChainSP> : (const void *)chain_kernel<0, kChainSP>;
+    return cudaLaunchCooperativeKernel(kern, dim3(pl.grid), dim3(kChainThreads), args, pl.smem, st);
+}
+
+}  // namespace fsb

@@ -15,6 +15,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -70,6 +71,8 @@ struct fsb_sim {
     float *f[kNumFields] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     float *temp[2] = {nullptr, nullptr};   // MacCormack scratch (src/fluid_sim.cpp:52-53 tempField1/2), lazy
     SweepScratch sweep;
+    ChainState *chain = nullptr;           // passes chained inside one launch (chain.cu), lazily created
+    bool chain_enabled = true;
     NoiseTables noise_tables;
     uint32_t noise_win[kRandDeg];          // window of the emulated rand() stream at noise_pos
     uint64_t noise_pos = 0;
@@ -464,15 +467,54 @@ int add_noise(fsb_sim *s)
     return FSB_OK;
 }
 
+// diffuse(u), diffuse(v) (with_diffuse) and project() as ONE launch whose CTAs move from pass to pass as soon as the
+// columns they need are done (chain.cu).  *done = false: no chained configuration for this grid / these sweep counts /
+// this tuning; the caller runs the passes one launch at a time.
+int chained_project(fsb_sim *s, bool with_diffuse, float dt, bool *done)
+{
+    *done = false;
+    if (!s->chain_enabled || s->is_block || s->tune_strips || s->tune_levels || s->tune_stages) return FSB_OK;
+    ChainProjectArgs A{};
+    A.W = s->W;
+    A.H = s->H;
+    A.u = s->f[FSB_VELOCITY_X];
+    A.v = s->f[FSB_VELOCITY_Y];
+    A.p = s->f[FSB_PREV_VEL_X];
+    A.div = s->f[FSB_PREV_VEL_Y];
+    A.gs_sweeps = s->prm.proj_iters;
+    A.sor_sweeps = 0;
+    A.a = 0.0f;
+    A.c_recip = 1.0f;
+    A.omega = s->prm.omega;
+    if (with_diffuse) {
+        A.a = dt * s->prm.viscosity * (float)s->W * (float)s->H;   // ((dt*diff)*W)*H, src/fluid_sim.cpp:45
+        A.c_recip = 1.0f / (1.0f + 4.0f * A.a);                    // :46
+        A.sor_sweeps = s->prm.diff_iters;
+        if (A.sor_sweeps <= 0 || A.a == 0.0f) return FSB_OK;
+    }
+    cudaError_t e = launch_chain_project(A, s->chain, s->sweep, s->stream, true);
+    if (e == cudaErrorNotSupported) return FSB_OK;
+    if (e == cudaSuccess) {
+        ProfScope ps(s, FSB_PROF_CHAIN);
+        e = launch_chain_project(A, s->chain, s->sweep, s->stream, false);
+    }
+    if (e != cudaSuccess) return fail_cuda(e, "chained diffuse/project launch");
+    s->launches += 1;
+    *done = true;
+    return FSB_OK;
+}
+
 int velocity_step(fsb_sim *s, float dt)
 {
     FSB_TRY(add_noise(s));
-    {
+    bool chained = false;
+    FSB_TRY(chained_project(s, true, dt, &chained));
+    if (!chained) {
         float *xs[2] = {s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y]};
         const int bs[2] = {1, 2};
         FSB_TRY(diffuse_fields(s, 2, xs, bs, s->prm.viscosity, dt, false, nullptr));
+        FSB_TRY(project(s, s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_X], s->f[FSB_PREV_VEL_Y]));
     }
-    FSB_TRY(project(s, s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_X], s->f[FSB_PREV_VEL_Y]));
     // advect both components out of (u, v) into the free prev buffers, then swap roles
     float *u = s->f[FSB_VELOCITY_X], *v = s->f[FSB_VELOCITY_Y];
     float *nu = s->f[FSB_PREV_VEL_X], *nv = s->f[FSB_PREV_VEL_Y];
@@ -490,6 +532,8 @@ int velocity_step(fsb_sim *s, float dt)
     }
     std::swap(s->f[FSB_VELOCITY_X], s->f[FSB_PREV_VEL_X]);
     std::swap(s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_Y]);
+    FSB_TRY(chained_project(s, false, dt, &chained));
+    if (chained) return FSB_OK;
     return project(s, s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_X], s->f[FSB_PREV_VEL_Y]);
 }
 
@@ -631,6 +675,10 @@ static int create_common(const fsb_params *p, const GridView *block, fsb_sim **o
         FSB_CREATE_CUDA(cudaMalloc(&s->link_buf, kLinkBytes));
         FSB_CREATE_CUDA(cudaMemsetAsync(s->link_buf, 0, kLinkBytes, s->stream));
     }
+    {
+        const char *e = std::getenv("FSB_CHAIN");      // FSB_CHAIN=0: every pass as its own launch (A/B timing, debugging)
+        s->chain_enabled = !(e && e[0] == '0');
+    }
     s->noise_step_jump = jump_matrix(2ull * (uint64_t)prm.width * (uint64_t)prm.height);
     set_noise_window(s, prm.noise_seed, prm.noise_pos);
     FSB_CREATE_CUDA(cudaStreamSynchronize(s->stream));
@@ -653,6 +701,8 @@ int fsb_destroy(fsb_sim *s)
             if (s->temp[k]) cudaFree(s->temp[k]);
         if (s->sweep.xchg) cudaFree(s->sweep.xchg);
         if (s->sweep.flags) cudaFree(s->sweep.flags);
+        chain_state_destroy(s->chain);
+        s->chain = nullptr;
         if (s->d_entries) cudaFree(s->d_entries);
         if (s->d_segs) cudaFree(s->d_segs);
         noise_tables_destroy(s->noise_tables);

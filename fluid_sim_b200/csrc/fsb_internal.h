@@ -89,6 +89,20 @@ bool sweep_config_fits(const SweepLaunch &L);   // can (levels, stages) be launc
 
 cudaError_t launch_sweep_pass(const SweepLaunch &L, SweepScratch &scr, cudaStream_t st, int *launches);
 
+// Passes of velocityStep chained inside one cooperative launch (chain.cu): diffuse(u), diffuse(v) when sor_sweeps > 0,
+// then project(u, v, p, div).  cudaErrorNotSupported: no chained configuration for this grid / these sweep counts.
+struct ChainState;
+struct ChainProjectArgs {
+    int W, H;
+    float *u, *v, *p, *div;
+    int sor_sweeps;            // 0: projection only
+    float a, c_recip, omega;   // SOR coefficients (src/fluid_sim.cpp:45-47)
+    int gs_sweeps;
+};
+cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st,
+                                 bool query_only);
+void chain_state_destroy(ChainState *cs);
+
 // Allocation-free pressure sweeps on caller-owned device buffers (wavefront.cu); see fsb_pressure_sweeps_noalloc.
 int pressure_sweeps_noalloc(const float *d_div, float *d_p, int W, int H, int sweeps, cudaStream_t st, std::string &msg);
 

@@ -167,7 +167,9 @@ enum {
     FSB_PROF_ADVECT_VELOCITY = 5,  /* both velocity components, :401-402  */
     FSB_PROF_ADVECT_SCALAR = 6,    /* one field, :421                     */
     FSB_PROF_BOUNDARY = 7,         /* setBoundary, :347-367               */
-    FSB_PROF_COUNT = 8
+    FSB_PROF_CHAIN = 8,            /* diffuse + project (or project alone) chained inside one launch: the sweep passes,
+                                    * divergence, gradient and their boundaries of :390-394 / :405 */
+    FSB_PROF_COUNT = 9
 };
 int fsb_profile_enable(fsb_sim *s, int on);
 int fsb_profile_read(fsb_sim *s, double *ms, uint64_t *counts, int reset);
