@@ -98,6 +98,7 @@ ABI = [
     ("fsb_get_stream", C.c_int, [_SIM, C.POINTER(C.c_void_p)]),
     ("fsb_profile_enable", C.c_int, [_SIM, C.c_int]),
     ("fsb_profile_read", C.c_int, [_SIM, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]),
+    ("fsb_chain_trace", C.c_int, [_SIM, C.c_int, C.POINTER(C.c_uint64), C.c_int, C.c_int, _ip]),
     ("fsb_create_block", C.c_int, [C.POINTER(Params), C.c_int, C.c_int, C.c_int, C.POINTER(_SIM)]),
     ("fsb_block_info", C.c_int, [_SIM, _ip, _ip, _ip, _ip]),
     ("fsb_link_handle", C.c_int, [_SIM, C.c_void_p]),
@@ -330,6 +331,14 @@ class FluidSim:
         cnt = (C.c_uint64 * n)()
         self._check(self._lib.fsb_profile_read(self._h, ms, cnt, 1 if reset else 0))
         return {name: (ms[i], cnt[i]) for i, name in enumerate(self.PROF_NAMES)}
+
+    def chain_trace(self, which=0, max_phases=12, max_items=160):
+        """[phases, max_items, 3] uint64 ns (wait begins, work begins, results published) of the last chained launch."""
+        out = np.zeros((max_phases, max_items, 3), np.uint64)
+        n = C.c_int()
+        self._check(self._lib.fsb_chain_trace(self._h, which, out.ctypes.data_as(C.POINTER(C.c_uint64)), max_phases, max_items,
+                                              C.byref(n)))
+        return out[:n.value]
 
     def set_tuning(self, strips_per_cta=0, sweeps_per_warp=0, max_stages=0):
         self._check(self._lib.fsb_set_tuning(self._h, strips_per_cta, sweeps_per_warp, max_stages))

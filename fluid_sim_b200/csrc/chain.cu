@@ -63,6 +63,7 @@ struct ChainParams {
     unsigned *done;                 // [kChainMaxPhases][kChainMaxItems]
     unsigned long long *err;        // watchdog report: (phase << 32 | item) + 1 of the first wait that timed out
     unsigned long long timeout_ns;
+    unsigned long long *trace;      // [kChainMaxPhases][kChainMaxItems][3] global-timer ns: wait begins, work begins, work ends
     ChainPhase ph[kChainMaxPhases];
     WfKernelParams wf[kChainMaxSweeps];
 };
@@ -304,7 +305,10 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
         const ChainPhase &ph = C.ph[p];
         for (int item = blockIdx.x; item < ph.nitems; item += gridDim.x) {
             const int cl = item / ph.nf, fi = item - cl * ph.nf;
+            unsigned long long *tr = C.trace + ((size_t)p * kChainMaxItems + item) * 3;
+            if (threadIdx.x == 0) tr[0] = global_timer_ns();
             chain_wait(C, p, cl);
+            if (threadIdx.x == 0) tr[1] = global_timer_ns();
             if (ph.kind == kPhSor) {
                 if constexpr (SD > 0) wf_pass<SD, kSor, true>(C.wf[ph.wf], cl, fi, smem);
             } else if (ph.kind == kPhGs) {
@@ -318,6 +322,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
             if (threadIdx.x == 0) {
                 __threadfence();
                 st_release_u32(C.done + (size_t)p * kChainMaxItems + item, C.epoch);
+                tr[2] = global_timer_ns();
             }
         }
     }
@@ -357,7 +362,8 @@ struct ChainPlan {
 
 struct ChainState {
     ChainPlan plan_full, plan_proj;       // diffuse + project / project only
-    unsigned char *buf = nullptr;         // [done | err | flags sor | flags gs | rings sor | rings gs]
+    unsigned char *buf = nullptr;         // [done | err | trace | flags sor | flags gs | rings sor | rings gs]
+    int last_nphases[2] = {0, 0};         // of the most recent launch of each kind (for chain_read_trace)
     size_t bytes = 0;
     unsigned epoch = 0;
 };
@@ -445,7 +451,9 @@ cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, Swe
     const size_t flag_bytes = sweep_flag_words() * sizeof(unsigned long long);
     const size_t sor_rings = std::max(cs->plan_full.sor_ring_floats, pl.sor_ring_floats) * sizeof(float);
     const size_t gs_rings = std::max(std::max(cs->plan_full.gs_ring_floats, cs->plan_proj.gs_ring_floats), pl.gs_ring_floats) * sizeof(float);
-    const size_t need = done_bytes + 256 + 2 * flag_bytes + sor_rings + gs_rings;
+    const size_t trace_one = (size_t)kChainMaxPhases * kChainMaxItems * 3 * sizeof(unsigned long long);
+    const size_t trace_bytes = 2 * trace_one;      // one timeline per kind of launch (with / without the diffusion phase)
+    const size_t need = done_bytes + 256 + trace_bytes + 2 * flag_bytes + sor_rings + gs_rings;
     if (need > cs->bytes) {
         cudaError_t e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) return e;
@@ -461,10 +469,12 @@ cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, Swe
     unsigned char *b = cs->buf;
     unsigned *done = reinterpret_cast<unsigned *>(b);
     unsigned long long *err = reinterpret_cast<unsigned long long *>(b + done_bytes);
-    unsigned long long *flags_sor = reinterpret_cast<unsigned long long *>(b + done_bytes + 256);
-    unsigned long long *flags_gs = reinterpret_cast<unsigned long long *>(b + done_bytes + 256 + flag_bytes);
-    float *rings_sor = reinterpret_cast<float *>(b + done_bytes + 256 + 2 * flag_bytes);
-    float *rings_gs = reinterpret_cast<float *>(b + done_bytes + 256 + 2 * flag_bytes + sor_rings);
+    unsigned long long *trace = reinterpret_cast<unsigned long long *>(b + done_bytes + 256 + (A.sor_sweeps > 0 ? 0 : trace_one));
+    unsigned char *b2 = b + done_bytes + 256 + trace_bytes;
+    unsigned long long *flags_sor = reinterpret_cast<unsigned long long *>(b2);
+    unsigned long long *flags_gs = reinterpret_cast<unsigned long long *>(b2 + flag_bytes);
+    float *rings_sor = reinterpret_cast<float *>(b2 + 2 * flag_bytes);
+    float *rings_gs = reinterpret_cast<float *>(b2 + 2 * flag_bytes + sor_rings);
 
     ChainParams C{};
     C.W = A.W;
@@ -473,6 +483,7 @@ cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, Swe
     C.done = done;
     C.err = err;
     C.timeout_ns = 20ull * 1000 * 1000 * 1000;
+    C.trace = trace;
     const int nblk = (A.H + kChainCols - 1) / kChainCols;
     int np = 0, nwf = 0;
     int ph_sor = -1;
@@ -541,10 +552,32 @@ cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, Swe
         ph.dep[ph.ndeps++] = ChainDep{ph_div, 1, 1, 1};   // the divergence blocks that read the u, v about to change
     }
     C.nphases = np;
+    cs->last_nphases[A.sor_sweeps > 0 ? 0 : 1] = np;
 
     void *args[] = {&C};
     const void *kern = A.sor_sweeps > 0 ? (const void *)chain_kernel<kChainSD, kChainSP> : (const void *)chain_kernel<0, kChainSP>;
     return cudaLaunchCooperativeKernel(kern, dim3(pl.grid), dim3(kChainThreads), args, pl.smem, st);
+}
+
+// Start / end times of every work item of the most recent chained launch of one kind (which = 0: diffuse + project,
+// 1: project alone): out[(phase * items + item) * 3 + k] in
+// nanoseconds of the GPU's global timer (k = 0 wait begins, 1 work begins, 2 results published); 0 = item did not run.
+// The caller synchronises the stream first.
+cudaError_t chain_read_trace(ChainState *cs, int which, unsigned long long *out, int max_phases, int max_items, int *nphases)
+{
+    *nphases = 0;
+    if (!cs || !cs->buf || which < 0 || which > 1) return cudaSuccess;
+    const size_t done_bytes = (size_t)kChainMaxPhases * kChainMaxItems * sizeof(unsigned);
+    const size_t trace_one = (size_t)kChainMaxPhases * kChainMaxItems * 3 * sizeof(unsigned long long);
+    const unsigned long long *trace = reinterpret_cast<const unsigned long long *>(cs->buf + done_bytes + 256 + which * trace_one);
+    const int np = std::min(cs->last_nphases[which], max_phases), ni = std::min(max_items, kChainMaxItems);
+    for (int p = 0; p < np; ++p) {
+        cudaError_t e = cudaMemcpy(out + (size_t)p * max_items * 3, trace + (size_t)p * kChainMaxItems * 3,
+                                   (size_t)ni * 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) return e;
+    }
+    *nphases = np;
+    return cudaSuccess;
 }
 
 }  // namespace fsb

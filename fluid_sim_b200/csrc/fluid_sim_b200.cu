@@ -1072,6 +1072,16 @@ int fsb_profile_enable(fsb_sim *s, int on)
     return FSB_OK;
 }
 
+int fsb_chain_trace(fsb_sim *s, int which, uint64_t *out, int max_phases, int max_items, int *nphases)
+{
+    if (!s || !out || !nphases || max_phases < 1 || max_items < 1) return fail(FSB_EINVAL, "fsb_chain_trace: bad argument");
+    DeviceGuard guard(s->device);
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    std::memset(out, 0, (size_t)max_phases * max_items * 3 * sizeof(uint64_t));
+    FSB_CUDA(chain_read_trace(s->chain, which, reinterpret_cast<unsigned long long *>(out), max_phases, max_items, nphases));
+    return FSB_OK;
+}
+
 int fsb_profile_read(fsb_sim *s, double *ms, uint64_t *counts, int reset)
 {
     if (!s) return fail(FSB_EINVAL, "fsb_profile_read: null handle");

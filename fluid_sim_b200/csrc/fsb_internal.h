@@ -102,6 +102,7 @@ struct ChainProjectArgs {
 cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st,
                                  bool query_only);
 void chain_state_destroy(ChainState *cs);
+cudaError_t chain_read_trace(ChainState *cs, int which, unsigned long long *out, int max_phases, int max_items, int *nphases);
 
 // Allocation-free pressure sweeps on caller-owned device buffers (wavefront.cu); see fsb_pressure_sweeps_noalloc.
 int pressure_sweeps_noalloc(const float *d_div, float *d_p, int W, int H, int sweeps, cudaStream_t st, std::string &msg);

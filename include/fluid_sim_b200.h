@@ -173,6 +173,11 @@ enum {
 };
 int fsb_profile_enable(fsb_sim *s, int on);
 int fsb_profile_read(fsb_sim *s, double *ms, uint64_t *counts, int reset);
+/* Diagnostic with no counterpart in the reference: timeline of the most recent chained launch of one kind (which = 0: the kernel that runs
+ * diffuse + project, 1: project alone, of velocityStep, src/fluid_sim.cpp:390-394 / :405, as phases of one launch).
+ * out[(phase * max_items + item) * 3 + k], k = 0 wait begins, 1 work begins, 2 results published, in nanoseconds of
+ * the GPU's global timer; items are blocks of columns, left to right.  Synchronises the simulation's stream. */
+int fsb_chain_trace(fsb_sim *s, int which, uint64_t *out, int max_phases, int max_items, int *nphases);
 
 /* ---- column blocks: one simulation per GPU, each owning all rows of a range of columns --------------------
  * No counterpart in the reference (it is single-process); this is the sharded form of the same passes.
