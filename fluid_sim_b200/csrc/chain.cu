@@ -22,6 +22,7 @@
 // Every wait loop carries a watchdog (global timer): a protocol error traps instead of hanging the GPU.
 // All arithmetic uses round-to-nearest intrinsics in the reference's association order (no FMA).
 #include "wavefront.cuh"
+#include "gather.cuh"
 
 #include <algorithm>
 
@@ -36,7 +37,7 @@ constexpr int kChainMaxDeps = 4;
 constexpr int kChainMaxSweeps = 3;      // sweep phases per launch
 constexpr int kChainCols = 64;          // columns of a pointwise work item
 
-enum ChainKind { kPhSor = 1, kPhGs = 2, kPhDiv = 3, kPhGrad = 4 };
+enum ChainKind { kPhSor = 1, kPhGs = 2, kPhDiv = 3, kPhGrad = 4, kPhAdvect = 5 };
 
 // "wait until phase `phase` has finished every item whose result columns meet [b0 - lo, b1 + hi]", where [b0, b1]
 // are the waiting item's own columns: the ones it reads (from_out = 0) or the ones it writes (from_out = 1).
@@ -52,9 +53,18 @@ struct ChainPhase {
     int wf;          // sweep phases: index into ChainParams::wf
     int ndeps;
     ChainDep dep[kChainMaxDeps];
-    float *u, *v;    // pointwise phases: velocity components
-    float *q;        // divergence (written) or pressure (read)
-    float c0;        // -0.5f * h (divergence) / h (gradient)
+    // pointwise phases
+    //   divergence: u, v -> q                      gradient: q = pressure, u / v updated in place, then boundaries;
+    //   advection : dst_a (dst_b) = src_a (src_b) traced back through u, v, then boundaries ba (bb) on dst
+    float *u, *v;
+    float *q;
+    float *dst_a, *dst_b;
+    const float *src_a, *src_b;
+    float *bnd_extra;   // gradient: one more field whose boundaries (b = 0, interior read as v + 0.0f) are set here
+    float c0;           // -0.5f * h (divergence) / h (gradient) / -dt0 (advection)
+    int reach_phase;    // advection: the gradient phase that published u, v (its per-block max |v| bounds the trace)
+    int ba, bb;         // advection: setBoundary's b of dst_a / dst_b
+    int pz;             // advection: interior taps of src_a are read as (v + 0.0f) (diffuse with a == 0)
 };
 
 struct ChainParams {
@@ -64,9 +74,11 @@ struct ChainParams {
     unsigned long long *err;        // watchdog report: (phase << 32 | item) + 1 of the first wait that timed out
     unsigned long long timeout_ns;
     unsigned long long *trace;      // [kChainMaxPhases][kChainMaxItems][3] global-timer ns: wait begins, work begins, work ends
+    float *vmax;                    // [kChainMaxPhases][kChainMaxItems] max |v| of a block after its gradient phase
     ChainPhase ph[kChainMaxPhases];
     WfKernelParams wf[kChainMaxSweeps];
 };
+static_assert(sizeof(ChainParams) <= 4000, "kernel parameter space");
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p)
 {
@@ -89,6 +101,25 @@ __device__ __forceinline__ unsigned long long global_timer_ns()
 
 __device__ __forceinline__ int floor_div(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
 
+// Spins until done-word `f` carries this launch's epoch; traps if that takes longer than the watchdog allows.
+__device__ __forceinline__ void chain_poll(const ChainParams &C, const unsigned *f, const int p, const int cl,
+                                           unsigned long long &t0)
+{
+    unsigned spins = 0;
+    while ((int)(ld_acquire_u32(f) - C.epoch) < 0) {
+        __nanosleep(64);
+        if ((++spins & 0x3ffu) == 0) {
+            const unsigned long long now = global_timer_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > C.timeout_ns) {
+                atomicCAS(C.err, 0ull, (((unsigned long long)p << 32) | (unsigned)cl) + 1ull);
+                __threadfence_system();
+                __trap();
+            }
+        }
+    }
+}
+
 // Blocks the CTA until the dependencies of item (phase p, column range cl) are met.  Thread d polls dependency d.
 __device__ __forceinline__ void chain_wait(const ChainParams &C, const int p, const int cl)
 {
@@ -104,23 +135,44 @@ __device__ __forceinline__ void chain_wait(const ChainParams &C, const int p, co
         b = min(b, q.ncl - 1);
         const unsigned *flags = C.done + (size_t)dep.phase * kChainMaxItems;
         unsigned long long t0 = 0;
-        for (int x = a * q.nf; x < (b + 1) * q.nf; ++x) {
-            unsigned spins = 0;
-            while ((int)(ld_acquire_u32(flags + x) - C.epoch) < 0) {
-                __nanosleep(64);
-                if ((++spins & 0x3ffu) == 0) {
-                    const unsigned long long now = global_timer_ns();
-                    if (t0 == 0) t0 = now;
-                    else if (now - t0 > C.timeout_ns) {
-                        atomicCAS(C.err, 0ull, (((unsigned long long)p << 32) | (unsigned)cl) + 1ull);
-                        __threadfence_system();
-                        __trap();
-                    }
-                }
-            }
-        }
+        for (int x = a * q.nf; x < (b + 1) * q.nf; ++x) chain_poll(C, flags + x, p, cl, t0);
     }
     __syncthreads();
+}
+
+// setBoundary(b, x) (src/fluid_sim.cpp:347-367) on the columns [c0, c0 + 64) of x, whose interior cells this CTA has
+// just written (the caller placed a CTA barrier after them).  Walls, then the corners the block contains, each
+// rebuilt from the interior so that no ordering between wall and corner threads is needed.  pz: interior values are
+// read as (v + 0.0f).
+__device__ __forceinline__ void chain_boundary(float *x, const int b, const int pz, const int W, const int H, const int c0)
+{
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const float si = (b == 1) ? -1.0f : 1.0f, sj = (b == 2) ? -1.0f : 1.0f;
+    auto in = [&](int i, int j) {
+        const float v = __ldcg(x + (size_t)i * H + j);
+        return pz ? __fadd_rn(v, 0.0f) : v;
+    };
+    for (int t = tid; t < 2 * kChainCols; t += nt) {
+        const int j = c0 + (t % kChainCols);
+        if (j < 1 || j > H - 2) continue;
+        const int i = (t < kChainCols) ? 0 : W - 1, iin = (t < kChainCols) ? 1 : W - 2;
+        const float v = in(iin, j);
+        x[(size_t)i * H + j] = (b == 1) ? -v : v;                  // :356-360
+    }
+    for (int side = 0; side < 2; ++side) {
+        const int j = side ? H - 1 : 0, jin = side ? H - 2 : 1;
+        if (j < c0 || j >= c0 + kChainCols) continue;
+        for (int i = 1 + tid; i <= W - 2; i += nt) {
+            const float v = in(i, jin);
+            x[(size_t)i * H + j] = (b == 2) ? -v : v;              // :350-354
+        }
+        if (tid < 2) {
+            // corner = 0.5f * (x[iin][j] + x[i][jin]): a j-wall cell and an i-wall cell (:363-366)
+            const int i = tid ? W - 1 : 0, iin = tid ? W - 2 : 1;
+            const float v = in(iin, jin);
+            x[(size_t)i * H + j] = __fmul_rn(0.5f, __fadd_rn(__fmul_rn(sj, v), __fmul_rn(si, v)));
+        }
+    }
 }
 
 // ---- divergence (src/fluid_sim.cpp:307-314) on the columns [c0, c0 + 64) ---------------------------------------------
@@ -198,8 +250,10 @@ __device__ __forceinline__ void chain_divergence(const ChainPhase &ph, const int
 // ---- pressure gradient (src/fluid_sim.cpp:334-341) on the columns [c0, c0 + 64), then setBoundary(1, u) and
 // setBoundary(2, v) (:342-343) for those columns.  Pressure walls are read as setBoundary(0, p) defines them
 // (p[0][j] = p[1][j], p[i][0] = p[i][1], ...), so the pressure array's own wall cells are never touched.
-__device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W, const int H, const int cl)
+__device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W, const int H, const int cl, float *vmax_out)
 {
+    __shared__ float s_vmax[kChainThreads / 32];
+    float vmax = 0.0f;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const int c0 = cl * kChainCols;
     float *u = ph.u, *v = ph.v;
@@ -256,12 +310,16 @@ __device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W
                 if (jb + 1 == H - 1) rb = pcb;
                 // u -= (0.5f*(p[i+1][j] - p[i-1][j])) / h ; v -= (0.5f*(p[i][j+1] - p[i][j-1])) / h
                 if (ina) {
+                    const float nv = __fsub_rn(va[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(ra, la)), h));
                     u[row + ja] = __fsub_rn(ua[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(npa, pma)), h));
-                    v[row + ja] = __fsub_rn(va[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(ra, la)), h));
+                    v[row + ja] = nv;
+                    vmax = fmaxf(vmax, fabsf(nv));
                 }
                 if (inb) {
+                    const float nv = __fsub_rn(vb[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(rb, lb)), h));
                     u[row + jb] = __fsub_rn(ub[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(npb, pmb)), h));
-                    v[row + jb] = __fsub_rn(vb[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(rb, lb)), h));
+                    v[row + jb] = nv;
+                    vmax = fmaxf(vmax, fabsf(nv));
                 }
                 pma = pca; pmb = pcb;
                 pca = npa; pcb = npb;
@@ -269,31 +327,138 @@ __device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W
             }
         }
     }
+    // largest |v| of the block (walls repeat interior magnitudes): bounds how many columns an advection trace that
+    // starts in or passes through this block can move
+    for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    if (lane == 0) s_vmax[w] = vmax;
     __syncthreads();   // every interior cell of the block carries its new velocity
-    // setBoundary(1, u), setBoundary(2, v) on this block's columns (src/fluid_sim.cpp:347-367)
-    const int tid = threadIdx.x, nt = blockDim.x;
-    for (int t = tid; t < 2 * kChainCols; t += nt) {
-        const int j = c0 + (t % kChainCols);
-        if (j < 1 || j > H - 2) continue;
-        const int i = (t < kChainCols) ? 0 : W - 1, iin = (t < kChainCols) ? 1 : W - 2;
-        u[(size_t)i * H + j] = -__ldcg(u + (size_t)iin * H + j);     // b == 1: negated on the i-walls (:357-358)
-        v[(size_t)i * H + j] = __ldcg(v + (size_t)iin * H + j);
+    if (threadIdx.x == 0) {
+        float m = 0.0f;
+        for (int k = 0; k < nw; ++k) m = fmaxf(m, s_vmax[k]);
+        *vmax_out = m;
     }
-    for (int side = 0; side < 2; ++side) {
-        const int j = side ? H - 1 : 0, jin = side ? H - 2 : 1;
-        if (j < c0 || j >= c0 + kChainCols) continue;
-        for (int i = 1 + tid; i <= W - 2; i += nt) {
-            u[(size_t)i * H + j] = __ldcg(u + (size_t)i * H + jin);
-            v[(size_t)i * H + j] = -__ldcg(v + (size_t)i * H + jin);  // b == 2: negated on the j-walls (:351-352)
+    chain_boundary(u, 1, 0, W, H, c0);    // setBoundary(1, u), :342
+    chain_boundary(v, 2, 0, W, H, c0);    // setBoundary(2, v), :343
+    // density "diffusion" with a == 0 leaves d + 0.0f in the interior and runs setBoundary(0, d): the
+    // walls are set here, the + 0.0f is folded into the taps of the density advection
+    if (ph.bnd_extra) chain_boundary(ph.bnd_extra, 0, 1, W, H, c0);
+}
+
+// ---- RK4 advection (src/fluid_sim.cpp:261-298) of the columns [c0, c0 + 64), then setBoundary on the result -------
+// The back-trace may leave the block: before it starts, the CTA waits until the gradient phase has published every
+// block the traces can reach.  A trace moves at most dt0 * max|v| columns per stage (bilinear samples never exceed
+// the largest tap), so with m = max |v| over the blocks [b - k, b + k] the reach is ceil(dt0 * m) + 2 columns; k grows
+// until that fits inside those blocks (one block for the 4-cell displacement of the bench input, the whole grid
+// in the worst case).
+__device__ __forceinline__ void chain_advect_wait(const ChainParams &C, const ChainPhase &ph, const int p, const int b,
+                                                  const float dt0)
+{
+    __shared__ int s_k;
+    const ChainPhase &g = C.ph[ph.reach_phase];
+    const unsigned *flags = C.done + (size_t)ph.reach_phase * kChainMaxItems;
+    const float *vm = C.vmax + (size_t)ph.reach_phase * kChainMaxItems;
+    const int nb = g.ncl;
+    int k = 1, waited_lo = b + 1, waited_hi = b;   // blocks [waited_lo, waited_hi] are known to be done
+    for (;;) {
+        const int lo = max(b - k, 0), hi = min(b + k, nb - 1);
+        unsigned long long t0 = 0;
+        for (int x = lo + (int)threadIdx.x; x <= hi; x += blockDim.x)
+            if (x < waited_lo || x > waited_hi) chain_poll(C, flags + x, p, b, t0);
+        __syncthreads();
+        waited_lo = lo;
+        waited_hi = hi;
+        if (threadIdx.x == 0) {
+            float m = 0.0f;
+            for (int x = lo; x <= hi; ++x) m = fmaxf(m, __ldcg(vm + x));
+            const float r = dt0 * m;
+            int need = nb;                                      // non-finite velocities: wait for everything
+            if (r < 1.0e8f) need = ((int)ceilf(r) + 2 + kChainCols - 1) / kChainCols;
+            s_k = max(need, 1);
         }
-        if (tid < 2) {
-            // corners: 0.5f * (x[iin][j] + x[i][jin]), both wall cells, rebuilt from the interior (:363-366)
-            const int i = tid ? W - 1 : 0, iin = tid ? W - 2 : 1;
-            const float ui = __ldcg(u + (size_t)iin * H + jin), vi = __ldcg(v + (size_t)iin * H + jin);
-            u[(size_t)i * H + j] = __fmul_rn(0.5f, __fadd_rn(ui, -ui));
-            v[(size_t)i * H + j] = __fmul_rn(0.5f, __fadd_rn(-vi, vi));
+        __syncthreads();
+        const int need = s_k;
+        __syncthreads();
+        if (need <= k || (lo == 0 && hi == nb - 1)) break;
+        k = need;
+    }
+}
+
+template <bool TWO, bool PZ>
+__device__ __forceinline__ void chain_advect(const ChainPhase &ph, const int W, const int H, const int cl)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int c0 = cl * kChainCols;
+    const GridView G{W, H, H, 0, 0, H};
+    const float *u = ph.u, *v = ph.v;
+    const float *src_a = ph.src_a, *src_b = ph.src_b;
+    float *dst_a = ph.dst_a, *dst_b = ph.dst_b;
+    const float ndt0 = ph.c0;
+    const float xm = (float)W - 1.5f, ym = (float)H - 1.5f;
+    constexpr int N = 4;     // independent traces per thread: two columns x two rows
+    for (int i0 = 1 + 2 * w; i0 <= W - 2; i0 += 2 * nw) {
+        int ci[N], cj[N];
+        bool ok[N];
+        float x[N], y[N], k1x[N], k1y[N], k2x[N], k2y[N], k3x[N], k3y[N], k4x[N], k4y[N];
+        Taps t[N];
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+            ci[n] = i0 + (n >> 1);
+            cj[n] = c0 + 32 * (n & 1) + lane;
+            ok[n] = ci[n] <= W - 2 && cj[n] >= 1 && cj[n] <= H - 2;
+            // cells outside the interior trace from a harmless in-grid position and store nothing
+            x[n] = ok[n] ? (float)ci[n] : 1.0f;
+            y[n] = ok[n] ? (float)cj[n] : 1.0f;
+            t[n] = make_taps(x[n], y[n], xm, ym);
+        }
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+            k1x[n] = __fmul_rn(sample<false, int, false>(u, t[n], G), ndt0);
+            k1y[n] = __fmul_rn(sample<false, int, false>(v, t[n], G), ndt0);
+        }
+#pragma unroll
+        for (int n = 0; n < N; ++n)
+            t[n] = make_taps(__fadd_rn(x[n], __fmul_rn(k1x[n], 0.5f)), __fadd_rn(y[n], __fmul_rn(k1y[n], 0.5f)), xm, ym);
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+            k2x[n] = __fmul_rn(sample<false, int, false>(u, t[n], G), ndt0);
+            k2y[n] = __fmul_rn(sample<false, int, false>(v, t[n], G), ndt0);
+        }
+#pragma unroll
+        for (int n = 0; n < N; ++n)
+            t[n] = make_taps(__fadd_rn(x[n], __fmul_rn(k2x[n], 0.5f)), __fadd_rn(y[n], __fmul_rn(k2y[n], 0.5f)), xm, ym);
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+            k3x[n] = __fmul_rn(sample<false, int, false>(u, t[n], G), ndt0);
+            k3y[n] = __fmul_rn(sample<false, int, false>(v, t[n], G), ndt0);
+        }
+#pragma unroll
+        for (int n = 0; n < N; ++n) t[n] = make_taps(__fadd_rn(x[n], k3x[n]), __fadd_rn(y[n], k3y[n]), xm, ym);
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+            k4x[n] = __fmul_rn(sample<false, int, false>(u, t[n], G), ndt0);
+            k4y[n] = __fmul_rn(sample<false, int, false>(v, t[n], G), ndt0);
+        }
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+            // ((k1 + 2*k2) + 2*k3 + k4) / 6, componentwise (:290)
+            const float dx = __fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(k1x[n], __fmul_rn(2.0f, k2x[n])), __fmul_rn(2.0f, k3x[n])), k4x[n]), 6.0f);
+            const float dy = __fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(k1y[n], __fmul_rn(2.0f, k2y[n])), __fmul_rn(2.0f, k3y[n])), k4y[n]), 6.0f);
+            t[n] = make_taps(__fadd_rn(x[n], dx), __fadd_rn(y[n], dy), xm, ym);
+        }
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+            const float ra = sample<PZ, int, false>(src_a, t[n], G);
+            const float rb = TWO ? sample<PZ, int, false>(src_b, t[n], G) : 0.0f;
+            if (ok[n]) {
+                const size_t c = (size_t)ci[n] * H + cj[n];
+                dst_a[c] = ra;
+                if (TWO) dst_b[c] = rb;
+            }
         }
     }
+    __syncthreads();
+    chain_boundary(dst_a, ph.ba, 0, W, H, c0);
+    if (TWO) chain_boundary(dst_b, ph.bb, 0, W, H, c0);
 }
 
 template <int SD, int SP>
@@ -308,6 +473,7 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
             unsigned long long *tr = C.trace + ((size_t)p * kChainMaxItems + item) * 3;
             if (threadIdx.x == 0) tr[0] = global_timer_ns();
             chain_wait(C, p, cl);
+            if (ph.kind == kPhAdvect) chain_advect_wait(C, ph, p, cl, -ph.c0);
             if (threadIdx.x == 0) tr[1] = global_timer_ns();
             if (ph.kind == kPhSor) {
                 if constexpr (SD > 0) wf_pass<SD, kSor, true>(C.wf[ph.wf], cl, fi, smem);
@@ -316,7 +482,11 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
             } else if (ph.kind == kPhDiv) {
                 chain_divergence(ph, C.W, C.H, cl);
             } else if (ph.kind == kPhGrad) {
-                chain_gradient(ph, C.W, C.H, cl);
+                chain_gradient(ph, C.W, C.H, cl, C.vmax + (size_t)p * kChainMaxItems + item);
+            } else if (ph.kind == kPhAdvect) {
+                if (ph.dst_b) chain_advect<true, false>(ph, C.W, C.H, cl);
+                else if (ph.pz) chain_advect<false, true>(ph, C.W, C.H, cl);
+                else chain_advect<false, false>(ph, C.W, C.H, cl);
             }
             __syncthreads();   // the item's results are written, its shared memory is free
             if (threadIdx.x == 0) {
@@ -361,16 +531,18 @@ struct ChainPlan {
 }  // namespace
 
 struct ChainState {
-    ChainPlan plan_full, plan_proj;       // diffuse + project / project only
-    unsigned char *buf = nullptr;         // [done | err | trace | flags sor | flags gs | rings sor | rings gs]
-    int last_nphases[2] = {0, 0};         // of the most recent launch of each kind (for chain_read_trace)
+    ChainPlan plan[2];                    // [0] with the diffusion phase, [1] without
+    unsigned char *buf = nullptr;         // [done | err | vmax | trace x 2 | flags x 3 | rings sor | rings gs x 2]
     size_t bytes = 0;
+    float *extra[2] = {nullptr, nullptr}; // pressure / divergence of the second projection of a whole-step launch
+    size_t extra_floats = 0;
     unsigned epoch = 0;
+    int last_nphases[2] = {0, 0};         // of the most recent launch of each kind (for chain_read_trace)
 };
 
 namespace {
 
-// Can (D diffusion sweeps of u and v +) P pressure sweeps run as one chained launch on this grid?
+// Can (D diffusion sweeps of u and v +) P pressure sweeps run as phases of one launch on this grid?
 ChainPlan make_plan(int W, int H, int D, int P)
 {
     ChainPlan pl;
@@ -425,37 +597,63 @@ void fill_wf(WfKernelParams &P, int W, int H, int nstr, int nstg, int ncta, floa
     P.link_seq_base = 0;
 }
 
+constexpr size_t kDoneBytes = (size_t)kChainMaxPhases * kChainMaxItems * sizeof(unsigned);
+constexpr size_t kVmaxBytes = (size_t)kChainMaxPhases * kChainMaxItems * sizeof(float);
+constexpr size_t kTraceOne = (size_t)kChainMaxPhases * kChainMaxItems * 3 * sizeof(unsigned long long);
+
 }  // namespace
 
 void chain_state_destroy(ChainState *cs)
 {
     if (!cs) return;
     if (cs->buf) cudaFree(cs->buf);
+    for (int k = 0; k < 2; ++k)
+        if (cs->extra[k]) cudaFree(cs->extra[k]);
     delete cs;
 }
 
-// diffuse(u), diffuse(v) (when A.sor_sweeps > 0) and project(u, v, p, div) of velocityStep as one launch.
-// Returns cudaErrorNotSupported when this grid / sweep counts have no chained configuration (the caller then
+// Passes of FluidSim::step as phases of one launch (see the head of this file):
+//   diffuse(u), diffuse(v)                               when A.sor_sweeps > 0          (src/fluid_sim.cpp:390-391)
+//   project(u, v, p, div)                                always                         (:394)
+//   advect(u), advect(v) into (p, div), project again    when A.with_advect             (:401-405)
+//   densityStep with DIFFUSION == 0                      when A.with_density            (:409-422)
+// Returns cudaErrorNotSupported when this grid / these sweep counts have no chained configuration (the caller then
 // runs the passes as separate launches).
-cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st,
-                                 bool query_only)
+cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st, bool query_only)
 {
     if (!cs) cs = new ChainState();
-    ChainPlan &pl = A.sor_sweeps > 0 ? cs->plan_full : cs->plan_proj;
+    const int kind = A.sor_sweeps > 0 ? 0 : 1;
+    ChainPlan &pl = cs->plan[kind];
     if (pl.W != A.W || pl.H != A.H || pl.D != A.sor_sweeps || pl.P != A.gs_sweeps) pl = make_plan(A.W, A.H, A.sor_sweeps, A.gs_sweeps);
     if (!pl.ok) return cudaErrorNotSupported;
+    if (A.with_density && !A.with_advect) return cudaErrorInvalidValue;
     if (query_only) return cudaSuccess;
 
-    // scratch: done words, watchdog word, progress words and boundary rings of the two sweep phases
-    const size_t done_bytes = (size_t)kChainMaxPhases * kChainMaxItems * sizeof(unsigned);
+    cudaError_t e;
+    if (A.with_advect) {
+        const size_t nfl = (size_t)A.W * A.H;
+        if (nfl > cs->extra_floats) {
+            e = cudaStreamSynchronize(st);
+            if (e != cudaSuccess) return e;
+            for (int k = 0; k < 2; ++k) {
+                if (cs->extra[k]) cudaFree(cs->extra[k]);
+                cs->extra[k] = nullptr;
+            }
+            cs->extra_floats = 0;
+            for (int k = 0; k < 2; ++k) {
+                e = cudaMalloc(&cs->extra[k], nfl * sizeof(float));
+                if (e != cudaSuccess) return e;
+            }
+            cs->extra_floats = nfl;
+        }
+    }
+    // scratch: done words, watchdog word, per-block maxima, timelines, progress words and boundary rings of the sweep phases
     const size_t flag_bytes = sweep_flag_words() * sizeof(unsigned long long);
-    const size_t sor_rings = std::max(cs->plan_full.sor_ring_floats, pl.sor_ring_floats) * sizeof(float);
-    const size_t gs_rings = std::max(std::max(cs->plan_full.gs_ring_floats, cs->plan_proj.gs_ring_floats), pl.gs_ring_floats) * sizeof(float);
-    const size_t trace_one = (size_t)kChainMaxPhases * kChainMaxItems * 3 * sizeof(unsigned long long);
-    const size_t trace_bytes = 2 * trace_one;      // one timeline per kind of launch (with / without the diffusion phase)
-    const size_t need = done_bytes + 256 + trace_bytes + 2 * flag_bytes + sor_rings + gs_rings;
+    const size_t sor_rings = std::max(cs->plan[0].sor_ring_floats, pl.sor_ring_floats) * sizeof(float);
+    const size_t gs_rings = std::max(std::max(cs->plan[0].gs_ring_floats, cs->plan[1].gs_ring_floats), pl.gs_ring_floats) * sizeof(float);
+    const size_t need = kDoneBytes + 256 + kVmaxBytes + 2 * kTraceOne + 3 * flag_bytes + sor_rings + 2 * gs_rings;
     if (need > cs->bytes) {
-        cudaError_t e = cudaStreamSynchronize(st);
+        e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) return e;
         if (cs->buf) cudaFree(cs->buf);
         cs->buf = nullptr;
@@ -468,13 +666,15 @@ cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, Swe
     }
     unsigned char *b = cs->buf;
     unsigned *done = reinterpret_cast<unsigned *>(b);
-    unsigned long long *err = reinterpret_cast<unsigned long long *>(b + done_bytes);
-    unsigned long long *trace = reinterpret_cast<unsigned long long *>(b + done_bytes + 256 + (A.sor_sweeps > 0 ? 0 : trace_one));
-    unsigned char *b2 = b + done_bytes + 256 + trace_bytes;
-    unsigned long long *flags_sor = reinterpret_cast<unsigned long long *>(b2);
-    unsigned long long *flags_gs = reinterpret_cast<unsigned long long *>(b2 + flag_bytes);
-    float *rings_sor = reinterpret_cast<float *>(b2 + 2 * flag_bytes);
-    float *rings_gs = reinterpret_cast<float *>(b2 + 2 * flag_bytes + sor_rings);
+    unsigned long long *err = reinterpret_cast<unsigned long long *>(b + kDoneBytes);
+    float *vmax = reinterpret_cast<float *>(b + kDoneBytes + 256);
+    unsigned long long *trace = reinterpret_cast<unsigned long long *>(b + kDoneBytes + 256 + kVmaxBytes + kind * kTraceOne);
+    unsigned char *b2 = b + kDoneBytes + 256 + kVmaxBytes + 2 * kTraceOne;
+    unsigned long long *flags[3];
+    for (int k = 0; k < 3; ++k) flags[k] = reinterpret_cast<unsigned long long *>(b2 + k * flag_bytes);
+    float *rings_sor = reinterpret_cast<float *>(b2 + 3 * flag_bytes);
+    float *rings_gs[2] = {reinterpret_cast<float *>(b2 + 3 * flag_bytes + sor_rings),
+                          reinterpret_cast<float *>(b2 + 3 * flag_bytes + sor_rings + gs_rings)};
 
     ChainParams C{};
     C.W = A.W;
@@ -484,8 +684,61 @@ cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, Swe
     C.err = err;
     C.timeout_ns = 20ull * 1000 * 1000 * 1000;
     C.trace = trace;
+    C.vmax = vmax;
     const int nblk = (A.H + kChainCols - 1) / kChainCols;
+    const float h = 1.0f / (float)A.W;            // src/fluid_sim.cpp:304
     int np = 0, nwf = 0;
+
+    auto pointwise_phase = [&](int kind_) -> ChainPhase & {
+        ChainPhase &ph = C.ph[np++];
+        ph.kind = kind_;
+        ph.ncl = ph.nitems = nblk;
+        ph.nf = 1;
+        ph.cpv = kChainCols;
+        ph.shift = 0;
+        ph.ndeps = 0;
+        return ph;
+    };
+    // divergence -> pressure sweeps -> gradient (+ boundaries) of (u, v) with scratch (p, div); `after` = phase that
+    // produced u, v (or -1); returns the index of the gradient phase
+    auto projection = [&](float *u, float *v, float *p, float *div, int after, int gs_slot, float *bnd_extra) -> int {
+        const int ph_div = np;
+        {
+            ChainPhase &ph = pointwise_phase(kPhDiv);
+            ph.u = u;
+            ph.v = v;
+            ph.q = div;
+            ph.c0 = -0.5f * h;                    // evaluated first (:311)
+            if (after >= 0) ph.dep[ph.ndeps++] = ChainDep{after, 0, 1, 1};    // u, v of the block and one column either side
+        }
+        const int ph_gs = np;
+        {
+            ChainPhase &ph = C.ph[np++];
+            ph.kind = kPhGs;
+            ph.ncl = ph.nitems = pl.gs_ncta;
+            ph.nf = 1;
+            ph.cpv = 32 * pl.gs_nstr;
+            ph.shift = A.gs_sweeps;
+            ph.wf = nwf;
+            ph.ndeps = 0;
+            ph.dep[ph.ndeps++] = ChainDep{ph_div, 0, 0, 0};                   // the divergence of the columns it loads
+            WfKernelParams &P = C.wf[nwf++];
+            fill_wf(P, A.W, A.H, pl.gs_nstr, A.gs_sweeps / kChainSP, pl.gs_ncta, 0.0f, 1.0f, 1.0f, rings_gs[gs_slot],
+                    flags[1 + gs_slot], ++scr.seq);
+            P.fld[0] = SweepField{nullptr, div, p, 1.0f, 1.0f};               // p starts at 0 (:313, :316)
+            P.fld[1] = P.fld[2] = P.fld[0];
+        }
+        ChainPhase &ph = pointwise_phase(kPhGrad);
+        ph.u = u;
+        ph.v = v;
+        ph.q = p;
+        ph.c0 = h;
+        ph.bnd_extra = bnd_extra;
+        ph.dep[ph.ndeps++] = ChainDep{ph_gs, 0, 1, 1};    // pressure of the block and one column either side
+        ph.dep[ph.ndeps++] = ChainDep{ph_div, 1, 1, 1};   // the divergence blocks that read the u, v about to change
+        return np - 1;
+    };
+
     int ph_sor = -1;
     if (A.sor_sweeps > 0) {
         ChainPhase &ph = C.ph[np];
@@ -498,78 +751,66 @@ cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, Swe
         ph.wf = nwf;
         ph.ndeps = 0;
         WfKernelParams &P = C.wf[nwf++];
-        fill_wf(P, A.W, A.H, pl.sor_nstr, A.sor_sweeps / kChainSD, pl.sor_ncta, A.a, A.c_recip, A.omega, rings_sor, flags_sor, ++scr.seq);
+        fill_wf(P, A.W, A.H, pl.sor_nstr, A.sor_sweeps / kChainSD, pl.sor_ncta, A.a, A.c_recip, A.omega, rings_sor, flags[0], ++scr.seq);
         P.fld[0] = SweepField{A.u, A.u, A.u, -1.0f, 1.0f};    // setBoundary(1, u): negated on the i-walls
         P.fld[1] = SweepField{A.v, A.v, A.v, 1.0f, -1.0f};    // setBoundary(2, v): negated on the j-walls
         P.fld[2] = P.fld[0];
         ph_sor = np++;
     }
-    const int ph_div = np;
-    {
-        ChainPhase &ph = C.ph[np++];
-        ph.kind = kPhDiv;
-        ph.ncl = ph.nitems = nblk;
-        ph.nf = 1;
-        ph.cpv = kChainCols;
-        ph.shift = 0;
-        ph.u = A.u;
-        ph.v = A.v;
-        ph.q = A.div;
-        const float h = 1.0f / (float)A.W;        // src/fluid_sim.cpp:304
-        ph.c0 = -0.5f * h;                        // evaluated first (:311)
-        ph.ndeps = 0;
-        if (ph_sor >= 0) ph.dep[ph.ndeps++] = ChainDep{ph_sor, 0, 1, 1};   // u, v of the block and one column either side
-    }
-    const int ph_gs = np;
-    {
-        ChainPhase &ph = C.ph[np++];
-        ph.kind = kPhGs;
-        ph.ncl = ph.nitems = pl.gs_ncta;
-        ph.nf = 1;
-        ph.cpv = 32 * pl.gs_nstr;
-        ph.shift = A.gs_sweeps;
-        ph.wf = nwf;
-        ph.ndeps = 0;
-        ph.dep[ph.ndeps++] = ChainDep{ph_div, 0, 0, 0};                    // the divergence of the columns it loads
-        WfKernelParams &P = C.wf[nwf++];
-        fill_wf(P, A.W, A.H, pl.gs_nstr, A.gs_sweeps / kChainSP, pl.gs_ncta, 0.0f, 1.0f, 1.0f, rings_gs, flags_gs, ++scr.seq);
-        P.fld[0] = SweepField{nullptr, A.div, A.p, 1.0f, 1.0f};           // p starts at 0 (:313, :316)
-        P.fld[1] = P.fld[2] = P.fld[0];
-    }
-    {
-        ChainPhase &ph = C.ph[np++];
-        ph.kind = kPhGrad;
-        ph.ncl = ph.nitems = nblk;
-        ph.nf = 1;
-        ph.cpv = kChainCols;
-        ph.shift = 0;
-        ph.u = A.u;
-        ph.v = A.v;
-        ph.q = A.p;
-        ph.c0 = 1.0f / (float)A.W;
-        ph.ndeps = 0;
-        ph.dep[ph.ndeps++] = ChainDep{ph_gs, 0, 1, 1};    // pressure of the block and one column either side
-        ph.dep[ph.ndeps++] = ChainDep{ph_div, 1, 1, 1};   // the divergence blocks that read the u, v about to change
+    const int ph_grad1 = projection(A.u, A.v, A.p, A.div, ph_sor, 0, nullptr);
+    if (A.with_advect) {
+        // advect(1, u), advect(2, v) (:401-402) into the buffers the first projection used as pressure / divergence
+        const int ph_gs1 = ph_grad1 - 1;
+        const int ph_adv = np;
+        {
+            ChainPhase &ph = pointwise_phase(kPhAdvect);
+            ph.u = A.u;
+            ph.v = A.v;
+            ph.src_a = A.u;
+            ph.src_b = A.v;
+            ph.dst_a = A.p;
+            ph.dst_b = A.div;
+            ph.ba = 1;
+            ph.bb = 2;
+            ph.pz = 0;
+            ph.c0 = -(A.dt * (float)A.W);              // -dt0, dt0 = dt * width (:264)
+            ph.reach_phase = ph_grad1;
+            ph.dep[ph.ndeps++] = ChainDep{ph_grad1, 1, 1, 1};                                // gradient blocks still reading p here
+            ph.dep[ph.ndeps++] = ChainDep{ph_gs1, 1, A.gs_sweeps, -A.gs_sweeps};           // sweep items that load div here
+        }
+        // the second projection works in scratch of its own: u, v stay intact for traces that start far away
+        const float *dens = A.with_density ? A.d : nullptr;
+        const int ph_grad2 = projection(A.p, A.div, cs->extra[0], cs->extra[1], ph_adv, 1,
+                                        (A.with_density && A.density_pz) ? A.d : nullptr);
+        if (dens) {
+            ChainPhase &ph = pointwise_phase(kPhAdvect);
+            ph.u = A.p;
+            ph.v = A.div;
+            ph.src_a = A.d;
+            ph.dst_a = A.nd;
+            ph.ba = 0;
+            ph.pz = A.density_pz;
+            ph.c0 = -(A.dt * (float)A.W);
+            ph.reach_phase = ph_grad2;
+        }
     }
     C.nphases = np;
-    cs->last_nphases[A.sor_sweeps > 0 ? 0 : 1] = np;
+    cs->last_nphases[kind] = np;
 
     void *args[] = {&C};
     const void *kern = A.sor_sweeps > 0 ? (const void *)chain_kernel<kChainSD, kChainSP> : (const void *)chain_kernel<0, kChainSP>;
     return cudaLaunchCooperativeKernel(kern, dim3(pl.grid), dim3(kChainThreads), args, pl.smem, st);
 }
 
-// Start / end times of every work item of the most recent chained launch of one kind (which = 0: diffuse + project,
-// 1: project alone): out[(phase * items + item) * 3 + k] in
-// nanoseconds of the GPU's global timer (k = 0 wait begins, 1 work begins, 2 results published); 0 = item did not run.
-// The caller synchronises the stream first.
+// Start / end times of every work item of the most recent chained launch of one kind (which = 0: launches that begin
+// with the diffusion phase, 1: the others): out[(phase * max_items + item) * 3 + k] in nanoseconds of the GPU's global
+// timer (k = 0 wait begins, 1 work begins, 2 results published); 0 = item did not run.  The caller synchronises first.
 cudaError_t chain_read_trace(ChainState *cs, int which, unsigned long long *out, int max_phases, int max_items, int *nphases)
 {
     *nphases = 0;
     if (!cs || !cs->buf || which < 0 || which > 1) return cudaSuccess;
-    const size_t done_bytes = (size_t)kChainMaxPhases * kChainMaxItems * sizeof(unsigned);
-    const size_t trace_one = (size_t)kChainMaxPhases * kChainMaxItems * 3 * sizeof(unsigned long long);
-    const unsigned long long *trace = reinterpret_cast<const unsigned long long *>(cs->buf + done_bytes + 256 + which * trace_one);
+    const unsigned long long *trace =
+        reinterpret_cast<const unsigned long long *>(cs->buf + kDoneBytes + 256 + kVmaxBytes + which * kTraceOne);
     const int np = std::min(cs->last_nphases[which], max_phases), ni = std::min(max_items, kChainMaxItems);
     for (int p = 0; p < np; ++p) {
         cudaError_t e = cudaMemcpy(out + (size_t)p * max_items * 3, trace + (size_t)p * kChainMaxItems * 3,

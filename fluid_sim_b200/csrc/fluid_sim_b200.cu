@@ -72,7 +72,7 @@ struct fsb_sim {
     float *temp[2] = {nullptr, nullptr};   // MacCormack scratch (src/fluid_sim.cpp:52-53 tempField1/2), lazy
     SweepScratch sweep;
     ChainState *chain = nullptr;           // passes chained inside one launch (chain.cu), lazily created
-    bool chain_enabled = true;
+    int chain_level = 2;                   // 0: every pass its own launch, 1: diffuse + project chained, 2: the whole step
     NoiseTables noise_tables;
     uint32_t noise_win[kRandDeg];          // window of the emulated rand() stream at noise_pos
     uint64_t noise_pos = 0;
@@ -94,7 +94,7 @@ struct fsb_sim {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_ready = nullptr, ev_copied = nullptr;
     bool copy_pending = false;
-    const float *copy_src = nullptr;
+    float *snapshot = nullptr;                  // device-side copy of the field an asynchronous read is transferring
     unsigned char *view_buf = nullptr;          // RGBA8 image of the last fsb_view_density* call
     size_t view_bytes = 0;
     unsigned char *link_buf = nullptr;          // [rings | in_prod | cons], shared with both neighbours through CUDA IPC
@@ -243,12 +243,8 @@ int set_boundary1(fsb_sim *s, float *x, int b, int plus_zero = 0)
     return set_boundary(s, &j, 1);
 }
 
-// Later work on the simulation's stream must not overwrite a buffer an asynchronous read is still copying.
-int order_after_copy(fsb_sim *s)
-{
-    if (s->copy_pending) FSB_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied, 0));
-    return FSB_OK;
-}
+// An asynchronous read transfers a device-side snapshot (fsb_read_field_async), so later work may overwrite the field.
+int order_after_copy(fsb_sim *) { return FSB_OK; }
 
 enum SourceSel { kAllSources = 0, kVelocitySources = 1, kDensitySources = 2 };
 
@@ -467,14 +463,18 @@ int add_noise(fsb_sim *s)
     return FSB_OK;
 }
 
-// diffuse(u), diffuse(v) (with_diffuse) and project() as ONE launch whose CTAs move from pass to pass as soon as the
-// columns they need are done (chain.cu).  *done = false: no chained configuration for this grid / these sweep counts /
-// this tuning; the caller runs the passes one launch at a time.
-int chained_project(fsb_sim *s, bool with_diffuse, float dt, bool *done)
+// Passes of the step as phases of ONE launch whose CTAs move from pass to pass as soon as the columns they need are
+// done (chain.cu).  with_diffuse: diffuse(u), diffuse(v) + project; otherwise project alone; whole_step: everything
+// after the noise (diffuse, project, advect, project, and the density step when its diffusion coefficient is 0).
+// *done = false: no chained configuration for this grid / these sweep counts / this tuning; the caller runs the passes
+// one launch at a time.  *density_done tells whether the density step was part of the launch.
+int chained_launch(fsb_sim *s, bool with_diffuse, bool whole_step, float dt, bool *done, bool *density_done)
 {
     *done = false;
-    if (!s->chain_enabled || s->is_block || s->tune_strips || s->tune_levels || s->tune_stages) return FSB_OK;
-    ChainProjectArgs A{};
+    if (density_done) *density_done = false;
+    if (s->chain_level < 1 || s->is_block || s->tune_strips || s->tune_levels || s->tune_stages) return FSB_OK;
+    if (whole_step && (s->chain_level < 2 || s->prm.advect_scheme != FSB_ADVECT_RK4)) return FSB_OK;
+    ChainArgs A{};
     A.W = s->W;
     A.H = s->H;
     A.u = s->f[FSB_VELOCITY_X];
@@ -486,27 +486,53 @@ int chained_project(fsb_sim *s, bool with_diffuse, float dt, bool *done)
     A.a = 0.0f;
     A.c_recip = 1.0f;
     A.omega = s->prm.omega;
+    A.dt = dt;
     if (with_diffuse) {
         A.a = dt * s->prm.viscosity * (float)s->W * (float)s->H;   // ((dt*diff)*W)*H, src/fluid_sim.cpp:45
         A.c_recip = 1.0f / (1.0f + 4.0f * A.a);                    // :46
         A.sor_sweeps = s->prm.diff_iters;
         if (A.sor_sweeps <= 0 || A.a == 0.0f) return FSB_OK;
     }
-    cudaError_t e = launch_chain_project(A, s->chain, s->sweep, s->stream, true);
+    if (whole_step) {
+        A.with_advect = 1;
+        const float ad = dt * s->prm.diffusion * (float)s->W * (float)s->H;
+        if (ad == 0.0f) {
+            // density diffusion with a == 0 (DIFFUSION, include/fluid_sim.h:14): identity d + 0.0f plus the boundary
+            // update when the loop runs at all; the advection is then a phase of the same launch
+            A.with_density = 1;
+            A.density_pz = s->prm.diff_iters > 0 ? 1 : 0;
+            A.d = s->f[FSB_DENSITY];
+            A.nd = s->f[FSB_PREV_DENSITY];
+        }
+    }
+    cudaError_t e = launch_chain(A, s->chain, s->sweep, s->stream, true);
     if (e == cudaErrorNotSupported) return FSB_OK;
     if (e == cudaSuccess) {
         ProfScope ps(s, FSB_PROF_CHAIN);
-        e = launch_chain_project(A, s->chain, s->sweep, s->stream, false);
+        e = launch_chain(A, s->chain, s->sweep, s->stream, false);
     }
-    if (e != cudaSuccess) return fail_cuda(e, "chained diffuse/project launch");
+    if (e != cudaSuccess) return fail_cuda(e, "chained launch");
     s->launches += 1;
     *done = true;
+    if (whole_step) {
+        // the advected velocity sits in the former prev buffers (src/fluid_sim.cpp:397-402 copies, here a swap of roles)
+        std::swap(s->f[FSB_VELOCITY_X], s->f[FSB_PREV_VEL_X]);
+        std::swap(s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_Y]);
+        if (A.with_density) {
+            std::swap(s->f[FSB_DENSITY], s->f[FSB_PREV_DENSITY]);
+            if (density_done) *density_done = true;
+        }
+    }
     return FSB_OK;
 }
 
-int velocity_step(fsb_sim *s, float dt)
+int chained_project(fsb_sim *s, bool with_diffuse, float dt, bool *done)
 {
-    FSB_TRY(add_noise(s));
+    return chained_launch(s, with_diffuse, false, dt, done, nullptr);
+}
+
+int velocity_step_after_noise(fsb_sim *s, float dt)
+{
     bool chained = false;
     FSB_TRY(chained_project(s, true, dt, &chained));
     if (!chained) {
@@ -535,6 +561,12 @@ int velocity_step(fsb_sim *s, float dt)
     FSB_TRY(chained_project(s, false, dt, &chained));
     if (chained) return FSB_OK;
     return project(s, s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_X], s->f[FSB_PREV_VEL_Y]);
+}
+
+int velocity_step(fsb_sim *s, float dt)
+{
+    FSB_TRY(add_noise(s));
+    return velocity_step_after_noise(s, dt);
 }
 
 int density_step(fsb_sim *s, float dt)
@@ -676,8 +708,10 @@ static int create_common(const fsb_params *p, const GridView *block, fsb_sim **o
         FSB_CREATE_CUDA(cudaMemsetAsync(s->link_buf, 0, kLinkBytes, s->stream));
     }
     {
-        const char *e = std::getenv("FSB_CHAIN");      // FSB_CHAIN=0: every pass as its own launch (A/B timing, debugging)
-        s->chain_enabled = !(e && e[0] == '0');
+        // FSB_CHAIN = 0: every pass as its own launch, 1: diffuse + project / project as chained launches, 2 (default):
+        // the whole step after the noise as one chained launch (A/B timing, debugging)
+        const char *e = std::getenv("FSB_CHAIN");
+        if (e && e[0] >= '0' && e[0] <= '2') s->chain_level = e[0] - '0';
     }
     s->noise_step_jump = jump_matrix(2ull * (uint64_t)prm.width * (uint64_t)prm.height);
     set_noise_window(s, prm.noise_seed, prm.noise_pos);
@@ -712,6 +746,7 @@ int fsb_destroy(fsb_sim *s)
         if (s->peer_right) cudaIpcCloseMemHandle(s->peer_right);
         if (s->link_buf) cudaFree(s->link_buf);
         if (s->view_buf) cudaFree(s->view_buf);
+        if (s->snapshot) cudaFree(s->snapshot);
         for (auto &r : s->prof_open) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         for (auto &e : s->prof_free) cudaEventDestroy(e);
         if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
@@ -741,15 +776,23 @@ int fsb_step(fsb_sim *s, float dt)
 {
     if (!s) return fail(FSB_EINVAL, "fsb_step: null handle");
     DeviceGuard guard(s->device);
-    // An asynchronous read of the density (fsb_read_field_async) may still be copying: the velocity step does not
-    // touch the density, so only the density half of the step waits for it; density sources are applied there too.
-    const bool copy_density = s->copy_pending && s->copy_src == s->f[FSB_DENSITY];
-    if (!copy_density) FSB_TRY(order_after_copy(s));
-    FSB_TRY(flush_sources(s, kVelocitySources));
+    FSB_TRY(flush_sources(s));       // density sources too: the velocity step never reads the density
     invalidate_mirror(s);
+    {
+        // everything after the noise as one launch, when this grid / these parameters have a chained configuration
+        bool query = false, dens = false;
+        if (s->chain_level >= 2 && !s->is_block) {
+            FSB_TRY(add_noise(s));
+            FSB_TRY(chained_launch(s, true, true, dt, &query, &dens));
+            if (query) {
+                if (!dens) FSB_TRY(density_step(s, dt));
+                return FSB_OK;
+            }
+            FSB_TRY(velocity_step_after_noise(s, dt));
+            return density_step(s, dt);
+        }
+    }
     FSB_TRY(velocity_step(s, dt));   // src/fluid_sim.cpp:26
-    FSB_TRY(order_after_copy(s));
-    FSB_TRY(flush_sources(s, kDensitySources));
     FSB_TRY(density_step(s, dt));    // src/fluid_sim.cpp:27
     return FSB_OK;
 }
@@ -893,25 +936,28 @@ int fsb_write_field(fsb_sim *s, int field, const float *host_src)
     return FSB_OK;
 }
 
-/* Queues a device-to-host copy of a field as it is after all work queued so far, on a second stream: it overlaps
- * with later fsb_step calls (the library orders later writers of that buffer after the copy).  One read at a time. */
+/* Queues a device-to-host copy of a field as it is after all work queued so far: a device-side snapshot on the
+ * simulation's stream (so later steps and sources may overwrite the field at once), then the transfer to the host on a
+ * second stream, overlapping with later fsb_step calls.  One read at a time. */
 int fsb_read_field_async(fsb_sim *s, int field, float *host_dst)
 {
     if (!s || !host_dst || !valid_field(field)) return fail(FSB_EINVAL, "fsb_read_field_async: bad argument");
     if (s->is_block) return fail(FSB_EINVAL, "fsb_read_field_async: not available on a column block");
     DeviceGuard guard(s->device);
-    FSB_TRY(flush_sources(s));               // also orders this read after a previous one
+    FSB_TRY(flush_sources(s));
     if (!s->copy_stream) {
         FSB_CUDA(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
         FSB_CUDA(cudaEventCreateWithFlags(&s->ev_ready, cudaEventDisableTiming));
         FSB_CUDA(cudaEventCreateWithFlags(&s->ev_copied, cudaEventDisableTiming));
     }
+    if (!s->snapshot) FSB_CUDA(cudaMalloc(&s->snapshot, s->ncells * sizeof(float)));
+    if (s->copy_pending) FSB_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied, 0));   // the snapshot buffer is free again
+    FSB_CUDA(cudaMemcpyAsync(s->snapshot, s->f[field], s->ncells * sizeof(float), cudaMemcpyDeviceToDevice, s->stream));
     FSB_CUDA(cudaEventRecord(s->ev_ready, s->stream));
     FSB_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_ready, 0));
-    FSB_CUDA(cudaMemcpyAsync(host_dst, s->f[field], s->ncells * sizeof(float), cudaMemcpyDeviceToHost, s->copy_stream));
+    FSB_CUDA(cudaMemcpyAsync(host_dst, s->snapshot, s->ncells * sizeof(float), cudaMemcpyDeviceToHost, s->copy_stream));
     FSB_CUDA(cudaEventRecord(s->ev_copied, s->copy_stream));
     s->copy_pending = true;
-    s->copy_src = s->f[field];
     return FSB_OK;
 }
 
@@ -923,7 +969,6 @@ int fsb_read_wait(fsb_sim *s)
     DeviceGuard guard(s->device);
     FSB_CUDA(cudaEventSynchronize(s->ev_copied));
     s->copy_pending = false;
-    s->copy_src = nullptr;
     return FSB_OK;
 }
 

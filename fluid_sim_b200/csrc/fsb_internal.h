@@ -89,18 +89,23 @@ bool sweep_config_fits(const SweepLaunch &L);   // can (levels, stages) be launc
 
 cudaError_t launch_sweep_pass(const SweepLaunch &L, SweepScratch &scr, cudaStream_t st, int *launches);
 
-// Passes of velocityStep chained inside one cooperative launch (chain.cu): diffuse(u), diffuse(v) when sor_sweeps > 0,
-// then project(u, v, p, div).  cudaErrorNotSupported: no chained configuration for this grid / these sweep counts.
+// Passes of FluidSim::step chained inside one cooperative launch (chain.cu): diffuse(u), diffuse(v) when
+// sor_sweeps > 0, project(u, v, p, div); with_advect: advect(u), advect(v) into (p, div) and the second projection on
+// them; with_density: densityStep (DIFFUSION == 0) with the final velocity, d -> nd.
+// cudaErrorNotSupported: no chained configuration for this grid / these sweep counts.
 struct ChainState;
-struct ChainProjectArgs {
+struct ChainArgs {
     int W, H;
     float *u, *v, *p, *div;
-    int sor_sweeps;            // 0: projection only
+    int sor_sweeps;            // 0: no diffusion phase
     float a, c_recip, omega;   // SOR coefficients (src/fluid_sim.cpp:45-47)
     int gs_sweeps;
+    int with_advect, with_density;
+    float dt;
+    float *d, *nd;             // density and the buffer that receives the advected density
+    int density_pz;            // diffusion sweeps ran with a == 0: boundaries of d + folded (v + 0.0f) taps
 };
-cudaError_t launch_chain_project(const ChainProjectArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st,
-                                 bool query_only);
+cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st, bool query_only);
 void chain_state_destroy(ChainState *cs);
 cudaError_t chain_read_trace(ChainState *cs, int which, unsigned long long *out, int max_phases, int max_items, int *nphases);
 

@@ -3,6 +3,7 @@
 // reference's association order and uses round-to-nearest intrinsics, so nothing is
 // contracted into an FMA (the reference's x86-64 -O2 build has none).
 #include "fsb_internal.h"
+#include "gather.cuh"
 
 namespace fsb {
 
@@ -17,7 +18,6 @@ __device__ __forceinline__ float plusz(float v, int plus_zero) { return plus_zer
 // the interior, so there is no ordering between wall and corner threads.
 struct BndJobs { BndJob j[4]; int n; };
 
-#define AT(G, i, j) ((size_t)(i) * (G).pitch + ((j) - (G).jbase))
 
 __device__ __forceinline__ float wall_j(const float *x, const GridView &G, int i, int jin, int b, int pz)
 {   // value setBoundary gives to (i, 0) or (i, H-1); jin = 1 or H-2
@@ -190,63 +190,6 @@ inline dim3 quad_grid(const GridView &G)
 {
     const int quads = (G.j1 - G.j0 + 3) / 4, rows = (G.W - 2 + kRows - 1) / kRows;
     return dim3((quads + kBx - 1) / kBx, (rows + kBy - 1) / kBy);
-}
-
-// ---- bilinear sample (src/fluid_sim.cpp:231-252) -------------------------------------------------------
-struct Taps { int i0, j0; float s0, s1, t0, t1; };
-
-__device__ __forceinline__ Taps make_taps(float x, float y, float xm, float ym)
-{
-    x = (x < xm) ? x : xm;        // std::min(width - 1.5f, x)
-    x = (0.5f < x) ? x : 0.5f;    // std::max(0.5f, .)
-    y = (y < ym) ? y : ym;
-    y = (0.5f < y) ? y : 0.5f;
-    const int i0 = __float2int_rz(x);
-    const int j0 = __float2int_rz(y);
-    Taps t;
-    t.s1 = __fsub_rn(x, (float)i0);
-    t.s0 = __fsub_rn(1.0f, t.s1);
-    t.t1 = __fsub_rn(y, (float)j0);
-    t.t0 = __fsub_rn(1.0f, t.t1);
-    t.i0 = i0;
-    t.j0 = j0;
-    return t;
-}
-
-template <bool PZ>
-__device__ __forceinline__ float tap_val(const float *__restrict__ f, int i, int j, const GridView &G)
-{
-    const int W = G.W, H = G.H;
-    float v = __ldg(f + AT(G, i, j));
-    if (PZ) {
-        // density only: the reference's diffuse pass with a == 0 rewrites every interior cell as
-        // d + 1.5f * ((d + 0*nb) - d), i.e. d + 0.0f (src/fluid_sim.cpp:56-57); folded in here.
-        if (i >= 1 && i <= W - 2 && j >= 1 && j <= H - 2) v = __fadd_rn(v, 0.0f);
-    }
-    return v;
-}
-
-// Idx: int when the local array has fewer than 2^31 elements (one 32-bit multiply-add per tap row instead of 64-bit
-// address arithmetic per tap), long long otherwise.
-template <bool PZ, typename Idx>
-__device__ __forceinline__ float sample(const float *__restrict__ f, const Taps &t, const GridView &G)
-{
-    const float *r0 = f + ((Idx)t.i0 * (Idx)G.pitch + (Idx)(t.j0 - G.jbase));
-    const float *r1 = r0 + G.pitch;
-    float f00 = __ldg(r0), f01 = __ldg(r0 + 1), f10 = __ldg(r1), f11 = __ldg(r1 + 1);
-    if (PZ) {
-        // density only: the reference's diffuse pass with a == 0 rewrites every interior cell as
-        // d + 1.5f * ((d + 0*nb) - d), i.e. d + 0.0f (src/fluid_sim.cpp:56-57); folded in here.
-        const bool i0in = t.i0 >= 1 && t.i0 <= G.W - 2, i1in = t.i0 + 1 >= 1 && t.i0 + 1 <= G.W - 2;
-        const bool j0in = t.j0 >= 1 && t.j0 <= G.H - 2, j1in = t.j0 + 1 >= 1 && t.j0 + 1 <= G.H - 2;
-        if (i0in && j0in) f00 = __fadd_rn(f00, 0.0f);
-        if (i0in && j1in) f01 = __fadd_rn(f01, 0.0f);
-        if (i1in && j0in) f10 = __fadd_rn(f10, 0.0f);
-        if (i1in && j1in) f11 = __fadd_rn(f11, 0.0f);
-    }
-    const float a = __fadd_rn(__fmul_rn(t.t0, f00), __fmul_rn(t.t1, f01));
-    const float b = __fadd_rn(__fmul_rn(t.t0, f10), __fmul_rn(t.t1, f11));
-    return __fadd_rn(__fmul_rn(t.s0, a), __fmul_rn(t.s1, b));
 }
 
 // ---- RK4 back-trace (src/fluid_sim.cpp:261-298) ------------------------------------------------------------
