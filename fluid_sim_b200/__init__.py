@@ -106,7 +106,8 @@ ABI = [
     ("fsb_field_handles", C.c_int, [_SIM, C.c_void_p]),
     ("fsb_link_connect_fields", C.c_int, [_SIM, C.c_void_p, C.c_int]),
     ("fsb_blk_wait_returns", C.c_int, [_SIM, C.c_int, C.c_uint64]),
-    ("fsb_blk_sweep", C.c_int, [_SIM, C.c_int, C.c_int, _ip, _ip, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_uint64]),
+    ("fsb_blk_sweep", C.c_int, [_SIM, C.c_int, C.c_int, _ip, _ip, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_uint64, _ip]),
+    ("fsb_blk_add_zero", C.c_int, [_SIM, C.c_int, _ip]),
     ("fsb_blk_set_boundary", C.c_int, [_SIM, C.c_int, _ip, _ip, _ip]),
     ("fsb_blk_divergence", C.c_int, [_SIM]),
     ("fsb_blk_gradient", C.c_int, [_SIM]),

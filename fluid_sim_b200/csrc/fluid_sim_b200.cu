@@ -1255,7 +1255,7 @@ static SweepLink make_link(const fsb_sim *s, unsigned long long seq)
  * place.  `seq` must be the same, strictly increasing number on every rank.  The result columns that belong to the
  * left neighbour land in this rank's left halo; the caller returns them and then applies the boundaries. */
 int fsb_blk_sweep(fsb_sim *s, int mode, int nfields, const int *fields, const int *bs, int levels, int stages, int first,
-                  float diff, float dt, unsigned long long seq)
+                  float diff, float dt, unsigned long long seq, const int *rhs_fields)
 {
     if (!s || !s->is_block || nfields < 1 || nfields > kMaxSweepFields) return fail(FSB_EINVAL, "fsb_blk_sweep: bad argument");
     DeviceGuard guard(s->device);
@@ -1288,7 +1288,14 @@ int fsb_blk_sweep(fsb_sim *s, int mode, int nfields, const int *fields, const in
         for (int i = 0; i < nfields; ++i) {
             if (!valid_field(fields[i])) return fail(FSB_EINVAL, "fsb_blk_sweep: bad field");
             float *x = s->f[fields[i]];
-            L.fld[i] = SweepField{x, x, x, sign_i(bs[i]), sign_j(bs[i])};
+            // several passes over one diffusion: the right-hand side stays the field as it was before the first pass
+            // (prev* in the reference, src/fluid_sim.cpp:386-391), kept by the caller in another buffer
+            const float *rhs = x;
+            if (rhs_fields) {
+                if (!valid_field(rhs_fields[i]) || rhs_fields[i] == fields[i]) return fail(FSB_EINVAL, "fsb_blk_sweep: bad rhs field");
+                rhs = s->f[rhs_fields[i]];
+            }
+            L.fld[i] = SweepField{x, rhs, x, sign_i(bs[i]), sign_j(bs[i])};
             if (L.link.left_ret) L.fld[i].out_peer = s->peer_left_f[fields[i]];
         }
     }
@@ -1311,6 +1318,20 @@ int fsb_blk_set_boundary(fsb_sim *s, int n, const int *fields, const int *bs, co
         jobs[i] = BndJob{s->f[fields[i]], bs[i], plus_zero ? plus_zero[i] : 0};
     }
     return set_boundary(s, jobs, n);
+}
+
+/* x = x + 0.0f over the local arrays: what the reference's diffuse() leaves in the interior when a == 0
+ * (src/fluid_sim.cpp:56-57); the caller applies the boundaries afterwards. */
+int fsb_blk_add_zero(fsb_sim *s, int n, const int *fields)
+{
+    if (!s || n < 1 || !fields) return fail(FSB_EINVAL, "fsb_blk_add_zero: bad argument");
+    DeviceGuard guard(s->device);
+    for (int i = 0; i < n; ++i) {
+        if (!valid_field(fields[i])) return fail(FSB_EINVAL, "fsb_blk_add_zero: bad field");
+        FSB_CUDA(launch_add_zero(s->f[fields[i]], s->ncells, s->stream));
+        s->launches += 1;
+    }
+    return FSB_OK;
 }
 
 int fsb_blk_divergence(fsb_sim *s)

@@ -18,7 +18,7 @@ import torch.distributed as dist
 from . import (DENSITY, VELOCITY_X, VELOCITY_Y, PREV_DENSITY, PREV_VEL_X, PREV_VEL_Y, NOISE_GLIBC, NOISE_ZERO,
                FsbError, Params, load_library, _SIM, _ip)
 
-__all__ = ["BlockFluidSim", "column_range", "plan_projection", "exchange_halo", "return_columns"]
+__all__ = ["BlockFluidSim", "column_range", "plan_projection", "plan_diffusion", "exchange_halo", "return_columns"]
 
 
 def column_range(height, rank, world, align=64):
@@ -39,6 +39,19 @@ def plan_projection(sweeps, levels=10, max_stages=5):
         out.append((levels, st))
         left -= levels * st
     for lv in (5, 2, 1):
+        while left >= lv:
+            out.append((lv, 1))
+            left -= lv
+    return out
+
+
+def plan_diffusion(sweeps):
+    """Launches (levels per warp, stages) covering `sweeps` diffusion sweeps: one launch for the counts that are an
+    instantiated sweeps-per-warp size (the reference's 5 among them), otherwise the largest sizes first."""
+    if sweeps in (1, 2, 5, 10, 20):
+        return [(sweeps, 1)]
+    out, left = [], sweeps
+    for lv in (10, 5, 2, 1):
         while left >= lv:
             out.append((lv, 1))
             left -= lv
@@ -112,14 +125,11 @@ class BlockFluidSim:
         self.P, self.D = proj_iters, diff_iters
         self.visc, self.diff = viscosity, diffusion
         self.halo, self.levels = halo, levels
-        if diffusion != 0.0:
-            raise FsbError("BlockFluidSim: density diffusion other than the reference's 0 is not sharded yet")
-        if diff_iters not in (0, 1, 2, 5, 10, 20):
-            raise FsbError("BlockFluidSim: diffusion sweeps must be 0, 1, 2, 5, 10 or 20 (one launch)")
         self.j0, self.j1 = column_range(height, self.rank, self.world, 32 * strips_per_cta)
         self.ncols = self.j1 - self.j0
         self.plan = plan_projection(proj_iters, levels)
-        if max([lv * st for lv, st in self.plan] + [diff_iters]) > halo:
+        self.dplan = plan_diffusion(diff_iters)
+        if max([lv * st for lv, st in self.plan + self.dplan] + [0]) > halo:
             raise FsbError("BlockFluidSim: halo narrower than the sweeps fused into one launch")
         self._lib = load_library()
         p = Params()
@@ -140,11 +150,21 @@ class BlockFluidSim:
         self.stream = torch.cuda.ExternalStream(st.value, device=self.device)
         self.seq = 0
         # columns exchanged before every advection: a neighbour can only supply columns it owns
+        # Columns exchanged before every advection.  A back-trace moves up to dt * width * max|v| columns per stage
+        # (src/fluid_sim.cpp:264, :275), so the width follows the velocity field: `reach=None` (default) exchanges what
+        # the all-reduced maximum of the previous step asks for, with a margin, up to `max_reach`; a number fixes it.
+        # Either way every rank checks on the device that the window it received was wide enough (sync() raises).
         narrowest = min(b - a for a, b in (column_range(height, r, self.world, 32 * strips_per_cta) for r in range(self.world)))
-        self.reach = min(halo, narrowest) if reach is None else reach
-        if not 3 <= self.reach <= min(halo, narrowest):
+        self.max_reach = min(halo, narrowest)
+        self.fixed_reach = reach
+        if reach is not None and not 3 <= reach <= self.max_reach:
             raise FsbError("BlockFluidSim: reach must be between 3 and min(halo, narrowest column block)")
+        self.reach = self.max_reach if reach is None else reach
         self._overshoot = torch.zeros((), dtype=torch.float32, device=self.device)
+        self._need = torch.zeros((), dtype=torch.float32, device=self.device)      # columns the last traces needed
+        self._need_host = torch.zeros((), dtype=torch.float32).pin_memory()
+        self._need_event = None
+        self._side = torch.cuda.Stream(device=self.device)
         self.trace = None      # set to {} to collect GPU time per phase (CUDA events on the simulation's stream)
         self._ev = []
         self._connect()
@@ -258,6 +278,35 @@ class BlockFluidSim:
         m = torch.maximum(u.abs().max(), v.abs().max())
         need = torch.ceil(m * (dt * self.width)) + 3.0      # + bilinear tap + rounding + the extra advected halo column
         self._overshoot = torch.maximum(self._overshoot, need - float(width))
+        self._need = torch.maximum(self._need, need)
+
+    def _publish_need(self):
+        """End of a step: all-reduce (max) the widest window any rank's traces needed and bring it to the host, on a
+        side stream, so that the next step can size its exchanges without waiting for anything."""
+        if self.fixed_reach is not None:
+            return
+        ready = torch.cuda.Event()
+        ready.record(self.stream)
+        self._side.wait_event(ready)
+        with torch.cuda.stream(self._side):
+            t = self._need.clone()
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+            self._need_host.copy_(t, non_blocking=True)
+            self._need_event = torch.cuda.Event()
+            self._need_event.record(self._side)
+        self._need = torch.zeros((), dtype=torch.float32, device=self.device)
+
+    def _choose_reach(self):
+        """Exchange width of this step: 1.5 x what the previous step needed + 4 columns, within [8, max_reach] and a
+        multiple of 4; the full width before anything is known."""
+        if self.fixed_reach is not None:
+            return self.fixed_reach
+        if self._need_event is None:
+            return self.max_reach
+        self._need_event.synchronize()                       # recorded a whole step ago: no wait in practice
+        want = int(math.ceil(1.5 * float(self._need_host.item()) + 4.0))
+        want = (max(want, 8) + 3) // 4 * 4
+        return min(want, self.max_reach)
 
     # -- inputs / outputs -----------------------------------------------------------------------------
     def set_from_global(self, field, full):
@@ -312,6 +361,36 @@ class BlockFluidSim:
     def addVelocity(self, x, y, ax, ay):
         self._check(self._lib.fsb_add_velocity(self._h, x, y, ax, ay))
 
+    def _coefficient(self, diff, dt):
+        """a = ((dt*diff)*width)*height in float32, src/fluid_sim.cpp:45"""
+        return np.float32(np.float32(np.float32(dt) * np.float32(diff)) * np.float32(self.width)) * np.float32(self.height)
+
+    def _diffuse(self, fields, bs, scratch, diff, dt, fold):
+        """diffuse() of src/fluid_sim.cpp:43-62 on `fields` (sharing the coefficient): any sweep count (several launches
+        keep the pre-diffusion fields in `scratch` as right-hand side), a == 0 (x + 0.0f and the boundary update).
+        Returns True if sweep launches ran (the one-column halos are then fresh)."""
+        if self.D <= 0:
+            return False
+        n = len(fields)
+        if self._coefficient(diff, dt) == 0:
+            self._check(self._lib.fsb_blk_add_zero(self._h, n, self._ids(fields)))
+            self._bnd(fields, bs)
+            return False
+        rhs = None
+        if len(self.dplan) > 1:
+            for f, sc in zip(fields, scratch):
+                self.tensor(sc).copy_(self.tensor(f))
+            rhs = self._ids(scratch)
+        for lv, st in self.dplan:
+            self.seq += 1
+            self._check(self._lib.fsb_blk_sweep(self._h, 1, n, self._ids(fields), self._ids(bs), lv, st, 0, diff, dt,
+                                                self.seq, rhs))
+            self._mark("sweep")
+            self._await_returns(n, lv * st)
+            self._mark("return")
+            self._bnd(fields, bs)
+        return True
+
     # -- the step (same order as velocityStep / densityStep, src/fluid_sim.cpp:370-422) ---------------------
     def _project(self, fresh_halo):
         if not fresh_halo:
@@ -321,7 +400,7 @@ class BlockFluidSim:
         self._mark("pointwise")
         for k, (lv, st) in enumerate(self.plan):
             self.seq += 1
-            self._check(self._lib.fsb_blk_sweep(self._h, 0, 1, None, None, lv, st, 1 if k == 0 else 0, 0.0, 0.0, self.seq))
+            self._check(self._lib.fsb_blk_sweep(self._h, 0, 1, None, None, lv, st, 1 if k == 0 else 0, 0.0, 0.0, self.seq, None))
             self._mark("sweep")
             self._await_returns(1, lv * st)
             self._mark("return")
@@ -339,18 +418,9 @@ class BlockFluidSim:
             self._mark("start")
             self._check(self._lib.fsb_op_add_noise(self._h))
             self._mark("pointwise")
-            if self.D > 0:
-                a = np.float32(np.float32(np.float32(dt) * np.float32(self.visc)) * np.float32(self.width)) * np.float32(self.height)
-                if a == 0:
-                    raise FsbError("BlockFluidSim: zero viscosity is not sharded yet")
-                self.seq += 1
-                self._check(self._lib.fsb_blk_sweep(self._h, 1, 2, self._ids([VELOCITY_X, VELOCITY_Y]), self._ids([1, 2]),
-                                                    self.D, 1, 0, self.visc, dt, self.seq))
-                self._mark("sweep")
-                self._await_returns(2, self.D)
-                self._mark("return")
-                self._bnd([VELOCITY_X, VELOCITY_Y], [1, 2])
-            self._project(fresh_halo=self.D > 0)
+            self.reach = self._choose_reach()
+            swept = self._diffuse([VELOCITY_X, VELOCITY_Y], [1, 2], [PREV_VEL_X, PREV_VEL_Y], self.visc, dt, fold=False)
+            self._project(fresh_halo=swept)
             self._halo([VELOCITY_X, VELOCITY_Y], self.reach)
             self._check_reach(dt, self.reach)
             self._mark("haloR")
@@ -362,12 +432,17 @@ class BlockFluidSim:
             self._project(fresh_halo=True)
             # density: diffusion 0 is the identity d + 0.0f plus the boundary update, folded into the gather; with no
             # diffusion sweeps at all (D == 0) the reference's loop body, boundary update included, never runs
-            fold = 1 if self.D > 0 else 0
-            if fold:
-                self._bnd([DENSITY], [0], [1])
+            fold = 0
+            if self._coefficient(self.diff, dt) == 0:
+                fold = 1 if self.D > 0 else 0
+                if fold:
+                    self._bnd([DENSITY], [0], [1])
+            else:
+                self._diffuse([DENSITY], [0], [PREV_DENSITY], self.diff, dt, fold=False)
             self._halo([DENSITY, VELOCITY_X, VELOCITY_Y], self.reach)
             self._check_reach(dt, self.reach)
             self._mark("haloR")
             self._check(self._lib.fsb_blk_advect_density(self._h, dt, fold))
             self._bnd([DENSITY], [0])
             self._mark("pointwise")
+            self._publish_need()

@@ -193,8 +193,11 @@ int fsb_link_connect(fsb_sim *s, const void *left_handle64, const void *right_ha
 int fsb_field_handles(fsb_sim *s, void *handles6x64);                             /* 6 IPC handles, role order */
 int fsb_link_connect_fields(fsb_sim *s, const void *left_handles6x64, int left_ncols);
 int fsb_blk_wait_returns(fsb_sim *s, int slot, unsigned long long expected);
+/* rhs_fields (mode 1, may be NULL): the buffers holding the fields as they were before the first pass of a diffusion
+ * that takes several passes; NULL = the field itself (single pass, in place). */
 int fsb_blk_sweep(fsb_sim *s, int mode, int nfields, const int *fields, const int *bs, int levels, int stages,
-                  int first, float diff, float dt, unsigned long long seq);
+                  int first, float diff, float dt, unsigned long long seq, const int *rhs_fields);
+int fsb_blk_add_zero(fsb_sim *s, int n, const int *fields);
 int fsb_blk_set_boundary(fsb_sim *s, int n, const int *fields, const int *bs, const int *plus_zero);
 int fsb_blk_divergence(fsb_sim *s);
 int fsb_blk_gradient(fsb_sim *s);

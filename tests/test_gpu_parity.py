@@ -395,7 +395,8 @@ def test_cpp_dropin_object_semantics_against_reference(tmp_path):
     assert out.returncode == 0 and "ALL IDENTICAL" in out.stdout, out.stdout + out.stderr
 
 
-@pytest.mark.parametrize("args", ["256 512 20 5 2", "200 1024 40 5 1", "300 256 33 0 2", "130 512 100 5 1"])
+@pytest.mark.parametrize("args", ["256 512 20 5 2", "200 1024 40 5 1", "300 256 33 0 2", "130 512 100 5 1",
+                                  "128 512 20 7 2 diff=2e-4", "128 512 10 5 2 visc=0", "8192 512 20 5 2 demo=1 halo=256"])
 def test_multi_gpu_matches_single_gpu(args):
     """Column blocks on 2 GPUs (sweep chain handed over through peer memory, NCCL halos) give the single-GPU bits."""
     import os

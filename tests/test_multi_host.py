@@ -9,7 +9,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from fluid_sim_b200.multi import column_range, exchange_halo, plan_projection, return_columns
+from fluid_sim_b200.multi import column_range, exchange_halo, plan_diffusion, plan_projection, return_columns
 
 
 def test_column_ranges_tile_the_grid():
@@ -30,6 +30,14 @@ def test_projection_plan_covers_all_sweeps():
         assert all(lv in (1, 2, 5, 10) and 1 <= st <= 5 for lv, st in plan)
     assert plan_projection(40) == [(10, 4)]
     assert plan_projection(100) == [(10, 5), (10, 5)]
+
+
+def test_diffusion_plan_covers_all_sweeps():
+    for d in range(0, 41):
+        plan = plan_diffusion(d)
+        assert sum(lv * st for lv, st in plan) == d
+        assert all(lv in (1, 2, 5, 10, 20) and st == 1 for lv, st in plan)
+    assert plan_diffusion(5) == [(5, 1)] and plan_diffusion(7) == [(5, 1), (2, 1)]
 
 
 def _free_port():

@@ -16,8 +16,10 @@ sim.write(fsb.DENSITY, d); sim.write(fsb.VELOCITY_X, u); sim.write(fsb.VELOCITY_
 for _ in range(3):
     sim.step(0.01)
 sim.sync()
-sim.velocityStep(0.01)
+sim.step(0.01)
 for name, tr in (("diffuse + project", sim.chain_trace(0).astype(np.float64)), ("project alone", sim.chain_trace(1).astype(np.float64))):
+    if not (tr > 0).any():
+        continue
     t0 = tr[tr > 0].min()
     print(name, "phases", tr.shape[0])
     for p in range(tr.shape[0]):
