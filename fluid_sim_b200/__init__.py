@@ -111,6 +111,7 @@ ABI = [
     ("fsb_blk_set_boundary", C.c_int, [_SIM, C.c_int, _ip, _ip, _ip]),
     ("fsb_blk_divergence", C.c_int, [_SIM]),
     ("fsb_blk_gradient", C.c_int, [_SIM]),
+    ("fsb_blk_vmax_word", C.c_int, [_SIM, C.POINTER(C.c_void_p)]),
     ("fsb_blk_advect_velocity", C.c_int, [_SIM, C.c_float, C.c_int]),
     ("fsb_blk_advect_density", C.c_int, [_SIM, C.c_float, C.c_int]),
     ("fsb_pressure_sweeps_noalloc", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),

@@ -94,6 +94,7 @@ struct fsb_sim {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_ready = nullptr, ev_copied = nullptr;
     bool copy_pending = false;
+    unsigned *vmax_word = nullptr;              // column blocks: largest |v| written by the gradient passes (float bits)
     float *snapshot = nullptr;                  // device-side copy of the field an asynchronous read is transferring
     unsigned char *view_buf = nullptr;          // RGBA8 image of the last fsb_view_density* call
     size_t view_bytes = 0;
@@ -747,6 +748,7 @@ int fsb_destroy(fsb_sim *s)
         if (s->link_buf) cudaFree(s->link_buf);
         if (s->view_buf) cudaFree(s->view_buf);
         if (s->snapshot) cudaFree(s->snapshot);
+        if (s->vmax_word) cudaFree(s->vmax_word);
         for (auto &r : s->prof_open) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         for (auto &e : s->prof_free) cudaEventDestroy(e);
         if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
@@ -1348,9 +1350,28 @@ int fsb_blk_gradient(fsb_sim *s)
 {
     if (!s) return fail(FSB_EINVAL, "null handle");
     DeviceGuard guard(s->device);
+    if (!s->vmax_word) {
+        FSB_CUDA(cudaMalloc(&s->vmax_word, 256));
+        FSB_CUDA(cudaMemsetAsync(s->vmax_word, 0, 256, s->stream));
+    }
     ProfScope ps(s, FSB_PROF_GRADIENT);
-    FSB_CUDA(launch_gradient(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_X], s->G, s->stream));
+    FSB_CUDA(launch_gradient(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->f[FSB_PREV_VEL_X], s->G, s->stream, s->vmax_word));
     s->launches += 1;
+    return FSB_OK;
+}
+
+/* Device address of one float: the largest |velocityY| the fsb_blk_gradient calls wrote into this rank's owned columns
+ * since the caller last cleared it (it only grows).  velocityY moves a back-trace along the columns
+ * (src/fluid_sim.cpp:275-291), so this bounds the halo width the next advection needs. */
+int fsb_blk_vmax_word(fsb_sim *s, void **dptr)
+{
+    if (!s || !dptr) return fail(FSB_EINVAL, "fsb_blk_vmax_word: bad argument");
+    DeviceGuard guard(s->device);
+    if (!s->vmax_word) {
+        FSB_CUDA(cudaMalloc(&s->vmax_word, 256));
+        FSB_CUDA(cudaMemsetAsync(s->vmax_word, 0, 256, s->stream));
+    }
+    *dptr = s->vmax_word;
     return FSB_OK;
 }
 

@@ -119,7 +119,9 @@ struct BndJob { float *x; int b; int plus_zero; };   // plus_zero: interior valu
 
 cudaError_t launch_set_boundary(const BndJob *jobs, int njobs, const GridView &G, cudaStream_t st);
 cudaError_t launch_divergence(const float *u, const float *v, float *div, const GridView &G, cudaStream_t st);
-cudaError_t launch_gradient(float *u, float *v, const float *p, const GridView &G, cudaStream_t st);
+// vmax_bits (optional): atomicMax target for the largest |v| written (bit pattern of a non-negative float)
+cudaError_t launch_gradient(float *u, float *v, const float *p, const GridView &G, cudaStream_t st,
+                            unsigned *vmax_bits = nullptr);
 // RK4 back-trace of (src_a[, src_b]) through (u, v); dst_b/src_b may be null.
 cudaError_t launch_advect_rk4(float *dst_a, const float *src_a, float *dst_b, const float *src_b,
                               const float *u, const float *v, int src_plus_zero, const GridView &G, float dt,

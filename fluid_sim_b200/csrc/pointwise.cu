@@ -84,18 +84,31 @@ __global__ void divergence_kernel(const float *__restrict__ u, const float *__re
 }
 
 // ---- pressure gradient (src/fluid_sim.cpp:334-341) ---------------------------------------------------
+// vmax_bits (may be null): receives the largest |v| written, as the bit pattern of a non-negative float (atomicMax on
+// unsigned keeps the float order).  It bounds how many columns the next advection's back-traces can move.
+__device__ __forceinline__ void publish_vmax(float m, unsigned *vmax_bits)
+{
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (((threadIdx.y * blockDim.x + threadIdx.x) & 31) == 0 && m > 0.0f) atomicMax(vmax_bits, __float_as_uint(m));
+}
+
 __global__ void gradient_kernel(float *__restrict__ u, float *__restrict__ v, const float *__restrict__ p,
-                                const GridView G, float h)
+                                const GridView G, float h, unsigned *vmax_bits)
 {
     const int W = G.W, H = G.H;
     const int j = G.j0 + blockIdx.x * kBx + threadIdx.x;
     const int i = blockIdx.y * kBy + threadIdx.y;
-    if (i < 1 || i > W - 2 || j < 1 || j > H - 2 || j >= G.j1) return;
-    const size_t c = AT(G, i, j);
-    const float gx = __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(p[c + G.pitch], p[c - G.pitch])), h);
-    const float gy = __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(p[c + 1], p[c - 1])), h);
-    u[c] = __fsub_rn(u[c], gx);
-    v[c] = __fsub_rn(v[c], gy);
+    float m = 0.0f;
+    if (!(i < 1 || i > W - 2 || j < 1 || j > H - 2 || j >= G.j1)) {
+        const size_t c = AT(G, i, j);
+        const float gx = __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(p[c + G.pitch], p[c - G.pitch])), h);
+        const float gy = __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(p[c + 1], p[c - 1])), h);
+        u[c] = __fsub_rn(u[c], gx);
+        const float nv = __fsub_rn(v[c], gy);
+        v[c] = nv;
+        m = fabsf(nv);
+    }
+    if (vmax_bits) publish_vmax(m, vmax_bits);
 }
 
 // ---- the same two stencils, four columns and kRows rows per thread -------------------------------------------------
@@ -151,12 +164,17 @@ __global__ void __launch_bounds__(256) divergence_vec_kernel(const float *__rest
 }
 
 __global__ void __launch_bounds__(256) gradient_vec_kernel(float *__restrict__ u, float *__restrict__ v,
-                                                           const float *__restrict__ p, const GridView G, float h)
+                                                           const float *__restrict__ p, const GridView G, float h,
+                                                           unsigned *vmax_bits)
 {
     const int W = G.W, H = G.H;
     const int j = G.j0 + 4 * (blockIdx.x * kBx + threadIdx.x);
     const int i0 = 1 + kRows * (blockIdx.y * kBy + threadIdx.y);
-    if (j >= G.j1 || i0 > W - 2) return;
+    float m = 0.0f;
+    if (j >= G.j1 || i0 > W - 2) {
+        if (vmax_bits) publish_vmax(m, vmax_bits);
+        return;
+    }
     const int jlo = max(1, G.j0), jhi = min(H - 2, G.j1 - 1);
     const int jmax = G.jbase + G.pitch - 1;
     size_t c = AT(G, i0, j);
@@ -179,10 +197,15 @@ __global__ void __launch_bounds__(256) gradient_vec_kernel(float *__restrict__ u
         vv.w = __fsub_rn(vv.w, __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(pr, pc.z)), h));
         store_quad(u + c, uu, j, jlo, jhi);
         store_quad(v + c, vv, j, jlo, jhi);
+        if (j >= jlo && j <= jhi) m = fmaxf(m, fabsf(vv.x));
+        if (j + 1 >= jlo && j + 1 <= jhi) m = fmaxf(m, fabsf(vv.y));
+        if (j + 2 >= jlo && j + 2 <= jhi) m = fmaxf(m, fabsf(vv.z));
+        if (j + 3 >= jlo && j + 3 <= jhi) m = fmaxf(m, fabsf(vv.w));
         pm = pc;
         pc = pp;
         c += G.pitch;
     }
+    if (vmax_bits) publish_vmax(m, vmax_bits);
 }
 
 inline bool quad_aligned(const GridView &G) { return (G.pitch % 4 == 0) && (G.jbase % 4 == 0) && (G.j0 % 4 == 0); }
@@ -334,11 +357,11 @@ cudaError_t launch_divergence(const float *u, const float *v, float *div, const 
     return cudaGetLastError();
 }
 
-cudaError_t launch_gradient(float *u, float *v, const float *p, const GridView &G, cudaStream_t st)
+cudaError_t launch_gradient(float *u, float *v, const float *p, const GridView &G, cudaStream_t st, unsigned *vmax_bits)
 {
     const float h = 1.0f / (float)G.W;
-    if (quad_aligned(G)) gradient_vec_kernel<<<quad_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, p, G, h);
-    else gradient_kernel<<<cell_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, p, G, h);
+    if (quad_aligned(G)) gradient_vec_kernel<<<quad_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, p, G, h, vmax_bits);
+    else gradient_kernel<<<cell_grid(G), dim3(kBx, kBy), 0, st>>>(u, v, p, G, h, vmax_bits);
     return cudaGetLastError();
 }
 

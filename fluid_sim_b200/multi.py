@@ -165,6 +165,10 @@ class BlockFluidSim:
         self._need_host = torch.zeros((), dtype=torch.float32).pin_memory()
         self._need_event = None
         self._side = torch.cuda.Stream(device=self.device)
+        vp = C.c_void_p()
+        self._check(self._lib.fsb_blk_vmax_word(self._h, C.byref(vp)))
+        self._vmax = torch.as_tensor(_DevicePointer(vp.value, (1,)), device=self.device)
+        self._used = 0          # widest exchange of the step being run
         self.trace = None      # set to {} to collect GPU time per phase (CUDA events on the simulation's stream)
         self._ev = []
         self._connect()
@@ -268,23 +272,22 @@ class BlockFluidSim:
             self._check(self._lib.fsb_blk_wait_returns(self._h, slot, self.returned[slot]))
 
     def _check_reach(self, dt, width):
-        """Columns an RK4 back-trace can reach: every stage moves at most dt*width*max|velocity| cells.  The halo
-        exchange before an advection always moves `width` columns; this records, on the device and without a host
-        wait or a collective, by how much the velocities now in [owned - width, owned + width) overshoot that.
-        The positions a trace samples stay inside that window whenever the bound computed from the window's own
-        maximum fits, so the local test is sufficient.  `sync()` raises if any step overshot."""
-        lo, hi = self.halo - width, self.halo + self.ncols + width
-        u, v = self.tensor(VELOCITY_X)[:, lo:hi], self.tensor(VELOCITY_Y)[:, lo:hi]
-        m = torch.maximum(u.abs().max(), v.abs().max())
+        """Columns an RK4 back-trace can move: every stage moves at most dt*width*max|velocityY| cells (bilinear samples
+        never exceed the largest tap).  The gradient kernel of the projection that has just run left the largest
+        |velocityY| of this rank's columns in one device word (atomicMax fused into the kernel); this turns it into
+        the window the traces need, records - on the device, without a host wait - by how much that exceeds the
+        `width` columns just exchanged, and clears the word.  The maxima of all ranks are all-reduced at the end of
+        the step (lagging one step: _publish_need), which is also how an overshoot on another rank's columns, which
+        could reach into this rank's window, is noticed everywhere.  `sync()` raises if any step overshot."""
+        m = self._vmax[0]
         need = torch.ceil(m * (dt * self.width)) + 3.0      # + bilinear tap + rounding + the extra advected halo column
         self._overshoot = torch.maximum(self._overshoot, need - float(width))
         self._need = torch.maximum(self._need, need)
+        self._vmax.zero_()
 
     def _publish_need(self):
         """End of a step: all-reduce (max) the widest window any rank's traces needed and bring it to the host, on a
         side stream, so that the next step can size its exchanges without waiting for anything."""
-        if self.fixed_reach is not None:
-            return
         ready = torch.cuda.Event()
         ready.record(self.stream)
         self._side.wait_event(ready)
@@ -299,12 +302,16 @@ class BlockFluidSim:
     def _choose_reach(self):
         """Exchange width of this step: 1.5 x what the previous step needed + 4 columns, within [8, max_reach] and a
         multiple of 4; the full width before anything is known."""
+        if self._need_event is None:
+            return self.max_reach if self.fixed_reach is None else self.fixed_reach
+        self._need_event.synchronize()                       # recorded a whole step ago: no wait in practice
+        needed = float(self._need_host.item())
+        if needed > self._used > 0:
+            raise FsbError(f"BlockFluidSim: the last step's traces needed {int(needed)} columns, {self._used} were "
+                           "exchanged; its results are invalid (raise `halo`, fix `reach`, or lower dt)")
         if self.fixed_reach is not None:
             return self.fixed_reach
-        if self._need_event is None:
-            return self.max_reach
-        self._need_event.synchronize()                       # recorded a whole step ago: no wait in practice
-        want = int(math.ceil(1.5 * float(self._need_host.item()) + 4.0))
+        want = int(math.ceil(1.5 * needed + 4.0))
         want = (max(want, 8) + 3) // 4 * 4
         return min(want, self.max_reach)
 
@@ -419,6 +426,7 @@ class BlockFluidSim:
             self._check(self._lib.fsb_op_add_noise(self._h))
             self._mark("pointwise")
             self.reach = self._choose_reach()
+            self._used = self.reach
             swept = self._diffuse([VELOCITY_X, VELOCITY_Y], [1, 2], [PREV_VEL_X, PREV_VEL_Y], self.visc, dt, fold=False)
             self._project(fresh_halo=swept)
             self._halo([VELOCITY_X, VELOCITY_Y], self.reach)

@@ -201,6 +201,9 @@ int fsb_blk_add_zero(fsb_sim *s, int n, const int *fields);
 int fsb_blk_set_boundary(fsb_sim *s, int n, const int *fields, const int *bs, const int *plus_zero);
 int fsb_blk_divergence(fsb_sim *s);
 int fsb_blk_gradient(fsb_sim *s);
+/* One float in device memory: largest |velocityY| written by fsb_blk_gradient into the owned columns since the caller
+ * cleared it; bounds the columns the next advection's back-traces can move (src/fluid_sim.cpp:264, :275). */
+int fsb_blk_vmax_word(fsb_sim *s, void **dptr);
 /* extend_halo: also advect the first halo column on every side that has a neighbour (the divergence that follows needs
  * it; computing it here saves a halo exchange -- the halo must then hold the neighbours' values one column further). */
 int fsb_blk_advect_velocity(fsb_sim *s, float dt, int extend_halo);
