@@ -54,6 +54,8 @@ int fail_cuda(cudaError_t e, const char *what)
 
 constexpr int kNumFields = 6;
 
+struct SweepPlan { int levels, stages; };   // one launch of the sweep pipeline: sweeps per warp x chained warps per strip
+
 // Position of the process-wide rand() stream (fsb_params.noise_process_stream): outputs consumed so far by all
 // simulations that share it.  The reference's generator is libc's, one per process (src/fluid_sim.cpp:378-379).
 std::mutex g_proc_noise_mu;
@@ -81,6 +83,10 @@ struct fsb_sim {
     SourceEntry *d_entries = nullptr;
     int *d_segs = nullptr;
     size_t d_entries_cap = 0, d_segs_cap = 0;
+    struct SourceStage { unsigned char *host = nullptr; size_t bytes = 0; cudaEvent_t done = nullptr; bool used = false; };
+    std::vector<std::pair<uint64_t, std::vector<SweepPlan>>> plan_cache;   // (sweeps, fields, mode) -> launches
+    SourceStage src_stage[2];              // page-locked staging of pending sources, used alternately
+    int src_next = 0;
     std::vector<float> mirror[3];
     bool mirror_valid[3] = {false, false, false};
     uint64_t launches = 0;
@@ -164,12 +170,24 @@ struct ProfScope {
 inline float sign_i(int b) { return b == 1 ? -1.0f : 1.0f; }
 inline float sign_j(int b) { return b == 2 ? -1.0f : 1.0f; }
 
-struct SweepPlan { int levels, stages; };
 
 // Splits n sweeps into launches of (sweeps per warp) x (stages): one launch when n factors into an
 // instantiated size that can be launched with every CTA resident, otherwise greedily.
 // pref / max_stages are tuning overrides (0 = automatic).
-std::vector<SweepPlan> plan_sweeps(const fsb_sim *s, int n, int nfields, int mode)
+std::vector<SweepPlan> plan_sweeps_uncached(const fsb_sim *s, int n, int nfields, int mode);
+
+// The plan depends on (sweeps, fields, mode) and the tuning only; probing a configuration costs several runtime calls
+// (function attributes, occupancy), so plans are kept until fsb_set_tuning changes the tuning.
+const std::vector<SweepPlan> &plan_sweeps(fsb_sim *s, int n, int nfields, int mode)
+{
+    const uint64_t key = ((uint64_t)(uint32_t)n << 8) | ((uint64_t)nfields << 4) | (uint64_t)mode;
+    for (auto &c : s->plan_cache)
+        if (c.first == key) return c.second;
+    s->plan_cache.emplace_back(key, plan_sweeps_uncached(s, n, nfields, mode));
+    return s->plan_cache.back().second;
+}
+
+std::vector<SweepPlan> plan_sweeps_uncached(const fsb_sim *s, int n, int nfields, int mode)
 {
     const int pref = s->tune_levels, max_stages = s->tune_stages;
     std::vector<int> sizes;
@@ -276,25 +294,46 @@ int flush_sources(fsb_sim *s, SourceSel sel = kAllSources)
         if (k == 0 || e[k].field != e[k - 1].field || e[k].cell != e[k - 1].cell) segs.push_back((int)k);
     const int nseg = (int)segs.size();
     segs.push_back((int)e.size());
+    // Staging: the entries and segment starts go to the device from one of two page-locked buffers; a buffer is reused
+    // only after the copy that read it last has finished (event), so fsb_step never waits for the GPU here (the
+    // reference's mouse handler adds sources every frame, src/main.cpp:216-252).  Buffers grow geometrically.
+    const size_t ebytes = e.size() * sizeof(SourceEntry), sbytes = segs.size() * sizeof(int);
+    const size_t need = ebytes + sbytes;
+    fsb_sim::SourceStage &stg = s->src_stage[s->src_next];
+    s->src_next ^= 1;
+    if (stg.used) FSB_CUDA(cudaEventSynchronize(stg.done));      // two flushes ago: long finished
+    if (need > stg.bytes) {
+        if (stg.host) cudaFreeHost(stg.host);
+        stg.host = nullptr;
+        stg.bytes = 0;
+        const size_t cap = std::max<size_t>(need * 2, 1 << 16);
+        FSB_CUDA(cudaHostAlloc(&stg.host, cap, cudaHostAllocDefault));
+        stg.bytes = cap;
+    }
+    if (!stg.done) FSB_CUDA(cudaEventCreateWithFlags(&stg.done, cudaEventDisableTiming));
     if (e.size() > s->d_entries_cap) {
+        FSB_CUDA(cudaStreamSynchronize(s->stream));                // rare: the device buffer grows
         if (s->d_entries) cudaFree(s->d_entries);
         s->d_entries = nullptr;
-        s->d_entries_cap = std::max<size_t>(e.size() * 2, 1024);
+        s->d_entries_cap = std::max<size_t>(e.size() * 2, 4096);
         FSB_CUDA(cudaMalloc(&s->d_entries, s->d_entries_cap * sizeof(SourceEntry)));
     }
     if (segs.size() > s->d_segs_cap) {
+        FSB_CUDA(cudaStreamSynchronize(s->stream));
         if (s->d_segs) cudaFree(s->d_segs);
         s->d_segs = nullptr;
-        s->d_segs_cap = std::max<size_t>(segs.size() * 2, 1024);
+        s->d_segs_cap = std::max<size_t>(segs.size() * 2, 4096);
         FSB_CUDA(cudaMalloc(&s->d_segs, s->d_segs_cap * sizeof(int)));
     }
-    FSB_CUDA(cudaMemcpyAsync(s->d_entries, e.data(), e.size() * sizeof(SourceEntry), cudaMemcpyHostToDevice, s->stream));
-    FSB_CUDA(cudaMemcpyAsync(s->d_segs, segs.data(), segs.size() * sizeof(int), cudaMemcpyHostToDevice, s->stream));
+    std::memcpy(stg.host, e.data(), ebytes);
+    std::memcpy(stg.host + ebytes, segs.data(), sbytes);
+    FSB_CUDA(cudaMemcpyAsync(s->d_entries, stg.host, ebytes, cudaMemcpyHostToDevice, s->stream));
+    FSB_CUDA(cudaMemcpyAsync(s->d_segs, stg.host + ebytes, sbytes, cudaMemcpyHostToDevice, s->stream));
     FSB_CUDA(launch_apply_sources(s->f[FSB_DENSITY], s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->d_entries,
                                   s->d_segs, nseg, s->stream));
+    FSB_CUDA(cudaEventRecord(stg.done, s->stream));
+    stg.used = true;
     s->launches += 1;
-    // the host vectors are reused right away: wait for the staged copies
-    FSB_CUDA(cudaStreamSynchronize(s->stream));
     e.clear();
     return FSB_OK;
 }
@@ -323,7 +362,7 @@ int diffuse_fields(fsb_sim *s, int nf, float *const *xs, const int *bs, float di
         if (folded && fold_identity) *folded = 1;
         return FSB_OK;
     }
-    const std::vector<SweepPlan> passes = plan_sweeps(s, D, nf, kSor);
+    const std::vector<SweepPlan> &passes = plan_sweeps(s, D, nf, kSor);
     const bool multi = passes.size() > 1;
     float *rhs[2] = {xs[0], nf > 1 ? xs[1] : nullptr};
     if (multi) {
@@ -369,7 +408,7 @@ int project(fsb_sim *s, float *u, float *v, float *p, float *div)
         FSB_CUDA(launch_divergence(u, v, div, s->G, s->stream));
     }
     s->launches += 1;
-    const std::vector<SweepPlan> passes = plan_sweeps(s, s->prm.proj_iters, 1, kGaussSeidel);
+    const std::vector<SweepPlan> &passes = plan_sweeps(s, s->prm.proj_iters, 1, kGaussSeidel);
     if (passes.empty()) FSB_CUDA(cudaMemsetAsync(p, 0, s->ncells * sizeof(float), s->stream));
     for (size_t pi = 0; pi < passes.size(); ++pi) {
         SweepLaunch L{};
@@ -661,6 +700,8 @@ static int create_common(const fsb_params *p, const GridView *block, fsb_sim **o
     if (prm.proj_iters < 0 || prm.diff_iters < 0) return fail(FSB_EINVAL, "fsb_create: negative sweep count");
     if (prm.advect_scheme < 0 || prm.advect_scheme > 2) return fail(FSB_EINVAL, "fsb_create: unknown advection scheme");
     if ((long long)prm.width * prm.height > (1ll << 31) - 1) return fail(FSB_ELIMIT, "fsb_create: more than 2^31-1 cells");
+    if (block && (long long)prm.width * block->pitch > (1ll << 31) - 1)
+        return fail(FSB_ELIMIT, "fsb_create_block: more than 2^31-1 cells in the local arrays (cell indices are 32-bit)");
 
     int ndev = 0;
     cudaError_t ce = cudaGetDeviceCount(&ndev);
@@ -740,6 +781,10 @@ int fsb_destroy(fsb_sim *s)
         s->chain = nullptr;
         if (s->d_entries) cudaFree(s->d_entries);
         if (s->d_segs) cudaFree(s->d_segs);
+        for (auto &stg : s->src_stage) {
+            if (stg.host) cudaFreeHost(stg.host);
+            if (stg.done) cudaEventDestroy(stg.done);
+        }
         noise_tables_destroy(s->noise_tables);
         for (int k = 0; k < 6; ++k)
             if (s->peer_left_base[k]) cudaIpcCloseMemHandle(s->peer_left_base[k]);
@@ -1102,6 +1147,7 @@ int fsb_set_tuning(fsb_sim *s, int strips_per_cta, int sweeps_per_warp, int max_
     s->tune_strips = strips_per_cta;
     s->tune_levels = sweeps_per_warp;
     s->tune_stages = max_stages;
+    s->plan_cache.clear();
     return FSB_OK;
 }
 

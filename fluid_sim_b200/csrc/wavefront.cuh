@@ -54,7 +54,7 @@ constexpr int kTileFloats = kTileRows * 32;
 //   WF_FLUSH_OFFLOAD (0)  result write-back by the export warp instead of the last-stage warp: 8 % slower
 //   WF_CLUSTER_MODE (0)   2 = hand-over through distributed shared memory inside thread-block clusters: slower
 //   WF_PROFILE            in-kernel cycle counters printed per warp (development builds only)
-//   WF_STRICT_FENCES      acquire/release instructions instead of volatile accesses on the shared-memory counters
+//   WF_RELAXED_FENCES     volatile accesses instead of acquire/release instructions on the shared-memory counters
 // Result rows are written back by the last-stage warp itself (0) or by the export helper warp (1).
 // Measured on B200 at 8192^2: the helper variant loses about 8 % (it competes for issue slots with the
 // compute warps of its scheduler), so the default is 0.
@@ -218,15 +218,16 @@ __device__ __forceinline__ int ld_acquire_cluster_s32(const int *p)
     return v;
 }
 
+// Progress words in shared memory: acquire / release at CTA scope, as the PTX memory model asks for a flag that
+// publishes data written by another warp.  -DWF_RELAXED_FENCES swaps them for volatile accesses (relying on an SM
+// performing shared-memory accesses in issue order, which is not a PTX guarantee): measured 0.9 % faster on the
+// whole step at 8192^2, P = 40 (profiles/), bit-identical in every parity test - not worth leaving the model.
 __device__ __forceinline__ int ld_acquire_cta_s32(const int *p)
 {
     int v;
-#ifdef WF_STRICT_FENCES
+#ifndef WF_RELAXED_FENCES
     asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
 #else
-    // Shared-memory accesses of an SM are performed in issue order, so a volatile flag access is enough
-    // here: the producer's data stores are issued (after __syncwarp) before its flag store, and this
-    // warp's data loads are issued after the flag load.  Avoids one MEMBAR per poll.
     asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
 #endif
     return v;
@@ -234,7 +235,7 @@ __device__ __forceinline__ int ld_acquire_cta_s32(const int *p)
 
 __device__ __forceinline__ void st_release_cta_s32(int *p, int v)
 {
-#ifdef WF_STRICT_FENCES
+#ifndef WF_RELAXED_FENCES
     asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
 #else
     asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
