@@ -462,46 +462,89 @@ def main():
 
     # -------- roofline of the dominant kernel and of the whole step
     peak, peak_src = measured_peak_gbs()
-    gs_ms, gs_n = prof["gs"]
-    gs_launch_ms = gs_ms / max(gs_n, 1)
     cells = W * (H // world)                                  # cells of one rank's block
-    launches_per_proj = max(1.0, gs_n / (2.0 * K))          # two projections per step
-    levels = P / launches_per_proj                            # sweeps fused into one launch
-    algo_bytes = 12.0 * levels * cells                        # reference pass structure: 12 B per cell per sweep
-    compulsory = 8.0 * cells if launches_per_proj <= 1.0 else (8.0 + 12.0 * (launches_per_proj - 1)) / launches_per_proj * cells
-    achieved = algo_bytes / (gs_launch_ms * 1e-3) / 1e9 if gs_launch_ms > 0 else 0.0
-    compulsory_gbs = compulsory / (gs_launch_ms * 1e-3) / 1e9 if gs_launch_ms > 0 else 0.0
-    fused_gbs = 12.0 * cells / (gs_launch_ms * 1e-3) / 1e9 if gs_launch_ms > 0 else 0.0   # 12 B per cell per fused launch
-    roofline = {"kernel": f"wf_kernel<S, GaussSeidel>: one launch fuses {levels:g} sweeps of a projection",
-                "bound": "dependency chain of the exact-order sweeps / instruction issue and shared-memory bandwidth "
-                         "(not HBM: see `frac`)",
-                "achieved": fused_gbs, "peak": peak, "unit": "GB/s", "frac": fused_gbs / peak,
-                "compulsory_gbs": compulsory_gbs, "effective_gbs": achieved, "effective_frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "launch_ms": gs_launch_ms, "launches_timed": gs_n,
-                "algorithmic_bytes_per_launch": algo_bytes,
-                "sweep_cell_updates_per_sec": levels * cells / (gs_launch_ms * 1e-3) if gs_launch_ms > 0 else 0.0,
-                "compulsory_bytes_per_launch": compulsory,
-                "note": "achieved / frac = SURVEY.md 8(d)'s fusion rule, 12 B per cell per fused launch, / launch time (the launch "
-                        "really moves the compulsory 8 B per cell: `compulsory_gbs`): the kernel is nowhere near HBM, it is bound "
-                        "by the dependency chain of the exact-order sweeps.  effective_gbs / effective_frac = the same launch counted "
-                        "at the reference's pass structure (12 B per cell per SWEEP), which fusion makes exceed the real "
-                        "traffic; `traffic` = ncu DRAM bytes per launch (profiles/)"}
+    tr = {}
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         try:
             tr = json.load(open(traffic_file))
-            key = f"{W}x{H}_p{P}_gs"
-            if key in tr:
-                roofline["traffic"] = tr[key]
         except Exception:
-            pass
+            tr = {}
+    chain_ms, chain_n = prof.get("chain", (0.0, 0))
+    gs_ms, gs_n = prof["gs"]
+    levels = float(P)
+    if chain_n > 0 and gs_n == 0:
+        # One chained launch per step: diffuse(u, v), project, advect(u, v), project and the density step as phases of
+        # one cooperative kernel (fluid_sim_b200/csrc/chain.cu).
+        launch_ms = chain_ms / chain_n
+        per_step = chain_n / float(K)
+        whole = abs(per_step - 1.0) < 1e-6
+        # SURVEY.md 8(d) fusion rule: inputs not produced inside the kernel + outputs consumed outside it
+        fused_bpc = 24.0 if whole else 20.0                   # u, v, d in and out / u, v in and out + the pressure
+        # what the phases really move: SOR 2 x 8, per projection div 12 + sweeps 8 + gradient 20, advections 16 + 16
+        moved_bpc = (16.0 + 2 * 40.0 + 32.0) if whole else 56.0
+        eff_bpc = (algorithmic_bytes_per_cell(P) - 16.0) if whole else (36.0 + 12.0 * P + 120.0)
+        fused_gbs = fused_bpc * cells / (launch_ms * 1e-3) / 1e9
+        roofline = {"kernel": "chain_kernel<5, 10>: diffuse(u), diffuse(v), project, advect(u, v), project and the density step of "
+                              "one FluidSim::step as phases of ONE cooperative launch (everything after the noise)" if whole else
+                              "chain_kernel: diffuse + project / project as phases of one launch",
+                    "bound": "dependency chain of the exact-order sweeps (stagger between column blocks + step latency of the "
+                             "sweep pipeline); not HBM: see `frac`, and `ceilings` for issue slots / shared-memory wavefronts",
+                    "achieved": fused_gbs, "peak": peak, "unit": "GB/s", "frac": fused_gbs / peak,
+                    "moved_gbs": moved_bpc * cells / (launch_ms * 1e-3) / 1e9,
+                    "effective_gbs": eff_bpc * cells / (launch_ms * 1e-3) / 1e9,
+                    "effective_frac": eff_bpc * cells / (launch_ms * 1e-3) / 1e9 / peak,
+                    "traffic": None, "peak_source": peak_src, "launch_ms": launch_ms, "launches_timed": chain_n,
+                    "algorithmic_bytes_per_launch": fused_bpc * cells, "moved_bytes_per_launch": moved_bpc * cells,
+                    "sweep_cell_updates_per_sec": (2 * P + 10) * cells / (launch_ms * 1e-3),
+                    "note": "achieved / frac = SURVEY.md 8(d)'s fusion rule (fields read once, results written once: "
+                            f"{fused_bpc:g} B per cell per launch) / launch time.  moved_gbs = the bytes the phases really move "
+                            f"({moved_bpc:g} B per cell: every phase streams its fields through HBM once; `traffic` = ncu DRAM bytes "
+                            "of one launch).  effective_gbs / effective_frac = the same launch counted at the reference's pass "
+                            "structure (B(P) minus the noise pass), which fusion makes exceed the real traffic"}
+        key = f"{W}x{H}_p{P}_chain"
+        if isinstance(tr.get(key), dict):
+            t = tr[key]
+            roofline["traffic"] = t.get("dram_bytes")
+            clk = (clocks.get("sm_mhz") or 1965.0) * 1e6
+            sm_cycles = t.get("grid", 130) * clk * launch_ms * 1e-3          # on the SMs the launch occupies
+            roofline["ceilings"] = {"issue_slot_frac": t["inst_executed"] / (4.0 * sm_cycles),
+                                    "smem_wavefront_frac": t["smem_wavefronts"] / sm_cycles,
+                                    "source": "instruction and shared-memory wavefront counts of one launch (ncu, profiles/) / "
+                                              "(SMs used x SM clock x event-timed launch duration): neither is the bound"}
+    else:
+        gs_launch_ms = gs_ms / max(gs_n, 1)
+        launches_per_proj = max(1.0, gs_n / (2.0 * K))          # two projections per step
+        levels = P / launches_per_proj                            # sweeps fused into one launch
+        algo_bytes = 12.0 * levels * cells                        # reference pass structure: 12 B per cell per sweep
+        compulsory = 8.0 * cells if launches_per_proj <= 1.0 else (8.0 + 12.0 * (launches_per_proj - 1)) / launches_per_proj * cells
+        achieved = algo_bytes / (gs_launch_ms * 1e-3) / 1e9 if gs_launch_ms > 0 else 0.0
+        compulsory_gbs = compulsory / (gs_launch_ms * 1e-3) / 1e9 if gs_launch_ms > 0 else 0.0
+        fused_gbs = 12.0 * cells / (gs_launch_ms * 1e-3) / 1e9 if gs_launch_ms > 0 else 0.0   # 12 B per cell per fused launch
+        roofline = {"kernel": f"wf_kernel<S, GaussSeidel>: one launch fuses {levels:g} sweeps of a projection",
+                    "bound": "dependency chain of the exact-order sweeps / instruction issue and shared-memory bandwidth "
+                             "(not HBM: see `frac`)",
+                    "achieved": fused_gbs, "peak": peak, "unit": "GB/s", "frac": fused_gbs / peak,
+                    "compulsory_gbs": compulsory_gbs, "effective_gbs": achieved, "effective_frac": achieved / peak,
+                    "traffic": None, "peak_source": peak_src, "launch_ms": gs_launch_ms, "launches_timed": gs_n,
+                    "algorithmic_bytes_per_launch": algo_bytes,
+                    "sweep_cell_updates_per_sec": levels * cells / (gs_launch_ms * 1e-3) if gs_launch_ms > 0 else 0.0,
+                    "compulsory_bytes_per_launch": compulsory,
+                    "note": "achieved / frac = SURVEY.md 8(d)'s fusion rule, 12 B per cell per fused launch, / launch time (the launch "
+                            "really moves the compulsory 8 B per cell: `compulsory_gbs`): the kernel is nowhere near HBM, it is bound "
+                            "by the dependency chain of the exact-order sweeps.  effective_gbs / effective_frac = the same launch counted "
+                            "at the reference's pass structure (12 B per cell per SWEEP), which fusion makes exceed the real "
+                            "traffic; `traffic` = ncu DRAM bytes per launch (profiles/)"}
+        key = f"{W}x{H}_p{P}_gs"
+        if key in tr and not isinstance(tr[key], dict):
+            roofline["traffic"] = tr[key]
     Bp = algorithmic_bytes_per_cell(P)
     step_gbs = Bp * cells / (ms_per_step * 1e-3) / 1e9
     step_roofline = {"bytes_per_cell": Bp, "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak}
     shares = {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items()}
     # per kernel class: effective GB/s at SURVEY.md 8(d)'s algorithmic bytes per cell and launch
     per_launch_bytes = {"noise": 16.0, "divergence": 16.0, "gradient": 20.0, "advect_velocity": 16.0, "advect_scalar": 16.0,
-                        "sor": 12.0 * 5 * 2, "gs": 12.0 * levels}
+                        "sor": 12.0 * 5 * 2, "gs": 12.0 * levels, "chain": algorithmic_bytes_per_cell(P) - 16.0}
     for k, bpc in per_launch_bytes.items():
         if k in shares and prof[k][1] > 0 and prof[k][0] > 0:
             gbs = bpc * cells / (prof[k][0] / prof[k][1] * 1e-3) / 1e9

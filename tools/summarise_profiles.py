@@ -5,6 +5,7 @@ usage: python tools/summarise_profiles.py <tag>          (tag = r01, r02, ... ; 
   gpurun_out/prof_<s>_wf.ncu-rep   -> profiles/<tag>_wf_kernel_ncu_metrics.json (selected raw metrics per launch),
                                       profiles/<tag>_wf_kernel_ncu_details.csv (--page details),
                                       profiles/<tag>_wf_kernel_stalls.json (warp-stall samples of the step loop)
+  gpurun_out/prof_<s>_chain.ncu-rep-> the same three files for the chained launch (profiles/<tag>_chain_kernel_*)
   gpurun_out/bench_<s>.json        -> profiles/<tag>_bench.json
 """
 import csv
@@ -60,7 +61,11 @@ def main():
     if os.path.exists(l):
         shutil.copy(l, os.path.join(OUT, f"{tag}_launches.csv"))
         launch_table(l)
+    kname = "wf_kernel"
     rep = os.path.join(SRC, f"prof_{suffix}_wf.ncu-rep")
+    if not os.path.exists(rep):
+        kname = "chain_kernel"
+        rep = os.path.join(SRC, f"prof_{suffix}_chain.ncu-rep")
     if not os.path.exists(rep):
         return
     raw = ncu(["-i", rep, "--page", "raw", "--csv"])
@@ -74,8 +79,8 @@ def main():
                 rec[m] = r[hdr.index(m)]
                 rec.setdefault("units", {})[m] = units[hdr.index(m)]
         out.append(rec)
-    json.dump(out, open(os.path.join(OUT, f"{tag}_wf_kernel_ncu_metrics.json"), "w"), indent=1)
-    open(os.path.join(OUT, f"{tag}_wf_kernel_ncu_details.csv"), "w").write(ncu(["-i", rep, "--page", "details", "--csv"]))
+    json.dump(out, open(os.path.join(OUT, f"{tag}_{kname}_ncu_metrics.json"), "w"), indent=1)
+    open(os.path.join(OUT, f"{tag}_{kname}_ncu_details.csv"), "w").write(ncu(["-i", rep, "--page", "details", "--csv"]))
     # warp-stall samples inside the step loop of the Gauss-Seidel launch (instructions executed once per step pair)
     src = ncu(["-i", rep, "--page", "source", "--csv", "--print-source", "sass"])
     blocks = src.split('"Kernel Name",')
@@ -91,16 +96,18 @@ def main():
         # the step bodies: the most common large execution count
         from collections import Counter
         cnt = Counter(e for e in execs if e > 1000)
-        cand = [(n * e, e) for e, n in cnt.items() if n >= 100]      # the fast step loop: most dynamic instructions
+        cand = sorted(((n * e, e) for e, n in cnt.items() if n >= 100), reverse=True)   # loops by dynamic instructions
         if not cand:
             continue
-        e0 = max(cand)[1]
-        sel = [r for r in rr if int(r[ix["Instructions Executed"]]) == e0]
-        tot = sum(int(r[ix["# Samples"]]) for r in sel) or 1
-        st = {n: sum(int(r[ix[n]] or 0) for r in sel) for n in names}
-        stalls_out.append({"kernel": lines[0].strip('",'), "loop_instructions": len(sel), "executions_each": e0,
-                           "samples": tot, "stall_share": {k: round(v / tot, 4) for k, v in sorted(st.items(), key=lambda kv: -kv[1]) if v}})
-    json.dump(stalls_out, open(os.path.join(OUT, f"{tag}_wf_kernel_stalls.json"), "w"), indent=1)
+        allsamples = sum(int(r[ix["# Samples"]] or 0) for r in rr) or 1
+        for _, e0 in cand[:3]:                                        # the step loops of the sweep phases come first
+            sel = [r for r in rr if int(r[ix["Instructions Executed"]]) == e0]
+            tot = sum(int(r[ix["# Samples"]]) for r in sel) or 1
+            st = {n: sum(int(r[ix[n]] or 0) for r in sel) for n in names}
+            stalls_out.append({"kernel": lines[0].strip('",'), "loop_instructions": len(sel), "executions_each": e0,
+                               "samples": tot, "share_of_all_samples": round(tot / allsamples, 4),
+                               "stall_share": {k: round(v / tot, 4) for k, v in sorted(st.items(), key=lambda kv: -kv[1]) if v}})
+    json.dump(stalls_out, open(os.path.join(OUT, f"{tag}_{kname}_stalls.json"), "w"), indent=1)
 
 
 if __name__ == "__main__":
