@@ -69,12 +69,13 @@ struct ChainPhase {
 
 struct ChainParams {
     int W, H, nphases;
+    int smem_floats;                // dynamic shared memory of the launch, in floats
     unsigned epoch;                 // number of this launch (done[] words hold the epoch of their last completion)
     unsigned *done;                 // [kChainMaxPhases][kChainMaxItems]
     unsigned long long *err;        // watchdog report: (phase << 32 | item) + 1 of the first wait that timed out
     unsigned long long timeout_ns;
     unsigned long long *trace;      // [kChainMaxPhases][kChainMaxItems][3] global-timer ns: wait begins, work begins, work ends
-    float *vmax;                    // [kChainMaxPhases][kChainMaxItems] max |v| of a block after its gradient phase
+    float *vmax;                    // [2][kChainMaxPhases][kChainMaxItems] max |v|, max |u| of a block after its gradient phase
     ChainPhase ph[kChainMaxPhases];
     WfKernelParams wf[kChainMaxSweeps];
 };
@@ -250,10 +251,11 @@ __device__ __forceinline__ void chain_divergence(const ChainPhase &ph, const int
 // ---- pressure gradient (src/fluid_sim.cpp:334-341) on the columns [c0, c0 + 64), then setBoundary(1, u) and
 // setBoundary(2, v) (:342-343) for those columns.  Pressure walls are read as setBoundary(0, p) defines them
 // (p[0][j] = p[1][j], p[i][0] = p[i][1], ...), so the pressure array's own wall cells are never touched.
-__device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W, const int H, const int cl, float *vmax_out)
+__device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W, const int H, const int cl, float *vmax_out,
+                                               float *umax_out)
 {
-    __shared__ float s_vmax[kChainThreads / 32];
-    float vmax = 0.0f;
+    __shared__ float s_vmax[kChainThreads / 32], s_umax[kChainThreads / 32];
+    float vmax = 0.0f, umax = 0.0f;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const int c0 = cl * kChainCols;
     float *u = ph.u, *v = ph.v;
@@ -311,15 +313,19 @@ __device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W
                 // u -= (0.5f*(p[i+1][j] - p[i-1][j])) / h ; v -= (0.5f*(p[i][j+1] - p[i][j-1])) / h
                 if (ina) {
                     const float nv = __fsub_rn(va[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(ra, la)), h));
-                    u[row + ja] = __fsub_rn(ua[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(npa, pma)), h));
+                    const float nu = __fsub_rn(ua[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(npa, pma)), h));
+                    u[row + ja] = nu;
                     v[row + ja] = nv;
                     vmax = fmaxf(vmax, fabsf(nv));
+                    umax = fmaxf(umax, fabsf(nu));
                 }
                 if (inb) {
                     const float nv = __fsub_rn(vb[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(rb, lb)), h));
-                    u[row + jb] = __fsub_rn(ub[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(npb, pmb)), h));
+                    const float nu = __fsub_rn(ub[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(npb, pmb)), h));
+                    u[row + jb] = nu;
                     v[row + jb] = nv;
                     vmax = fmaxf(vmax, fabsf(nv));
+                    umax = fmaxf(umax, fabsf(nu));
                 }
                 pma = pca; pmb = pcb;
                 pca = npa; pcb = npb;
@@ -329,13 +335,23 @@ __device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W
     }
     // largest |v| of the block (walls repeat interior magnitudes): bounds how many columns an advection trace that
     // starts in or passes through this block can move
-    for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
-    if (lane == 0) s_vmax[w] = vmax;
+    for (int o = 16; o > 0; o >>= 1) {
+        vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+        umax = fmaxf(umax, __shfl_xor_sync(0xffffffffu, umax, o));
+    }
+    if (lane == 0) {
+        s_vmax[w] = vmax;
+        s_umax[w] = umax;
+    }
     __syncthreads();   // every interior cell of the block carries its new velocity
     if (threadIdx.x == 0) {
-        float m = 0.0f;
-        for (int k = 0; k < nw; ++k) m = fmaxf(m, s_vmax[k]);
+        float m = 0.0f, mu = 0.0f;
+        for (int k = 0; k < nw; ++k) {
+            m = fmaxf(m, s_vmax[k]);
+            mu = fmaxf(mu, s_umax[k]);
+        }
         *vmax_out = m;
+        *umax_out = mu;     // bounds the rows a trace can move: sizes the shared-memory tiles of the advection phase
     }
     chain_boundary(u, 1, 0, W, H, c0);    // setBoundary(1, u), :342
     chain_boundary(v, 2, 0, W, H, c0);    // setBoundary(2, v), :343
@@ -351,9 +367,9 @@ __device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W
 // until that fits inside those blocks (one block for the 4-cell displacement of the bench input, the whole grid
 // in the worst case).
 __device__ __forceinline__ void chain_advect_wait(const ChainParams &C, const ChainPhase &ph, const int p, const int b,
-                                                  const float dt0)
+                                                  const float dt0, int *reach_rows, int *reach_cols)
 {
-    __shared__ int s_k;
+    __shared__ int s_k, s_ri, s_rj;
     const ChainPhase &g = C.ph[ph.reach_phase];
     const unsigned *flags = C.done + (size_t)ph.reach_phase * kChainMaxItems;
     const float *vm = C.vmax + (size_t)ph.reach_phase * kChainMaxItems;
@@ -368,19 +384,171 @@ __device__ __forceinline__ void chain_advect_wait(const ChainParams &C, const Ch
         waited_lo = lo;
         waited_hi = hi;
         if (threadIdx.x == 0) {
-            float m = 0.0f;
-            for (int x = lo; x <= hi; ++x) m = fmaxf(m, __ldcg(vm + x));
-            const float r = dt0 * m;
+            float m = 0.0f, mu = 0.0f;
+            for (int x = lo; x <= hi; ++x) {
+                m = fmaxf(m, __ldcg(vm + x));
+                mu = fmaxf(mu, __ldcg(vm + (size_t)kChainMaxPhases * kChainMaxItems + x));
+            }
+            const float r = dt0 * m, ru = dt0 * mu;
             int need = nb;                                      // non-finite velocities: wait for everything
             if (r < 1.0e8f) need = ((int)ceilf(r) + 2 + kChainCols - 1) / kChainCols;
             s_k = max(need, 1);
+            s_rj = (r < 1.0e8f) ? (int)ceilf(r) + 2 : (1 << 30);
+            s_ri = (ru < 1.0e8f) ? (int)ceilf(ru) + 2 : (1 << 30);
         }
         __syncthreads();
         const int need = s_k;
+        *reach_rows = s_ri;
+        *reach_cols = s_rj;
         __syncthreads();
         if (need <= k || (lo == 0 && hi == nb - 1)) break;
         k = need;
     }
+}
+
+// ---- the same advection with the fields staged in shared memory -----------------------------------------------------
+// A CTA is alone on its SM and nearly all of the SM's memory is shared memory (the sweep phases need it), so the L1
+// that would serve the 36 taps of a cell is tiny and the plain version waits on L2 for most of them (57 % of its
+// stall samples are long-scoreboard).  When the traces of the block stay within `ri` rows and `rj` columns (from the
+// per-block velocity maxima, see chain_advect_wait), the rows a stage of 40 output rows can reach are copied into shared
+// memory with cp.async (double buffered) and every tap is a shared-memory load.  Same taps, same arithmetic.
+constexpr int kAdvRows = 40;
+
+template <bool PZ>
+__device__ __forceinline__ float sample_tile(const float *T, const Taps &t, const int row0, const int cb, const int TC,
+                                             const int W, const int H)
+{
+    const float *r0 = T + (t.i0 - row0) * TC + (t.j0 - cb);
+    float f00 = r0[0], f01 = r0[1], f10 = r0[TC], f11 = r0[TC + 1];
+    if (PZ) {   // density only: interior cells are read as d + 0.0f (diffuse with a == 0, src/fluid_sim.cpp:56-57)
+        const bool i0in = t.i0 >= 1 && t.i0 <= W - 2, i1in = t.i0 + 1 >= 1 && t.i0 + 1 <= W - 2;
+        const bool j0in = t.j0 >= 1 && t.j0 <= H - 2, j1in = t.j0 + 1 >= 1 && t.j0 + 1 <= H - 2;
+        if (i0in && j0in) f00 = __fadd_rn(f00, 0.0f);
+        if (i0in && j1in) f01 = __fadd_rn(f01, 0.0f);
+        if (i1in && j0in) f10 = __fadd_rn(f10, 0.0f);
+        if (i1in && j1in) f11 = __fadd_rn(f11, 0.0f);
+    }
+    const float a = __fadd_rn(__fmul_rn(t.t0, f00), __fmul_rn(t.t1, f01));
+    const float b = __fadd_rn(__fmul_rn(t.t0, f10), __fmul_rn(t.t1, f11));
+    return __fadd_rn(__fmul_rn(t.s0, a), __fmul_rn(t.s1, b));
+}
+
+// returns false (nothing done) when the tiles for this reach do not fit the shared memory of the launch
+template <bool TWO, bool PZ>
+__device__ __forceinline__ bool chain_advect_tiled(const ChainPhase &ph, const int W, const int H, const int cl, float *smem,
+                                                   const int smem_floats, const int ri, const int rj)
+{
+    constexpr int NARR = TWO ? 2 : 3;            // velocity: u, v are sources as well; density: u, v and the density
+    if ((H & 3) != 0 || ri > 64 || rj > 60) return false;
+    const int halo_c = (rj + 1 + 3) & ~3;        // columns staged on each side (taps j0, j0 + 1), 16-byte aligned
+    const int halo_r = ri + 1;
+    const int TC = kChainCols + 2 * halo_c, TR = kAdvRows + 2 * halo_r;
+    const int stage_floats = NARR * TR * TC;
+    if (2 * stage_floats > smem_floats) return false;
+    const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, w = tid >> 5;
+    const int c0 = cl * kChainCols, cb = c0 - halo_c;
+    const float *arr[3] = {ph.u, ph.v, ph.src_a};
+    float *dst_a = ph.dst_a, *dst_b = ph.dst_b;
+    const float ndt0 = ph.c0;
+    const float xm = (float)W - 1.5f, ym = (float)H - 1.5f;
+    const int nq = TC >> 2;                      // 16-byte pieces per tile row
+    const int my_q = tid % nq, my_r = tid / nq, r_step = nt / nq;
+    const int nstages = (W - 2 + kAdvRows - 1) / kAdvRows;
+    auto issue = [&](int k) {
+        if (k < nstages && my_r < r_step) {
+            float *slot = smem + (k & 1) * stage_floats;
+            const int row_lo = 1 + k * kAdvRows - halo_r;
+            const int col = cb + 4 * my_q;
+            if (col >= 0 && col < H) {
+#pragma unroll
+                for (int a = 0; a < NARR; ++a)
+                    for (int r = my_r; r < TR; r += r_step) {
+                        const int row = row_lo + r;
+                        if (row < 0 || row > W - 1) continue;
+                        cp_async_f32x4(slot + (a * TR + r) * TC + 4 * my_q, arr[a] + (size_t)row * H + col, true);
+                    }
+            }
+        }
+        cp_async_commit();
+    };
+    issue(0);
+    for (int k = 0; k < nstages; ++k) {
+        issue(k + 1);                            // the other buffer: consumed in iteration k - 1 (barrier at its end)
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        __syncthreads();                         // stage k has landed for every thread
+        const float *slot = smem + (k & 1) * stage_floats;
+        const float *Tu = slot, *Tv = slot + TR * TC, *Ts = slot + 2 * TR * TC;
+        const int row0 = 1 + k * kAdvRows - halo_r;
+        constexpr int N = 4;                     // independent traces per thread: two columns x two rows
+#pragma unroll 1
+        for (int it = 0; it < 2; ++it) {
+            int ci[N], cj[N];
+            bool ok[N];
+            float x[N], y[N], k1x[N], k1y[N], k2x[N], k2y[N], k3x[N], k3y[N], k4x[N], k4y[N];
+            Taps t[N];
+#pragma unroll
+            for (int n = 0; n < N; ++n) {
+                const int r = 4 * w + 2 * it + (n >> 1);
+                ci[n] = 1 + k * kAdvRows + r;
+                cj[n] = c0 + 32 * (n & 1) + lane;
+                ok[n] = r < kAdvRows && ci[n] <= W - 2 && cj[n] >= 1 && cj[n] <= H - 2;
+                // cells outside the interior trace from the first cell of the stage's block (inside the tile), store nothing
+                x[n] = ok[n] ? (float)ci[n] : (float)(1 + k * kAdvRows);
+                y[n] = ok[n] ? (float)cj[n] : (float)max(c0, 1);
+                t[n] = make_taps(x[n], y[n], xm, ym);
+            }
+#pragma unroll
+            for (int n = 0; n < N; ++n) {
+                k1x[n] = __fmul_rn(sample_tile<false>(Tu, t[n], row0, cb, TC, W, H), ndt0);
+                k1y[n] = __fmul_rn(sample_tile<false>(Tv, t[n], row0, cb, TC, W, H), ndt0);
+            }
+#pragma unroll
+            for (int n = 0; n < N; ++n)
+                t[n] = make_taps(__fadd_rn(x[n], __fmul_rn(k1x[n], 0.5f)), __fadd_rn(y[n], __fmul_rn(k1y[n], 0.5f)), xm, ym);
+#pragma unroll
+            for (int n = 0; n < N; ++n) {
+                k2x[n] = __fmul_rn(sample_tile<false>(Tu, t[n], row0, cb, TC, W, H), ndt0);
+                k2y[n] = __fmul_rn(sample_tile<false>(Tv, t[n], row0, cb, TC, W, H), ndt0);
+            }
+#pragma unroll
+            for (int n = 0; n < N; ++n)
+                t[n] = make_taps(__fadd_rn(x[n], __fmul_rn(k2x[n], 0.5f)), __fadd_rn(y[n], __fmul_rn(k2y[n], 0.5f)), xm, ym);
+#pragma unroll
+            for (int n = 0; n < N; ++n) {
+                k3x[n] = __fmul_rn(sample_tile<false>(Tu, t[n], row0, cb, TC, W, H), ndt0);
+                k3y[n] = __fmul_rn(sample_tile<false>(Tv, t[n], row0, cb, TC, W, H), ndt0);
+            }
+#pragma unroll
+            for (int n = 0; n < N; ++n) t[n] = make_taps(__fadd_rn(x[n], k3x[n]), __fadd_rn(y[n], k3y[n]), xm, ym);
+#pragma unroll
+            for (int n = 0; n < N; ++n) {
+                k4x[n] = __fmul_rn(sample_tile<false>(Tu, t[n], row0, cb, TC, W, H), ndt0);
+                k4y[n] = __fmul_rn(sample_tile<false>(Tv, t[n], row0, cb, TC, W, H), ndt0);
+            }
+#pragma unroll
+            for (int n = 0; n < N; ++n) {
+                const float dx = __fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(k1x[n], __fmul_rn(2.0f, k2x[n])), __fmul_rn(2.0f, k3x[n])), k4x[n]), 6.0f);
+                const float dy = __fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(k1y[n], __fmul_rn(2.0f, k2y[n])), __fmul_rn(2.0f, k3y[n])), k4y[n]), 6.0f);
+                t[n] = make_taps(__fadd_rn(x[n], dx), __fadd_rn(y[n], dy), xm, ym);
+            }
+#pragma unroll
+            for (int n = 0; n < N; ++n) {
+                const float ra = sample_tile<PZ>(TWO ? Tu : Ts, t[n], row0, cb, TC, W, H);
+                const float rb = TWO ? sample_tile<false>(Tv, t[n], row0, cb, TC, W, H) : 0.0f;
+                if (ok[n]) {
+                    const size_t c = (size_t)ci[n] * H + cj[n];
+                    dst_a[c] = ra;
+                    if (TWO) dst_b[c] = rb;
+                }
+            }
+        }
+        __syncthreads();                         // stage k is consumed: its buffer may be refilled
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    chain_boundary(dst_a, ph.ba, 0, W, H, c0);
+    if (TWO) chain_boundary(dst_b, ph.bb, 0, W, H, c0);
+    return true;
 }
 
 template <bool TWO, bool PZ>
@@ -473,7 +641,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
             unsigned long long *tr = C.trace + ((size_t)p * kChainMaxItems + item) * 3;
             if (threadIdx.x == 0) tr[0] = global_timer_ns();
             chain_wait(C, p, cl);
-            if (ph.kind == kPhAdvect) chain_advect_wait(C, ph, p, cl, -ph.c0);
+            int reach_rows = 1 << 30, reach_cols = 1 << 30;
+            if (ph.kind == kPhAdvect) chain_advect_wait(C, ph, p, cl, -ph.c0, &reach_rows, &reach_cols);
             if (threadIdx.x == 0) tr[1] = global_timer_ns();
             if (ph.kind == kPhSor) {
                 if constexpr (SD > 0) wf_pass<SD, kSor, true>(C.wf[ph.wf], cl, fi, smem);
@@ -482,11 +651,19 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
             } else if (ph.kind == kPhDiv) {
                 chain_divergence(ph, C.W, C.H, cl);
             } else if (ph.kind == kPhGrad) {
-                chain_gradient(ph, C.W, C.H, cl, C.vmax + (size_t)p * kChainMaxItems + item);
+                chain_gradient(ph, C.W, C.H, cl, C.vmax + (size_t)p * kChainMaxItems + item,
+                               C.vmax + (size_t)(kChainMaxPhases + p) * kChainMaxItems + item);
             } else if (ph.kind == kPhAdvect) {
-                if (ph.dst_b) chain_advect<true, false>(ph, C.W, C.H, cl);
-                else if (ph.pz) chain_advect<false, true>(ph, C.W, C.H, cl);
-                else chain_advect<false, false>(ph, C.W, C.H, cl);
+                if (ph.dst_b) {
+                    if (!chain_advect_tiled<true, false>(ph, C.W, C.H, cl, smem, C.smem_floats, reach_rows, reach_cols))
+                        chain_advect<true, false>(ph, C.W, C.H, cl);
+                } else if (ph.pz) {
+                    if (!chain_advect_tiled<false, true>(ph, C.W, C.H, cl, smem, C.smem_floats, reach_rows, reach_cols))
+                        chain_advect<false, true>(ph, C.W, C.H, cl);
+                } else {
+                    if (!chain_advect_tiled<false, false>(ph, C.W, C.H, cl, smem, C.smem_floats, reach_rows, reach_cols))
+                        chain_advect<false, false>(ph, C.W, C.H, cl);
+                }
             }
             __syncthreads();   // the item's results are written, its shared memory is free
             if (threadIdx.x == 0) {
@@ -555,7 +732,8 @@ ChainPlan make_plan(int W, int H, int D, int P)
     size_t smem_gs = 0, smem_sor = 0;
     if (!chain_pick<kChainSP>(H, P / kChainSP, 1, nsm, &pl.gs_nstr, &pl.gs_ncta, &smem_gs)) return pl;
     if (D > 0 && !chain_pick<kChainSD>(H, D / kChainSD, 2, nsm, &pl.sor_nstr, &pl.sor_ncta, &smem_sor)) return pl;
-    pl.smem = std::max(smem_gs, smem_sor);
+    // the advection phases stage their fields in the same shared memory: give them room on small grids too
+    pl.smem = std::max(std::max(smem_gs, smem_sor), (size_t)160 * 1024);
     const int nblk = (H + kChainCols - 1) / kChainCols;
     pl.grid = std::max(std::max(pl.gs_ncta, 2 * pl.sor_ncta), std::min(nblk, nsm));
     if (pl.grid > nsm || nblk > kChainMaxItems || pl.grid > kChainMaxItems) return pl;
@@ -598,7 +776,7 @@ void fill_wf(WfKernelParams &P, int W, int H, int nstr, int nstg, int ncta, floa
 }
 
 constexpr size_t kDoneBytes = (size_t)kChainMaxPhases * kChainMaxItems * sizeof(unsigned);
-constexpr size_t kVmaxBytes = (size_t)kChainMaxPhases * kChainMaxItems * sizeof(float);
+constexpr size_t kVmaxBytes = (size_t)2 * kChainMaxPhases * kChainMaxItems * sizeof(float);   // max |v|, then max |u|
 constexpr size_t kTraceOne = (size_t)kChainMaxPhases * kChainMaxItems * 3 * sizeof(unsigned long long);
 
 }  // namespace
@@ -679,6 +857,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     ChainParams C{};
     C.W = A.W;
     C.H = A.H;
+    C.smem_floats = (int)(pl.smem / sizeof(float));
     C.epoch = ++cs->epoch;
     C.done = done;
     C.err = err;
