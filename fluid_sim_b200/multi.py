@@ -162,8 +162,10 @@ class BlockFluidSim:
         self.reach = self.max_reach if reach is None else reach
         self._overshoot = torch.zeros((), dtype=torch.float32, device=self.device)
         self._need = torch.zeros((), dtype=torch.float32, device=self.device)      # columns the last traces needed
-        self._need_host = torch.zeros((), dtype=torch.float32).pin_memory()
-        self._need_event = None
+        self._need_hosts = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(4)]
+        self._pending = []      # (event, pinned host scalar, width used) of the steps whose all-reduced need is not read yet
+        self._known_need = None
+        self._step_no = 0
         self._side = torch.cuda.Stream(device=self.device)
         vp = C.c_void_p()
         self._check(self._lib.fsb_blk_vmax_word(self._h, C.byref(vp)))
@@ -287,31 +289,39 @@ class BlockFluidSim:
 
     def _publish_need(self):
         """End of a step: all-reduce (max) the widest window any rank's traces needed and bring it to the host, on a
-        side stream, so that the next step can size its exchanges without waiting for anything."""
+        side stream.  The result is read two steps later (_choose_reach), so the host never waits for the GPU."""
         ready = torch.cuda.Event()
         ready.record(self.stream)
         self._side.wait_event(ready)
+        host = self._need_hosts[self._step_no % len(self._need_hosts)]
         with torch.cuda.stream(self._side):
             t = self._need.clone()
             dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
-            self._need_host.copy_(t, non_blocking=True)
-            self._need_event = torch.cuda.Event()
-            self._need_event.record(self._side)
+            host.copy_(t, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._side)
+        self._pending.append((ev, host, self._used))
         self._need = torch.zeros((), dtype=torch.float32, device=self.device)
+        self._step_no += 1
 
     def _choose_reach(self):
-        """Exchange width of this step: 1.5 x what the previous step needed + 4 columns, within [8, max_reach] and a
-        multiple of 4; the full width before anything is known."""
-        if self._need_event is None:
-            return self.max_reach if self.fixed_reach is None else self.fixed_reach
-        self._need_event.synchronize()                       # recorded a whole step ago: no wait in practice
-        needed = float(self._need_host.item())
-        if needed > self._used > 0:
-            raise FsbError(f"BlockFluidSim: the last step's traces needed {int(needed)} columns, {self._used} were "
-                           "exchanged; its results are invalid (raise `halo`, fix `reach`, or lower dt)")
+        """Exchange width of this step, the same number on every rank: 2 x what the step before the previous one needed
+        + 4 columns (velocities change little in two steps; the device-side check catches the rest), within
+        [8, max_reach] and a multiple of 4; the full width until that is known.  Using the step before the previous
+        one keeps the host a full step ahead of the GPU."""
+        while len(self._pending) > 1:                        # everything but the previous step's record
+            ev, host, used = self._pending.pop(0)
+            ev.synchronize()                                 # recorded two steps ago: long finished
+            needed = float(host.item())
+            if needed > used > 0:
+                raise FsbError(f"BlockFluidSim: a step's traces needed {int(needed)} columns, {used} were exchanged; the "
+                               "results since then are invalid (raise `halo`, fix `reach`, or lower dt)")
+            self._known_need = needed
         if self.fixed_reach is not None:
             return self.fixed_reach
-        want = int(math.ceil(1.5 * needed + 4.0))
+        if self._known_need is None:
+            return self.max_reach
+        want = int(math.ceil(2.0 * self._known_need + 4.0))
         want = (max(want, 8) + 3) // 4 * 4
         return min(want, self.max_reach)
 
