@@ -117,6 +117,7 @@ ABI = [
     ("fsb_pressure_sweeps_noalloc", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     ("fsb_launch_count", C.c_int, [_SIM, C.POINTER(C.c_uint64)]),
     ("fsb_set_tuning", C.c_int, [_SIM, C.c_int, C.c_int, C.c_int]),
+    ("fsb_set_chain_level", C.c_int, [_SIM, C.c_int]),
     ("fsb_last_error", C.c_char_p, []),
     ("fsb_version", C.c_char_p, []),
 ]
@@ -145,7 +146,7 @@ class FluidSim:
 
     def __init__(self, width=200, height=200, proj_iters=20, diff_iters=5, viscosity=1e-4, diffusion=0.0,
                  omega=1.5, advect_scheme=ADVECT_RK4, noise="glibc", noise_seed=1, noise_pos=0, device=-1,
-                 strips_per_cta=0, sweeps_per_warp=0, max_stages=0, process_stream=False):
+                 strips_per_cta=0, sweeps_per_warp=0, max_stages=0, process_stream=False, chain=None):
         self._lib = load_library()
         p = Params()
         self._lib.fsb_default_params(C.byref(p))
@@ -160,6 +161,8 @@ class FluidSim:
         self._check(self._lib.fsb_create(C.byref(p), C.byref(self._h)))
         if strips_per_cta or sweeps_per_warp or max_stages:
             self._check(self._lib.fsb_set_tuning(self._h, strips_per_cta, sweeps_per_warp, max_stages))
+        if chain is not None:
+            self._check(self._lib.fsb_set_chain_level(self._h, chain))
 
     # -- plumbing ---------------------------------------------------------------------------
     def _check(self, rc):

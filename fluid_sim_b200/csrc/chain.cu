@@ -31,13 +31,14 @@ namespace fsb {
 namespace {
 
 constexpr int kChainThreads = 320;      // 8 compute warps + 2 transfer warps: the widest sweep pass
-constexpr int kChainMaxPhases = 12;
+constexpr int kChainMaxPhases = 24;
 constexpr int kChainMaxItems = 1024;    // items per phase the done[] array is sized for
 constexpr int kChainMaxDeps = 4;
-constexpr int kChainMaxSweeps = 3;      // sweep phases per launch
+constexpr int kChainMaxSweeps = 7;      // sweep phases per launch: diffusion + up to three passes per projection
+constexpr int kChainMaxGsPasses = 3;
 constexpr int kChainCols = 64;          // columns of a pointwise work item
 
-enum ChainKind { kPhSor = 1, kPhGs = 2, kPhDiv = 3, kPhGrad = 4, kPhAdvect = 5 };
+enum ChainKind { kPhSor = 1, kPhGs = 2, kPhDiv = 3, kPhGrad = 4, kPhAdvect = 5, kPhGsX0 = 6, kPhBndP = 7 };
 
 // "wait until phase `phase` has finished every item whose result columns meet [b0 - lo, b1 + hi]", where [b0, b1]
 // are the waiting item's own columns: the ones it reads (from_out = 0) or the ones it writes (from_out = 1).
@@ -79,7 +80,7 @@ struct ChainParams {
     ChainPhase ph[kChainMaxPhases];
     WfKernelParams wf[kChainMaxSweeps];
 };
-static_assert(sizeof(ChainParams) <= 4000, "kernel parameter space");
+static_assert(sizeof(ChainParams) <= 16000, "kernel parameter space (CUDA 12.1+: up to 32764 bytes)");
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p)
 {
@@ -161,8 +162,10 @@ __device__ __forceinline__ void chain_boundary(float *x, const int b, const int 
         x[(size_t)i * H + j] = (b == 1) ? -v : v;                  // :356-360
     }
     for (int side = 0; side < 2; ++side) {
+        // a wall column is written by the block that owns the interior column it mirrors (the CTA that has just
+        // written it), which need not be the block the wall column itself falls into
         const int j = side ? H - 1 : 0, jin = side ? H - 2 : 1;
-        if (j < c0 || j >= c0 + kChainCols) continue;
+        if (jin < c0 || jin >= c0 + kChainCols) continue;
         for (int i = 1 + tid; i <= W - 2; i += nt) {
             const float v = in(i, jin);
             x[(size_t)i * H + j] = (b == 2) ? -v : v;              // :350-354
@@ -648,6 +651,10 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
                 if constexpr (SD > 0) wf_pass<SD, kSor, true>(C.wf[ph.wf], cl, fi, smem);
             } else if (ph.kind == kPhGs) {
                 wf_pass<SP, kGaussSeidel, false>(C.wf[ph.wf], cl, fi, smem);
+            } else if (ph.kind == kPhGsX0) {
+                wf_pass<SP, kGaussSeidel, true>(C.wf[ph.wf], cl, fi, smem);     // a later pass of the same projection
+            } else if (ph.kind == kPhBndP) {
+                chain_boundary(ph.q, 0, 0, C.W, C.H, cl * kChainCols);           // setBoundary(0, p) between two passes (:330)
             } else if (ph.kind == kPhDiv) {
                 chain_divergence(ph, C.W, C.H, cl);
             } else if (ph.kind == kPhGrad) {
@@ -701,6 +708,7 @@ struct ChainPlan {
     bool ok = false;
     int W = 0, H = 0, D = 0, P = 0;
     int sor_nstr = 0, sor_ncta = 0, gs_nstr = 0, gs_ncta = 0, grid = 0;
+    int gs_npass = 0, gs_stages[kChainMaxGsPasses] = {0, 0, 0};   // passes of one projection (gs_ncta: of the widest pass)
     size_t smem = 0;
     size_t sor_ring_floats = 0, gs_ring_floats = 0;
 };
@@ -730,7 +738,32 @@ ChainPlan make_plan(int W, int H, int D, int P)
     if (cudaGetDevice(&dev) != cudaSuccess) return pl;
     if (cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return pl;
     size_t smem_gs = 0, smem_sor = 0;
-    if (!chain_pick<kChainSP>(H, P / kChainSP, 1, nsm, &pl.gs_nstr, &pl.gs_ncta, &smem_gs)) return pl;
+    {
+        // Passes of one projection: the fewest strips per CTA for which a pass fits the SMs (more SMs at work, fewer
+        // warps sharing one), as many chained warps per strip as the 8 compute warps and the shared memory allow, the
+        // P / 10 stages spread evenly over the passes.
+        using L = WfLayout<kChainSP>;
+        const int T = P / kChainSP;
+        bool found = false;
+        for (int nstr = 1; nstr <= 4 && !found; nstr *= 2) {
+            int maxst = std::min((kChainThreads / 32 - 2) / nstr, L::kMaxStagesS);
+            while (maxst >= 1 && wf_smem_bytes<kChainSP>(nstr, maxst) > 227 * 1024) --maxst;
+            if (maxst < 1) continue;
+            const int npass = (T + maxst - 1) / maxst;
+            if (npass > kChainMaxGsPasses) continue;
+            const int widest = (T + npass - 1) / npass;
+            const int NS = (H + kChainSP * widest + 31) / 32;
+            const int ncta = (NS + std::min(nstr, NS) - 1) / std::min(nstr, NS);
+            if (ncta > nsm || ncta > kWfMaxCtas) continue;
+            pl.gs_nstr = std::min(nstr, NS);
+            pl.gs_ncta = ncta;
+            pl.gs_npass = npass;
+            for (int k = 0; k < npass; ++k) pl.gs_stages[k] = T / npass + (k < T % npass ? 1 : 0);
+            smem_gs = wf_smem_bytes<kChainSP>(pl.gs_nstr, widest);
+            found = true;
+        }
+        if (!found) return pl;
+    }
     if (D > 0 && !chain_pick<kChainSD>(H, D / kChainSD, 2, nsm, &pl.sor_nstr, &pl.sor_ncta, &smem_sor)) return pl;
     // the advection phases stage their fields in the same shared memory: give them room on small grids too
     pl.smem = std::max(std::max(smem_gs, smem_sor), (size_t)160 * 1024);
@@ -748,7 +781,7 @@ ChainPlan make_plan(int W, int H, int D, int P)
         return pl;
     }
     if ((long long)per_sm * nsm < pl.grid) return pl;
-    pl.gs_ring_floats = (size_t)(P / kChainSP) * pl.gs_ncta * WfLayout<kChainSP>::kBoundaryFloats;
+    pl.gs_ring_floats = (size_t)pl.gs_stages[0] * pl.gs_ncta * WfLayout<kChainSP>::kBoundaryFloats;   // of the widest pass
     pl.sor_ring_floats = D > 0 ? (size_t)2 * (D / kChainSD) * pl.sor_ncta * WfLayout<kChainSD>::kBoundaryFloats : 0;
     pl.ok = true;
     return pl;
@@ -829,7 +862,8 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     const size_t flag_bytes = sweep_flag_words() * sizeof(unsigned long long);
     const size_t sor_rings = std::max(cs->plan[0].sor_ring_floats, pl.sor_ring_floats) * sizeof(float);
     const size_t gs_rings = std::max(std::max(cs->plan[0].gs_ring_floats, cs->plan[1].gs_ring_floats), pl.gs_ring_floats) * sizeof(float);
-    const size_t need = kDoneBytes + 256 + kVmaxBytes + 2 * kTraceOne + 3 * flag_bytes + sor_rings + 2 * gs_rings;
+    const size_t need = kDoneBytes + 256 + kVmaxBytes + 2 * kTraceOne + kChainMaxSweeps * flag_bytes + sor_rings +
+                        2 * kChainMaxGsPasses * gs_rings;
     if (need > cs->bytes) {
         e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) return e;
@@ -848,11 +882,12 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     float *vmax = reinterpret_cast<float *>(b + kDoneBytes + 256);
     unsigned long long *trace = reinterpret_cast<unsigned long long *>(b + kDoneBytes + 256 + kVmaxBytes + kind * kTraceOne);
     unsigned char *b2 = b + kDoneBytes + 256 + kVmaxBytes + 2 * kTraceOne;
-    unsigned long long *flags[3];
-    for (int k = 0; k < 3; ++k) flags[k] = reinterpret_cast<unsigned long long *>(b2 + k * flag_bytes);
-    float *rings_sor = reinterpret_cast<float *>(b2 + 3 * flag_bytes);
-    float *rings_gs[2] = {reinterpret_cast<float *>(b2 + 3 * flag_bytes + sor_rings),
-                          reinterpret_cast<float *>(b2 + 3 * flag_bytes + sor_rings + gs_rings)};
+    unsigned long long *flags[kChainMaxSweeps];
+    for (int k = 0; k < kChainMaxSweeps; ++k) flags[k] = reinterpret_cast<unsigned long long *>(b2 + k * flag_bytes);
+    float *rings_sor = reinterpret_cast<float *>(b2 + kChainMaxSweeps * flag_bytes);
+    float *rings_gs[2 * kChainMaxGsPasses];
+    for (int k = 0; k < 2 * kChainMaxGsPasses; ++k)
+        rings_gs[k] = reinterpret_cast<float *>(b2 + kChainMaxSweeps * flag_bytes + sor_rings + k * gs_rings);
 
     ChainParams C{};
     C.W = A.W;
@@ -890,21 +925,34 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             ph.c0 = -0.5f * h;                    // evaluated first (:311)
             if (after >= 0) ph.dep[ph.ndeps++] = ChainDep{after, 0, 1, 1};    // u, v of the block and one column either side
         }
-        const int ph_gs = np;
-        {
+        int ph_gs = -1, ph_prev = ph_div;
+        for (int k = 0; k < pl.gs_npass; ++k) {
+            if (k > 0) {
+                // setBoundary(0, p) after the previous pass's last sweep (:330): the next pass reads the walls of its
+                // first sweep from the array
+                ChainPhase &pb = pointwise_phase(kPhBndP);
+                pb.q = p;
+                pb.dep[pb.ndeps++] = ChainDep{ph_gs, 0, 0, 0};
+                ph_prev = np - 1;
+            }
+            const int ph_last = ph_gs;
+            ph_gs = np;
             ChainPhase &ph = C.ph[np++];
-            ph.kind = kPhGs;
-            ph.ncl = ph.nitems = pl.gs_ncta;
+            ph.kind = k == 0 ? kPhGs : kPhGsX0;
+            const int nstrips = (A.H + kChainSP * pl.gs_stages[k] + 31) / 32;     // the last stage's frame is shifted left by the pass's sweeps
+            const int ncta = (nstrips + pl.gs_nstr - 1) / pl.gs_nstr;
+            ph.ncl = ph.nitems = ncta;
             ph.nf = 1;
             ph.cpv = 32 * pl.gs_nstr;
-            ph.shift = A.gs_sweeps;
+            ph.shift = kChainSP * pl.gs_stages[k];
             ph.wf = nwf;
             ph.ndeps = 0;
-            ph.dep[ph.ndeps++] = ChainDep{ph_div, 0, 0, 0};                   // the divergence of the columns it loads
+            ph.dep[ph.ndeps++] = ChainDep{ph_prev, 0, 0, 0};                  // divergence (first pass) / walls of p (later passes) of the columns it loads
+            if (k > 0) ph.dep[ph.ndeps++] = ChainDep{ph_last, 1, 0, 0};       // the previous pass has produced the columns this one overwrites
             WfKernelParams &P = C.wf[nwf++];
-            fill_wf(P, A.W, A.H, pl.gs_nstr, A.gs_sweeps / kChainSP, pl.gs_ncta, 0.0f, 1.0f, 1.0f, rings_gs[gs_slot],
-                    flags[1 + gs_slot], ++scr.seq);
-            P.fld[0] = SweepField{nullptr, div, p, 1.0f, 1.0f};               // p starts at 0 (:313, :316)
+            const int slot = gs_slot * kChainMaxGsPasses + k;
+            fill_wf(P, A.W, A.H, pl.gs_nstr, pl.gs_stages[k], ncta, 0.0f, 1.0f, 1.0f, rings_gs[slot], flags[1 + slot], ++scr.seq);
+            P.fld[0] = SweepField{k == 0 ? nullptr : p, div, p, 1.0f, 1.0f};  // p starts at 0 (:313, :316)
             P.fld[1] = P.fld[2] = P.fld[0];
         }
         ChainPhase &ph = pointwise_phase(kPhGrad);
@@ -955,7 +1003,8 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             ph.c0 = -(A.dt * (float)A.W);              // -dt0, dt0 = dt * width (:264)
             ph.reach_phase = ph_grad1;
             ph.dep[ph.ndeps++] = ChainDep{ph_grad1, 1, 1, 1};                                // gradient blocks still reading p here
-            ph.dep[ph.ndeps++] = ChainDep{ph_gs1, 1, A.gs_sweeps, -A.gs_sweeps};           // sweep items that load div here
+            const int sh = C.ph[ph_gs1].shift;                                             // of the projection's last pass
+            ph.dep[ph.ndeps++] = ChainDep{ph_gs1, 1, sh, -sh};                             // sweep items that load div here
         }
         // the second projection works in scratch of its own: u, v stay intact for traces that start far away
         const float *dens = A.with_density ? A.d : nullptr;

@@ -513,6 +513,11 @@ int chained_launch(fsb_sim *s, bool with_diffuse, bool whole_step, float dt, boo
     *done = false;
     if (density_done) *density_done = false;
     if (s->chain_level < 1 || s->is_block || s->tune_strips || s->tune_levels || s->tune_stages) return FSB_OK;
+    // Measured (tools/chain_ab.py): the chained launch wins when the grid has enough 64-column blocks to spread its
+    // pointwise phases over the SMs and is not much taller than wide (1024 x 8192: 2.0x, 8192^2: 1.26x, 4096^2: 1.07x);
+    // narrow or tall grids (2048^2: 1.0x, 200^2: 0.92x, 16384 x 2048: 0.73x, 32768 x 4096: 0.86x) keep one launch per pass.
+    // FSB_CHAIN=3 forces the chained launch wherever a configuration exists.
+    if (s->chain_level < 3 && (s->H < 4096 || s->W > 2 * s->H)) return FSB_OK;
     if (whole_step && (s->chain_level < 2 || s->prm.advect_scheme != FSB_ADVECT_RK4)) return FSB_OK;
     ChainArgs A{};
     A.W = s->W;
@@ -751,9 +756,9 @@ static int create_common(const fsb_params *p, const GridView *block, fsb_sim **o
     }
     {
         // FSB_CHAIN = 0: every pass as its own launch, 1: diffuse + project / project as chained launches, 2 (default):
-        // the whole step after the noise as one chained launch (A/B timing, debugging)
+        // the whole step after the noise as one chained launch where that is faster, 3: wherever it is possible
         const char *e = std::getenv("FSB_CHAIN");
-        if (e && e[0] >= '0' && e[0] <= '2') s->chain_level = e[0] - '0';
+        if (e && e[0] >= '0' && e[0] <= '3') s->chain_level = e[0] - '0';
     }
     s->noise_step_jump = jump_matrix(2ull * (uint64_t)prm.width * (uint64_t)prm.height);
     set_noise_window(s, prm.noise_seed, prm.noise_pos);
@@ -1148,6 +1153,13 @@ int fsb_set_tuning(fsb_sim *s, int strips_per_cta, int sweeps_per_warp, int max_
     s->tune_levels = sweeps_per_warp;
     s->tune_stages = max_stages;
     s->plan_cache.clear();
+    return FSB_OK;
+}
+
+int fsb_set_chain_level(fsb_sim *s, int level)
+{
+    if (!s || level < 0 || level > 3) return fail(FSB_EINVAL, "fsb_set_chain_level: bad argument");
+    s->chain_level = level;
     return FSB_OK;
 }
 

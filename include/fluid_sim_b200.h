@@ -274,6 +274,11 @@ int fsb_launch_count(const fsb_sim *s, uint64_t *count);
 /* Tuning knobs of the relaxation pipeline, for experiments (0 = library default): column strips per
  * CTA, sweeps kept in flight per warp (1, 2, 5, 10 or 20), cap on warps chained per strip. */
 int fsb_set_tuning(fsb_sim *s, int strips_per_cta, int sweeps_per_warp, int max_stages);
+/* Tuning with no counterpart in the reference: how many passes of a step share one kernel launch.  0: every pass is its
+ * own launch; 1: diffuse + project (and the second project) as chained launches; 2 (default): the whole step after the
+ * noise as one chained launch on the grid shapes where that was measured faster; 3: wherever a chained configuration
+ * exists.  Results are bit-identical at every level.  The environment variable FSB_CHAIN sets the initial level. */
+int fsb_set_chain_level(fsb_sim *s, int level);
 
 const char *fsb_last_error(void);
 const char *fsb_version(void);

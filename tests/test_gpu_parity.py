@@ -152,13 +152,15 @@ def test_advect(w, h, scheme):
         assert_bits(gpu.read(fsb.PREV_DENSITY), ora.read(orasim.PREV_DENSITY), f"advect scheme={scheme} b={b}")
 
 
+@pytest.mark.parametrize("chain", [0, 1, 3])
 @pytest.mark.parametrize("name", ["config1_200x200_p20_d5", "small_48x40_p3_d2", "odd_257x131_p20_d5",
                                   "tall_131x257_p7_d3"])
-def test_step_against_reference_golden(name):
-    """Whole-step parity against fields produced by the unmodified reference (tests/golden)."""
+def test_step_against_reference_golden(name, chain):
+    """Whole-step parity against fields produced by the unmodified reference (tests/golden), with every pass as its own
+    launch (chain 0), diffuse + project chained (1) and the whole step as one chained launch wherever one exists (3)."""
     g = load_golden(name)
     w, h, p, d = int(g["w"]), int(g["h"]), int(g["p"]), int(g["d"])
-    gpu = fsb.FluidSim(w, h, p, d)
+    gpu = fsb.FluidSim(w, h, p, d, chain=chain)
     apply_golden_inputs(gpu, g)
     checkpoints = sorted(int(k[2:]) for k in g.files if k.startswith("d_"))
     step = 0
@@ -231,7 +233,7 @@ def test_random_configurations(seed):
     w, h = int(rng.integers(3, 140)), int(rng.integers(3, 400))
     p, d = int(rng.integers(0, 46)), int(rng.integers(0, 13))
     kw = dict(viscosity=float(rng.choice([0.0, 1e-4, 3e-3])), diffusion=float(rng.choice([0.0, 0.0, 2e-4])),
-              noise=str(rng.choice(["glibc", "zero"])), strips_per_cta=int(rng.choice([0, 1, 2, 4])))
+              noise=str(rng.choice(["glibc", "zero"])), strips_per_cta=int(rng.choice([0, 1, 2, 4])), chain=3)
     gpu, ora = make_pair(w, h, p, d, **kw)
     seed_state(gpu, ora, rng, w, h, scale=2.0)
     for k in range(2):
@@ -241,6 +243,30 @@ def test_random_configurations(seed):
         gpu.step(0.01); ora.step(0.01)
     for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
         assert_bits(a, b, f"{w}x{h} P={p} D={d} {kw}: field {n}")
+
+
+@pytest.mark.parametrize("w,h,p,d,steps", [(96, 200, 20, 5, 3), (64, 300, 100, 5, 2), (300, 1100, 40, 10, 2), (40, 257, 30, 5, 3),
+                                           (2048, 2048, 20, 5, 2), (37, 4100, 50, 5, 2)])
+@pytest.mark.parametrize("inject", ["lattice", "demo"])
+def test_whole_step_as_one_chained_launch(w, h, p, d, steps, inject):
+    """The whole step after the noise as ONE launch (chain level 3: also on shapes where the default keeps separate
+    launches): several passes per projection (P = 100, 50, 30), two SOR stages (D = 10), odd widths, a grid wide enough
+    for several CTAs per phase, and the reference's injection, whose |v| = 2 makes the back-traces leave their column
+    block (the advection phases then wait for more gradient blocks and take the global-memory path)."""
+    gpu, ora = make_pair(w, h, p, d, chain=3)
+    if inject == "demo":
+        for s in (gpu, ora):
+            demo_injection(s, w, h)
+    else:
+        dd, uu, vv = vortex_lattice(w, h)
+        for s, ids in ((gpu, (fsb.DENSITY, fsb.VELOCITY_X, fsb.VELOCITY_Y)), (ora, (0, 1, 2))):
+            s.write(ids[0], dd); s.write(ids[1], uu); s.write(ids[2], vv)
+    n0 = gpu.launch_count()
+    for _ in range(steps):
+        gpu.step(0.01); ora.step(0.01)
+    assert gpu.launch_count() - n0 <= 3 * steps            # noise (+ its zero-mode twin) + the chained launch
+    for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+        assert_bits(a, b, f"{w}x{h} P={p} D={d} {inject}: field {n}")
 
 
 def test_many_launches_ring_tags_wrap():
