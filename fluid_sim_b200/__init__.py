@@ -112,6 +112,11 @@ ABI = [
     ("fsb_blk_divergence", C.c_int, [_SIM]),
     ("fsb_blk_gradient", C.c_int, [_SIM]),
     ("fsb_blk_vmax_word", C.c_int, [_SIM, C.POINTER(C.c_void_p)]),
+    ("fsb_blk_chain_prepare", C.c_int, [_SIM, C.c_float]),
+    ("fsb_blk_chain_handles", C.c_int, [_SIM, C.c_void_p]),
+    ("fsb_blk_chain_connect", C.c_int, [_SIM, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ("fsb_blk_step", C.c_int, [_SIM, C.c_float]),
+    ("fsb_blk_chain_error", C.c_int, [_SIM, C.POINTER(C.c_uint64)]),
     ("fsb_blk_advect_velocity", C.c_int, [_SIM, C.c_float, C.c_int]),
     ("fsb_blk_advect_density", C.c_int, [_SIM, C.c_float, C.c_int]),
     ("fsb_pressure_sweeps_noalloc", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),

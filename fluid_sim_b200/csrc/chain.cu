@@ -44,10 +44,22 @@ enum ChainKind { kPhSor = 1, kPhGs = 2, kPhDiv = 3, kPhGrad = 4, kPhAdvect = 5, 
 // are the waiting item's own columns: the ones it reads (from_out = 0) or the ones it writes (from_out = 1).
 struct ChainDep { int phase, from_out, lo, hi; };
 
+// This rank's view of the grid (one GPU: the whole grid) and its neighbours in a multi-rank run.
+struct ChainGrid {
+    int W, H;                  // global grid
+    int pitch, jbase;          // local arrays: floats per row, global column of local column 0
+    int j0, j1;                // owned columns
+    int cw;                    // columns of a pointwise work item: 64, or 32 when the owned range has few blocks
+    int halo;                  // columns stored (and kept current by the neighbours' pushes) beyond the owned range
+    int has_left, has_right;
+    int jbase_l, jbase_r;      // the neighbours' jbase (same pitch everywhere)
+};
+
 struct ChainPhase {
     int kind;
-    int nitems;      // work items = ncl * nf
-    int ncl;         // column ranges
+    int item0;       // global index of this rank's first work item (items are numbered along the whole grid)
+    int nitems;      // this rank's work items
+    int ncl;         // column ranges of the whole grid (nitems of all ranks / nf)
     int nf;          // fields per column range (sweep passes over several fields: one item per field)
     int cpv;         // columns per range
     int shift;       // range c reads columns [c*cpv, (c+1)*cpv) and writes [c*cpv - shift, (c+1)*cpv - shift)
@@ -63,6 +75,10 @@ struct ChainPhase {
     const float *src_a, *src_b;
     float *bnd_extra;   // gradient: one more field whose boundaries (b = 0, interior read as v + 0.0f) are set here
     float c0;           // -0.5f * h (divergence) / h (gradient) / -dt0 (advection)
+    // multi-rank: the same fields in the neighbours' memory (peer mappings).  Blocks within push_cols columns of a rank
+    // boundary write their results there as well, so every rank reads only its own memory.
+    float *peer_l[3], *peer_r[3];   // gradient: u, v, bnd_extra; advection: dst_a, dst_b
+    int push_cols;
     int reach_phase;    // advection: the gradient phase that published u, v (its per-block max |v| bounds the trace)
     int ba, bb;         // advection: setBoundary's b of dst_a / dst_b
     int pz;             // advection: interior taps of src_a are read as (v + 0.0f) (diffuse with a == 0)
@@ -70,7 +86,15 @@ struct ChainPhase {
 
 struct ChainParams {
     int W, H, nphases;
+    ChainGrid g;
     int smem_floats;                // dynamic shared memory of the launch, in floats
+    // multi-rank: the neighbours' done[] / vmax[] arrays (items near a rank boundary publish there too), the words in
+    // which the neighbours announce the last step they have finished, and the words this rank announces its own in
+    unsigned *done_l, *done_r;
+    float *vmax_l, *vmax_r;
+    unsigned *step_in;              // [0]: written by the left neighbour, [1]: by the right one
+    unsigned *step_out_l, *step_out_r;
+    unsigned *cta_count;            // CTAs of this launch that have finished
     unsigned epoch;                 // number of this launch (done[] words hold the epoch of their last completion)
     unsigned *done;                 // [kChainMaxPhases][kChainMaxItems]
     unsigned long long *err;        // watchdog report: (phase << 32 | item) + 1 of the first wait that timed out
@@ -82,11 +106,19 @@ struct ChainParams {
 };
 static_assert(sizeof(ChainParams) <= 16000, "kernel parameter space (CUDA 12.1+: up to 32764 bytes)");
 
+// system scope on a multi-rank launch: the word may have been written by a neighbouring GPU through peer memory
+template <bool MR>
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p)
 {
     unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    if constexpr (MR) asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    else asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
+}
+
+__device__ __forceinline__ void st_release_sys_u32(unsigned *p, unsigned v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 __device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v)
@@ -103,12 +135,13 @@ __device__ __forceinline__ unsigned long long global_timer_ns()
 
 __device__ __forceinline__ int floor_div(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
 
-// Spins until done-word `f` carries this launch's epoch; traps if that takes longer than the watchdog allows.
-__device__ __forceinline__ void chain_poll(const ChainParams &C, const unsigned *f, const int p, const int cl,
+// Spins until word `f` has reached `want` (words only grow); traps if that takes longer than the watchdog allows.
+template <bool MR>
+__device__ __forceinline__ void chain_poll(const ChainParams &C, const unsigned *f, const unsigned want, const int p, const int cl,
                                            unsigned long long &t0)
 {
     unsigned spins = 0;
-    while ((int)(ld_acquire_u32(f) - C.epoch) < 0) {
+    while ((int)(ld_acquire_u32<MR>(f) - want) < 0) {
         __nanosleep(64);
         if ((++spins & 0x3ffu) == 0) {
             const unsigned long long now = global_timer_ns();
@@ -122,11 +155,19 @@ __device__ __forceinline__ void chain_poll(const ChainParams &C, const unsigned 
     }
 }
 
-// Blocks the CTA until the dependencies of item (phase p, column range cl) are met.  Thread d polls dependency d.
-__device__ __forceinline__ void chain_wait(const ChainParams &C, const int p, const int cl)
+// does the item with result columns [lo, hi] lie within `dist` columns of the boundary to the left / right rank?
+__device__ __forceinline__ bool near_left(const ChainGrid &g, int lo, int dist) { return g.has_left && lo < g.j0 + dist; }
+__device__ __forceinline__ bool near_right(const ChainGrid &g, int hi, int dist) { return g.has_right && hi >= g.j1 - dist; }
+
+// Blocks the CTA until the dependencies of item (phase p, column range cl, numbered along the whole grid) are met.
+// Thread d polls dependency d; `wait_l` / `wait_r`: the item is about to write into the left / right neighbour's
+// memory, which that rank may still be reading in its previous step: wait until it has announced the end of that step.
+template <bool MR>
+__device__ __forceinline__ void chain_wait(const ChainParams &C, const int p, const int cl, const bool wait_l, const bool wait_r)
 {
     const ChainPhase &ph = C.ph[p];
     const int d = threadIdx.x;
+    unsigned long long t0 = 0;
     if (d < ph.ndeps) {
         const ChainDep dep = ph.dep[d];
         const ChainPhase &q = C.ph[dep.phase];
@@ -136,90 +177,129 @@ __device__ __forceinline__ void chain_wait(const ChainParams &C, const int p, co
         a = max(a, 0);
         b = min(b, q.ncl - 1);
         const unsigned *flags = C.done + (size_t)dep.phase * kChainMaxItems;
-        unsigned long long t0 = 0;
-        for (int x = a * q.nf; x < (b + 1) * q.nf; ++x) chain_poll(C, flags + x, p, cl, t0);
+        for (int x = a * q.nf; x < (b + 1) * q.nf; ++x) chain_poll<MR>(C, flags + x, C.epoch, p, cl, t0);
+    } else if (d == 32 && wait_l) {
+        chain_poll<MR>(C, C.step_in + 0, C.epoch - 1, p, cl, t0);
+    } else if (d == 33 && wait_r) {
+        chain_poll<MR>(C, C.step_in + 1, C.epoch - 1, p, cl, t0);
     }
     __syncthreads();
 }
 
-// setBoundary(b, x) (src/fluid_sim.cpp:347-367) on the columns [c0, c0 + 64) of x, whose interior cells this CTA has
+// Where a pointwise item's results go besides this rank's arrays: the neighbours' halo copies of the same fields.
+struct ChainPush {
+    bool l, r;
+    long long off_l, off_r;     // add to a local element index to get the element index in the neighbour's array
+};
+__device__ __forceinline__ ChainPush make_push(const ChainGrid &g, const ChainPhase &ph, const int c0)
+{
+    ChainPush P;
+    P.l = ph.push_cols > 0 && near_left(g, c0, ph.push_cols);
+    P.r = ph.push_cols > 0 && near_right(g, c0 + g.cw - 1, ph.push_cols);
+    P.off_l = (long long)g.jbase - g.jbase_l;     // local column j - jbase  ->  j - jbase_l
+    P.off_r = (long long)g.jbase - g.jbase_r;
+    return P;
+}
+// MR: multi-rank launch (on one GPU the pushes are compiled out)
+template <bool MR>
+__device__ __forceinline__ void store_pushed(float *x, float *xl, float *xr, const ChainPush &P, const long long idx, const float v)
+{
+    x[idx] = v;
+    if constexpr (MR) {
+        if (P.l) xl[idx + P.off_l] = v;
+        if (P.r) xr[idx + P.off_r] = v;
+    }
+}
+
+#define CAT(g, i, j) ((long long)(i) * (g).pitch + ((j) - (g).jbase))
+
+// setBoundary(b, x) (src/fluid_sim.cpp:347-367) on the columns [c0, c0 + cw) of x, whose interior cells this CTA has
 // just written (the caller placed a CTA barrier after them).  Walls, then the corners the block contains, each
 // rebuilt from the interior so that no ordering between wall and corner threads is needed.  pz: interior values are
 // read as (v + 0.0f).
-__device__ __forceinline__ void chain_boundary(float *x, const int b, const int pz, const int W, const int H, const int c0)
+template <bool MR, int CW>
+__device__ __forceinline__ void chain_boundary(float *x, float *xl, float *xr, const ChainPush &P, const int b, const int pz,
+                                               const ChainGrid &g, const int c0)
 {
+    const int W = g.W, H = g.H;
+    constexpr int cw = CW;
     const int tid = threadIdx.x, nt = blockDim.x;
     const float si = (b == 1) ? -1.0f : 1.0f, sj = (b == 2) ? -1.0f : 1.0f;
     auto in = [&](int i, int j) {
-        const float v = __ldcg(x + (size_t)i * H + j);
+        const float v = __ldcg(x + CAT(g, i, j));
         return pz ? __fadd_rn(v, 0.0f) : v;
     };
-    for (int t = tid; t < 2 * kChainCols; t += nt) {
-        const int j = c0 + (t % kChainCols);
+    for (int t = tid; t < 2 * cw; t += nt) {
+        const int j = c0 + (t % cw);
         if (j < 1 || j > H - 2) continue;
-        const int i = (t < kChainCols) ? 0 : W - 1, iin = (t < kChainCols) ? 1 : W - 2;
+        const int i = (t < cw) ? 0 : W - 1, iin = (t < cw) ? 1 : W - 2;
         const float v = in(iin, j);
-        x[(size_t)i * H + j] = (b == 1) ? -v : v;                  // :356-360
+        store_pushed<MR>(x, xl, xr, P, CAT(g, i, j), (b == 1) ? -v : v);                  // :356-360
     }
     for (int side = 0; side < 2; ++side) {
         // a wall column is written by the block that owns the interior column it mirrors (the CTA that has just
         // written it), which need not be the block the wall column itself falls into
         const int j = side ? H - 1 : 0, jin = side ? H - 2 : 1;
-        if (jin < c0 || jin >= c0 + kChainCols) continue;
+        if (jin < c0 || jin >= c0 + cw) continue;
         for (int i = 1 + tid; i <= W - 2; i += nt) {
             const float v = in(i, jin);
-            x[(size_t)i * H + j] = (b == 2) ? -v : v;              // :350-354
+            store_pushed<MR>(x, xl, xr, P, CAT(g, i, j), (b == 2) ? -v : v);              // :350-354
         }
         if (tid < 2) {
             // corner = 0.5f * (x[iin][j] + x[i][jin]): a j-wall cell and an i-wall cell (:363-366)
             const int i = tid ? W - 1 : 0, iin = tid ? W - 2 : 1;
             const float v = in(iin, jin);
-            x[(size_t)i * H + j] = __fmul_rn(0.5f, __fadd_rn(__fmul_rn(sj, v), __fmul_rn(si, v)));
+            store_pushed<MR>(x, xl, xr, P, CAT(g, i, j), __fmul_rn(0.5f, __fadd_rn(__fmul_rn(sj, v), __fmul_rn(si, v))));
         }
     }
 }
 
-// ---- divergence (src/fluid_sim.cpp:307-314) on the columns [c0, c0 + 64) ---------------------------------------------
-// A warp walks a run of rows with the rows above / below kept in registers; every lane owns two columns (c0 + lane,
-// c0 + 32 + lane), the j-neighbours come from the neighbouring lanes (two edge loads per row for the columns outside
-// the block).  Wall cells are read as setBoundary(1, u) / setBoundary(2, v) would have left them:
+// ---- divergence (src/fluid_sim.cpp:307-314) on the columns [c0, c0 + cw) ---------------------------------------------
+// A warp walks a run of rows with the rows above / below kept in registers; every lane owns one column (cw = 32) or two
+// (c0 + lane, c0 + 32 + lane), the j-neighbours come from the neighbouring lanes (two edge loads per row for the columns
+// outside the block).  Wall cells are read as setBoundary(1, u) / setBoundary(2, v) would have left them:
 //   u[0][j] = -u[1][j], u[W-1][j] = -u[W-2][j], v[i][0] = -v[i][1], v[i][H-1] = -v[i][H-2]   (:350-360)
 constexpr int kPwRun = 64;   // rows per warp run
 constexpr int kPwBatch = 4;  // rows whose loads are in flight together
 
-__device__ __forceinline__ void chain_divergence(const ChainPhase &ph, const int W, const int H, const int cl)
+template <int CW>
+__device__ __forceinline__ void chain_divergence(const ChainPhase &ph, const ChainGrid &g, const int blk)
 {
+    const int W = g.W, H = g.H;
+    constexpr int cw = CW;
+    const long long pitch = g.pitch;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    const int c0 = cl * kChainCols;
+    const int c0 = blk * cw;
     const float *u = ph.u, *v = ph.v;
     float *div = ph.q;
     const float mhh = ph.c0;
+    constexpr bool two = cw == 64;
     const int ja = c0 + lane, jb = c0 + 32 + lane;
-    const bool ina = ja >= 1 && ja <= H - 2, inb = jb >= 1 && jb <= H - 2;
-    const bool edge_l = (lane == 0) && (c0 - 1 >= 1), edge_r = (lane == 31) && (c0 + 64 <= H - 2);
-    const int je = (lane == 0) ? c0 - 1 : c0 + 64;
+    const bool ina = ja >= 1 && ja <= H - 2, inb = two && jb >= 1 && jb <= H - 2;
+    const bool edge_l = (lane == 0) && (c0 - 1 >= 1), edge_r = (lane == 31) && (c0 + cw <= H - 2);
+    const int je = (lane == 0) ? c0 - 1 : c0 + cw;
     for (int r0 = 1 + kPwRun * w; r0 <= W - 2; r0 += kPwRun * nw) {
         const int r1 = min(r0 + kPwRun, W - 1);   // rows [r0, r1)
-        const size_t row0 = (size_t)r0 * H;
+        const long long row0 = (long long)r0 * pitch - g.jbase;
         float uca = ina ? __ldcg(u + row0 + ja) : 0.0f, ucb = inb ? __ldcg(u + row0 + jb) : 0.0f;
         float uma, umb;
         if (r0 == 1) {
             uma = -uca;
             umb = -ucb;
         } else {
-            uma = ina ? __ldcg(u + row0 - H + ja) : 0.0f;
-            umb = inb ? __ldcg(u + row0 - H + jb) : 0.0f;
+            uma = ina ? __ldcg(u + row0 - pitch + ja) : 0.0f;
+            umb = inb ? __ldcg(u + row0 - pitch + jb) : 0.0f;
         }
         for (int i0 = r0; i0 < r1; i0 += kPwBatch) {
             float upa[kPwBatch], upb[kPwBatch], vca[kPwBatch], vcb[kPwBatch], ve[kPwBatch];
 #pragma unroll
             for (int k = 0; k < kPwBatch; ++k) {
                 const int i = i0 + k;
-                const size_t row = (size_t)i * H;
+                const long long row = (long long)i * pitch - g.jbase;
                 const bool rv = i < r1;
                 const bool nx = rv && (i + 1 <= W - 2);
-                upa[k] = (nx && ina) ? __ldcg(u + row + H + ja) : 0.0f;
-                upb[k] = (nx && inb) ? __ldcg(u + row + H + jb) : 0.0f;
+                upa[k] = (nx && ina) ? __ldcg(u + row + pitch + ja) : 0.0f;
+                upb[k] = (nx && inb) ? __ldcg(u + row + pitch + jb) : 0.0f;
                 vca[k] = (rv && ina) ? __ldcg(v + row + ja) : 0.0f;
                 vcb[k] = (rv && inb) ? __ldcg(v + row + jb) : 0.0f;
                 ve[k] = (rv && (edge_l || edge_r)) ? __ldcg(v + row + je) : 0.0f;
@@ -228,7 +308,7 @@ __device__ __forceinline__ void chain_divergence(const ChainPhase &ph, const int
             for (int k = 0; k < kPwBatch; ++k) {
                 const int i = i0 + k;
                 if (i >= r1) break;                       // warp-uniform
-                const size_t row = (size_t)i * H;
+                const long long row = (long long)i * pitch - g.jbase;
                 const float nua = (i + 1 == W - 1) ? -uca : upa[k];
                 const float nub = (i + 1 == W - 1) ? -ucb : upb[k];
                 // j-neighbours from the neighbouring lanes
@@ -236,7 +316,7 @@ __device__ __forceinline__ void chain_divergence(const ChainPhase &ph, const int
                 float lb = __shfl_up_sync(0xffffffffu, vcb[k], 1), rb = __shfl_down_sync(0xffffffffu, vcb[k], 1);
                 const float b_first = __shfl_sync(0xffffffffu, vcb[k], 0), a_last = __shfl_sync(0xffffffffu, vca[k], 31);
                 if (lane == 0) { la = ve[k]; lb = a_last; }
-                if (lane == 31) { ra = b_first; rb = ve[k]; }
+                if (lane == 31) { ra = two ? b_first : ve[k]; rb = ve[k]; }
                 if (ja - 1 == 0) la = -vca[k];
                 if (ja + 1 == H - 1) ra = -vca[k];
                 if (jb - 1 == 0) lb = -vcb[k];
@@ -251,34 +331,40 @@ __device__ __forceinline__ void chain_divergence(const ChainPhase &ph, const int
     }
 }
 
-// ---- pressure gradient (src/fluid_sim.cpp:334-341) on the columns [c0, c0 + 64), then setBoundary(1, u) and
+// ---- pressure gradient (src/fluid_sim.cpp:334-341) on the columns [c0, c0 + cw), then setBoundary(1, u) and
 // setBoundary(2, v) (:342-343) for those columns.  Pressure walls are read as setBoundary(0, p) defines them
 // (p[0][j] = p[1][j], p[i][0] = p[i][1], ...), so the pressure array's own wall cells are never touched.
-__device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W, const int H, const int cl, float *vmax_out,
+template <bool MR, int CW>
+__device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const ChainGrid &g, const int blk, float *vmax_out,
                                                float *umax_out)
 {
     __shared__ float s_vmax[kChainThreads / 32], s_umax[kChainThreads / 32];
     float vmax = 0.0f, umax = 0.0f;
+    const int W = g.W, H = g.H;
+    constexpr int cw = CW;
+    const long long pitch = g.pitch;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    const int c0 = cl * kChainCols;
+    const int c0 = blk * cw;
+    const ChainPush P = make_push(g, ph, c0);
     float *u = ph.u, *v = ph.v;
     const float *p = ph.q;
     const float h = ph.c0;
+    constexpr bool two = cw == 64;
     const int ja = c0 + lane, jb = c0 + 32 + lane;
-    const bool ina = ja >= 1 && ja <= H - 2, inb = jb >= 1 && jb <= H - 2;
-    const bool edge_l = (lane == 0) && (c0 - 1 >= 1), edge_r = (lane == 31) && (c0 + 64 <= H - 2);
-    const int je = (lane == 0) ? c0 - 1 : c0 + 64;
+    const bool ina = ja >= 1 && ja <= H - 2, inb = two && jb >= 1 && jb <= H - 2;
+    const bool edge_l = (lane == 0) && (c0 - 1 >= 1), edge_r = (lane == 31) && (c0 + cw <= H - 2);
+    const int je = (lane == 0) ? c0 - 1 : c0 + cw;
     for (int r0 = 1 + kPwRun * w; r0 <= W - 2; r0 += kPwRun * nw) {
         const int r1 = min(r0 + kPwRun, W - 1);
-        const size_t row0 = (size_t)r0 * H;
+        const long long row0 = (long long)r0 * pitch - g.jbase;
         float pca = ina ? __ldcg(p + row0 + ja) : 0.0f, pcb = inb ? __ldcg(p + row0 + jb) : 0.0f;
         float pma, pmb;
         if (r0 == 1) {
             pma = pca;
             pmb = pcb;
         } else {
-            pma = ina ? __ldcg(p + row0 - H + ja) : 0.0f;
-            pmb = inb ? __ldcg(p + row0 - H + jb) : 0.0f;
+            pma = ina ? __ldcg(p + row0 - pitch + ja) : 0.0f;
+            pmb = inb ? __ldcg(p + row0 - pitch + jb) : 0.0f;
         }
         float pe = (edge_l || edge_r) ? __ldcg(p + row0 + je) : 0.0f;   // this row's pressure just outside the block
         for (int i0 = r0; i0 < r1; i0 += kPwBatch) {
@@ -286,12 +372,12 @@ __device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W
 #pragma unroll
             for (int k = 0; k < kPwBatch; ++k) {
                 const int i = i0 + k;
-                const size_t row = (size_t)i * H;
+                const long long row = (long long)i * pitch - g.jbase;
                 const bool rv = i < r1;
                 const bool nx = rv && (i + 1 <= W - 2);
-                ppa[k] = (nx && ina) ? __ldcg(p + row + H + ja) : 0.0f;
-                ppb[k] = (nx && inb) ? __ldcg(p + row + H + jb) : 0.0f;
-                pen[k] = (nx && (edge_l || edge_r)) ? __ldcg(p + row + H + je) : 0.0f;
+                ppa[k] = (nx && ina) ? __ldcg(p + row + pitch + ja) : 0.0f;
+                ppb[k] = (nx && inb) ? __ldcg(p + row + pitch + jb) : 0.0f;
+                pen[k] = (nx && (edge_l || edge_r)) ? __ldcg(p + row + pitch + je) : 0.0f;
                 ua[k] = (rv && ina) ? __ldcg(u + row + ja) : 0.0f;
                 ub[k] = (rv && inb) ? __ldcg(u + row + jb) : 0.0f;
                 va[k] = (rv && ina) ? __ldcg(v + row + ja) : 0.0f;
@@ -301,14 +387,14 @@ __device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W
             for (int k = 0; k < kPwBatch; ++k) {
                 const int i = i0 + k;
                 if (i >= r1) break;
-                const size_t row = (size_t)i * H;
+                const long long row = (long long)i * pitch - g.jbase;
                 const float npa = (i + 1 == W - 1) ? pca : ppa[k];
                 const float npb = (i + 1 == W - 1) ? pcb : ppb[k];
                 float la = __shfl_up_sync(0xffffffffu, pca, 1), ra = __shfl_down_sync(0xffffffffu, pca, 1);
                 float lb = __shfl_up_sync(0xffffffffu, pcb, 1), rb = __shfl_down_sync(0xffffffffu, pcb, 1);
                 const float b_first = __shfl_sync(0xffffffffu, pcb, 0), a_last = __shfl_sync(0xffffffffu, pca, 31);
                 if (lane == 0) { la = pe; lb = a_last; }
-                if (lane == 31) { ra = b_first; rb = pe; }
+                if (lane == 31) { ra = two ? b_first : pe; rb = pe; }
                 if (ja - 1 == 0) la = pca;
                 if (ja + 1 == H - 1) ra = pca;
                 if (jb - 1 == 0) lb = pcb;
@@ -317,16 +403,16 @@ __device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W
                 if (ina) {
                     const float nv = __fsub_rn(va[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(ra, la)), h));
                     const float nu = __fsub_rn(ua[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(npa, pma)), h));
-                    u[row + ja] = nu;
-                    v[row + ja] = nv;
+                    store_pushed<MR>(u, ph.peer_l[0], ph.peer_r[0], P, row + ja, nu);
+                    store_pushed<MR>(v, ph.peer_l[1], ph.peer_r[1], P, row + ja, nv);
                     vmax = fmaxf(vmax, fabsf(nv));
                     umax = fmaxf(umax, fabsf(nu));
                 }
                 if (inb) {
                     const float nv = __fsub_rn(vb[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(rb, lb)), h));
                     const float nu = __fsub_rn(ub[k], __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(npb, pmb)), h));
-                    u[row + jb] = nu;
-                    v[row + jb] = nv;
+                    store_pushed<MR>(u, ph.peer_l[0], ph.peer_r[0], P, row + jb, nu);
+                    store_pushed<MR>(v, ph.peer_l[1], ph.peer_r[1], P, row + jb, nv);
                     vmax = fmaxf(vmax, fabsf(nv));
                     umax = fmaxf(umax, fabsf(nu));
                 }
@@ -336,8 +422,8 @@ __device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W
             }
         }
     }
-    // largest |v| of the block (walls repeat interior magnitudes): bounds how many columns an advection trace that
-    // starts in or passes through this block can move
+    // largest |v| and |u| of the block (walls repeat interior magnitudes): they bound how many columns / rows an
+    // advection trace that starts in or passes through this block can move
     for (int o = 16; o > 0; o >>= 1) {
         vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
         umax = fmaxf(umax, __shfl_xor_sync(0xffffffffu, umax, o));
@@ -356,33 +442,38 @@ __device__ __forceinline__ void chain_gradient(const ChainPhase &ph, const int W
         *vmax_out = m;
         *umax_out = mu;     // bounds the rows a trace can move: sizes the shared-memory tiles of the advection phase
     }
-    chain_boundary(u, 1, 0, W, H, c0);    // setBoundary(1, u), :342
-    chain_boundary(v, 2, 0, W, H, c0);    // setBoundary(2, v), :343
+    chain_boundary<MR, CW>(u, ph.peer_l[0], ph.peer_r[0], P, 1, 0, g, c0);    // setBoundary(1, u), :342
+    chain_boundary<MR, CW>(v, ph.peer_l[1], ph.peer_r[1], P, 2, 0, g, c0);    // setBoundary(2, v), :343
     // density "diffusion" with a == 0 leaves d + 0.0f in the interior and runs setBoundary(0, d): the
     // walls are set here, the + 0.0f is folded into the taps of the density advection
-    if (ph.bnd_extra) chain_boundary(ph.bnd_extra, 0, 1, W, H, c0);
+    if (ph.bnd_extra) chain_boundary<MR, CW>(ph.bnd_extra, ph.peer_l[2], ph.peer_r[2], P, 0, 1, g, c0);
 }
 
-// ---- RK4 advection (src/fluid_sim.cpp:261-298) of the columns [c0, c0 + 64), then setBoundary on the result -------
+// ---- RK4 advection (src/fluid_sim.cpp:261-298) of the columns [c0, c0 + cw), then setBoundary on the result -------
 // The back-trace may leave the block: before it starts, the CTA waits until the gradient phase has published every
 // block the traces can reach.  A trace moves at most dt0 * max|v| columns per stage (bilinear samples never exceed
 // the largest tap), so with m = max |v| over the blocks [b - k, b + k] the reach is ceil(dt0 * m) + 2 columns; k grows
 // until that fits inside those blocks (one block for the 4-cell displacement of the bench input, the whole grid
-// in the worst case).
+// in the worst case).  On a column block of a multi-rank run the traces must stay inside the halo the neighbours keep
+// current: a trace that would leave it is reported (err word) instead of waited for.
+template <bool MR>
 __device__ __forceinline__ void chain_advect_wait(const ChainParams &C, const ChainPhase &ph, const int p, const int b,
                                                   const float dt0, int *reach_rows, int *reach_cols)
 {
     __shared__ int s_k, s_ri, s_rj;
-    const ChainPhase &g = C.ph[ph.reach_phase];
+    const ChainGrid &g = C.g;
+    const ChainPhase &gr = C.ph[ph.reach_phase];
     const unsigned *flags = C.done + (size_t)ph.reach_phase * kChainMaxItems;
     const float *vm = C.vmax + (size_t)ph.reach_phase * kChainMaxItems;
-    const int nb = g.ncl;
+    // blocks whose gradient results this rank can see: the whole grid on one GPU, own blocks + halo on a column block
+    const int vis_lo = g.has_left ? max((g.j0 - g.halo) / g.cw, 0) : 0;
+    const int vis_hi = g.has_right ? min((g.j1 + g.halo) / g.cw - 1, gr.ncl - 1) : gr.ncl - 1;
     int k = 1, waited_lo = b + 1, waited_hi = b;   // blocks [waited_lo, waited_hi] are known to be done
     for (;;) {
-        const int lo = max(b - k, 0), hi = min(b + k, nb - 1);
+        const int lo = max(b - k, vis_lo), hi = min(b + k, vis_hi);
         unsigned long long t0 = 0;
         for (int x = lo + (int)threadIdx.x; x <= hi; x += blockDim.x)
-            if (x < waited_lo || x > waited_hi) chain_poll(C, flags + x, p, b, t0);
+            if (x < waited_lo || x > waited_hi) chain_poll<MR>(C, flags + x, C.epoch, p, b, t0);
         __syncthreads();
         waited_lo = lo;
         waited_hi = hi;
@@ -393,8 +484,8 @@ __device__ __forceinline__ void chain_advect_wait(const ChainParams &C, const Ch
                 mu = fmaxf(mu, __ldcg(vm + (size_t)kChainMaxPhases * kChainMaxItems + x));
             }
             const float r = dt0 * m, ru = dt0 * mu;
-            int need = nb;                                      // non-finite velocities: wait for everything
-            if (r < 1.0e8f) need = ((int)ceilf(r) + 2 + kChainCols - 1) / kChainCols;
+            int need = gr.ncl;                                  // non-finite velocities: wait for everything
+            if (r < 1.0e8f) need = ((int)ceilf(r) + 2 + g.cw - 1) / g.cw;
             s_k = max(need, 1);
             s_rj = (r < 1.0e8f) ? (int)ceilf(r) + 2 : (1 << 30);
             s_ri = (ru < 1.0e8f) ? (int)ceilf(ru) + 2 : (1 << 30);
@@ -404,7 +495,12 @@ __device__ __forceinline__ void chain_advect_wait(const ChainParams &C, const Ch
         *reach_rows = s_ri;
         *reach_cols = s_rj;
         __syncthreads();
-        if (need <= k || (lo == 0 && hi == nb - 1)) break;
+        if (need <= k || (lo == vis_lo && hi == vis_hi)) {
+            // the traces may want blocks this rank cannot see: the step's result is invalid, say so
+            if (threadIdx.x == 0 && need > k && (b - need < vis_lo && vis_lo > 0 || b + need > vis_hi && vis_hi < gr.ncl - 1))
+                atomicCAS(C.err, 0ull, 0x8000000000000000ull | (unsigned)b);
+            break;
+        }
         k = need;
     }
 }
@@ -436,39 +532,54 @@ __device__ __forceinline__ float sample_tile(const float *T, const Taps &t, cons
     return __fadd_rn(__fmul_rn(t.s0, a), __fmul_rn(t.s1, b));
 }
 
+// The four independent traces of a thread: two columns x two rows on 64-column items, one column x four rows on
+// 32-column items.  `r` = row inside the stage / run, `c` = column offset inside the block.
+__device__ __forceinline__ void trace_cell(const bool two, const int n, const int lane, int *r, int *c)
+{
+    *r = two ? (n >> 1) : n;
+    *c = (two ? 32 * (n & 1) : 0) + lane;
+}
+
 // returns false (nothing done) when the tiles for this reach do not fit the shared memory of the launch
-template <bool TWO, bool PZ>
-__device__ __forceinline__ bool chain_advect_tiled(const ChainPhase &ph, const int W, const int H, const int cl, float *smem,
+template <bool TWO, bool PZ, bool MR, int CW>
+__device__ __forceinline__ bool chain_advect_tiled(const ChainPhase &ph, const ChainGrid &g, const int blk, float *smem,
                                                    const int smem_floats, const int ri, const int rj)
 {
     constexpr int NARR = TWO ? 2 : 3;            // velocity: u, v are sources as well; density: u, v and the density
-    if ((H & 3) != 0 || ri > 64 || rj > 60) return false;
+    const int W = g.W, H = g.H;
+    constexpr int cw = CW;
+    if ((g.pitch & 3) != 0 || (g.jbase & 3) != 0 || (H & 3) != 0 || ri > 64 || rj > 60) return false;
     const int halo_c = (rj + 1 + 3) & ~3;        // columns staged on each side (taps j0, j0 + 1), 16-byte aligned
     const int halo_r = ri + 1;
-    const int TC = kChainCols + 2 * halo_c, TR = kAdvRows + 2 * halo_r;
+    const int TC = cw + 2 * halo_c, TR = kAdvRows + 2 * halo_r;
     const int stage_floats = NARR * TR * TC;
     if (2 * stage_floats > smem_floats) return false;
     const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, w = tid >> 5;
-    const int c0 = cl * kChainCols, cb = c0 - halo_c;
+    const int c0 = blk * cw, cb = c0 - halo_c;
+    const ChainPush P = make_push(g, ph, c0);
     const float *arr[3] = {ph.u, ph.v, ph.src_a};
     float *dst_a = ph.dst_a, *dst_b = ph.dst_b;
     const float ndt0 = ph.c0;
     const float xm = (float)W - 1.5f, ym = (float)H - 1.5f;
+    constexpr bool two = cw == 64;
+    constexpr int rows_per_pass = two ? 2 : 4, npass = two ? 2 : 1;     // 4 rows per warp and stage either way
     const int nq = TC >> 2;                      // 16-byte pieces per tile row
     const int my_q = tid % nq, my_r = tid / nq, r_step = nt / nq;
     const int nstages = (W - 2 + kAdvRows - 1) / kAdvRows;
+    // columns the local arrays hold: [jbase, jbase + pitch) within the grid
+    const int col_lo = max(g.jbase, 0), col_hi = min(g.jbase + g.pitch, H);
     auto issue = [&](int k) {
         if (k < nstages && my_r < r_step) {
             float *slot = smem + (k & 1) * stage_floats;
             const int row_lo = 1 + k * kAdvRows - halo_r;
             const int col = cb + 4 * my_q;
-            if (col >= 0 && col < H) {
+            if (col >= col_lo && col + 3 < col_hi) {
 #pragma unroll
                 for (int a = 0; a < NARR; ++a)
                     for (int r = my_r; r < TR; r += r_step) {
                         const int row = row_lo + r;
                         if (row < 0 || row > W - 1) continue;
-                        cp_async_f32x4(slot + (a * TR + r) * TC + 4 * my_q, arr[a] + (size_t)row * H + col, true);
+                        cp_async_f32x4(slot + (a * TR + r) * TC + 4 * my_q, arr[a] + CAT(g, row, col), true);
                     }
             }
         }
@@ -482,18 +593,20 @@ __device__ __forceinline__ bool chain_advect_tiled(const ChainPhase &ph, const i
         const float *slot = smem + (k & 1) * stage_floats;
         const float *Tu = slot, *Tv = slot + TR * TC, *Ts = slot + 2 * TR * TC;
         const int row0 = 1 + k * kAdvRows - halo_r;
-        constexpr int N = 4;                     // independent traces per thread: two columns x two rows
+        constexpr int N = 4;
 #pragma unroll 1
-        for (int it = 0; it < 2; ++it) {
+        for (int it = 0; it < npass; ++it) {
             int ci[N], cj[N];
             bool ok[N];
             float x[N], y[N], k1x[N], k1y[N], k2x[N], k2y[N], k3x[N], k3y[N], k4x[N], k4y[N];
             Taps t[N];
 #pragma unroll
             for (int n = 0; n < N; ++n) {
-                const int r = 4 * w + 2 * it + (n >> 1);
+                int rr, cc;
+                trace_cell(two, n, lane, &rr, &cc);
+                const int r = 4 * w + rows_per_pass * it + rr;
                 ci[n] = 1 + k * kAdvRows + r;
-                cj[n] = c0 + 32 * (n & 1) + lane;
+                cj[n] = c0 + cc;
                 ok[n] = r < kAdvRows && ci[n] <= W - 2 && cj[n] >= 1 && cj[n] <= H - 2;
                 // cells outside the interior trace from the first cell of the stage's block (inside the tile), store nothing
                 x[n] = ok[n] ? (float)ci[n] : (float)(1 + k * kAdvRows);
@@ -539,9 +652,9 @@ __device__ __forceinline__ bool chain_advect_tiled(const ChainPhase &ph, const i
                 const float ra = sample_tile<PZ>(TWO ? Tu : Ts, t[n], row0, cb, TC, W, H);
                 const float rb = TWO ? sample_tile<false>(Tv, t[n], row0, cb, TC, W, H) : 0.0f;
                 if (ok[n]) {
-                    const size_t c = (size_t)ci[n] * H + cj[n];
-                    dst_a[c] = ra;
-                    if (TWO) dst_b[c] = rb;
+                    const long long c = CAT(g, ci[n], cj[n]);
+                    store_pushed<MR>(dst_a, ph.peer_l[0], ph.peer_r[0], P, c, ra);
+                    if (TWO) store_pushed<MR>(dst_b, ph.peer_l[1], ph.peer_r[1], P, c, rb);
                 }
             }
         }
@@ -549,36 +662,43 @@ __device__ __forceinline__ bool chain_advect_tiled(const ChainPhase &ph, const i
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
-    chain_boundary(dst_a, ph.ba, 0, W, H, c0);
-    if (TWO) chain_boundary(dst_b, ph.bb, 0, W, H, c0);
+    chain_boundary<MR, CW>(dst_a, ph.peer_l[0], ph.peer_r[0], P, ph.ba, 0, g, c0);
+    if (TWO) chain_boundary<MR, CW>(dst_b, ph.peer_l[1], ph.peer_r[1], P, ph.bb, 0, g, c0);
     return true;
 }
 
-template <bool TWO, bool PZ>
-__device__ __forceinline__ void chain_advect(const ChainPhase &ph, const int W, const int H, const int cl)
+template <bool TWO, bool PZ, bool MR, int CW>
+__device__ __forceinline__ void chain_advect(const ChainPhase &ph, const ChainGrid &g, const int blk)
 {
+    const int W = g.W, H = g.H;
+    constexpr int cw = CW;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    const int c0 = cl * kChainCols;
-    const GridView G{W, H, H, 0, 0, H};
+    const int c0 = blk * cw;
+    const ChainPush P = make_push(g, ph, c0);
+    const GridView G{W, H, g.pitch, g.jbase, g.j0, g.j1};
     const float *u = ph.u, *v = ph.v;
     const float *src_a = ph.src_a, *src_b = ph.src_b;
     float *dst_a = ph.dst_a, *dst_b = ph.dst_b;
     const float ndt0 = ph.c0;
     const float xm = (float)W - 1.5f, ym = (float)H - 1.5f;
-    constexpr int N = 4;     // independent traces per thread: two columns x two rows
-    for (int i0 = 1 + 2 * w; i0 <= W - 2; i0 += 2 * nw) {
+    constexpr bool two = cw == 64;
+    constexpr int rows_per_pass = two ? 2 : 4;
+    constexpr int N = 4;     // independent traces per thread
+    for (int i0 = 1 + rows_per_pass * w; i0 <= W - 2; i0 += rows_per_pass * nw) {
         int ci[N], cj[N];
         bool ok[N];
         float x[N], y[N], k1x[N], k1y[N], k2x[N], k2y[N], k3x[N], k3y[N], k4x[N], k4y[N];
         Taps t[N];
 #pragma unroll
         for (int n = 0; n < N; ++n) {
-            ci[n] = i0 + (n >> 1);
-            cj[n] = c0 + 32 * (n & 1) + lane;
+            int rr, cc;
+            trace_cell(two, n, lane, &rr, &cc);
+            ci[n] = i0 + rr;
+            cj[n] = c0 + cc;
             ok[n] = ci[n] <= W - 2 && cj[n] >= 1 && cj[n] <= H - 2;
-            // cells outside the interior trace from a harmless in-grid position and store nothing
+            // cells outside the interior trace from a harmless position this rank holds and store nothing
             x[n] = ok[n] ? (float)ci[n] : 1.0f;
-            y[n] = ok[n] ? (float)cj[n] : 1.0f;
+            y[n] = ok[n] ? (float)cj[n] : (float)max(g.j0, 1);
             t[n] = make_taps(x[n], y[n], xm, ym);
         }
 #pragma unroll
@@ -621,62 +741,130 @@ __device__ __forceinline__ void chain_advect(const ChainPhase &ph, const int W, 
             const float ra = sample<PZ, int, false>(src_a, t[n], G);
             const float rb = TWO ? sample<PZ, int, false>(src_b, t[n], G) : 0.0f;
             if (ok[n]) {
-                const size_t c = (size_t)ci[n] * H + cj[n];
-                dst_a[c] = ra;
-                if (TWO) dst_b[c] = rb;
+                const long long c = CAT(g, ci[n], cj[n]);
+                store_pushed<MR>(dst_a, ph.peer_l[0], ph.peer_r[0], P, c, ra);
+                if (TWO) store_pushed<MR>(dst_b, ph.peer_l[1], ph.peer_r[1], P, c, rb);
             }
         }
     }
     __syncthreads();
-    chain_boundary(dst_a, ph.ba, 0, W, H, c0);
-    if (TWO) chain_boundary(dst_b, ph.bb, 0, W, H, c0);
+    chain_boundary<MR, CW>(dst_a, ph.peer_l[0], ph.peer_r[0], P, ph.ba, 0, g, c0);
+    if (TWO) chain_boundary<MR, CW>(dst_b, ph.peer_l[1], ph.peer_r[1], P, ph.bb, 0, g, c0);
 }
 
-template <int SD, int SP>
+// What an item does besides its arithmetic, recomputed from (phase, local item) wherever it is needed so that nothing
+// but those two integers stays live across the sweep pipeline's loops (the kernel runs at the 168-register cap of a
+// 10-warp CTA, and anything more spills inside those loops).
+struct ChainItem {
+    int item, cl, fi, lo, hi;
+    bool sweep, data_l, data_r;
+};
+__device__ __forceinline__ ChainItem chain_item(const ChainParams &C, const int p, const int li)
+{
+    const ChainPhase &ph = C.ph[p];
+    const ChainGrid &g = C.g;
+    ChainItem I;
+    I.sweep = ph.kind == kPhSor || ph.kind == kPhGs || ph.kind == kPhGsX0;
+    I.item = ph.item0 + li;                       // numbered along the whole grid
+    I.cl = I.item / ph.nf;
+    I.fi = I.item - I.cl * ph.nf;
+    I.lo = I.cl * ph.cpv - ph.shift;              // result columns
+    I.hi = I.lo + ph.cpv - 1;
+    // does this item write into a neighbour's memory?  (sweep phases: the result columns owed to the left rank)
+    I.data_l = I.sweep ? (g.has_left && I.lo < g.j0 + 1) : (ph.push_cols > 0 && near_left(g, I.lo, ph.push_cols));
+    I.data_r = I.sweep ? false : (ph.push_cols > 0 && near_right(g, I.hi, ph.push_cols));
+    return I;
+}
+
+template <int SD, int SP, bool MR, int CW>
 __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_constant__ ChainParams C)
 {
     extern __shared__ float4 smem4[];
     float *smem = reinterpret_cast<float *>(smem4);
+    const ChainGrid &g = C.g;
     for (int p = 0; p < C.nphases; ++p) {
         const ChainPhase &ph = C.ph[p];
-        for (int item = blockIdx.x; item < ph.nitems; item += gridDim.x) {
-            const int cl = item / ph.nf, fi = item - cl * ph.nf;
-            unsigned long long *tr = C.trace + ((size_t)p * kChainMaxItems + item) * 3;
-            if (threadIdx.x == 0) tr[0] = global_timer_ns();
-            chain_wait(C, p, cl);
+        for (int li = blockIdx.x; li < ph.nitems; li += gridDim.x) {
             int reach_rows = 1 << 30, reach_cols = 1 << 30;
-            if (ph.kind == kPhAdvect) chain_advect_wait(C, ph, p, cl, -ph.c0, &reach_rows, &reach_cols);
-            if (threadIdx.x == 0) tr[1] = global_timer_ns();
+            {
+                const ChainItem I = chain_item(C, p, li);
+                if (threadIdx.x == 0) C.trace[((size_t)p * kChainMaxItems + li) * 3] = global_timer_ns();
+                chain_wait<MR>(C, p, I.cl, MR && I.data_l, MR && I.data_r);
+                if (ph.kind == kPhAdvect) chain_advect_wait<MR>(C, ph, p, I.cl, -ph.c0, &reach_rows, &reach_cols);
+                if (threadIdx.x == 0) C.trace[((size_t)p * kChainMaxItems + li) * 3 + 1] = global_timer_ns();
+            }
             if (ph.kind == kPhSor) {
-                if constexpr (SD > 0) wf_pass<SD, kSor, true>(C.wf[ph.wf], cl, fi, smem);
+                if constexpr (SD > 0) wf_pass<SD, kSor, true>(C.wf[ph.wf], li / ph.nf, li % ph.nf, smem);
             } else if (ph.kind == kPhGs) {
-                wf_pass<SP, kGaussSeidel, false>(C.wf[ph.wf], cl, fi, smem);
+                wf_pass<SP, kGaussSeidel, false>(C.wf[ph.wf], li, 0, smem);
             } else if (ph.kind == kPhGsX0) {
-                wf_pass<SP, kGaussSeidel, true>(C.wf[ph.wf], cl, fi, smem);     // a later pass of the same projection
-            } else if (ph.kind == kPhBndP) {
-                chain_boundary(ph.q, 0, 0, C.W, C.H, cl * kChainCols);           // setBoundary(0, p) between two passes (:330)
-            } else if (ph.kind == kPhDiv) {
-                chain_divergence(ph, C.W, C.H, cl);
-            } else if (ph.kind == kPhGrad) {
-                chain_gradient(ph, C.W, C.H, cl, C.vmax + (size_t)p * kChainMaxItems + item,
-                               C.vmax + (size_t)(kChainMaxPhases + p) * kChainMaxItems + item);
-            } else if (ph.kind == kPhAdvect) {
-                if (ph.dst_b) {
-                    if (!chain_advect_tiled<true, false>(ph, C.W, C.H, cl, smem, C.smem_floats, reach_rows, reach_cols))
-                        chain_advect<true, false>(ph, C.W, C.H, cl);
-                } else if (ph.pz) {
-                    if (!chain_advect_tiled<false, true>(ph, C.W, C.H, cl, smem, C.smem_floats, reach_rows, reach_cols))
-                        chain_advect<false, true>(ph, C.W, C.H, cl);
-                } else {
-                    if (!chain_advect_tiled<false, false>(ph, C.W, C.H, cl, smem, C.smem_floats, reach_rows, reach_cols))
-                        chain_advect<false, false>(ph, C.W, C.H, cl);
+                wf_pass<SP, kGaussSeidel, true>(C.wf[ph.wf], li, 0, smem);     // a later pass of the same projection
+            } else {
+                const int cl = ph.item0 + li;     // pointwise phases: one field, item = block
+                if (ph.kind == kPhBndP) {
+                    ChainPush none{false, false, 0, 0};
+                    chain_boundary<MR, CW>(ph.q, nullptr, nullptr, none, 0, 0, g, cl * CW);       // setBoundary(0, p) between two passes (:330)
+                } else if (ph.kind == kPhDiv) {
+                    chain_divergence<CW>(ph, g, cl);
+                } else if (ph.kind == kPhGrad) {
+                    chain_gradient<MR, CW>(ph, g, cl, C.vmax + (size_t)p * kChainMaxItems + cl,
+                                   C.vmax + (size_t)(kChainMaxPhases + p) * kChainMaxItems + cl);
+                } else if (ph.kind == kPhAdvect) {
+                    if (ph.dst_b) {
+                        if (!chain_advect_tiled<true, false, MR, CW>(ph, g, cl, smem, C.smem_floats, reach_rows, reach_cols))
+                            chain_advect<true, false, MR, CW>(ph, g, cl);
+                    } else if (ph.pz) {
+                        if (!chain_advect_tiled<false, true, MR, CW>(ph, g, cl, smem, C.smem_floats, reach_rows, reach_cols))
+                            chain_advect<false, true, MR, CW>(ph, g, cl);
+                    } else {
+                        if (!chain_advect_tiled<false, false, MR, CW>(ph, g, cl, smem, C.smem_floats, reach_rows, reach_cols))
+                            chain_advect<false, false, MR, CW>(ph, g, cl);
+                    }
                 }
+            }
+            asm volatile("" : "+r"(li), "+r"(p));        // everything below is recomputed, not kept
+            const ChainItem I = chain_item(C, p, li);
+            if constexpr (MR) {
+                if (I.data_l || I.data_r) __threadfence_system();   // this thread's stores into the neighbour's memory
             }
             __syncthreads();   // the item's results are written, its shared memory is free
             if (threadIdx.x == 0) {
-                __threadfence();
-                st_release_u32(C.done + (size_t)p * kChainMaxItems + item, C.epoch);
-                tr[2] = global_timer_ns();
+                const size_t vi = (size_t)p * kChainMaxItems + I.item, ui = (size_t)(kChainMaxPhases + p) * kChainMaxItems + I.item;
+                bool pushed = false;
+                if constexpr (MR) {
+                    // Items near a rank boundary publish in the neighbour's arrays as well (results, where the neighbour
+                    // needs them, were stored there by this item): velocity maxima first, then the done-word.
+                    const int reach = g.halo + 2 * ph.cpv;
+                    const bool flag_l = near_left(g, I.lo, reach), flag_r = near_right(g, I.hi, reach);
+                    if (flag_l || flag_r) {
+                        pushed = true;
+                        __threadfence_system();
+                        if (ph.kind == kPhGrad) {
+                            const float m = C.vmax[vi], mu = C.vmax[ui];
+                            if (flag_l) { C.vmax_l[vi] = m; C.vmax_l[ui] = mu; }
+                            if (flag_r) { C.vmax_r[vi] = m; C.vmax_r[ui] = mu; }
+                            __threadfence_system();
+                        }
+                        if (flag_l) st_release_sys_u32(C.done_l + vi, C.epoch);
+                        if (flag_r) st_release_sys_u32(C.done_r + vi, C.epoch);
+                    }
+                }
+                if (!pushed) __threadfence();
+                st_release_u32(C.done + vi, C.epoch);
+                C.trace[((size_t)p * kChainMaxItems + li) * 3 + 2] = global_timer_ns();
+            }
+        }
+    }
+    if constexpr (MR) {
+        // the last CTA to finish tells the neighbours that this rank no longer reads what they wrote for this step
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            const unsigned old = atomicAdd(C.cta_count, 1u);
+            if (old == gridDim.x - 1) {
+                *C.cta_count = 0;
+                if (g.has_left) st_release_sys_u32(C.step_out_l, C.epoch);
+                if (g.has_right) st_release_sys_u32(C.step_out_r, C.epoch);
             }
         }
     }
@@ -704,11 +892,25 @@ bool chain_pick(int H, int nstg, int nfields, int max_ctas, int *nstr_out, int *
 
 constexpr int kChainSD = 5, kChainSP = 10;   // sweeps per warp of the diffusion / pressure phases (the instantiated pair)
 
+const void *chain_kernel_ptr(bool with_sor, bool multi_rank, int cw)
+{
+#define FSB_CK(SD_, MR_, CW_) (const void *)chain_kernel<SD_, kChainSP, MR_, CW_>
+    if (with_sor) {
+        if (multi_rank) return cw == 64 ? FSB_CK(kChainSD, true, 64) : FSB_CK(kChainSD, true, 32);
+        return cw == 64 ? FSB_CK(kChainSD, false, 64) : FSB_CK(kChainSD, false, 32);
+    }
+    if (multi_rank) return cw == 64 ? FSB_CK(0, true, 64) : FSB_CK(0, true, 32);
+    return cw == 64 ? FSB_CK(0, false, 64) : FSB_CK(0, false, 32);
+#undef FSB_CK
+}
+
 struct ChainPlan {
     bool ok = false;
-    int W = 0, H = 0, D = 0, P = 0;
-    int sor_nstr = 0, sor_ncta = 0, gs_nstr = 0, gs_ncta = 0, grid = 0;
-    int gs_npass = 0, gs_stages[kChainMaxGsPasses] = {0, 0, 0};   // passes of one projection (gs_ncta: of the widest pass)
+    int W = 0, H = 0, D = 0, P = 0, ncols = 0;
+    bool multi = false;
+    int sor_nstr = 0, sor_ncta = 0, gs_nstr = 0, gs_ncta = 0, grid = 0;   // ncta: upper bounds for this rank
+    int cw = kChainCols;                                          // columns of a pointwise item
+    int gs_npass = 0, gs_stages[kChainMaxGsPasses] = {0, 0, 0};   // passes of one projection
     size_t smem = 0;
     size_t sor_ring_floats = 0, gs_ring_floats = 0;
 };
@@ -717,7 +919,7 @@ struct ChainPlan {
 
 struct ChainState {
     ChainPlan plan[2];                    // [0] with the diffusion phase, [1] without
-    unsigned char *buf = nullptr;         // [done | err | vmax | trace x 2 | flags x 3 | rings sor | rings gs x 2]
+    unsigned char *buf = nullptr;         // [done | misc | vmax | trace x 2 | link regions | flags | rings sor | rings gs]
     size_t bytes = 0;
     float *extra[2] = {nullptr, nullptr}; // pressure / divergence of the second projection of a whole-step launch
     size_t extra_floats = 0;
@@ -727,17 +929,21 @@ struct ChainState {
 
 namespace {
 
-// Can (D diffusion sweeps of u and v +) P pressure sweeps run as phases of one launch on this grid?
-ChainPlan make_plan(int W, int H, int D, int P)
+// Can (D diffusion sweeps of u and v +) P pressure sweeps run as phases of one launch on this grid (or on a column
+// block of `ncols` columns of it: every rank must arrive at the same strips per CTA, so only W, H, ncols enter)?
+ChainPlan make_plan(int W, int H, int D, int P, int ncols, bool multi)
 {
     ChainPlan pl;
-    pl.W = W; pl.H = H; pl.D = D; pl.P = P;
+    pl.W = W; pl.H = H; pl.D = D; pl.P = P; pl.ncols = ncols; pl.multi = multi;
     if (P < kChainSP || P % kChainSP != 0) return pl;
     if (D != 0 && D % kChainSD != 0) return pl;
+    if (multi && D == 0) return pl;
     int dev = 0, nsm = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return pl;
     if (cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return pl;
     size_t smem_gs = 0, smem_sor = 0;
+    // strips a rank may have to run: its own columns, plus (last rank) the strips the result shift adds
+    auto strips_of = [&](int shift) { return multi ? ncols / 32 + (shift + 31) / 32 + 1 : (H + shift + 31) / 32; };
     {
         // Passes of one projection: the fewest strips per CTA for which a pass fits the SMs (more SMs at work, fewer
         // warps sharing one), as many chained warps per strip as the 8 compute warps and the shared memory allow, the
@@ -746,13 +952,15 @@ ChainPlan make_plan(int W, int H, int D, int P)
         const int T = P / kChainSP;
         bool found = false;
         for (int nstr = 1; nstr <= 4 && !found; nstr *= 2) {
+            if (multi && ncols % (32 * nstr) != 0) continue;
             int maxst = std::min((kChainThreads / 32 - 2) / nstr, L::kMaxStagesS);
+            if (multi) maxst = std::min(maxst, kLinkStages);
             while (maxst >= 1 && wf_smem_bytes<kChainSP>(nstr, maxst) > 227 * 1024) --maxst;
             if (maxst < 1) continue;
             const int npass = (T + maxst - 1) / maxst;
             if (npass > kChainMaxGsPasses) continue;
             const int widest = (T + npass - 1) / npass;
-            const int NS = (H + kChainSP * widest + 31) / 32;
+            const int NS = strips_of(kChainSP * widest);
             const int ncta = (NS + std::min(nstr, NS) - 1) / std::min(nstr, NS);
             if (ncta > nsm || ncta > kWfMaxCtas) continue;
             pl.gs_nstr = std::min(nstr, NS);
@@ -764,13 +972,36 @@ ChainPlan make_plan(int W, int H, int D, int P)
         }
         if (!found) return pl;
     }
-    if (D > 0 && !chain_pick<kChainSD>(H, D / kChainSD, 2, nsm, &pl.sor_nstr, &pl.sor_ncta, &smem_sor)) return pl;
+    if (D > 0) {
+        // diffusion: as many strips per CTA as fit (a hand-over inside a CTA is far cheaper than one through the rings)
+        using L = WfLayout<kChainSD>;
+        const int nstg = D / kChainSD;
+        if (nstg < 1 || nstg > L::kMaxStagesS) return pl;
+        const int NS = strips_of(D);
+        int nstr = 4;
+        auto bad = [&](int n) {
+            return n * nstg > kChainThreads / 32 - 2 || wf_smem_bytes<kChainSD>(n, nstg) > 227 * 1024 || n > NS ||
+                   (multi && ncols % (32 * n) != 0);
+        };
+        while (nstr > 1 && bad(nstr)) nstr >>= 1;
+        if (bad(nstr)) return pl;
+        pl.sor_nstr = nstr;
+        pl.sor_ncta = (NS + nstr - 1) / nstr;
+        if (2 * pl.sor_ncta > nsm || pl.sor_ncta > kWfMaxCtas) return pl;
+        smem_sor = wf_smem_bytes<kChainSD>(nstr, nstg);
+    }
     // the advection phases stage their fields in the same shared memory: give them room on small grids too
     pl.smem = std::max(std::max(smem_gs, smem_sor), (size_t)160 * 1024);
-    const int nblk = (H + kChainCols - 1) / kChainCols;
+    // pointwise items: 64 columns, or 32 when that is what it takes to give most SMs a block
+    {
+        static const int forced = [] { const char *e = std::getenv("FSB_CHAIN_CW"); return e ? std::atoi(e) : 0; }();
+        pl.cw = (forced == 32 || forced == 64) ? forced : (((ncols + 63) / 64 < (3 * nsm) / 4) ? 32 : 64);
+        if (multi && ncols % pl.cw != 0) return pl;
+    }
+    const int nblk = (ncols + pl.cw - 1) / pl.cw;
     pl.grid = std::max(std::max(pl.gs_ncta, 2 * pl.sor_ncta), std::min(nblk, nsm));
-    if (pl.grid > nsm || nblk > kChainMaxItems || pl.grid > kChainMaxItems) return pl;
-    auto kern = D > 0 ? chain_kernel<kChainSD, kChainSP> : chain_kernel<0, kChainSP>;
+    if (pl.grid > nsm || (H + pl.cw - 1) / pl.cw > kChainMaxItems || pl.grid > kChainMaxItems) return pl;
+    const void *kern = chain_kernel_ptr(D > 0, multi, pl.cw);
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem) != cudaSuccess) {
         (void)cudaGetLastError();
         return pl;
@@ -809,8 +1040,38 @@ void fill_wf(WfKernelParams &P, int W, int H, int nstr, int nstg, int ncta, floa
 }
 
 constexpr size_t kDoneBytes = (size_t)kChainMaxPhases * kChainMaxItems * sizeof(unsigned);
+constexpr size_t kMiscBytes = 256;        // +0 error word, +64 step words written by the neighbours, +128 finished-CTA count
 constexpr size_t kVmaxBytes = (size_t)2 * kChainMaxPhases * kChainMaxItems * sizeof(float);   // max |v|, then max |u|
 constexpr size_t kTraceOne = (size_t)kChainMaxPhases * kChainMaxItems * 3 * sizeof(unsigned long long);
+// everything up to here sits at the same offsets on every rank (the neighbours address it through peer mappings)
+constexpr size_t kVmaxOff = kDoneBytes + kMiscBytes;
+constexpr size_t kTraceOff = kVmaxOff + kVmaxBytes;
+constexpr size_t kLinksOff = kTraceOff + 2 * kTraceOne;            // one link region per sweep phase
+constexpr size_t kFixedBytes = kLinksOff + kChainMaxSweeps * kLinkBytes;
+
+// hand-over of the strip chain to / from the neighbouring ranks for sweep phase `slot`
+SweepLink chain_link(const ChainBlock &B, unsigned char *buf, int slot, unsigned long long seq)
+{
+    SweepLink L;
+    const size_t off = kLinksOff + (size_t)slot * kLinkBytes;
+    L.has_left = B.has_left;
+    L.has_right = B.has_right;
+    L.in_rings = reinterpret_cast<const float *>(buf + off);
+    L.in_prod = reinterpret_cast<const unsigned long long *>(buf + off + kLinkRingBytes);
+    L.cons = reinterpret_cast<const unsigned long long *>(buf + off + kLinkRingBytes + kLinkFlagBytes);
+    if (B.has_left) {
+        L.left_cons = reinterpret_cast<unsigned long long *>(B.left.chain_buf + off + kLinkRingBytes + kLinkFlagBytes);
+        L.left_ret = reinterpret_cast<unsigned long long *>(B.left.chain_buf + off + kLinkRingBytes + 2 * kLinkFlagBytes);
+        L.peer_jbase = B.G.jbase - B.ncols;        // same halo width and pitch on every rank
+        L.peer_hi = B.G.j0 + 1;                    // the left rank's last owned columns and its first halo column
+    }
+    if (B.has_right) {
+        L.right_rings = reinterpret_cast<float *>(B.right.chain_buf + off);
+        L.right_prod = reinterpret_cast<unsigned long long *>(B.right.chain_buf + off + kLinkRingBytes);
+    }
+    L.seq = seq;
+    return L;
+}
 
 }  // namespace
 
@@ -823,6 +1084,20 @@ void chain_state_destroy(ChainState *cs)
     delete cs;
 }
 
+void chain_shared_buffers(ChainState *cs, void *out[3])
+{
+    out[0] = cs ? cs->buf : nullptr;
+    out[1] = cs ? cs->extra[0] : nullptr;
+    out[2] = cs ? cs->extra[1] : nullptr;
+}
+
+cudaError_t chain_read_error(ChainState *cs, unsigned long long *word)
+{
+    *word = 0;
+    if (!cs || !cs->buf) return cudaSuccess;
+    return cudaMemcpy(word, cs->buf + kDoneBytes, sizeof(*word), cudaMemcpyDeviceToHost);
+}
+
 // Passes of FluidSim::step as phases of one launch (see the head of this file):
 //   diffuse(u), diffuse(v)                               when A.sor_sweeps > 0          (src/fluid_sim.cpp:390-391)
 //   project(u, v, p, div)                                always                         (:394)
@@ -830,20 +1105,27 @@ void chain_state_destroy(ChainState *cs)
 //   densityStep with DIFFUSION == 0                      when A.with_density            (:409-422)
 // Returns cudaErrorNotSupported when this grid / these sweep counts have no chained configuration (the caller then
 // runs the passes as separate launches).
-cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st, bool query_only)
+cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st, int mode)
 {
     if (!cs) cs = new ChainState();
+    const ChainBlock *B = A.blk;
+    const bool multi = B != nullptr;
     const int kind = A.sor_sweeps > 0 ? 0 : 1;
+    const int ncols = multi ? B->ncols : A.H;
     ChainPlan &pl = cs->plan[kind];
-    if (pl.W != A.W || pl.H != A.H || pl.D != A.sor_sweeps || pl.P != A.gs_sweeps) pl = make_plan(A.W, A.H, A.sor_sweeps, A.gs_sweeps);
+    if (pl.W != A.W || pl.H != A.H || pl.D != A.sor_sweeps || pl.P != A.gs_sweeps || pl.ncols != ncols || pl.multi != multi)
+        pl = make_plan(A.W, A.H, A.sor_sweeps, A.gs_sweeps, ncols, multi);
     if (!pl.ok) return cudaErrorNotSupported;
     if (A.with_density && !A.with_advect) return cudaErrorInvalidValue;
-    if (query_only) return cudaSuccess;
+    if (multi && (!A.with_advect || B->halo < pl.cw || B->halo < A.gs_sweeps + 2)) return cudaErrorNotSupported;
+    if (mode == 1) return cudaSuccess;
 
+    const GridView G = multi ? B->G : whole_grid(A.W, A.H);
     cudaError_t e;
     if (A.with_advect) {
-        const size_t nfl = (size_t)A.W * A.H;
+        const size_t nfl = (size_t)A.W * G.pitch;
         if (nfl > cs->extra_floats) {
+            if (multi && cs->extra[0]) return cudaErrorInvalidValue;   // the neighbours have these buffers mapped
             e = cudaStreamSynchronize(st);
             if (e != cudaSuccess) return e;
             for (int k = 0; k < 2; ++k) {
@@ -854,17 +1136,20 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             for (int k = 0; k < 2; ++k) {
                 e = cudaMalloc(&cs->extra[k], nfl * sizeof(float));
                 if (e != cudaSuccess) return e;
+                e = cudaMemsetAsync(cs->extra[k], 0, nfl * sizeof(float), st);
+                if (e != cudaSuccess) return e;
             }
             cs->extra_floats = nfl;
         }
     }
-    // scratch: done words, watchdog word, per-block maxima, timelines, progress words and boundary rings of the sweep phases
+    // scratch: done words, watchdog / step words, per-block maxima, timelines, link regions, then progress words and
+    // boundary rings of the sweep phases
     const size_t flag_bytes = sweep_flag_words() * sizeof(unsigned long long);
     const size_t sor_rings = std::max(cs->plan[0].sor_ring_floats, pl.sor_ring_floats) * sizeof(float);
     const size_t gs_rings = std::max(std::max(cs->plan[0].gs_ring_floats, cs->plan[1].gs_ring_floats), pl.gs_ring_floats) * sizeof(float);
-    const size_t need = kDoneBytes + 256 + kVmaxBytes + 2 * kTraceOne + kChainMaxSweeps * flag_bytes + sor_rings +
-                        2 * kChainMaxGsPasses * gs_rings;
+    const size_t need = kFixedBytes + kChainMaxSweeps * flag_bytes + sor_rings + 2 * kChainMaxGsPasses * gs_rings;
     if (need > cs->bytes) {
+        if (multi && cs->buf) return cudaErrorInvalidValue;            // mapped by the neighbours: must not move
         e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) return e;
         if (cs->buf) cudaFree(cs->buf);
@@ -876,12 +1161,13 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         if (e != cudaSuccess) return e;
         cs->bytes = need;
     }
+    if (mode == 2) return cudaStreamSynchronize(st);
     unsigned char *b = cs->buf;
     unsigned *done = reinterpret_cast<unsigned *>(b);
     unsigned long long *err = reinterpret_cast<unsigned long long *>(b + kDoneBytes);
-    float *vmax = reinterpret_cast<float *>(b + kDoneBytes + 256);
-    unsigned long long *trace = reinterpret_cast<unsigned long long *>(b + kDoneBytes + 256 + kVmaxBytes + kind * kTraceOne);
-    unsigned char *b2 = b + kDoneBytes + 256 + kVmaxBytes + 2 * kTraceOne;
+    float *vmax = reinterpret_cast<float *>(b + kVmaxOff);
+    unsigned long long *trace = reinterpret_cast<unsigned long long *>(b + kTraceOff + kind * kTraceOne);
+    unsigned char *b2 = b + kFixedBytes;
     unsigned long long *flags[kChainMaxSweeps];
     for (int k = 0; k < kChainMaxSweeps; ++k) flags[k] = reinterpret_cast<unsigned long long *>(b2 + k * flag_bytes);
     float *rings_sor = reinterpret_cast<float *>(b2 + kChainMaxSweeps * flag_bytes);
@@ -889,9 +1175,12 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     for (int k = 0; k < 2 * kChainMaxGsPasses; ++k)
         rings_gs[k] = reinterpret_cast<float *>(b2 + kChainMaxSweeps * flag_bytes + sor_rings + k * gs_rings);
 
+    const int cw = pl.cw;
     ChainParams C{};
     C.W = A.W;
     C.H = A.H;
+    C.g = ChainGrid{A.W, A.H, G.pitch, G.jbase, G.j0, G.j1, cw, multi ? B->halo : 0, multi && B->has_left, multi && B->has_right,
+                    multi ? G.jbase - B->ncols : 0, multi ? G.jbase + B->ncols : 0};
     C.smem_floats = (int)(pl.smem / sizeof(float));
     C.epoch = ++cs->epoch;
     C.done = done;
@@ -899,23 +1188,72 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     C.timeout_ns = 20ull * 1000 * 1000 * 1000;
     C.trace = trace;
     C.vmax = vmax;
-    const int nblk = (A.H + kChainCols - 1) / kChainCols;
+    C.step_in = reinterpret_cast<unsigned *>(b + kDoneBytes + 64);
+    C.cta_count = reinterpret_cast<unsigned *>(b + kDoneBytes + 128);
+    const ChainPeer none;
+    const ChainPeer &PL = (multi && B->has_left) ? B->left : none, &PR = (multi && B->has_right) ? B->right : none;
+    if (PL.chain_buf) {
+        C.done_l = reinterpret_cast<unsigned *>(PL.chain_buf);
+        C.vmax_l = reinterpret_cast<float *>(PL.chain_buf + kVmaxOff);
+        C.step_out_l = reinterpret_cast<unsigned *>(PL.chain_buf + kDoneBytes + 64) + 1;    // this rank is its right neighbour
+    }
+    if (PR.chain_buf) {
+        C.done_r = reinterpret_cast<unsigned *>(PR.chain_buf);
+        C.vmax_r = reinterpret_cast<float *>(PR.chain_buf + kVmaxOff);
+        C.step_out_r = reinterpret_cast<unsigned *>(PR.chain_buf + kDoneBytes + 64) + 0;
+    }
+    // this rank's pointwise items: blocks of cw columns, numbered along the whole grid
+    const int nblk_all = (A.H + cw - 1) / cw;
+    const int blk0 = G.j0 / cw;
+    const int nblk = (G.j1 >= A.H ? nblk_all : G.j1 / cw) - blk0;
     const float h = 1.0f / (float)A.W;            // src/fluid_sim.cpp:304
     int np = 0, nwf = 0;
 
     auto pointwise_phase = [&](int kind_) -> ChainPhase & {
         ChainPhase &ph = C.ph[np++];
         ph.kind = kind_;
-        ph.ncl = ph.nitems = nblk;
+        ph.item0 = blk0;
+        ph.nitems = nblk;
+        ph.ncl = nblk_all;
         ph.nf = 1;
-        ph.cpv = kChainCols;
+        ph.cpv = cw;
         ph.shift = 0;
         ph.ndeps = 0;
         return ph;
     };
+    // a sweep phase of nstg stages with nstr strips per CTA over nf fields: this rank's CTAs of the global chain
+    auto sweep_phase = [&](int kind_, int nstr, int nstg, int S, int nf, float a, float c_recip, float omega, float *rings,
+                           int slot) -> ChainPhase & {
+        ChainPhase &ph = C.ph[np++];
+        const int shift = S * nstg;
+        const int NS_all = (A.H + shift + 31) / 32;       // the last stage's frame is shifted left by the pass's sweeps
+        const int s_begin = multi ? B->strip_begin : 0;
+        const int s_end = (!multi || B->strip_end < 0 || B->strip_end > NS_all) ? NS_all : B->strip_end;
+        const int ncta = (s_end - s_begin + nstr - 1) / nstr;
+        ph.kind = kind_;
+        ph.item0 = (s_begin / nstr) * nf;
+        ph.nitems = ncta * nf;
+        ph.ncl = (NS_all + nstr - 1) / nstr;
+        ph.nf = nf;
+        ph.cpv = 32 * nstr;
+        ph.shift = shift;
+        ph.wf = nwf;
+        ph.ndeps = 0;
+        WfKernelParams &P = C.wf[nwf++];
+        fill_wf(P, A.W, A.H, nstr, nstg, ncta, a, c_recip, omega, rings, flags[slot], ++scr.seq);
+        P.pitch = G.pitch;
+        P.jbase = G.jbase;
+        P.c_base = s_begin / nstr;
+        if (multi) {
+            P.link = chain_link(*B, b, slot, B->step * 8 + (unsigned long long)slot + 1);
+            P.link_seq_base = P.link.seq << 32;
+        }
+        return ph;
+    };
     // divergence -> pressure sweeps -> gradient (+ boundaries) of (u, v) with scratch (p, div); `after` = phase that
-    // produced u, v (or -1); returns the index of the gradient phase
-    auto projection = [&](float *u, float *v, float *p, float *div, int after, int gs_slot, float *bnd_extra) -> int {
+    // produced u, v (or -1); returns the index of the gradient phase.  lu, lv, lp / ru, rv: the neighbours' copies.
+    auto projection = [&](float *u, float *v, float *p, float *div, int after, int gs_slot, float *bnd_extra, float *lu, float *lv,
+                          float *lp, float *lx, float *ru, float *rv, float *rx) -> int {
         const int ph_div = np;
         {
             ChainPhase &ph = pointwise_phase(kPhDiv);
@@ -937,22 +1275,14 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             }
             const int ph_last = ph_gs;
             ph_gs = np;
-            ChainPhase &ph = C.ph[np++];
-            ph.kind = k == 0 ? kPhGs : kPhGsX0;
-            const int nstrips = (A.H + kChainSP * pl.gs_stages[k] + 31) / 32;     // the last stage's frame is shifted left by the pass's sweeps
-            const int ncta = (nstrips + pl.gs_nstr - 1) / pl.gs_nstr;
-            ph.ncl = ph.nitems = ncta;
-            ph.nf = 1;
-            ph.cpv = 32 * pl.gs_nstr;
-            ph.shift = kChainSP * pl.gs_stages[k];
-            ph.wf = nwf;
-            ph.ndeps = 0;
+            const int slot = 1 + gs_slot * kChainMaxGsPasses + k;
+            ChainPhase &ph = sweep_phase(k == 0 ? kPhGs : kPhGsX0, pl.gs_nstr, pl.gs_stages[k], kChainSP, 1, 0.0f, 1.0f, 1.0f,
+                                         rings_gs[slot - 1], slot);
             ph.dep[ph.ndeps++] = ChainDep{ph_prev, 0, 0, 0};                  // divergence (first pass) / walls of p (later passes) of the columns it loads
             if (k > 0) ph.dep[ph.ndeps++] = ChainDep{ph_last, 1, 0, 0};       // the previous pass has produced the columns this one overwrites
-            WfKernelParams &P = C.wf[nwf++];
-            const int slot = gs_slot * kChainMaxGsPasses + k;
-            fill_wf(P, A.W, A.H, pl.gs_nstr, pl.gs_stages[k], ncta, 0.0f, 1.0f, 1.0f, rings_gs[slot], flags[1 + slot], ++scr.seq);
+            WfKernelParams &P = C.wf[ph.wf];
             P.fld[0] = SweepField{k == 0 ? nullptr : p, div, p, 1.0f, 1.0f};  // p starts at 0 (:313, :316)
+            P.fld[0].out_peer = lp;                                           // result columns owed to the left rank
             P.fld[1] = P.fld[2] = P.fld[0];
         }
         ChainPhase &ph = pointwise_phase(kPhGrad);
@@ -961,6 +1291,9 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         ph.q = p;
         ph.c0 = h;
         ph.bnd_extra = bnd_extra;
+        ph.peer_l[0] = lu; ph.peer_l[1] = lv; ph.peer_l[2] = lx;
+        ph.peer_r[0] = ru; ph.peer_r[1] = rv; ph.peer_r[2] = rx;
+        ph.push_cols = multi ? B->halo : 0;               // the neighbours' traces reach this far into these columns
         ph.dep[ph.ndeps++] = ChainDep{ph_gs, 0, 1, 1};    // pressure of the block and one column either side
         ph.dep[ph.ndeps++] = ChainDep{ph_div, 1, 1, 1};   // the divergence blocks that read the u, v about to change
         return np - 1;
@@ -968,23 +1301,17 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
 
     int ph_sor = -1;
     if (A.sor_sweeps > 0) {
-        ChainPhase &ph = C.ph[np];
-        ph.kind = kPhSor;
-        ph.ncl = pl.sor_ncta;
-        ph.nf = 2;
-        ph.nitems = 2 * pl.sor_ncta;
-        ph.cpv = 32 * pl.sor_nstr;
-        ph.shift = A.sor_sweeps;
-        ph.wf = nwf;
-        ph.ndeps = 0;
-        WfKernelParams &P = C.wf[nwf++];
-        fill_wf(P, A.W, A.H, pl.sor_nstr, A.sor_sweeps / kChainSD, pl.sor_ncta, A.a, A.c_recip, A.omega, rings_sor, flags[0], ++scr.seq);
+        ph_sor = np;
+        ChainPhase &ph = sweep_phase(kPhSor, pl.sor_nstr, A.sor_sweeps / kChainSD, kChainSD, 2, A.a, A.c_recip, A.omega, rings_sor, 0);
+        WfKernelParams &P = C.wf[ph.wf];
         P.fld[0] = SweepField{A.u, A.u, A.u, -1.0f, 1.0f};    // setBoundary(1, u): negated on the i-walls
         P.fld[1] = SweepField{A.v, A.v, A.v, 1.0f, -1.0f};    // setBoundary(2, v): negated on the j-walls
+        P.fld[0].out_peer = PL.u;
+        P.fld[1].out_peer = PL.v;
         P.fld[2] = P.fld[0];
-        ph_sor = np++;
     }
-    const int ph_grad1 = projection(A.u, A.v, A.p, A.div, ph_sor, 0, nullptr);
+    const bool fold = A.with_density && A.density_pz;
+    const int ph_grad1 = projection(A.u, A.v, A.p, A.div, ph_sor, 0, nullptr, PL.u, PL.v, PL.p, nullptr, PR.u, PR.v, nullptr);
     if (A.with_advect) {
         // advect(1, u), advect(2, v) (:401-402) into the buffers the first projection used as pressure / divergence
         const int ph_gs1 = ph_grad1 - 1;
@@ -1002,15 +1329,17 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             ph.pz = 0;
             ph.c0 = -(A.dt * (float)A.W);              // -dt0, dt0 = dt * width (:264)
             ph.reach_phase = ph_grad1;
+            ph.peer_l[0] = PL.p; ph.peer_l[1] = PL.div;
+            ph.peer_r[0] = PR.p; ph.peer_r[1] = PR.div;
+            ph.push_cols = multi ? cw : 0;             // the neighbour's divergence reads one column across
             ph.dep[ph.ndeps++] = ChainDep{ph_grad1, 1, 1, 1};                                // gradient blocks still reading p here
             const int sh = C.ph[ph_gs1].shift;                                             // of the projection's last pass
             ph.dep[ph.ndeps++] = ChainDep{ph_gs1, 1, sh, -sh};                             // sweep items that load div here
         }
         // the second projection works in scratch of its own: u, v stay intact for traces that start far away
-        const float *dens = A.with_density ? A.d : nullptr;
-        const int ph_grad2 = projection(A.p, A.div, cs->extra[0], cs->extra[1], ph_adv, 1,
-                                        (A.with_density && A.density_pz) ? A.d : nullptr);
-        if (dens) {
+        const int ph_grad2 = projection(A.p, A.div, cs->extra[0], cs->extra[1], ph_adv, 1, fold ? A.d : nullptr, PL.p, PL.div,
+                                        PL.extra[0], fold ? PL.d : nullptr, PR.p, PR.div, fold ? PR.d : nullptr);
+        if (A.with_density) {
             ChainPhase &ph = pointwise_phase(kPhAdvect);
             ph.u = A.p;
             ph.v = A.div;
@@ -1020,13 +1349,16 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             ph.pz = A.density_pz;
             ph.c0 = -(A.dt * (float)A.W);
             ph.reach_phase = ph_grad2;
+            ph.peer_l[0] = PL.nd;
+            ph.peer_r[0] = PR.nd;
+            ph.push_cols = multi ? B->halo : 0;        // the next step's density traces reach into these columns
         }
     }
     C.nphases = np;
     cs->last_nphases[kind] = np;
 
     void *args[] = {&C};
-    const void *kern = A.sor_sweeps > 0 ? (const void *)chain_kernel<kChainSD, kChainSP> : (const void *)chain_kernel<0, kChainSP>;
+    const void *kern = chain_kernel_ptr(A.sor_sweeps > 0, multi, pl.cw);
     return cudaLaunchCooperativeKernel(kern, dim3(pl.grid), dim3(kChainThreads), args, pl.smem, st);
 }
 
@@ -1038,7 +1370,7 @@ cudaError_t chain_read_trace(ChainState *cs, int which, unsigned long long *out,
     *nphases = 0;
     if (!cs || !cs->buf || which < 0 || which > 1) return cudaSuccess;
     const unsigned long long *trace =
-        reinterpret_cast<const unsigned long long *>(cs->buf + kDoneBytes + 256 + kVmaxBytes + which * kTraceOne);
+        reinterpret_cast<const unsigned long long *>(cs->buf + kTraceOff + which * kTraceOne);
     const int np = std::min(cs->last_nphases[which], max_phases), ni = std::min(max_items, kChainMaxItems);
     for (int p = 0; p < np; ++p) {
         cudaError_t e = cudaMemcpy(out + (size_t)p * max_items * 3, trace + (size_t)p * kChainMaxItems * 3,

@@ -109,6 +109,15 @@ struct fsb_sim {
     float *peer_left_f[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // left rank's fields (same roles)
     void *peer_left_base[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; // as opened (for closing)
     int left_ncols = 0;                                  // columns owned by the left rank
+    // chained launch on column blocks: the neighbours' fields (role order, swapped with this rank's), second-projection
+    // scratch and chain buffers, mapped through CUDA IPC
+    int halo = 0;
+    bool blk_chain_ready = false;
+    float *peer_l_f[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    float *peer_r_f[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    void *peer_chain[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};   // [left / right][buf, extra0, extra1]
+    void *peer_r_base[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    unsigned long long blk_steps = 0;
     // optional per-kernel-class timing (CUDA events on the simulation's stream)
     bool profiling = false;
     struct ProfRec { int cat; cudaEvent_t a, b; };
@@ -550,11 +559,11 @@ int chained_launch(fsb_sim *s, bool with_diffuse, bool whole_step, float dt, boo
             A.nd = s->f[FSB_PREV_DENSITY];
         }
     }
-    cudaError_t e = launch_chain(A, s->chain, s->sweep, s->stream, true);
+    cudaError_t e = launch_chain(A, s->chain, s->sweep, s->stream, 1);
     if (e == cudaErrorNotSupported) return FSB_OK;
     if (e == cudaSuccess) {
         ProfScope ps(s, FSB_PROF_CHAIN);
-        e = launch_chain(A, s->chain, s->sweep, s->stream, false);
+        e = launch_chain(A, s->chain, s->sweep, s->stream, 0);
     }
     if (e != cudaSuccess) return fail_cuda(e, "chained launch");
     s->launches += 1;
@@ -673,12 +682,6 @@ static int create_common(const fsb_params *p, const GridView *block, fsb_sim **o
 
 int fsb_create(const fsb_params *p, fsb_sim **out) { return create_common(p, nullptr, out); }
 
-/* layout of the link buffer shared between neighbouring ranks */
-static const size_t kLinkRingBytes = (size_t)kMaxSweepFields * kLinkStages * kLinkRingFloats * sizeof(float);
-static const size_t kLinkFlagBytes = (size_t)kMaxSweepFields * kLinkStages * sizeof(unsigned long long);
-static const size_t kLinkRetBytes = 64;   // completion counters of the columns stored here by the right rank
-static const size_t kLinkBytes = kLinkRingBytes + 2 * kLinkFlagBytes + kLinkRetBytes;
-
 int fsb_create_block(const fsb_params *p, int col_begin, int col_end, int halo, fsb_sim **out)
 {
     if (!p || !out) return fail(FSB_EINVAL, "fsb_create_block: null argument");
@@ -691,7 +694,9 @@ int fsb_create_block(const fsb_params *p, int col_begin, int col_end, int halo, 
     G.jbase = col_begin - halo;
     G.j0 = col_begin;
     G.j1 = col_end;
-    return create_common(p, &G, out);
+    const int rc = create_common(p, &G, out);
+    if (rc == FSB_OK) (*out)->halo = halo;
+    return rc;
 }
 
 static int create_common(const fsb_params *p, const GridView *block, fsb_sim **out)
@@ -793,6 +798,11 @@ int fsb_destroy(fsb_sim *s)
         noise_tables_destroy(s->noise_tables);
         for (int k = 0; k < 6; ++k)
             if (s->peer_left_base[k]) cudaIpcCloseMemHandle(s->peer_left_base[k]);
+        for (int k = 0; k < 6; ++k)
+            if (s->peer_r_base[k]) cudaIpcCloseMemHandle(s->peer_r_base[k]);
+        for (int side = 0; side < 2; ++side)
+            for (int k = 0; k < 3; ++k)
+                if (s->peer_chain[side][k]) cudaIpcCloseMemHandle(s->peer_chain[side][k]);
         if (s->peer_left) cudaIpcCloseMemHandle(s->peer_left);
         if (s->peer_right) cudaIpcCloseMemHandle(s->peer_right);
         if (s->link_buf) cudaFree(s->link_buf);
@@ -861,7 +871,8 @@ int fsb_add_density(fsb_sim *s, int x, int y, float amount)
 {
     if (!s) return fail(FSB_EINVAL, "fsb_add_density: null handle");
     if (!in_range(s, x, y)) return FSB_OK;   // silently ignored, src/fluid_sim.cpp:426
-    if (y < s->G.j0 || y >= s->G.j1) return FSB_OK;   // another rank's column
+    // a column block also keeps the columns of its halo current (the neighbour that owns them applies the same call)
+    if (y < s->G.jbase || y >= s->G.jbase + s->G.pitch) return FSB_OK;   // a column this rank does not store
     const int cell = x * s->G.pitch + (y - s->G.jbase);
     s->pending.push_back(SourceEntry{cell, 0, amount});
     if (s->mirror_valid[0]) s->mirror[0][cell] += amount;
@@ -872,7 +883,7 @@ int fsb_add_velocity(fsb_sim *s, int x, int y, float ax, float ay)
 {
     if (!s) return fail(FSB_EINVAL, "fsb_add_velocity: null handle");
     if (!in_range(s, x, y)) return FSB_OK;   // src/fluid_sim.cpp:434
-    if (y < s->G.j0 || y >= s->G.j1) return FSB_OK;   // another rank's column
+    if (y < s->G.jbase || y >= s->G.jbase + s->G.pitch) return FSB_OK;   // a column this rank does not store
     const int cell = x * s->G.pitch + (y - s->G.jbase);
     s->pending.push_back(SourceEntry{cell, 1, ax});
     s->pending.push_back(SourceEntry{cell, 2, ay});
@@ -1284,6 +1295,170 @@ int fsb_blk_wait_returns(fsb_sim *s, int slot, unsigned long long expected)
     const unsigned long long *c = reinterpret_cast<const unsigned long long *>(s->link_buf + kLinkRingBytes + 2 * kLinkFlagBytes) + slot;
     FSB_CUDA(launch_wait_counter(c, expected, s->stream));
     s->launches += 1;
+    return FSB_OK;
+}
+
+/* ---- the whole step of a column block as ONE chained launch (chain.cu) -----------------------------------------------
+ * Every rank runs its blocks of the wave; items near a rank boundary store their results into the neighbour's halo as
+ * well and publish their done-words there, so a rank only ever reads its own memory and no collective, halo exchange
+ * or host round trip sits inside a step.  Set-up: fsb_blk_chain_prepare on every rank, exchange the handles
+ * (fsb_blk_chain_handles, fsb_field_handles), fsb_blk_chain_connect; then fsb_blk_step per step. */
+static ChainArgs blk_chain_args(fsb_sim *s, float dt, const ChainBlock *B)
+{
+    ChainArgs A{};
+    A.W = s->W;
+    A.H = s->H;
+    A.u = s->f[FSB_VELOCITY_X];
+    A.v = s->f[FSB_VELOCITY_Y];
+    A.p = s->f[FSB_PREV_VEL_X];
+    A.div = s->f[FSB_PREV_VEL_Y];
+    A.d = s->f[FSB_DENSITY];
+    A.nd = s->f[FSB_PREV_DENSITY];
+    A.gs_sweeps = s->prm.proj_iters;
+    A.sor_sweeps = s->prm.diff_iters;
+    A.a = dt * s->prm.viscosity * (float)s->W * (float)s->H;
+    A.c_recip = 1.0f / (1.0f + 4.0f * A.a);
+    A.omega = s->prm.omega;
+    A.dt = dt;
+    A.with_advect = 1;
+    A.with_density = 1;
+    A.density_pz = s->prm.diff_iters > 0 ? 1 : 0;
+    A.blk = B;
+    return A;
+}
+
+static void blk_chain_block(const fsb_sim *s, ChainBlock &B)
+{
+    B.G = s->G;
+    B.halo = s->halo;
+    B.strip_begin = s->strip_begin;
+    B.strip_end = s->strip_end;
+    B.has_left = s->peer_chain[0][0] != nullptr;
+    B.has_right = s->peer_chain[1][0] != nullptr;
+    B.ncols = s->G.j1 - s->G.j0;
+    B.step = s->blk_steps;
+    auto fill = [&](ChainPeer &P, float *const *f, void *const *c) {
+        P.d = f[FSB_DENSITY]; P.u = f[FSB_VELOCITY_X]; P.v = f[FSB_VELOCITY_Y];
+        P.nd = f[FSB_PREV_DENSITY]; P.p = f[FSB_PREV_VEL_X]; P.div = f[FSB_PREV_VEL_Y];
+        P.chain_buf = static_cast<unsigned char *>(c[0]);
+        P.extra[0] = static_cast<float *>(c[1]);
+        P.extra[1] = static_cast<float *>(c[2]);
+    };
+    if (B.has_left) fill(B.left, s->peer_l_f, s->peer_chain[0]);
+    if (B.has_right) fill(B.right, s->peer_r_f, s->peer_chain[1]);
+}
+
+/* Is there a chained configuration for this block (sweep counts that are multiples of 10 / 5, non-zero viscosity, zero
+ * density diffusion, RK4, a halo at least as wide as the fused sweeps)?  Allocates the buffers the neighbours will map.
+ * Returns FSB_OK, or FSB_ELIMIT when the block must use the pass-by-pass entry points instead. */
+int fsb_blk_chain_prepare(fsb_sim *s, float dt)
+{
+    if (!s || !s->is_block) return fail(FSB_EINVAL, "fsb_blk_chain_prepare: not a block simulation");
+    DeviceGuard guard(s->device);
+    const float ad = dt * s->prm.diffusion * (float)s->W * (float)s->H;
+    const float av = dt * s->prm.viscosity * (float)s->W * (float)s->H;
+    if (s->prm.advect_scheme != FSB_ADVECT_RK4 || ad != 0.0f || av == 0.0f || s->prm.diff_iters <= 0 || s->chain_level < 1)
+        return fail(FSB_ELIMIT, "fsb_blk_chain_prepare: these parameters have no chained configuration");
+    ChainBlock B;
+    blk_chain_block(s, B);
+    B.has_left = B.has_right = false;        // sizes do not depend on the neighbours
+    ChainArgs A = blk_chain_args(s, dt, &B);
+    const cudaError_t e = launch_chain(A, s->chain, s->sweep, s->stream, 2);
+    if (e == cudaErrorNotSupported) return fail(FSB_ELIMIT, "fsb_blk_chain_prepare: this grid / these sweep counts have no chained configuration");
+    if (e != cudaSuccess) return fail_cuda(e, "fsb_blk_chain_prepare");
+    return FSB_OK;
+}
+
+/* 3 x 64 bytes: CUDA IPC handles of the chain buffer and the two second-projection scratch fields. */
+int fsb_blk_chain_handles(fsb_sim *s, void *handles3x64)
+{
+    if (!s || !handles3x64 || !s->chain) return fail(FSB_EINVAL, "fsb_blk_chain_handles: call fsb_blk_chain_prepare first");
+    DeviceGuard guard(s->device);
+    void *bufs[3];
+    chain_shared_buffers(s->chain, bufs);
+    for (int k = 0; k < 3; ++k) {
+        if (!bufs[k]) return fail(FSB_EINVAL, "fsb_blk_chain_handles: buffers not allocated");
+        FSB_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t *>(static_cast<unsigned char *>(handles3x64) + 64 * k), bufs[k]));
+    }
+    return FSB_OK;
+}
+
+/* left / right: the neighbours' fsb_blk_chain_handles (3 x 64) and fsb_field_handles (6 x 64) output, NULL where there
+ * is no neighbour.  The left neighbour's fields may already be mapped by fsb_link_connect_fields. */
+int fsb_blk_chain_connect(fsb_sim *s, const void *left_chain3x64, const void *left_fields6x64, const void *right_chain3x64,
+                          const void *right_fields6x64)
+{
+    if (!s || !s->is_block || !s->chain) return fail(FSB_EINVAL, "fsb_blk_chain_connect: call fsb_blk_chain_prepare first");
+    DeviceGuard guard(s->device);
+    auto open = [&](const void *h64, void **out) -> int {
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, h64, sizeof(h));
+        FSB_CUDA(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+        return FSB_OK;
+    };
+    if (left_chain3x64) {
+        for (int k = 0; k < 3; ++k) FSB_TRY(open(static_cast<const unsigned char *>(left_chain3x64) + 64 * k, &s->peer_chain[0][k]));
+        if (!s->peer_left_f[0]) {
+            if (!left_fields6x64) return fail(FSB_EINVAL, "fsb_blk_chain_connect: left field handles missing");
+            for (int k = 0; k < 6; ++k) {
+                FSB_TRY(open(static_cast<const unsigned char *>(left_fields6x64) + 64 * k, &s->peer_left_base[k]));
+                s->peer_left_f[k] = static_cast<float *>(s->peer_left_base[k]);
+            }
+        }
+        for (int k = 0; k < 6; ++k) s->peer_l_f[k] = s->peer_left_f[k];
+    }
+    if (right_chain3x64) {
+        if (!right_fields6x64) return fail(FSB_EINVAL, "fsb_blk_chain_connect: right field handles missing");
+        for (int k = 0; k < 3; ++k) FSB_TRY(open(static_cast<const unsigned char *>(right_chain3x64) + 64 * k, &s->peer_chain[1][k]));
+        for (int k = 0; k < 6; ++k) {
+            FSB_TRY(open(static_cast<const unsigned char *>(right_fields6x64) + 64 * k, &s->peer_r_base[k]));
+            s->peer_r_f[k] = static_cast<float *>(s->peer_r_base[k]);
+        }
+    }
+    s->blk_chain_ready = true;
+    return FSB_OK;
+}
+
+/* One FluidSim::step of this rank's column block: the velocity noise, then everything else as one chained launch.
+ * Every rank calls it once per step.  Asynchronous; fsb_blk_chain_error tells, after a sync, whether a back-trace
+ * left the halo (the step's results are then invalid: create the blocks with a wider halo). */
+int fsb_blk_step(fsb_sim *s, float dt)
+{
+    if (!s || !s->is_block || !s->blk_chain_ready) return fail(FSB_EINVAL, "fsb_blk_step: chain not connected");
+    DeviceGuard guard(s->device);
+    FSB_TRY(flush_sources(s));
+    invalidate_mirror(s);
+    FSB_TRY(add_noise(s));
+    ChainBlock B;
+    blk_chain_block(s, B);
+    ChainArgs A = blk_chain_args(s, dt, &B);
+    cudaError_t e;
+    {
+        ProfScope ps(s, FSB_PROF_CHAIN);
+        e = launch_chain(A, s->chain, s->sweep, s->stream, 0);
+    }
+    if (e != cudaSuccess) return fail_cuda(e, "fsb_blk_step: chained launch");
+    s->launches += 1;
+    s->blk_steps += 1;
+    // the advected fields sit in the former prev buffers: swap roles, here and in the neighbours' tables
+    auto swap_roles = [](float **f) {
+        std::swap(f[FSB_VELOCITY_X], f[FSB_PREV_VEL_X]);
+        std::swap(f[FSB_VELOCITY_Y], f[FSB_PREV_VEL_Y]);
+        std::swap(f[FSB_DENSITY], f[FSB_PREV_DENSITY]);
+    };
+    swap_roles(s->f);
+    swap_roles(s->peer_l_f);
+    swap_roles(s->peer_r_f);
+    swap_roles(s->peer_left_f);
+    return FSB_OK;
+}
+
+int fsb_blk_chain_error(fsb_sim *s, unsigned long long *word)
+{
+    if (!s || !word) return fail(FSB_EINVAL, "fsb_blk_chain_error: bad argument");
+    DeviceGuard guard(s->device);
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    FSB_CUDA(chain_read_error(s->chain, word));
     return FSB_OK;
 }
 

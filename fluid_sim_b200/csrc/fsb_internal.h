@@ -93,7 +93,28 @@ cudaError_t launch_sweep_pass(const SweepLaunch &L, SweepScratch &scr, cudaStrea
 // sor_sweeps > 0, project(u, v, p, div); with_advect: advect(u), advect(v) into (p, div) and the second projection on
 // them; with_density: densityStep (DIFFUSION == 0) with the final velocity, d -> nd.
 // cudaErrorNotSupported: no chained configuration for this grid / these sweep counts.
+// layout of a link buffer (the rings, flags and counters through which neighbouring ranks hand the strip chain over)
+constexpr size_t kLinkRingBytes = (size_t)kMaxSweepFields * kLinkStages * kLinkRingFloats * sizeof(float);
+constexpr size_t kLinkFlagBytes = (size_t)kMaxSweepFields * kLinkStages * sizeof(unsigned long long);
+constexpr size_t kLinkRetBytes = 64;   // completion counters of the columns stored here by the right rank
+constexpr size_t kLinkBytes = kLinkRingBytes + 2 * kLinkFlagBytes + kLinkRetBytes;
+
 struct ChainState;
+// One neighbouring rank of a column block, as seen from this GPU (every pointer is a peer mapping).
+struct ChainPeer {
+    float *u = nullptr, *v = nullptr, *p = nullptr, *div = nullptr, *d = nullptr, *nd = nullptr;
+    float *extra[2] = {nullptr, nullptr};      // its second-projection scratch
+    unsigned char *chain_buf = nullptr;        // its ChainState buffer (done words, maxima, step words, link regions)
+};
+struct ChainBlock {
+    GridView G;
+    int halo;
+    int strip_begin, strip_end;                // 32-column strips of the sweep chain this rank runs (-1: to the end)
+    bool has_left, has_right;
+    ChainPeer left, right;
+    int ncols;                                 // columns every rank owns
+    unsigned long long step;                   // number of this step, identical on all ranks
+};
 struct ChainArgs {
     int W, H;
     float *u, *v, *p, *div;
@@ -104,8 +125,15 @@ struct ChainArgs {
     float dt;
     float *d, *nd;             // density and the buffer that receives the advected density
     int density_pz;            // diffusion sweeps ran with a == 0: boundaries of d + folded (v + 0.0f) taps
+    const ChainBlock *blk = nullptr;   // column block of a multi-rank run (nullptr: the whole grid on this GPU)
 };
-cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st, bool query_only);
+// mode 0: launch; 1: only tell whether a configuration exists; 2: also allocate the scratch (so that its IPC handles can
+// be exchanged before the first launch)
+cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr, cudaStream_t st, int mode);
+// the buffers neighbouring ranks map: [0] ChainState buffer, [1], [2] second-projection scratch (after mode 2)
+void chain_shared_buffers(ChainState *cs, void *out[3]);
+// error word of the chained launches (0: none; bit 63: an advection trace left the columns this rank can see)
+cudaError_t chain_read_error(ChainState *cs, unsigned long long *word);
 void chain_state_destroy(ChainState *cs);
 cudaError_t chain_read_trace(ChainState *cs, int which, unsigned long long *out, int max_phases, int max_items, int *nphases);
 

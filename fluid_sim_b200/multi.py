@@ -118,7 +118,8 @@ class BlockFluidSim:
     """This rank's column block of a width x height simulation spread over `dist.get_world_size()` GPUs."""
 
     def __init__(self, width, height, proj_iters=20, diff_iters=5, viscosity=1e-4, diffusion=0.0, omega=1.5,
-                 noise="glibc", noise_seed=1, noise_pos=0, device=0, halo=128, levels=10, strips_per_cta=1, reach=None, group=None):
+                 noise="glibc", noise_seed=1, noise_pos=0, device=0, halo=128, levels=10, strips_per_cta=1, reach=None, group=None,
+                 chain=True):
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.group = group
         self.width, self.height = width, height
@@ -174,6 +175,9 @@ class BlockFluidSim:
         self.trace = None      # set to {} to collect GPU time per phase (CUDA events on the simulation's stream)
         self._ev = []
         self._connect()
+        self.chained = False
+        if chain:
+            self._connect_chain()
 
     # -- plumbing ----------------------------------------------------------------------------------
     def _check(self, rc):
@@ -203,6 +207,36 @@ class BlockFluidSim:
         self.returned = [0, 0, 0]    # strips' worth of columns the right rank has stored here so far, per sweep slot
         dist.barrier(group=self.group)
 
+    def _connect_chain(self):
+        """The whole step as one chained launch per rank (csrc/chain.cu): possible when every rank has a chained
+        configuration (sweep counts that are multiples of 10 / 5, non-zero viscosity, zero density diffusion).  The
+        ranks then map each other's fields, second-projection scratch and chain buffers (CUDA IPC); a step is
+        `fsb_blk_step` and nothing else - no halo exchange, no collective, no tensor operation."""
+        rc = self._lib.fsb_blk_chain_prepare(self._h, C.c_float(0.01))
+        ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        if int(ok.item()) != 1:
+            return
+        ch = (C.c_ubyte * 192)()
+        self._check(self._lib.fsb_blk_chain_handles(self._h, ch))
+        fh = (C.c_ubyte * 384)()
+        self._check(self._lib.fsb_field_handles(self._h, fh))
+        t = torch.tensor(list(ch) + list(fh), dtype=torch.uint8, device=self.device)
+        allh = [torch.empty_like(t) for _ in range(self.world)]
+        dist.all_gather(allh, t, group=self.group)
+        left, right = _neighbours(self.rank, self.world)
+
+        def pack(r):
+            if r is None:
+                return None, None
+            raw = allh[r].cpu().tolist()
+            return (C.c_ubyte * 192)(*raw[:192]), (C.c_ubyte * 384)(*raw[192:])
+        lc, lf = pack(left)
+        rc_, rf = pack(right)
+        self._check(self._lib.fsb_blk_chain_connect(self._h, lc, lf, rc_, rf))
+        dist.barrier(group=self.group)
+        self.chained = True
+
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
             self._lib.fsb_destroy(self._h)
@@ -225,6 +259,13 @@ class BlockFluidSim:
 
     def sync(self):
         self._check(self._lib.fsb_sync(self._h))
+        if self.chained:
+            w = C.c_uint64()
+            self._check(self._lib.fsb_blk_chain_error(self._h, C.byref(w)))
+            if w.value:
+                raise FsbError("BlockFluidSim: a back-trace left the halo columns (or a wait timed out) in a chained step, "
+                               f"error word {w.value:#x}; results are invalid (create the blocks with a wider `halo`)")
+            return
         over = float(self._overshoot.item())
         if over > 0:
             raise FsbError(f"BlockFluidSim: an advection reached {int(over)} columns past the {self.reach} exchanged; "
@@ -431,6 +472,9 @@ class BlockFluidSim:
         self._mark("pointwise")
 
     def step(self, dt=0.01):
+        if self.chained:
+            self._check(self._lib.fsb_blk_step(self._h, C.c_float(dt)))
+            return
         with torch.cuda.stream(self.stream):
             self._mark("start")
             self._check(self._lib.fsb_op_add_noise(self._h))

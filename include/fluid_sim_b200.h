@@ -201,6 +201,18 @@ int fsb_blk_add_zero(fsb_sim *s, int n, const int *fields);
 int fsb_blk_set_boundary(fsb_sim *s, int n, const int *fields, const int *bs, const int *plus_zero);
 int fsb_blk_divergence(fsb_sim *s);
 int fsb_blk_gradient(fsb_sim *s);
+/* The whole step of a column block as one chained launch (no halo exchange, collective or host round trip inside a
+ * step: blocks near a rank boundary store their results into the neighbour's halo through peer mappings and publish
+ * their progress words there).  Set-up on every rank: fsb_blk_chain_prepare (FSB_ELIMIT: these parameters need the
+ * pass-by-pass entry points above), exchange fsb_blk_chain_handles (3 x 64 bytes) and fsb_field_handles with both
+ * neighbours, fsb_blk_chain_connect; then fsb_blk_step once per step on every rank.  fsb_blk_chain_error (synchronises):
+ * non-zero if a back-trace left the halo (bit 63) or a wait timed out. */
+int fsb_blk_chain_prepare(fsb_sim *s, float dt);
+int fsb_blk_chain_handles(fsb_sim *s, void *handles3x64);
+int fsb_blk_chain_connect(fsb_sim *s, const void *left_chain3x64, const void *left_fields6x64, const void *right_chain3x64,
+                          const void *right_fields6x64);
+int fsb_blk_step(fsb_sim *s, float dt);
+int fsb_blk_chain_error(fsb_sim *s, unsigned long long *word);
 /* One float in device memory: largest |velocityY| written by fsb_blk_gradient into the owned columns since the caller
  * cleared it; bounds the columns the next advection's back-traces can move (src/fluid_sim.cpp:264, :275). */
 int fsb_blk_vmax_word(fsb_sim *s, void **dptr);

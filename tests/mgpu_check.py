@@ -28,6 +28,7 @@ def main():
     visc, diff = float(opt.get("visc", 1e-4)), float(opt.get("diff", 0.0))
     halo = int(opt.get("halo", 128))
     demo = int(opt.get("demo", 0))           # 1: the reference's start-up injection (|v| = 2, src/main.cpp:351-360)
+    chain = int(opt.get("chain", 1))         # 0: pass-by-pass launches with NCCL halo exchanges
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -42,13 +43,13 @@ def main():
                 if i * i + j * j < 25:
                     d[W // 2 + i, H // 2 + j] += np.float32(10.0)
                     v[W // 2 + i, H // 2 + j] += np.float32(2.0)
-    sim = BlockFluidSim(W, H, P, D, viscosity=visc, diffusion=diff, device=local, halo=halo)
+    sim = BlockFluidSim(W, H, P, D, viscosity=visc, diffusion=diff, device=local, halo=halo, chain=bool(chain))
     for f, arr in ((fsb.DENSITY, d), (fsb.VELOCITY_X, u), (fsb.VELOCITY_Y, v)):
         sim.set_from_global(f, arr)
     reaches = []
     for _ in range(steps):
         sim.step(0.01)
-        reaches.append(sim.reach)
+        reaches.append("chained" if sim.chained else sim.reach)
     sim.sync()
     got = [sim.gather(f) for f in (fsb.DENSITY, fsb.VELOCITY_X, fsb.VELOCITY_Y)]
     ok = True
