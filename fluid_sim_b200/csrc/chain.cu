@@ -785,22 +785,25 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
     for (int p = 0; p < C.nphases; ++p) {
         const ChainPhase &ph = C.ph[p];
         for (int li = blockIdx.x; li < ph.nitems; li += gridDim.x) {
-            int reach_rows = 1 << 30, reach_cols = 1 << 30;
             {
                 const ChainItem I = chain_item(C, p, li);
                 if (threadIdx.x == 0) C.trace[((size_t)p * kChainMaxItems + li) * 3] = global_timer_ns();
                 chain_wait<MR>(C, p, I.cl, MR && I.data_l, MR && I.data_r);
-                if (ph.kind == kPhAdvect) chain_advect_wait<MR>(C, ph, p, I.cl, -ph.c0, &reach_rows, &reach_cols);
-                if (threadIdx.x == 0) C.trace[((size_t)p * kChainMaxItems + li) * 3 + 1] = global_timer_ns();
             }
             if (ph.kind == kPhSor) {
+                if (threadIdx.x == 0) C.trace[((size_t)p * kChainMaxItems + li) * 3 + 1] = global_timer_ns();
                 if constexpr (SD > 0) wf_pass<SD, kSor, true>(C.wf[ph.wf], li / ph.nf, li % ph.nf, smem);
             } else if (ph.kind == kPhGs) {
+                if (threadIdx.x == 0) C.trace[((size_t)p * kChainMaxItems + li) * 3 + 1] = global_timer_ns();
                 wf_pass<SP, kGaussSeidel, false>(C.wf[ph.wf], li, 0, smem);
             } else if (ph.kind == kPhGsX0) {
+                if (threadIdx.x == 0) C.trace[((size_t)p * kChainMaxItems + li) * 3 + 1] = global_timer_ns();
                 wf_pass<SP, kGaussSeidel, true>(C.wf[ph.wf], li, 0, smem);     // a later pass of the same projection
             } else {
                 const int cl = ph.item0 + li;     // pointwise phases: one field, item = block
+                int reach_rows = 1 << 30, reach_cols = 1 << 30;
+                if (ph.kind == kPhAdvect) chain_advect_wait<MR>(C, ph, p, cl, -ph.c0, &reach_rows, &reach_cols);
+                if (threadIdx.x == 0) C.trace[((size_t)p * kChainMaxItems + li) * 3 + 1] = global_timer_ns();
                 if (ph.kind == kPhBndP) {
                     ChainPush none{false, false, 0, 0};
                     chain_boundary<MR, CW>(ph.q, nullptr, nullptr, none, 0, 0, g, cl * CW);       // setBoundary(0, p) between two passes (:330)
