@@ -522,12 +522,11 @@ int chained_launch(fsb_sim *s, bool with_diffuse, bool whole_step, float dt, boo
     *done = false;
     if (density_done) *density_done = false;
     if (s->chain_level < 1 || s->is_block || s->tune_strips || s->tune_levels || s->tune_stages) return FSB_OK;
-    // Measured (tools/chain_ab.py): the chained launch wins when the grid has enough 64-column blocks to spread its
-    // pointwise phases over the SMs and is not much taller than wide (1024 x 8192: 2.0x, 8192^2: 1.26x, 4096^2: 1.07x);
-    // narrow or tall grids (2048^2: 1.0x, 200^2: 0.92x, 16384 x 2048: 0.73x, 32768 x 4096: 0.86x) keep one launch per pass.
-    // FSB_CHAIN=3 forces the chained launch wherever a configuration exists.
-    if (s->chain_level < 3 && (s->H < 4096 || s->W > 2 * s->H)) return FSB_OK;
-    if (whole_step && (s->chain_level < 2 || s->prm.advect_scheme != FSB_ADVECT_RK4)) return FSB_OK;
+    // Measured (tools/chain_ab.py, ms per step, one launch per pass -> chained): 8192^2 P=40 20.9 -> 16.4, 1024 x 8192
+    // 12.7 -> 6.5, 4096^2 10.0 -> 7.8, 2048^2 4.33 -> 3.69, 200^2 0.64 -> 0.62; grids much taller than wide lose
+    // (16384 x 2048: 14.8 -> 18.7, 32768 x 4096: 68.4 -> 71.2: every block is a long serial walk for one CTA) and keep
+    // one launch per pass.  FSB_CHAIN=3 / fsb_set_chain_level(3) forces the chained launch wherever a configuration exists.
+    if (s->chain_level < 3 && s->W > 2 * s->H) return FSB_OK;
     ChainArgs A{};
     A.W = s->W;
     A.H = s->H;
