@@ -196,7 +196,8 @@ def main():
     ap.add_argument("--proj", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-scaling-base", action="store_true", help="skip the extra single-GPU run of the weak-scaling workload")
-    ap.add_argument("--workload", default="", help="config5: run the weak-scaling per-GPU workload at N=1 too; config4: 16384^2, P=20, strong scaling")
+    ap.add_argument("--workload", default="", help="config5: run the weak-scaling per-GPU workload at N=1 too; config4: 16384^2, P=20, strong scaling; "
+                    "view: time the headless density / velocity-glyph views")
     ap.add_argument("--strips-per-cta", type=int, default=0)
     ap.add_argument("--sweeps-per-warp", type=int, default=0)
     ap.add_argument("--max-stages", type=int, default=0)
@@ -244,6 +245,52 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    if args.workload == "view":
+        # the headless views (what the reference's viewer draws, src/main.cpp:383-514) at the reference's
+        # 800 x 600 window.  Not the north-star metric: a separate line, pixels per second per view.
+        import ctypes as C
+        pw, ph = 800, 600
+        out = {"metric": "view_pixels_per_sec", "unit": "pixels/s", "n_gpus": 1, "steps": K, "warmup": max(Wm, 3),
+               "higher_is_better": True, "dtype": "f32 -> rgba8", "data": "synthetic", "vs_baseline": None,
+               "config": {"workload": "headless density and velocity-glyph views, 800x600 window", "grids": []}, "views": []}
+        peak, _ = measured_peak_gbs()
+        for n in (200, 2048):
+            sim = fsb.FluidSim(n, n, 20, 5, device=local_rank)
+            d, u, v = vortex_lattice(n, n)
+            sim.write(fsb.DENSITY, d); sim.write(fsb.VELOCITY_X, u); sim.write(fsb.VELOCITY_Y, v)
+            for _ in range(2):
+                sim.step(0.01)
+            sim.sync()
+            st = torch.cuda.ExternalStream(sim.stream(), device=torch.device("cuda", local_rank))
+            img = np.empty((ph, pw, 4), np.uint8)
+            dptr = C.c_void_p()
+            res = {}
+            for name, call in (("density", lambda: sim._check(sim._lib.fsb_view_density_device(sim._h, pw, ph, C.byref(dptr)))),
+                               ("density+glyphs (with the 1.9 MB read-back)", lambda: sim.view_velocity(pw, ph, img))):
+                for _ in range(max(Wm, 3)):
+                    call()
+                sim.sync()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0 = time.perf_counter()
+                e0.record(st)
+                for _ in range(K):
+                    call()
+                e1.record(st)
+                sim.sync()
+                ms = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / K
+                res[name] = {"ms_per_frame": ms, "pixels_per_sec": pw * ph / (ms * 1e-3),
+                             "gbs_at_8_bytes_per_pixel": pw * ph * 8 / (ms * 1e-3) / 1e9}
+            out["config"]["grids"].append([n, n])
+            out["views"].append({"grid": [n, n], **res})
+            sim.close()
+        out["value"] = out["views"][-1]["density"]["pixels_per_sec"]
+        out["ms_per_step"] = out["views"][-1]["density"]["ms_per_frame"]
+        out["roofline"] = {"bound": "launch latency (480 000 pixels x 8 bytes = 3.8 MB per frame)", "achieved":
+                           out["views"][-1]["density"]["gbs_at_8_bytes_per_pixel"], "peak": peak, "unit": "GB/s",
+                           "frac": out["views"][-1]["density"]["gbs_at_8_bytes_per_pixel"] / peak, "traffic": None}
+        print(json.dumps(out))
+        return 0
 
     multi = world > 1
     parity = None

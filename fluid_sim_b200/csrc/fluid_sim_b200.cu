@@ -104,6 +104,8 @@ struct fsb_sim {
     float *snapshot = nullptr;                  // device-side copy of the field an asynchronous read is transferring
     unsigned char *view_buf = nullptr;          // RGBA8 image of the last fsb_view_density* call
     size_t view_bytes = 0;
+    void *glyph_buf = nullptr;                  // per-cell line records of the velocity-glyph view
+    size_t glyph_bytes = 0;
     unsigned char *link_buf = nullptr;          // [rings | in_prod | cons], shared with both neighbours through CUDA IPC
     void *peer_left = nullptr, *peer_right = nullptr;   // the neighbours' link_buf mapped into this process
     float *peer_left_f[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // left rank's fields (same roles)
@@ -806,6 +808,7 @@ int fsb_destroy(fsb_sim *s)
         if (s->peer_right) cudaIpcCloseMemHandle(s->peer_right);
         if (s->link_buf) cudaFree(s->link_buf);
         if (s->view_buf) cudaFree(s->view_buf);
+        if (s->glyph_buf) cudaFree(s->glyph_buf);
         if (s->snapshot) cudaFree(s->snapshot);
         if (s->vmax_word) cudaFree(s->vmax_word);
         for (auto &r : s->prof_open) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
@@ -1674,8 +1677,19 @@ int fsb_view_velocity(fsb_sim *s, int px_w, int px_h, unsigned char *host_rgba)
     if (!s || !host_rgba) return fail(FSB_EINVAL, "fsb_view_velocity: bad argument");
     DeviceGuard guard(s->device);
     FSB_TRY(render_density(s, px_w, px_h));
-    FSB_CUDA(launch_view_glyphs(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->G, px_w, px_h, s->view_buf, s->stream));
-    s->launches += 1;
+    {
+        const size_t need = view_glyph_scratch_bytes(s->G);
+        if (need > s->glyph_bytes) {
+            FSB_CUDA(cudaStreamSynchronize(s->stream));
+            if (s->glyph_buf) cudaFree(s->glyph_buf);
+            s->glyph_buf = nullptr;
+            s->glyph_bytes = 0;
+            FSB_CUDA(cudaMalloc(&s->glyph_buf, need));
+            s->glyph_bytes = need;
+        }
+    }
+    FSB_CUDA(launch_view_glyphs(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->G, px_w, px_h, s->view_buf, s->glyph_buf, s->stream));
+    s->launches += 2;
     FSB_CUDA(cudaMemcpyAsync(host_rgba, s->view_buf, (size_t)px_w * px_h * 4, cudaMemcpyDeviceToHost, s->stream));
     FSB_CUDA(cudaStreamSynchronize(s->stream));
     return FSB_OK;

@@ -172,8 +172,10 @@ cudaError_t launch_apply_sources(float *d, float *u, float *v, const SourceEntry
 cudaError_t launch_view_density(const float *d, const GridView &G, int px_w, int px_h, unsigned char *rgba,
                                 cudaStream_t st);
 // velocity glyph lines (every second cell, |v| >= 0.1) blended over the image already in `rgba`
+// scratch: view_glyph_scratch_bytes(G) bytes of device memory (one 32-byte record per sampled cell)
+size_t view_glyph_scratch_bytes(const GridView &G);
 cudaError_t launch_view_glyphs(const float *u, const float *v, const GridView &G, int px_w, int px_h, unsigned char *rgba,
-                               cudaStream_t st);
+                               void *scratch, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------
 // Noise (noise.cu): u, v += ((float)rand()/RAND_MAX - 0.5f) * 1e-4f over the full grid

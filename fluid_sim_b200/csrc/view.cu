@@ -143,7 +143,40 @@ __device__ __forceinline__ bool glyph_covers(const Glyph &q, float pcx, float pc
     return off >= -1.0f && off < 1.0f;
 }
 
-__global__ void view_glyphs_kernel(const float *__restrict__ u, const float *__restrict__ v, const GridView G, int pw, int ph,
+// One record per sampled cell, built once per image: everything a pixel needs to test and blend the cell's line without
+// redoing the square root, the six divisions and the colour ramp for every (pixel, cell) pair.
+struct GlyphRec {
+    float a0, a1;        // start / end along the major axis (window coordinates)
+    float m0, slope;     // minor-axis coordinate at the start, d(minor) / d(major)
+    float cr, cg, cb;    // source colour, already clamped and multiplied by the source alpha
+    unsigned flags;      // bit 0: drawn (|v| >= 0.1 and non-degenerate), bit 1: x is the major axis
+};
+static_assert(sizeof(GlyphRec) == 32, "two 16-byte loads per record");
+
+__global__ void glyph_build_kernel(const float *__restrict__ u, const float *__restrict__ v, const GridView G, int pw, int ph,
+                                   int ni, int nj, GlyphRec *__restrict__ rec)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x, a = blockIdx.y * blockDim.y + threadIdx.y;   // a: i / 2, b: j / 2
+    if (a >= ni || b >= nj) return;
+    const int i = 2 * a, j = 2 * b;
+    const size_t o = (size_t)i * G.pitch + (j - G.jbase);
+    const Glyph q = make_glyph(u[o], v[o], i, j, (float)G.W, (float)G.H, (float)pw, (float)ph);
+    const float dx = __fsub_rn(q.bx, q.ax), dy = __fsub_rn(q.by, q.ay);
+    const bool xmajor = fabsf(dx) >= fabsf(dy);
+    const float dmaj = xmajor ? dx : dy, dmin = xmajor ? dy : dx;
+    GlyphRec r;
+    r.a0 = xmajor ? q.ax : q.ay;
+    r.a1 = xmajor ? q.bx : q.by;
+    r.m0 = xmajor ? q.ay : q.ax;
+    r.slope = (dmaj == 0.0f) ? 0.0f : __fdiv_rn(dmin, dmaj);
+    r.cr = __fmul_rn(clamp01(q.r), 0.8f);
+    r.cg = __fmul_rn(clamp01(q.g), 0.8f);
+    r.cb = __fmul_rn(clamp01(q.b), 0.8f);
+    r.flags = ((q.on && dmaj != 0.0f) ? 1u : 0u) | (xmajor ? 2u : 0u);
+    rec[(size_t)a * nj + b] = r;
+}
+
+__global__ void view_glyphs_kernel(const GlyphRec *__restrict__ rec, int ni, int nj, const GridView G, int pw, int ph,
                                    uchar4 *__restrict__ img)
 {
     const int px = blockIdx.x * blockDim.x + threadIdx.x;
@@ -151,7 +184,9 @@ __global__ void view_glyphs_kernel(const float *__restrict__ u, const float *__r
     if (px >= pw || py >= ph) return;
     const float fw = (float)G.W, fh = (float)G.H, fpw = (float)pw, fph = (float)ph;
     const float pcx = __fadd_rn((float)px, 0.5f), pcy = __fadd_rn((float)py, 0.5f);
-    // sampled cells whose line can reach this pixel: centre within 0.05 NDC (+ 2 pixels) of it, generously rounded
+    // sampled cells whose line can reach this pixel: centre within 0.05 NDC (+ 2 pixels) of it, generously rounded.
+    // (Their number grows with the grid: the reference draws one line per sampled cell, and all of them within reach
+    // are blended in draw order.)
     const float rx = 0.05f * 0.5f * fw + 2.0f * fw / fpw + 2.0f, ry = 0.05f * 0.5f * fh + 2.0f * fh / fph + 2.0f;
     const float ci = pcx / fpw * fw, cj = pcy / fph * fh;          // the pixel in cell units
     int i0 = max(0, (int)floorf(ci - rx)), i1 = min(G.W - 1, (int)ceilf(ci + rx));
@@ -161,27 +196,45 @@ __global__ void view_glyphs_kernel(const float *__restrict__ u, const float *__r
     const uchar4 in = img[(size_t)py * pw + px];
     int c[4] = {in.x, in.y, in.z, in.w};
     const float sa = 0.8f, ia = __fsub_rn(1.0f, 0.8f);
+    const float ca = __fmul_rn(sa, sa);
     for (int i = i0; i <= i1; i += 2)
         for (int j = j0; j <= j1; j += 2) {
-            const size_t o = (size_t)i * G.pitch + (j - G.jbase);
-            const Glyph q = make_glyph(u[o], v[o], i, j, fw, fh, fpw, fph);
-            if (!q.on || !glyph_covers(q, pcx, pcy)) continue;
-            const float src[4] = {clamp01(q.r), clamp01(q.g), clamp01(q.b), sa};
+            const float4 *rp = reinterpret_cast<const float4 *>(rec + (size_t)(i >> 1) * nj + (j >> 1));
+            const float4 g0 = __ldg(rp);                                   // a0, a1, m0, slope
+            const float lo = fminf(g0.x, g0.y), hi = fmaxf(g0.x, g0.y);
+            const float4 g1 = __ldg(rp + 1);                               // colour, flags
+            const unsigned fl = __float_as_uint(g1.w);
+            const float pc = (fl & 2u) ? pcx : pcy, pm = (fl & 2u) ? pcy : pcx;
+            if (!(fl & 1u) || !(pc >= lo && pc < hi)) continue;
+            const float at = __fadd_rn(g0.z, __fmul_rn(__fsub_rn(pc, g0.x), g0.w));
+            const float off = __fsub_rn(pm, at);
+            if (!(off >= -1.0f && off < 1.0f)) continue;
+            const float cs[4] = {g1.x, g1.y, g1.z, ca};
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-                c[k] = to_unorm8(__fadd_rn(__fmul_rn(src[k], sa), __fmul_rn(__fdiv_rn((float)c[k], 255.0f), ia)));
+                c[k] = to_unorm8(__fadd_rn(cs[k], __fmul_rn(__fdiv_rn((float)c[k], 255.0f), ia)));
         }
     img[(size_t)py * pw + px] = make_uchar4((unsigned char)c[0], (unsigned char)c[1], (unsigned char)c[2], (unsigned char)c[3]);
 }
 
 }  // namespace
 
-cudaError_t launch_view_glyphs(const float *u, const float *v, const GridView &G, int pw, int ph, unsigned char *rgba,
-                               cudaStream_t st)
+size_t view_glyph_scratch_bytes(const GridView &G)
 {
-    if (pw < 1 || ph < 1) return cudaErrorInvalidValue;
+    return (size_t)((G.W + 1) / 2) * ((G.H + 1) / 2) * sizeof(GlyphRec);
+}
+
+// scratch: view_glyph_scratch_bytes(G) bytes of device memory for the per-cell line records
+cudaError_t launch_view_glyphs(const float *u, const float *v, const GridView &G, int pw, int ph, unsigned char *rgba,
+                               void *scratch, cudaStream_t st)
+{
+    if (pw < 1 || ph < 1 || !scratch) return cudaErrorInvalidValue;
+    const int ni = (G.W + 1) / 2, nj = (G.H + 1) / 2;
+    GlyphRec *rec = static_cast<GlyphRec *>(scratch);
+    const dim3 bb(32, 8), gb((nj + 31) / 32, (ni + 7) / 8);
+    glyph_build_kernel<<<gb, bb, 0, st>>>(u, v, G, pw, ph, ni, nj, rec);
     const dim3 b(32, 8), g((pw + 31) / 32, (ph + 7) / 8);
-    view_glyphs_kernel<<<g, b, 0, st>>>(u, v, G, pw, ph, reinterpret_cast<uchar4 *>(rgba));
+    view_glyphs_kernel<<<g, b, 0, st>>>(rec, ni, nj, G, pw, ph, reinterpret_cast<uchar4 *>(rgba));
     return cudaGetLastError();
 }
 
