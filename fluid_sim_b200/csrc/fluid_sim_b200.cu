@@ -526,9 +526,10 @@ int chained_launch(fsb_sim *s, bool with_diffuse, bool whole_step, float dt, boo
     if (s->chain_level < 1 || s->is_block || s->tune_strips || s->tune_levels || s->tune_stages) return FSB_OK;
     // Measured (tools/chain_ab.py, ms per step, one launch per pass -> chained): 8192^2 P=40 20.9 -> 16.4, 1024 x 8192
     // 12.7 -> 6.5, 4096^2 10.0 -> 7.8, 2048^2 4.33 -> 3.69, 200^2 0.64 -> 0.62; grids much taller than wide lose
-    // (16384 x 2048: 14.8 -> 18.7, 32768 x 4096: 68.4 -> 71.2: every block is a long serial walk for one CTA) and keep
-    // one launch per pass.  FSB_CHAIN=3 / fsb_set_chain_level(3) forces the chained launch wherever a configuration exists.
-    if (s->chain_level < 3 && s->W > 2 * s->H) return FSB_OK;
+    // with few columns lose (16384 x 2048: 14.8 -> 18.7: every block is a long serial walk for one CTA and there are not
+    // enough blocks for the SMs) and keep one launch per pass; 32768 x 4096: 68.4 -> 66.2.
+    // FSB_CHAIN=3 / fsb_set_chain_level(3) forces the chained launch wherever a configuration exists.
+    if (s->chain_level < 3 && s->W > 2 * s->H && s->H < 4096) return FSB_OK;
     ChainArgs A{};
     A.W = s->W;
     A.H = s->H;
@@ -756,7 +757,7 @@ static int create_common(const fsb_params *p, const GridView *block, fsb_sim **o
     FSB_CREATE_CUDA(cudaMemsetAsync(s->sweep.flags, 0, sweep_flag_words() * sizeof(unsigned long long), s->stream));
     FSB_CREATE_CUDA(noise_tables_create(s->noise_tables));
     if (block) {
-        FSB_CREATE_CUDA(noise_tables_create_pow2(s->noise_tables));
+        FSB_CREATE_CUDA(noise_tables_create_pow2(s->noise_tables, prm.height));
         FSB_CREATE_CUDA(cudaMalloc(&s->link_buf, kLinkBytes));
         FSB_CREATE_CUDA(cudaMemsetAsync(s->link_buf, 0, kLinkBytes, s->stream));
     }

@@ -195,7 +195,7 @@ cudaError_t noise_tables_create(NoiseTables &t);
 void noise_tables_destroy(NoiseTables &t);
 cudaError_t launch_noise(float *u, float *v, size_t ncells, const NoiseWindow &base, const NoiseTables &t,
                          int zero_mode, cudaStream_t st);
-cudaError_t noise_tables_create_pow2(NoiseTables &t);
+cudaError_t noise_tables_create_pow2(NoiseTables &t, int H);
 cudaError_t launch_noise_block(float *u, float *v, const GridView &G, const NoiseWindow &base, const NoiseTables &t,
                                int zero_mode, cudaStream_t st);
 

@@ -120,6 +120,8 @@ constexpr int kNbCells = 1024;
 constexpr int kNbLevels = 40;
 constexpr int kNbPitch = 65;
 
+constexpr int kNbRows = 8;    // consecutive rows of one piece a warp handles: one full jump, then one fixed jump per row
+
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) noise_block_kernel(float *__restrict__ u, float *__restrict__ v,
                                                                          const GridView G, const NoiseWindow base,
                                                                          const uint32_t *__restrict__ pow2)
@@ -129,41 +131,51 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) noise_block_kernel(float 
     const int wib = threadIdx.x >> 5;
     const int nown = G.j1 - G.j0;
     const int pieces = (nown + kNbCells - 1) / kNbCells;
+    const int row_groups = (G.W + kNbRows - 1) / kNbRows;
     const long long wg = (long long)blockIdx.x * kWarpsPerBlock + wib;
-    if (wg >= (long long)G.W * pieces) return;
-    const int i = (int)(wg / pieces);
+    if (wg >= (long long)row_groups * pieces) return;
+    const int i_first = (int)(wg / pieces) * kNbRows;
     const int jstart = G.j0 + (int)(wg % pieces) * kNbCells;
-    const unsigned long long pos = 2ull * ((unsigned long long)i * G.H + jstart);
+    const unsigned long long pos = 2ull * ((unsigned long long)i_first * G.H + jstart);
 
-    uint32_t win = (lane < kRandDeg) ? base.w[lane] : 0u;
+    // window at the piece's first cell of the first row: binary decomposition of the stream position
+    uint32_t row_win = (lane < kRandDeg) ? base.w[lane] : 0u;
     for (int b = 0; b < kNbLevels; ++b)
-        if ((pos >> b) & 1ull) win = matvec(pow2 + (size_t)b * kMatStride, win, lane);
+        if ((pos >> b) & 1ull) row_win = matvec(pow2 + (size_t)b * kMatStride, row_win, lane);
     uint32_t *sw = reinterpret_cast<uint32_t *>(s_stage[wib]);
-    for (int r = 0; r < 32; ++r) {
-        if (lane < kRandDeg) sw[r * kWinPitch + lane] = win;
-        win = matvec(pow2 + (size_t)6 * kMatStride, win, lane);   // x^64: the next lane's 32 cells
-    }
-    __syncwarp();
-    uint32_t w[kRandDeg];
-#pragma unroll
-    for (int m = 0; m < kRandDeg; ++m) w[m] = sw[lane * kWinPitch + m];
-    __syncwarp();
     float *stg = s_stage[wib];
-#pragma unroll
-    for (int n = 0; n < 64; ++n) {
-        const uint32_t nw = w[n % kRandDeg] + w[(n + 28) % kRandDeg];
-        w[n % kRandDeg] = nw;
-        stg[lane * kNbPitch + n] = noise_of(nw);
-    }
-    __syncwarp();
-#pragma unroll 4
-    for (int r = 0; r < 32; ++r) {
-        const int j = jstart + 32 * r + lane;
-        if (j < G.j1) {
-            const size_t c = (size_t)i * G.pitch + (j - G.jbase);
-            u[c] = __fadd_rn(u[c], stg[r * kNbPitch + 2 * lane]);
-            v[c] = __fadd_rn(v[c], stg[r * kNbPitch + 2 * lane + 1]);
+    for (int ri = 0; ri < kNbRows; ++ri) {
+        const int i = i_first + ri;
+        if (i >= G.W) break;
+        uint32_t win = row_win;
+        for (int r = 0; r < 32; ++r) {
+            if (lane < kRandDeg) sw[r * kWinPitch + lane] = win;
+            win = matvec(pow2 + (size_t)6 * kMatStride, win, lane);   // x^64: the next lane's 32 cells
         }
+        __syncwarp();
+        uint32_t w[kRandDeg];
+#pragma unroll
+        for (int m = 0; m < kRandDeg; ++m) w[m] = sw[lane * kWinPitch + m];
+        __syncwarp();
+#pragma unroll
+        for (int n = 0; n < 64; ++n) {
+            const uint32_t nw = w[n % kRandDeg] + w[(n + 28) % kRandDeg];
+            w[n % kRandDeg] = nw;
+            stg[lane * kNbPitch + n] = noise_of(nw);
+        }
+        __syncwarp();
+#pragma unroll 4
+        for (int r = 0; r < 32; ++r) {
+            const int j = jstart + 32 * r + lane;
+            if (j < G.j1) {
+                const size_t c = (size_t)i * G.pitch + (j - G.jbase);
+                u[c] = __fadd_rn(u[c], stg[r * kNbPitch + 2 * lane]);
+                v[c] = __fadd_rn(v[c], stg[r * kNbPitch + 2 * lane + 1]);
+            }
+        }
+        __syncwarp();
+        // the same piece one row down is 2 * H outputs further on: one fixed jump (the matrix after the powers of two)
+        row_win = matvec(pow2 + (size_t)kNbLevels * kMatStride, row_win, lane);
     }
 }
 
@@ -188,17 +200,21 @@ cudaError_t noise_tables_create(NoiseTables &t)
     return cudaMemcpy(t.dev, host.data(), words * sizeof(uint32_t), cudaMemcpyHostToDevice);
 }
 
-cudaError_t noise_tables_create_pow2(NoiseTables &t)
+cudaError_t noise_tables_create_pow2(NoiseTables &t, int H)
 {
-    const size_t words = (size_t)kNbLevels * kMatStride;
+    // x^(2^b), b = 0 .. kNbLevels - 1, then x^(2 H): one grid row further on in the stream
+    const size_t words = (size_t)(kNbLevels + 1) * kMatStride;
     std::vector<uint32_t> host(words, 0u);
+    auto put = [&](int slot, const RandJump &J) {
+        for (int m = 0; m < kRandDeg; ++m)
+            for (int j = 0; j < kRandDeg; ++j) host[(size_t)slot * kMatStride + j * 32 + m] = J.m[m][j];
+    };
     RandPoly p = poly_x_pow(1);
     for (int b = 0; b < kNbLevels; ++b) {
-        const RandJump J = jump_from_poly(p);
-        for (int m = 0; m < kRandDeg; ++m)
-            for (int j = 0; j < kRandDeg; ++j) host[(size_t)b * kMatStride + j * 32 + m] = J.m[m][j];
+        put(b, jump_from_poly(p));
         p = poly_mul(p, p);
     }
+    put(kNbLevels, jump_matrix(2ull * (unsigned long long)H));
     cudaError_t e = cudaMalloc(&t.dev_pow2, words * sizeof(uint32_t));
     if (e != cudaSuccess) return e;
     return cudaMemcpy(t.dev_pow2, host.data(), words * sizeof(uint32_t), cudaMemcpyHostToDevice);
@@ -223,7 +239,7 @@ cudaError_t launch_noise_block(float *u, float *v, const GridView &G, const Nois
     }
     if (!t.dev_pow2) return cudaErrorInvalidValue;
     const long long pieces = ((G.j1 - G.j0) + kNbCells - 1) / kNbCells;
-    const long long warps = (long long)G.W * pieces;
+    const long long warps = (long long)((G.W + kNbRows - 1) / kNbRows) * pieces;
     const unsigned blocks = (unsigned)((warps + kWarpsPerBlock - 1) / kWarpsPerBlock);
     noise_block_kernel<<<blocks, kWarpsPerBlock * 32, 0, st>>>(u, v, G, base, t.dev_pow2);
     return cudaGetLastError();
