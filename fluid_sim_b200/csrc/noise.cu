@@ -116,26 +116,33 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) noise_kernel(float *__res
 // One warp per (row, 1024-cell piece of the owned columns).  The piece starts at stream position
 // 2 * (i * H + j): the warp reaches it from the step's base window through the binary decomposition of
 // that position (matrices x^(2^b)), lane windows are 64 outputs apart.
-constexpr int kNbCells = 1024;
 constexpr int kNbLevels = 40;
 constexpr int kNbPitch = 65;
 
-constexpr int kNbRows = 8;    // consecutive rows of one piece a warp handles: one full jump, then one fixed jump per row
+// consecutive rows of one piece a warp handles (one full position jump, then one fixed jump per row): fewer for long
+// pieces, so that the number of warps - the only parallelism of these dependent mat-vec chains - stays the same
+constexpr int nb_rows(int cpl) { return 256 / cpl; }
 
+// CPL: cells per lane (32, 64 or 128): a warp's piece is 32 * CPL consecutive cells of one row.  The 32 lane windows of
+// a piece cost 32 dependent mat-vecs whatever its length, so wide blocks use long pieces.
+template <int CPL>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) noise_block_kernel(float *__restrict__ u, float *__restrict__ v,
                                                                          const GridView G, const NoiseWindow base,
                                                                          const uint32_t *__restrict__ pow2)
 {
+    constexpr int kPiece = 32 * CPL;
+    constexpr int kNbRows = 256 / CPL;      // = nb_rows(CPL)
+    constexpr int kLaneJump = (CPL == 32) ? 6 : ((CPL == 64) ? 7 : 8);   // x^(2 * CPL)
     __shared__ float s_stage[kWarpsPerBlock][32 * kNbPitch];   // also holds the lane windows before generation
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
     const int nown = G.j1 - G.j0;
-    const int pieces = (nown + kNbCells - 1) / kNbCells;
+    const int pieces = (nown + kPiece - 1) / kPiece;
     const int row_groups = (G.W + kNbRows - 1) / kNbRows;
     const long long wg = (long long)blockIdx.x * kWarpsPerBlock + wib;
     if (wg >= (long long)row_groups * pieces) return;
     const int i_first = (int)(wg / pieces) * kNbRows;
-    const int jstart = G.j0 + (int)(wg % pieces) * kNbCells;
+    const int jstart = G.j0 + (int)(wg % pieces) * kPiece;
     const unsigned long long pos = 2ull * ((unsigned long long)i_first * G.H + jstart);
 
     // window at the piece's first cell of the first row: binary decomposition of the stream position
@@ -150,30 +157,37 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) noise_block_kernel(float 
         uint32_t win = row_win;
         for (int r = 0; r < 32; ++r) {
             if (lane < kRandDeg) sw[r * kWinPitch + lane] = win;
-            win = matvec(pow2 + (size_t)6 * kMatStride, win, lane);   // x^64: the next lane's 32 cells
+            win = matvec(pow2 + (size_t)kLaneJump * kMatStride, win, lane);   // the next lane's CPL cells
         }
         __syncwarp();
         uint32_t w[kRandDeg];
 #pragma unroll
         for (int m = 0; m < kRandDeg; ++m) w[m] = sw[lane * kWinPitch + m];
         __syncwarp();
+        // lane l generates the cells [l * CPL, (l + 1) * CPL) of the piece, 32 cells (64 outputs) per round
 #pragma unroll
-        for (int n = 0; n < 64; ++n) {
-            const uint32_t nw = w[n % kRandDeg] + w[(n + 28) % kRandDeg];
-            w[n % kRandDeg] = nw;
-            stg[lane * kNbPitch + n] = noise_of(nw);
-        }
-        __syncwarp();
-#pragma unroll 4
-        for (int r = 0; r < 32; ++r) {
-            const int j = jstart + 32 * r + lane;
-            if (j < G.j1) {
-                const size_t c = (size_t)i * G.pitch + (j - G.jbase);
-                u[c] = __fadd_rn(u[c], stg[r * kNbPitch + 2 * lane]);
-                v[c] = __fadd_rn(v[c], stg[r * kNbPitch + 2 * lane + 1]);
+        for (int round = 0; round < CPL / 32; ++round) {
+            // w[] is a circular buffer: output number N overwrites index N mod 31, and 64 mod 31 = 2, so round r starts
+            // at index 2 r (the rounds are unrolled: every index is a compile-time constant, w[] stays in registers)
+            const int rot = (2 * round) % kRandDeg;
+#pragma unroll
+            for (int n = 0; n < 64; ++n) {
+                const uint32_t nw = w[(n + rot) % kRandDeg] + w[(n + rot + 28) % kRandDeg];
+                w[(n + rot) % kRandDeg] = nw;
+                stg[lane * kNbPitch + n] = noise_of(nw);
             }
+            __syncwarp();
+#pragma unroll 4
+            for (int r = 0; r < 32; ++r) {
+                const int j = jstart + r * CPL + 32 * round + lane;
+                if (j < G.j1) {
+                    const size_t c = (size_t)i * G.pitch + (j - G.jbase);
+                    u[c] = __fadd_rn(u[c], stg[r * kNbPitch + 2 * lane]);
+                    v[c] = __fadd_rn(v[c], stg[r * kNbPitch + 2 * lane + 1]);
+                }
+            }
+            __syncwarp();
         }
-        __syncwarp();
         // the same piece one row down is 2 * H outputs further on: one fixed jump (the matrix after the powers of two)
         row_win = matvec(pow2 + (size_t)kNbLevels * kMatStride, row_win, lane);
     }
@@ -238,10 +252,15 @@ cudaError_t launch_noise_block(float *u, float *v, const GridView &G, const Nois
         return launch_add_zero(v, (size_t)G.W * G.pitch, st);
     }
     if (!t.dev_pow2) return cudaErrorInvalidValue;
-    const long long pieces = ((G.j1 - G.j0) + kNbCells - 1) / kNbCells;
-    const long long warps = (long long)((G.W + kNbRows - 1) / kNbRows) * pieces;
+    const int nown = G.j1 - G.j0;
+    const int cpl = nown >= 4096 ? 128 : (nown >= 2048 ? 64 : 32);
+    const long long pieces = (nown + 32 * cpl - 1) / (32 * cpl);
+    const int rows = nb_rows(cpl);
+    const long long warps = (long long)((G.W + rows - 1) / rows) * pieces;
     const unsigned blocks = (unsigned)((warps + kWarpsPerBlock - 1) / kWarpsPerBlock);
-    noise_block_kernel<<<blocks, kWarpsPerBlock * 32, 0, st>>>(u, v, G, base, t.dev_pow2);
+    if (cpl == 128) noise_block_kernel<128><<<blocks, kWarpsPerBlock * 32, 0, st>>>(u, v, G, base, t.dev_pow2);
+    else if (cpl == 64) noise_block_kernel<64><<<blocks, kWarpsPerBlock * 32, 0, st>>>(u, v, G, base, t.dev_pow2);
+    else noise_block_kernel<32><<<blocks, kWarpsPerBlock * 32, 0, st>>>(u, v, G, base, t.dev_pow2);
     return cudaGetLastError();
 }
 

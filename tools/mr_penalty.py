@@ -28,10 +28,16 @@ for name, sim in (("block (MR kernel)", BlockFluidSim(W, H, P, 5, device=0, chai
     for _ in range(3):
         sim.step(0.01)
     sim.sync()
+    import ctypes as C
+    sim._check(sim._lib.fsb_profile_enable(sim._h, 1))
     t = time.perf_counter()
     for _ in range(5):
         sim.step(0.01)
     sim.sync()
-    print(name, W, H, P, "ms/step %.3f" % ((time.perf_counter() - t) / 5 * 1e3), flush=True)
+    names = fsb.FluidSim.PROF_NAMES
+    ms = (C.c_double * len(names))(); cnt = (C.c_uint64 * len(names))()
+    sim._check(sim._lib.fsb_profile_read(sim._h, ms, cnt, 1))
+    print(name, W, H, P, "ms/step %.3f" % ((time.perf_counter() - t) / 5 * 1e3),
+          {n: round(ms[i] / 5, 3) for i, n in enumerate(names) if ms[i] > 0}, flush=True)
     sim.close()
 dist.destroy_process_group()
