@@ -89,6 +89,7 @@ struct fsb_sim {
     int src_next = 0;
     std::vector<float> mirror[3];
     bool mirror_valid[3] = {false, false, false};
+    int probes[3] = {0, 0, 0};             // single-cell reads served from the device since the fields last changed
     uint64_t launches = 0;
     int tune_strips = 0;   // strips per CTA (0 = automatic)
     int tune_levels = 0;   // sweeps per warp (0 = automatic)
@@ -637,7 +638,29 @@ int density_step(fsb_sim *s, float dt)
     return FSB_OK;
 }
 
-void invalidate_mirror(fsb_sim *s) { s->mirror_valid[0] = s->mirror_valid[1] = s->mirror_valid[2] = false; }
+void invalidate_mirror(fsb_sim *s)
+{
+    s->mirror_valid[0] = s->mirror_valid[1] = s->mirror_valid[2] = false;
+    s->probes[0] = s->probes[1] = s->probes[2] = 0;
+}
+
+// A caller that probes a few cells after a step (not the viewer's full sweep over the grid, src/main.cpp:388-396) should
+// not pay for a whole-field download: the first kProbeCells reads after a change fetch single cells; a caller that keeps
+// reading gets the host mirror of the whole field, as the reference's per-cell read loop wants.
+constexpr int kProbeCells = 32;
+
+int read_cell(fsb_sim *s, int field, int x, int y, float *out, bool *served)
+{
+    *served = false;
+    if (s->is_block) return fail(FSB_EINVAL, "per-cell getters are not available on a column block; read the field instead");
+    if (s->mirror_valid[field] || s->probes[field] >= kProbeCells) return FSB_OK;
+    FSB_TRY(flush_sources(s));
+    s->probes[field] += 1;
+    FSB_CUDA(cudaMemcpyAsync(out, s->f[field] + (size_t)x * s->H + y, sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    FSB_CUDA(cudaStreamSynchronize(s->stream));
+    *served = true;
+    return FSB_OK;
+}
 
 int refresh_mirror(fsb_sim *s, int field)
 {
@@ -915,6 +938,9 @@ int fsb_get_density(fsb_sim *s, int x, int y, float *out)
     *out = 0.0f;
     if (!in_range(s, x, y)) return FSB_OK;   // src/fluid_sim.cpp:447
     DeviceGuard guard(s->device);
+    bool served = false;
+    FSB_TRY(read_cell(s, 0, x, y, out, &served));
+    if (served) return FSB_OK;
     FSB_TRY(refresh_mirror(s, 0));
     *out = s->mirror[0][(size_t)x * s->H + y];
     return FSB_OK;
@@ -926,10 +952,13 @@ int fsb_get_velocity(fsb_sim *s, int x, int y, float *out_xy)
     out_xy[0] = out_xy[1] = 0.0f;
     if (!in_range(s, x, y)) return FSB_OK;   // src/fluid_sim.cpp:456
     DeviceGuard guard(s->device);
-    FSB_TRY(refresh_mirror(s, 1));
-    FSB_TRY(refresh_mirror(s, 2));
-    out_xy[0] = s->mirror[1][(size_t)x * s->H + y];
-    out_xy[1] = s->mirror[2][(size_t)x * s->H + y];
+    for (int k = 0; k < 2; ++k) {
+        bool served = false;
+        FSB_TRY(read_cell(s, 1 + k, x, y, out_xy + k, &served));
+        if (served) continue;
+        FSB_TRY(refresh_mirror(s, 1 + k));
+        out_xy[k] = s->mirror[1 + k][(size_t)x * s->H + y];
+    }
     return FSB_OK;
 }
 

@@ -269,6 +269,44 @@ def test_whole_step_as_one_chained_launch(w, h, p, d, steps, inject):
         assert_bits(a, b, f"{w}x{h} P={p} D={d} {inject}: field {n}")
 
 
+def test_velocity_and_density_step_entry_points():
+    """fsb_op_velocity_step / fsb_op_density_step (velocityStep, densityStep of src/fluid_sim.cpp:370-422) called one after
+    the other equal step(); checked against the oracle's two halves after each call."""
+    w, h = 90, 140
+    gpu, ora = make_pair(w, h, 20, 5)
+    for s in (gpu, ora):
+        demo_injection(s, w, h)
+    for k in range(3):
+        gpu.velocityStep(0.01); ora.velocityStep(0.01)
+        for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+            assert_bits(a, b, f"after velocityStep {k}: field {n}")
+        gpu.densityStep(0.01); ora.densityStep(0.01)
+        for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+            assert_bits(a, b, f"after densityStep {k}: field {n}")
+
+
+def test_single_cell_reads_after_a_step():
+    """A caller that probes a few cells gets them without a whole-field download (the first reads after a change fetch
+    single cells); a caller that keeps reading is served from the host mirror.  Same values either way, and sources
+    added in between are visible."""
+    w, h = 70, 66
+    gpu, ora = make_pair(w, h, 10, 5)
+    for s in (gpu, ora):
+        demo_injection(s, w, h)
+    gpu.step(0.01); ora.step(0.01)
+    d, u, v = ora.fields()
+    cells = [(i, j) for i in range(0, w, 3) for j in range(0, h, 5)]          # more than the probe budget
+    for (i, j) in cells:
+        assert gpu.getDensity(i, j).view(np.uint32) == d[i, j].view(np.uint32)
+        gu, gv = gpu.getVelocity(i, j)
+        assert gu.view(np.uint32) == u[i, j].view(np.uint32) and gv.view(np.uint32) == v[i, j].view(np.uint32)
+    gpu.addDensity(7, 9, 1.25); ora.addDensity(7, 9, 1.25)
+    assert gpu.getDensity(7, 9).view(np.uint32) == ora.read(0)[7, 9].view(np.uint32)
+    gpu.step(0.01); ora.step(0.01)
+    assert gpu.getDensity(35, 33).view(np.uint32) == ora.read(0)[35, 33].view(np.uint32)     # one probe after the step
+    assert gpu.getDensity(-1, 3) == 0 and gpu.getDensity(3, h) == 0
+
+
 def test_many_launches_ring_tags_wrap():
     """The rings between CTAs carry a tag made of the launch number (14 bits) and the hand-over unit: more than 2^14
     launches on one simulation must stay exact.  One strip per CTA, so every strip boundary crosses a ring."""
