@@ -531,6 +531,8 @@ int chained_launch(fsb_sim *s, bool with_diffuse, bool whole_step, float dt, boo
     // enough blocks for the SMs) and keep one launch per pass; 32768 x 4096: 68.4 -> 66.2.
     // FSB_CHAIN=3 / fsb_set_chain_level(3) forces the chained launch wherever a configuration exists.
     if (s->chain_level < 3 && s->W > 2 * s->H && s->H < 4096) return FSB_OK;
+    // the advection phases of the chained launch are RK4 (the live scheme, src/fluid_sim.cpp:219)
+    if (whole_step && (s->chain_level < 2 || s->prm.advect_scheme != FSB_ADVECT_RK4)) return FSB_OK;
     ChainArgs A{};
     A.W = s->W;
     A.H = s->H;
