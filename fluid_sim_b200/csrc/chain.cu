@@ -260,7 +260,7 @@ __device__ __forceinline__ void chain_boundary(float *x, float *xl, float *xr, c
 // outside the block).  Wall cells are read as setBoundary(1, u) / setBoundary(2, v) would have left them:
 //   u[0][j] = -u[1][j], u[W-1][j] = -u[W-2][j], v[i][0] = -v[i][1], v[i][H-1] = -v[i][H-2]   (:350-360)
 constexpr int kPwRun = 64;   // rows per warp run
-constexpr int kPwBatch = 4;  // rows whose loads are in flight together
+constexpr int kPwBatch = 8;  // rows whose loads are in flight together
 
 template <int CW>
 __device__ __forceinline__ void chain_divergence(const ChainPhase &ph, const ChainGrid &g, const int blk)
