@@ -375,9 +375,9 @@ def main():
         sim.step(0.01)
     sim.sync()
 
-    # -------- value: K steps, state resident in HBM, CUDA events on the launching stream
-    sim.profile_enable(True)
-    sim.profile_read(reset=True)
+    # -------- value: K steps, state resident in HBM, CUDA events on the launching stream at both ends of the region.
+    # Nothing else is recorded inside it: on one GPU the launches of consecutive steps overlap (the first blocks of step
+    # n+1 run while the last blocks of step n finish), and a timing event between two launches would serialise them.
     sampler = ClockSampler(local_rank)
     sampler.start()
     l0 = sim.launch_count()
@@ -392,6 +392,13 @@ def main():
     clocks = sampler.stop()
     ms_total = ev0.elapsed_time(ev1)
     launches = sim.launch_count() - l0
+    # -------- per kernel class: the same K steps once more, untimed for `value`, with timing events around every launch
+    # (kernel_ms_per_step).  Those events serialise the launches: a class's time is its launches alone on the GPU.
+    sim.profile_enable(True)
+    sim.profile_read(reset=True)
+    for _ in range(K):
+        sim.step(0.01)
+    sim.sync()
     prof = sim.profile_read(reset=True)
     sim.profile_enable(False)
     if world > 1:
@@ -525,25 +532,41 @@ def main():
     if chain_n > 0 and gs_n == 0:
         # One chained launch per step: diffuse(u, v), project, advect(u, v), project and the density step as phases of
         # one cooperative kernel (fluid_sim_b200/csrc/chain.cu).
-        launch_ms = chain_ms / chain_n
+        launch_alone_ms = chain_ms / chain_n
         per_step = chain_n / float(K)
         whole = abs(per_step - 1.0) < 1e-6
+        # the step is this one launch (noise included) and consecutive launches overlap: the launch's share of the timed
+        # region is the region / launches (CUDA events at its ends); `launch_alone_ms` is the same launch with the GPU to
+        # itself (profiled pass)
+        everything = whole and int(launches) == K and prof.get("noise", (0.0, 0))[1] == 0
+        launch_ms = ms_per_step if everything else launch_alone_ms
         # SURVEY.md 8(d) fusion rule: inputs not produced inside the kernel + outputs consumed outside it
         fused_bpc = 24.0 if whole else 20.0                   # u, v, d in and out / u, v in and out + the pressure
         # what the phases really move: SOR 2 x 8, per projection div 12 + sweeps 8 + gradient 20, advections 16 + 16
         moved_bpc = (16.0 + 2 * 40.0 + 32.0) if whole else 56.0
         eff_bpc = (algorithmic_bytes_per_cell(P) - 16.0) if whole else (36.0 + 12.0 * P + 120.0)
+        if everything:
+            moved_bpc += 16.0                                     # the noise phase: u, v read and written
+            eff_bpc += 16.0
         fused_gbs = fused_bpc * cells / (launch_ms * 1e-3) / 1e9
-        roofline = {"kernel": "chain_kernel<5, 10>: diffuse(u), diffuse(v), project, advect(u, v), project and the density step of "
-                              "one FluidSim::step as phases of ONE cooperative launch (everything after the noise)" if whole else
+        roofline = {"kernel": ("chain_kernel<5, 10>: noise, diffuse(u), diffuse(v), project, advect(u, v), project and the density step: "
+                               "ALL of FluidSim::step as phases of ONE launch; launches of consecutive steps overlap" if everything else
+                               "chain_kernel<5, 10>: diffuse(u), diffuse(v), project, advect(u, v), project and the density step of "
+                               "one FluidSim::step as phases of ONE cooperative launch (everything after the noise)") if whole else
                               "chain_kernel: diffuse + project / project as phases of one launch",
-                    "bound": "dependency chain of the exact-order sweeps (stagger between column blocks + step latency of the "
-                             "sweep pipeline); not HBM: see `frac`, and `ceilings` for issue slots / shared-memory wavefronts",
+                    "bound": ("the serial work of one thread block on its block of columns (every SM that holds a block is busy "
+                              "from launch to launch: the sweep phases run at the step latency of the exact-order pipeline); " if everything else
+                              "dependency chain of the exact-order sweeps (stagger between column blocks + step latency of the "
+                              "sweep pipeline); ") + "not HBM: see `frac`, and `ceilings` for issue slots / shared-memory wavefronts",
                     "achieved": fused_gbs, "peak": peak, "unit": "GB/s", "frac": fused_gbs / peak,
                     "moved_gbs": moved_bpc * cells / (launch_ms * 1e-3) / 1e9,
                     "effective_gbs": eff_bpc * cells / (launch_ms * 1e-3) / 1e9,
                     "effective_frac": eff_bpc * cells / (launch_ms * 1e-3) / 1e9 / peak,
-                    "traffic": None, "peak_source": peak_src, "launch_ms": launch_ms, "launches_timed": chain_n,
+                    "traffic": None, "peak_source": peak_src, "launch_ms": launch_ms, "launches_timed": int(launches) if everything else chain_n,
+                    "launch_alone_ms": launch_alone_ms,
+                    "launch_timing": ("timed region (CUDA events at both ends, K back-to-back launches that overlap) / K; "
+                                      "launch_alone_ms: one launch with the GPU to itself (events around every launch)") if everything
+                                     else "CUDA events around every launch",
                     "algorithmic_bytes_per_launch": fused_bpc * cells, "moved_bytes_per_launch": moved_bpc * cells,
                     "sweep_cell_updates_per_sec": (2 * P + 10) * cells / (launch_ms * 1e-3),
                     "note": "achieved / frac = SURVEY.md 8(d)'s fusion rule (fields read once, results written once: "
@@ -593,7 +616,8 @@ def main():
     shares = {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items()}
     # per kernel class: effective GB/s at SURVEY.md 8(d)'s algorithmic bytes per cell and launch
     per_launch_bytes = {"noise": 16.0, "divergence": 16.0, "gradient": 20.0, "advect_velocity": 16.0, "advect_scalar": 16.0,
-                        "sor": 12.0 * 5 * 2, "gs": 12.0 * levels, "chain": algorithmic_bytes_per_cell(P) - 16.0}
+                        "sor": 12.0 * 5 * 2, "gs": 12.0 * levels,
+                        "chain": algorithmic_bytes_per_cell(P) - (16.0 if prof.get("noise", (0.0, 0))[1] > 0 else 0.0)}
     for k, bpc in per_launch_bytes.items():
         if k in shares and prof[k][1] > 0 and prof[k][0] > 0:
             gbs = bpc * cells / (prof[k][0] / prof[k][1] * 1e-3) / 1e9
@@ -624,6 +648,9 @@ def main():
                         "column blocks, one per GPU: the exact-order sweep chain crosses GPUs through CUDA-IPC peer rings "
                         "inside the kernel, halo columns move with NCCL send/recv between passes")},
             "roofline": roofline, "step_roofline": step_roofline, "kernel_ms_per_step": shares,
+            "kernel_ms_per_step_note": "from a second, untimed pass of K steps with CUDA timing events around every launch; the events "
+                                       "serialise launches that otherwise overlap, so an entry is that class alone on the GPU and the "
+                                       "entries may add up to more than ms_per_step",
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": e2e_ms / K, "density_checksum": checksum},

@@ -123,6 +123,7 @@ ABI = [
     ("fsb_launch_count", C.c_int, [_SIM, C.POINTER(C.c_uint64)]),
     ("fsb_set_tuning", C.c_int, [_SIM, C.c_int, C.c_int, C.c_int]),
     ("fsb_set_chain_level", C.c_int, [_SIM, C.c_int]),
+    ("fsb_set_chain_overlap", C.c_int, [_SIM, C.c_int]),
     ("fsb_last_error", C.c_char_p, []),
     ("fsb_version", C.c_char_p, []),
 ]
@@ -151,7 +152,7 @@ class FluidSim:
 
     def __init__(self, width=200, height=200, proj_iters=20, diff_iters=5, viscosity=1e-4, diffusion=0.0,
                  omega=1.5, advect_scheme=ADVECT_RK4, noise="glibc", noise_seed=1, noise_pos=0, device=-1,
-                 strips_per_cta=0, sweeps_per_warp=0, max_stages=0, process_stream=False, chain=None):
+                 strips_per_cta=0, sweeps_per_warp=0, max_stages=0, process_stream=False, chain=None, overlap=None):
         self._lib = load_library()
         p = Params()
         self._lib.fsb_default_params(C.byref(p))
@@ -168,6 +169,8 @@ class FluidSim:
             self._check(self._lib.fsb_set_tuning(self._h, strips_per_cta, sweeps_per_warp, max_stages))
         if chain is not None:
             self._check(self._lib.fsb_set_chain_level(self._h, chain))
+        if overlap is not None:
+            self._check(self._lib.fsb_set_chain_overlap(self._h, 1 if overlap else 0))
 
     # -- plumbing ---------------------------------------------------------------------------
     def _check(self, rc):

@@ -23,6 +23,7 @@
 // All arithmetic uses round-to-nearest intrinsics in the reference's association order (no FMA).
 #include "wavefront.cuh"
 #include "gather.cuh"
+#include "noise.cuh"
 
 #include <algorithm>
 
@@ -34,11 +35,12 @@ constexpr int kChainThreads = 320;      // 8 compute warps + 2 transfer warps: t
 constexpr int kChainMaxPhases = 24;
 constexpr int kChainMaxItems = 1024;    // items per phase the done[] array is sized for
 constexpr int kChainMaxDeps = 4;
+constexpr int kChainMaxXDeps = 3;     // dependencies on the previous launch (overlapped steps)
 constexpr int kChainMaxSweeps = 7;      // sweep phases per launch: diffusion + up to three passes per projection
 constexpr int kChainMaxGsPasses = 3;
 constexpr int kChainCols = 64;          // columns of a pointwise work item
 
-enum ChainKind { kPhSor = 1, kPhGs = 2, kPhDiv = 3, kPhGrad = 4, kPhAdvect = 5, kPhGsX0 = 6, kPhBndP = 7 };
+enum ChainKind { kPhSor = 1, kPhGs = 2, kPhDiv = 3, kPhGrad = 4, kPhAdvect = 5, kPhGsX0 = 6, kPhBndP = 7, kPhNoise = 8 };
 
 // "wait until phase `phase` has finished every item whose result columns meet [b0 - lo, b1 + hi]", where [b0, b1]
 // are the waiting item's own columns: the ones it reads (from_out = 0) or the ones it writes (from_out = 1).
@@ -66,9 +68,14 @@ struct ChainPhase {
     int wf;          // sweep phases: index into ChainParams::wf
     int ndeps;
     ChainDep dep[kChainMaxDeps];
+    // the same against the PREVIOUS launch (same phase numbering), used when two steps overlap: the items of the step
+    // before whose results this item reads, or which still read what this item overwrites
+    int nxdeps;
+    ChainDep xdep[kChainMaxXDeps];
     // pointwise phases
     //   divergence: u, v -> q                      gradient: q = pressure, u / v updated in place, then boundaries;
     //   advection : dst_a (dst_b) = src_a (src_b) traced back through u, v, then boundaries ba (bb) on dst
+    //   noise     : u, v = src_a, src_b + the step's noise, every cell of the block (walls included)
     float *u, *v;
     float *q;
     float *dst_a, *dst_b;
@@ -94,17 +101,26 @@ struct ChainParams {
     float *vmax_l, *vmax_r;
     unsigned *step_in;              // [0]: written by the left neighbour, [1]: by the right one
     unsigned *step_out_l, *step_out_r;
-    unsigned *cta_count;            // CTAs of this launch that have finished
+    unsigned *cta_count;            // [2], by launch parity: CTAs of the launch that have finished
+    unsigned *completed;            // [2], by launch parity: number of the last launch all of whose CTAs have finished
+    // steps that overlap (one GPU): launch n + 1 starts on the SMs the first CTAs of launch n have left, see launch_chain
+    int xstep;                      // the previous launch was the step before this one: ChainPhase::xdep applies
+    int pdl;                        // let the next launch of the stream start before this one has drained
+    // noise phase (chain_noise)
+    int nz_zero;                    // FSB_NOISE_ZERO: every cell gets + 0.0f
+    uint32_t nz_base[kRandDeg];     // window of the rand() stream at the step's first output
+    const uint32_t *nz_polys;       // jump polynomials
     unsigned epoch;                 // number of this launch (done[] words hold the epoch of their last completion)
     unsigned *done;                 // [kChainMaxPhases][kChainMaxItems]
     unsigned long long *err;        // watchdog report: (phase << 32 | item) + 1 of the first wait that timed out
     unsigned long long timeout_ns;
     unsigned long long *trace;      // [kChainMaxPhases][kChainMaxItems][3] global-timer ns: wait begins, work begins, work ends
     float *vmax;                    // [2][kChainMaxPhases][kChainMaxItems] max |v|, max |u| of a block after its gradient phase
+                                    // (overlapping launches alternate between two such arrays)
     ChainPhase ph[kChainMaxPhases];
     WfKernelParams wf[kChainMaxSweeps];
 };
-static_assert(sizeof(ChainParams) <= 16000, "kernel parameter space (CUDA 12.1+: up to 32764 bytes)");
+static_assert(sizeof(ChainParams) <= 24000, "kernel parameter space (CUDA 12.1+: up to 32764 bytes)");
 
 // system scope on a multi-rank launch: the word may have been written by a neighbouring GPU through peer memory
 template <bool MR>
@@ -168,8 +184,7 @@ __device__ __forceinline__ void chain_wait(const ChainParams &C, const int p, co
     const ChainPhase &ph = C.ph[p];
     const int d = threadIdx.x;
     unsigned long long t0 = 0;
-    if (d < ph.ndeps) {
-        const ChainDep dep = ph.dep[d];
+    auto wait_for = [&](const ChainDep dep, const unsigned want) {
         const ChainPhase &q = C.ph[dep.phase];
         const int b0 = cl * ph.cpv - (dep.from_out ? ph.shift : 0);
         const int b1 = b0 + ph.cpv - 1;
@@ -177,7 +192,12 @@ __device__ __forceinline__ void chain_wait(const ChainParams &C, const int p, co
         a = max(a, 0);
         b = min(b, q.ncl - 1);
         const unsigned *flags = C.done + (size_t)dep.phase * kChainMaxItems;
-        for (int x = a * q.nf; x < (b + 1) * q.nf; ++x) chain_poll<MR>(C, flags + x, C.epoch, p, cl, t0);
+        for (int x = a * q.nf; x < (b + 1) * q.nf; ++x) chain_poll<MR>(C, flags + x, want, p, cl, t0);
+    };
+    if (d < ph.ndeps) {
+        wait_for(ph.dep[d], C.epoch);
+    } else if (!MR && d >= 8 && d - 8 < ph.nxdeps && C.xstep) {
+        wait_for(ph.xdep[d - 8], C.epoch - 1);      // the step before, still running
     } else if (d == 32 && wait_l) {
         chain_poll<MR>(C, C.step_in + 0, C.epoch - 1, p, cl, t0);
     } else if (d == 33 && wait_r) {
@@ -752,6 +772,116 @@ __device__ __forceinline__ void chain_advect(const ChainPhase &ph, const ChainGr
     if (TWO) chain_boundary<MR, CW>(dst_b, ph.peer_l[1], ph.peer_r[1], P, ph.bb, 0, g, c0);
 }
 
+
+// ---- velocity noise (src/fluid_sim.cpp:374-383) on the columns [c0, c0 + cw), all rows: u, v = src + noise ----------
+// The reference draws two rand() numbers per cell, X then Y, rows outer / columns inner over the full grid, so cell
+// (i, j) uses the outputs 2 (i H + j) and 2 (i H + j) + 1 of the step.  rand() is a linear recurrence over Z/2^32
+// (glibc_rand.h): the window k outputs further on is new[m] = sum_j p[j] a[m + j], p = x^k mod (x^31 - x^28 - 1) and a[]
+// the window extended by 30 sequential outputs -- a correlation every thread can do on its own registers (961 multiply-adds,
+// 31 coefficients from shared memory).  Work split: a warp takes 32 consecutive rows of the block, lane = row.  Each lane
+// reaches the window of (its row, c0) from the step's base window through the bits of the block index (x^(2 cw 2^b),
+// skipped warp-wide where the bit is clear), of the warp index (x^(64 H 2^b)) and of the lane (x^(2 H 2^b)), generates the
+// row's 2 cw outputs sequentially, and jumps on to the same columns 32 * (warps of the CTA) rows further down with one
+// fixed polynomial.  The values are staged in shared memory so that the warp applies them one row at a time (coalesced).
+constexpr int kNzPitch = 65;                 // 64 outputs per lane and round, odd pitch
+static_assert(kNzWarps == kChainThreads / 32, "noise.cuh: warps of a CTA");
+
+template <int CW>
+__device__ __forceinline__ void chain_noise(const ChainParams &C, const ChainPhase &ph, const ChainGrid &g, const int blk, float *smem)
+{
+    const int W = g.W, H = g.H;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int c0 = blk * CW;
+    const float *su = ph.src_a, *sv = ph.src_b;
+    float *du = ph.u, *dv = ph.v;
+    if (C.nz_zero) {
+        // rand() replaced by the value that makes the noise + 0.0f (FSB_NOISE_ZERO): the reference still adds it
+        for (int i = wid; i < W; i += kNzWarps)
+#pragma unroll
+            for (int k = 0; k < CW / 32; ++k) {
+                const int j = c0 + 32 * k + lane;
+                if (j < H) {
+                    const long long c = CAT(g, i, j);
+                    du[c] = __fadd_rn(__ldcg(su + c), 0.0f);
+                    dv[c] = __fadd_rn(__ldcg(sv + c), 0.0f);
+                }
+            }
+        return;
+    }
+    uint32_t *s_poly = reinterpret_cast<uint32_t *>(smem);
+    float *stg = smem + kNzPolys * 32 + wid * (32 * kNzPitch);
+    for (int i = tid; i < kNzPolys * 32; i += blockDim.x) s_poly[i] = C.nz_polys[i];
+    __syncthreads();
+    uint32_t w[kRandDeg];
+#pragma unroll
+    for (int m = 0; m < kRandDeg; ++m) w[m] = C.nz_base[m];
+    int R0 = 32 * wid;                                   // first row of the warp's current group of 32
+#pragma unroll 1
+    for (int it = 0;; ++it) {
+        const uint32_t *p;
+        bool take = true;
+        if (it < 10) {                                   // columns: 2 c0 = 2 cw blk outputs
+            if (!((blk >> it) & 1)) continue;
+            p = s_poly + (kNzBlockPoly + it) * 32;
+        } else if (it < 14) {                            // rows: 32 wid ...
+            if (!((wid >> (it - 10)) & 1)) continue;
+            p = s_poly + (kNzWarpPoly + it - 10) * 32;
+        } else if (it < 19) {                            // ... + lane
+            take = (lane >> (it - 14)) & 1;
+            p = s_poly + (kNzLanePoly + it - 14) * 32;
+        } else {
+            if (R0 >= W) break;
+#pragma unroll
+            for (int round = 0; round < CW / 32; ++round) {
+                // w[] is a circular buffer: output number n overwrites index n mod 31; 64 mod 31 = 2, so round r starts
+                // at index 2 r (everything unrolled: the indices are constants, w[] stays in registers)
+                const int rot = (64 * round) % kRandDeg;
+#pragma unroll
+                for (int n = 0; n < 64; ++n) {
+                    const uint32_t x = w[(n + rot) % kRandDeg] + w[(n + rot + 28) % kRandDeg];
+                    w[(n + rot) % kRandDeg] = x;
+                    stg[lane * kNzPitch + n] = noise_of(x);
+                }
+                __syncwarp();
+                const int j = c0 + 32 * round + lane;
+#pragma unroll 1
+                for (int r0 = 0; r0 < 32; r0 += 8) {
+                    float uu[8], vv[8];
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        const int i = R0 + r0 + r;
+                        const bool ok = i < W && j < H;
+                        const long long c = CAT(g, ok ? i : 0, ok ? j : g.jbase);
+                        uu[r] = ok ? __ldcg(su + c) : 0.0f;
+                        vv[r] = ok ? __ldcg(sv + c) : 0.0f;
+                    }
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        const int i = R0 + r0 + r;
+                        if (i < W && j < H) {
+                            const long long c = CAT(g, i, j);
+                            du[c] = __fadd_rn(uu[r], stg[(r0 + r) * kNzPitch + 2 * lane]);       // X component first
+                            dv[c] = __fadd_rn(vv[r], stg[(r0 + r) * kNzPitch + 2 * lane + 1]);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            R0 += 32 * kNzWarps;
+            if (R0 >= W) break;
+            // back to natural order: 2 cw outputs later the window starts at index (2 cw) mod 31
+            constexpr int rot_end = (2 * CW) % kRandDeg;
+            uint32_t t[kRandDeg];
+#pragma unroll
+            for (int m = 0; m < kRandDeg; ++m) t[m] = w[(m + rot_end) % kRandDeg];
+#pragma unroll
+            for (int m = 0; m < kRandDeg; ++m) w[m] = t[m];
+            p = s_poly + kNzStridePoly * 32;
+        }
+        nz_jump(w, p, take);
+    }
+}
+
 // What an item does besides its arithmetic, recomputed from (phase, local item) wherever it is needed so that nothing
 // but those two integers stays live across the sweep pipeline's loops (the kernel runs at the 168-register cap of a
 // 10-warp CTA, and anything more spills inside those loops).
@@ -782,6 +912,22 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
     extern __shared__ float4 smem4[];
     float *smem = reinterpret_cast<float *>(smem4);
     const ChainGrid &g = C.g;
+    if constexpr (!MR) {
+        // Overlapping steps.  Every CTA of this launch is resident by the time all of them have executed the instruction
+        // below; from then on the next launch of the stream (if it was launched for programmatic stream serialization)
+        // may take the SMs this launch's CTAs leave one by one.  It orders itself against this launch through the
+        // done-words (ChainPhase::xdep); what it overwrites that the launch before this one was still reading far from
+        // the writing block (traced velocities, densities, block maxima) it protects by waiting, once, for that launch
+        // to have finished altogether: the buffers alternate, so nothing closer in time is at risk.
+        if (C.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        if (C.xstep) {
+            if (threadIdx.x == 0) {
+                unsigned long long t0 = 0;
+                chain_poll<MR>(C, C.completed + (C.epoch & 1u), C.epoch - 2u, kChainMaxPhases, 0, t0);
+            }
+            __syncthreads();
+        }
+    }
     for (int p = 0; p < C.nphases; ++p) {
         const ChainPhase &ph = C.ph[p];
         for (int li = blockIdx.x; li < ph.nitems; li += gridDim.x) {
@@ -807,6 +953,8 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
                 if (ph.kind == kPhBndP) {
                     ChainPush none{false, false, 0, 0};
                     chain_boundary<MR, CW>(ph.q, nullptr, nullptr, none, 0, 0, g, cl * CW);       // setBoundary(0, p) between two passes (:330)
+                } else if (ph.kind == kPhNoise) {
+                    if constexpr (!MR) chain_noise<CW>(C, ph, g, cl, smem);
                 } else if (ph.kind == kPhDiv) {
                     chain_divergence<CW>(ph, g, cl);
                 } else if (ph.kind == kPhGrad) {
@@ -858,17 +1006,22 @@ __global__ void __launch_bounds__(kChainThreads, 1) chain_kernel(const __grid_co
             }
         }
     }
-    if constexpr (MR) {
-        // the last CTA to finish tells the neighbours that this rank no longer reads what they wrote for this step
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            __threadfence_system();
-            const unsigned old = atomicAdd(C.cta_count, 1u);
-            if (old == gridDim.x - 1) {
-                *C.cta_count = 0;
+    // the last CTA to finish announces that this launch no longer reads anything: to the neighbouring ranks (which write
+    // into this rank's arrays in their next step) and to the launch after next of this GPU (overlapping steps)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if constexpr (MR) __threadfence_system();
+        else __threadfence();
+        unsigned *count = C.cta_count + (C.epoch & 1u);
+        const unsigned old = atomicAdd(count, 1u);
+        if (old == gridDim.x - 1) {
+            __threadfence();
+            *count = 0;
+            if constexpr (MR) {
                 if (g.has_left) st_release_sys_u32(C.step_out_l, C.epoch);
                 if (g.has_right) st_release_sys_u32(C.step_out_r, C.epoch);
             }
+            st_release_u32(C.completed + (C.epoch & 1u), C.epoch);
         }
     }
 }
@@ -920,14 +1073,27 @@ struct ChainPlan {
 
 }  // namespace
 
+// What the most recent launch was: the next one may overlap with it only if it is the step after it
+struct ChainLast {
+    bool valid = false;
+    unsigned epoch = 0;
+    int kind = 0, nphases = 0, with_density = 0, density_pz = 0, noise_zero = 0;
+    const float *vin_u = nullptr, *vin_v = nullptr;
+    float *u = nullptr, *v = nullptr, *p = nullptr, *div = nullptr, *yu = nullptr, *yv = nullptr, *d = nullptr, *nd = nullptr;
+};
+
 struct ChainState {
     ChainPlan plan[2];                    // [0] with the diffusion phase, [1] without
-    unsigned char *buf = nullptr;         // [done | misc | vmax | trace x 2 | link regions | flags | rings sor | rings gs]
+    unsigned char *buf = nullptr;         // [done | misc | vmax x 2 | trace x 4 | link regions | flags | rings sor | rings gs]
     size_t bytes = 0;
     float *extra[2] = {nullptr, nullptr}; // pressure / divergence of the second projection of a whole-step launch
     size_t extra_floats = 0;
     unsigned epoch = 0;
     int last_nphases[2] = {0, 0};         // of the most recent launch of each kind (for chain_read_trace)
+    int last_trace[2] = {0, 1};           // ... and the timeline buffer it wrote
+    uint32_t *nz_polys = nullptr;         // jump polynomials of the noise phase for (nz_H, nz_cw)
+    int nz_H = 0, nz_cw = 0;
+    ChainLast last;
 };
 
 namespace {
@@ -1043,13 +1209,14 @@ void fill_wf(WfKernelParams &P, int W, int H, int nstr, int nstg, int ncta, floa
 }
 
 constexpr size_t kDoneBytes = (size_t)kChainMaxPhases * kChainMaxItems * sizeof(unsigned);
-constexpr size_t kMiscBytes = 256;        // +0 error word, +64 step words written by the neighbours, +128 finished-CTA count
-constexpr size_t kVmaxBytes = (size_t)2 * kChainMaxPhases * kChainMaxItems * sizeof(float);   // max |v|, then max |u|
+constexpr size_t kMiscBytes = 256;        // +0 error word, +64 step words written by the neighbours, +128 finished-CTA counts, +192 completed launches
+constexpr size_t kVmaxOne = (size_t)2 * kChainMaxPhases * kChainMaxItems * sizeof(float);     // max |v|, then max |u|
+constexpr size_t kVmaxBytes = 2 * kVmaxOne;                                                  // overlapping launches alternate
 constexpr size_t kTraceOne = (size_t)kChainMaxPhases * kChainMaxItems * 3 * sizeof(unsigned long long);
 // everything up to here sits at the same offsets on every rank (the neighbours address it through peer mappings)
 constexpr size_t kVmaxOff = kDoneBytes + kMiscBytes;
 constexpr size_t kTraceOff = kVmaxOff + kVmaxBytes;
-constexpr size_t kLinksOff = kTraceOff + 2 * kTraceOne;            // one link region per sweep phase
+constexpr size_t kLinksOff = kTraceOff + 4 * kTraceOne;            // one link region per sweep phase
 constexpr size_t kFixedBytes = kLinksOff + kChainMaxSweeps * kLinkBytes;
 
 // hand-over of the strip chain to / from the neighbouring ranks for sweep phase `slot`
@@ -1084,6 +1251,7 @@ void chain_state_destroy(ChainState *cs)
     if (cs->buf) cudaFree(cs->buf);
     for (int k = 0; k < 2; ++k)
         if (cs->extra[k]) cudaFree(cs->extra[k]);
+    if (cs->nz_polys) cudaFree(cs->nz_polys);
     delete cs;
 }
 
@@ -1117,10 +1285,17 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     const int ncols = multi ? B->ncols : A.H;
     ChainPlan &pl = cs->plan[kind];
     if (pl.W != A.W || pl.H != A.H || pl.D != A.sor_sweeps || pl.P != A.gs_sweeps || pl.ncols != ncols || pl.multi != multi)
+    {
         pl = make_plan(A.W, A.H, A.sor_sweeps, A.gs_sweeps, ncols, multi);
+        cs->last.valid = false;
+    }
     if (!pl.ok) return cudaErrorNotSupported;
     if (A.with_density && !A.with_advect) return cudaErrorInvalidValue;
     if (multi && (!A.with_advect || B->halo < pl.cw || B->halo < A.gs_sweeps + 2)) return cudaErrorNotSupported;
+    const bool with_noise = A.vin_u != nullptr;
+    const bool ovl = A.overlap && !multi;      // launches of consecutive steps may overlap
+    if (with_noise && (multi || !A.vin_v || !A.with_advect || (!A.noise_zero && !A.noise_base))) return cudaErrorInvalidValue;
+    if ((A.yu == nullptr) != (A.yv == nullptr) || (A.yu && !A.with_advect)) return cudaErrorInvalidValue;
     if (mode == 1) return cudaSuccess;
 
     const GridView G = multi ? B->G : whole_grid(A.W, A.H);
@@ -1165,11 +1340,29 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         cs->bytes = need;
     }
     if (mode == 2) return cudaStreamSynchronize(st);
+    if (with_noise && !A.noise_zero && (cs->nz_H != A.H || cs->nz_cw != pl.cw || !cs->nz_polys)) {
+        // jump polynomials of the noise phase (chain_noise): x^k mod (x^31 - x^28 - 1), 32 words each
+        std::vector<uint32_t> host((size_t)kNzPolys * 32, 0u);
+        nz_fill_polys(A.H, pl.cw, host.data());
+        e = cudaStreamSynchronize(st);         // a launch in flight may still read the old table
+        if (e != cudaSuccess) return e;
+        if (!cs->nz_polys) {
+            e = cudaMalloc(&cs->nz_polys, host.size() * sizeof(uint32_t));
+            if (e != cudaSuccess) return e;
+        }
+        e = cudaMemcpy(cs->nz_polys, host.data(), host.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) return e;
+        cs->nz_H = A.H;
+        cs->nz_cw = pl.cw;
+    }
     unsigned char *b = cs->buf;
     unsigned *done = reinterpret_cast<unsigned *>(b);
     unsigned long long *err = reinterpret_cast<unsigned long long *>(b + kDoneBytes);
-    float *vmax = reinterpret_cast<float *>(b + kVmaxOff);
-    unsigned long long *trace = reinterpret_cast<unsigned long long *>(b + kTraceOff + kind * kTraceOne);
+    const unsigned epoch = ++cs->epoch;
+    const int par = ovl ? (int)(epoch & 1u) : 0;          // overlapping launches alternate between two sets of these
+    float *vmax = reinterpret_cast<float *>(b + kVmaxOff + par * kVmaxOne);
+    const int trace_idx = kind + 2 * par;
+    unsigned long long *trace = reinterpret_cast<unsigned long long *>(b + kTraceOff + trace_idx * kTraceOne);
     unsigned char *b2 = b + kFixedBytes;
     unsigned long long *flags[kChainMaxSweeps];
     for (int k = 0; k < kChainMaxSweeps; ++k) flags[k] = reinterpret_cast<unsigned long long *>(b2 + k * flag_bytes);
@@ -1185,7 +1378,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     C.g = ChainGrid{A.W, A.H, G.pitch, G.jbase, G.j0, G.j1, cw, multi ? B->halo : 0, multi && B->has_left, multi && B->has_right,
                     multi ? G.jbase - B->ncols : 0, multi ? G.jbase + B->ncols : 0};
     C.smem_floats = (int)(pl.smem / sizeof(float));
-    C.epoch = ++cs->epoch;
+    C.epoch = epoch;
     C.done = done;
     C.err = err;
     C.timeout_ns = 20ull * 1000 * 1000 * 1000;
@@ -1193,6 +1386,29 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     C.vmax = vmax;
     C.step_in = reinterpret_cast<unsigned *>(b + kDoneBytes + 64);
     C.cta_count = reinterpret_cast<unsigned *>(b + kDoneBytes + 128);
+    C.completed = reinterpret_cast<unsigned *>(b + kDoneBytes + 192);
+    C.pdl = ovl ? 1 : 0;
+    C.nz_zero = A.noise_zero;
+    C.nz_polys = cs->nz_polys;
+    if (with_noise && !A.noise_zero) std::memcpy(C.nz_base, A.noise_base, sizeof(C.nz_base));
+    // Is this the step after the one the previous launch ran, in buffers that rotate as the overlap needs?  Then it may
+    // start while that launch drains.  What this launch writes must not be anything the previous one reads far from
+    // the writing block: its two velocity sets (traced by its advection phases), the density it advects from; its
+    // results must be this step's inputs.  Otherwise: an ordinary launch, which starts when the stream is idle.
+    {
+        const ChainLast &L = cs->last;
+        auto differs = [](const void *x, std::initializer_list<const void *> ys) {
+            for (const void *y : ys)
+                if (x == y) return false;
+            return true;
+        };
+        C.xstep = ovl && with_noise && A.yu && A.with_density && L.valid && L.epoch + 1 == epoch && L.kind == kind &&
+                  L.with_density == A.with_density && L.density_pz == A.density_pz && L.noise_zero == A.noise_zero &&
+                  L.yu && A.vin_u == L.yu && A.vin_v == L.yv && A.d == L.nd && A.p == L.p && A.div == L.div &&
+                  differs(A.u, {L.u, L.v, L.yu, L.yv}) && differs(A.v, {L.u, L.v, L.yu, L.yv}) &&
+                  differs(A.yu, {L.u, L.v, L.yu, L.yv, L.vin_u, L.vin_v}) && differs(A.yv, {L.u, L.v, L.yu, L.yv, L.vin_u, L.vin_v}) &&
+                  differs(A.nd, {L.d, L.nd});
+    }
     const ChainPeer none;
     const ChainPeer &PL = (multi && B->has_left) ? B->left : none, &PR = (multi && B->has_right) ? B->right : none;
     if (PL.chain_buf) {
@@ -1222,6 +1438,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         ph.cpv = cw;
         ph.shift = 0;
         ph.ndeps = 0;
+        ph.nxdeps = 0;
         return ph;
     };
     // a sweep phase of nstg stages with nstr strips per CTA over nf fields: this rank's CTAs of the global chain
@@ -1242,6 +1459,10 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         ph.shift = shift;
         ph.wf = nwf;
         ph.ndeps = 0;
+        ph.nxdeps = 0;
+        // overlapping steps: the rings between this item and the next are reused by the next launch; the item on the
+        // right must have taken everything the step before sent it (items cl and cl + 1 of the same phase)
+        ph.xdep[ph.nxdeps++] = ChainDep{np - 1, 1, 0, 32 * nstr};
         WfKernelParams &P = C.wf[nwf++];
         fill_wf(P, A.W, A.H, nstr, nstg, ncta, a, c_recip, omega, rings, flags[slot], ++scr.seq);
         P.pitch = G.pitch;
@@ -1266,7 +1487,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             ph.c0 = -0.5f * h;                    // evaluated first (:311)
             if (after >= 0) ph.dep[ph.ndeps++] = ChainDep{after, 0, 1, 1};    // u, v of the block and one column either side
         }
-        int ph_gs = -1, ph_prev = ph_div;
+        int ph_gs = -1, ph_prev = ph_div, ph_gs_first = -1;
         for (int k = 0; k < pl.gs_npass; ++k) {
             if (k > 0) {
                 // setBoundary(0, p) after the previous pass's last sweep (:330): the next pass reads the walls of its
@@ -1278,6 +1499,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             }
             const int ph_last = ph_gs;
             ph_gs = np;
+            if (k == 0) ph_gs_first = np;
             const int slot = 1 + gs_slot * kChainMaxGsPasses + k;
             ChainPhase &ph = sweep_phase(k == 0 ? kPhGs : kPhGsX0, pl.gs_nstr, pl.gs_stages[k], kChainSP, 1, 0.0f, 1.0f, 1.0f,
                                          rings_gs[slot - 1], slot);
@@ -1299,13 +1521,38 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         ph.push_cols = multi ? B->halo : 0;               // the neighbours' traces reach this far into these columns
         ph.dep[ph.ndeps++] = ChainDep{ph_gs, 0, 1, 1};    // pressure of the block and one column either side
         ph.dep[ph.ndeps++] = ChainDep{ph_div, 1, 1, 1};   // the divergence blocks that read the u, v about to change
-        return np - 1;
+        // Overlapping steps: pressure and divergence are scratch of this projection alone, but the step before used the
+        // same arrays.  Its sweep items must have loaded the divergence this step overwrites (all passes: the last
+        // one's items, a block wider for the passes' different shifts), its gradient blocks must have read the
+        // pressure this step's sweeps (and wall updates) overwrite.
+        const int ph_grad = np - 1;
+        {
+            const int sh = C.ph[ph_gs].shift;
+            ChainPhase &dv = C.ph[ph_div];
+            dv.xdep[dv.nxdeps++] = ChainDep{ph_gs, 1, sh + kChainCols, -sh + kChainCols};
+            for (int q = ph_gs_first; q < ph_grad; ++q) {
+                ChainPhase &g = C.ph[q];
+                g.xdep[g.nxdeps++] = ChainDep{ph_grad, 1, 1, 1};
+            }
+        }
+        return ph_grad;
     };
 
+    int ph_noise = -1;
+    if (with_noise) {
+        // u, v = (velocity the step starts from) + noise, every cell (src/fluid_sim.cpp:374-383)
+        ph_noise = np;
+        ChainPhase &ph = pointwise_phase(kPhNoise);
+        ph.u = A.u;
+        ph.v = A.v;
+        ph.src_a = A.vin_u;
+        ph.src_b = A.vin_v;
+    }
     int ph_sor = -1;
     if (A.sor_sweeps > 0) {
         ph_sor = np;
         ChainPhase &ph = sweep_phase(kPhSor, pl.sor_nstr, A.sor_sweeps / kChainSD, kChainSD, 2, A.a, A.c_recip, A.omega, rings_sor, 0);
+        if (ph_noise >= 0) ph.dep[ph.ndeps++] = ChainDep{ph_noise, 0, 0, 0};        // the columns the item loads
         WfKernelParams &P = C.wf[ph.wf];
         P.fld[0] = SweepField{A.u, A.u, A.u, -1.0f, 1.0f};    // setBoundary(1, u): negated on the i-walls
         P.fld[1] = SweepField{A.v, A.v, A.v, 1.0f, -1.0f};    // setBoundary(2, v): negated on the j-walls
@@ -1314,7 +1561,9 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         P.fld[2] = P.fld[0];
     }
     const bool fold = A.with_density && A.density_pz;
-    const int ph_grad1 = projection(A.u, A.v, A.p, A.div, ph_sor, 0, nullptr, PL.u, PL.v, PL.p, nullptr, PR.u, PR.v, nullptr);
+    const int ph_grad1 = projection(A.u, A.v, A.p, A.div, ph_sor >= 0 ? ph_sor : ph_noise, 0, nullptr, PL.u, PL.v, PL.p, nullptr,
+                                    PR.u, PR.v, nullptr);
+    float *yu = A.yu ? A.yu : A.p, *yv = A.yu ? A.yv : A.div;     // the advected velocity
     if (A.with_advect) {
         // advect(1, u), advect(2, v) (:401-402) into the buffers the first projection used as pressure / divergence
         const int ph_gs1 = ph_grad1 - 1;
@@ -1325,8 +1574,8 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             ph.v = A.v;
             ph.src_a = A.u;
             ph.src_b = A.v;
-            ph.dst_a = A.p;
-            ph.dst_b = A.div;
+            ph.dst_a = yu;
+            ph.dst_b = yv;
             ph.ba = 1;
             ph.bb = 2;
             ph.pz = 0;
@@ -1335,17 +1584,20 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             ph.peer_l[0] = PL.p; ph.peer_l[1] = PL.div;
             ph.peer_r[0] = PR.p; ph.peer_r[1] = PR.div;
             ph.push_cols = multi ? cw : 0;             // the neighbour's divergence reads one column across
-            ph.dep[ph.ndeps++] = ChainDep{ph_grad1, 1, 1, 1};                                // gradient blocks still reading p here
-            const int sh = C.ph[ph_gs1].shift;                                             // of the projection's last pass
-            ph.dep[ph.ndeps++] = ChainDep{ph_gs1, 1, sh, -sh};                             // sweep items that load div here
+            if (!A.yu) {
+                ph.dep[ph.ndeps++] = ChainDep{ph_grad1, 1, 1, 1};                            // gradient blocks still reading p here
+                const int sh = C.ph[ph_gs1].shift;                                         // of the projection's last pass
+                ph.dep[ph.ndeps++] = ChainDep{ph_gs1, 1, sh, -sh};                         // sweep items that load div here
+            }
         }
         // the second projection works in scratch of its own: u, v stay intact for traces that start far away
-        const int ph_grad2 = projection(A.p, A.div, cs->extra[0], cs->extra[1], ph_adv, 1, fold ? A.d : nullptr, PL.p, PL.div,
+        const int ph_grad2 = projection(yu, yv, cs->extra[0], cs->extra[1], ph_adv, 1, fold ? A.d : nullptr, PL.p, PL.div,
                                         PL.extra[0], fold ? PL.d : nullptr, PR.p, PR.div, fold ? PR.d : nullptr);
         if (A.with_density) {
+            const int ph_advd = np;
             ChainPhase &ph = pointwise_phase(kPhAdvect);
-            ph.u = A.p;
-            ph.v = A.div;
+            ph.u = yu;
+            ph.v = yv;
             ph.src_a = A.d;
             ph.dst_a = A.nd;
             ph.ba = 0;
@@ -1355,14 +1607,64 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             ph.peer_l[0] = PL.nd;
             ph.peer_r[0] = PR.nd;
             ph.push_cols = multi ? B->halo : 0;        // the next step's density traces reach into these columns
+            // Overlapping steps: the density this step starts from is the result of the step before.  Its gradient
+            // phase (which sets that density's walls, and which the density advection waits for over its whole reach)
+            // takes the block from the previous launch's density advection ...
+            ChainPhase &g2 = C.ph[ph_grad2];
+            g2.xdep[g2.nxdeps++] = ChainDep{ph_advd, 0, 1, 1};
+        }
+        if (ph_noise >= 0) {
+            // ... and the noise phase takes the velocity from its second gradient phase; it overwrites what the step
+            // before read as ITS starting velocity, block by block
+            ChainPhase &nz = C.ph[ph_noise];
+            nz.xdep[nz.nxdeps++] = ChainDep{ph_grad2, 0, 1, 1};
+            nz.xdep[nz.nxdeps++] = ChainDep{ph_noise, 0, 0, 0};
         }
     }
     C.nphases = np;
+    C.xstep = C.xstep && cs->last.nphases == np;
     cs->last_nphases[kind] = np;
+    cs->last_trace[kind] = trace_idx;
+    {
+        ChainLast &L = cs->last;
+        L.valid = true;
+        L.epoch = epoch;
+        L.kind = kind;
+        L.nphases = np;
+        L.with_density = A.with_density;
+        L.density_pz = A.density_pz;
+        L.noise_zero = A.noise_zero;
+        L.vin_u = A.vin_u; L.vin_v = A.vin_v;
+        L.u = A.u; L.v = A.v; L.p = A.p; L.div = A.div;
+        L.yu = A.yu; L.yv = A.yv;
+        L.d = A.d; L.nd = A.nd;
+    }
 
     void *args[] = {&C};
     const void *kern = chain_kernel_ptr(A.sor_sweeps > 0, multi, pl.cw);
-    return cudaLaunchCooperativeKernel(kern, dim3(pl.grid), dim3(kChainThreads), args, pl.smem, st);
+    // Cooperative (all CTAs guaranteed co-resident) unless steps may overlap: a cooperative launch never starts before
+    // the launch before it has drained, a launch with programmatic stream serialization does, and is given its SMs
+    // only once every CTA of that launch is resident (they trigger at their first instruction), so the CTAs of both
+    // are co-resident by construction (the grid fits the GPU: make_plan).  It still starts after everything else the
+    // stream holds between the two.
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3(pl.grid);
+    lc.blockDim = dim3(kChainThreads);
+    lc.dynamicSmemBytes = pl.smem;
+    lc.stream = st;
+    cudaLaunchAttribute at[1];
+    lc.attrs = at;
+    lc.numAttrs = 0;
+    if (!ovl) {
+        at[0].id = cudaLaunchAttributeCooperative;
+        at[0].val.cooperative = 1;
+        lc.numAttrs = 1;
+    } else if (C.xstep) {
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        lc.numAttrs = 1;
+    }
+    return cudaLaunchKernelExC(&lc, kern, args);
 }
 
 // Start / end times of every work item of the most recent chained launch of one kind (which = 0: launches that begin
@@ -1373,7 +1675,7 @@ cudaError_t chain_read_trace(ChainState *cs, int which, unsigned long long *out,
     *nphases = 0;
     if (!cs || !cs->buf || which < 0 || which > 1) return cudaSuccess;
     const unsigned long long *trace =
-        reinterpret_cast<const unsigned long long *>(cs->buf + kTraceOff + which * kTraceOne);
+        reinterpret_cast<const unsigned long long *>(cs->buf + kTraceOff + cs->last_trace[which] * kTraceOne);
     const int np = std::min(cs->last_nphases[which], max_phases), ni = std::min(max_items, kChainMaxItems);
     for (int p = 0; p < np; ++p) {
         cudaError_t e = cudaMemcpy(out + (size_t)p * max_items * 3, trace + (size_t)p * kChainMaxItems * 3,

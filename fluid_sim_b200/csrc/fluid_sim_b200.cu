@@ -75,6 +75,11 @@ struct fsb_sim {
     SweepScratch sweep;
     ChainState *chain = nullptr;           // passes chained inside one launch (chain.cu), lazily created
     int chain_level = 2;                   // 0: every pass its own launch, 1: diffuse + project chained, 2: the whole step
+    int chain_overlap = 1;                 // the whole step INCLUDING the noise as one launch, consecutive steps overlapping
+    // Buffers the overlapping steps rotate through besides f[]: [0..1], [2..3] two more velocity sets (a step must not
+    // write what the step before still traces through), [4..5] pressure / divergence of the first projection (f[]'s prev
+    // arrays hold a velocity set then), [6] a third density.  Allocated on the first such step.
+    float *spare[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     NoiseTables noise_tables;
     uint32_t noise_win[kRandDeg];          // window of the emulated rand() stream at noise_pos
     uint64_t noise_pos = 0;
@@ -485,7 +490,9 @@ int advect_one(fsb_sim *s, int b, float *dst, const float *src, const float *u, 
     return set_boundary1(s, dst, b);
 }
 
-int add_noise(fsb_sim *s)
+// The window of the rand() stream at the first output of this step's noise; moves the stream on by the 2*W*H outputs
+// the step consumes (src/fluid_sim.cpp:374-383).
+void take_noise_window(fsb_sim *s, NoiseWindow *nw)
 {
     const bool shared = s->prm.noise_process_stream && s->prm.noise_mode == FSB_NOISE_GLIBC && !s->is_block;
     std::unique_lock<std::mutex> lock(g_proc_noise_mu, std::defer_lock);
@@ -494,12 +501,19 @@ int add_noise(fsb_sim *s)
         lock.lock();
         if (s->noise_pos != g_proc_noise_pos) set_noise_window(s, s->prm.noise_seed, g_proc_noise_pos);
     }
-    struct Publish {
-        fsb_sim *s; bool on;
-        ~Publish() { if (on) g_proc_noise_pos = s->noise_pos; }
-    } publish{s, shared};
+    std::memcpy(nw->w, s->noise_win, sizeof(nw->w));
+    // the reference consumes 2*W*H outputs per step in either mode (the zero mode replaces rand() itself)
+    if (s->prm.noise_mode != FSB_NOISE_ZERO) {
+        apply_jump(s->noise_step_jump, s->noise_win);
+        s->noise_pos += 2ull * (uint64_t)s->W * (uint64_t)s->H;
+    }
+    if (shared) g_proc_noise_pos = s->noise_pos;
+}
+
+int add_noise(fsb_sim *s)
+{
     NoiseWindow nw;
-    std::memcpy(nw.w, s->noise_win, sizeof(nw.w));
+    take_noise_window(s, &nw);
     const int zero = s->prm.noise_mode == FSB_NOISE_ZERO;
     ProfScope ps(s, FSB_PROF_NOISE);
     if (s->is_block)
@@ -507,11 +521,6 @@ int add_noise(fsb_sim *s)
     else
         FSB_CUDA(launch_noise(s->f[FSB_VELOCITY_X], s->f[FSB_VELOCITY_Y], s->ncells, nw, s->noise_tables, zero, s->stream));
     s->launches += zero ? 2 : 1;
-    // the reference consumes 2*W*H outputs per step in either case (the zero mode replaces rand() itself)
-    if (!zero) {
-        apply_jump(s->noise_step_jump, s->noise_win);
-        s->noise_pos += 2ull * (uint64_t)s->W * (uint64_t)s->H;
-    }
     return FSB_OK;
 }
 
@@ -582,6 +591,84 @@ int chained_launch(fsb_sim *s, bool with_diffuse, bool whole_step, float dt, boo
             if (density_done) *density_done = true;
         }
     }
+    return FSB_OK;
+}
+
+// FluidSim::step (src/fluid_sim.cpp:25-28) as ONE launch, noise included, in buffers that rotate so that the launch of
+// the next step may start on the SMs this one's first CTAs have left (chain.cu, launch_chain).  Step n reads the velocity
+// V(n-1) = f[velocity], writes V(n-1) + noise, diffuses and projects in X(n), advects into Y(n) and projects again; it
+// advects the density f[density] into D(n).  Afterwards f[velocity] = Y(n), f[prev velocity] = X(n), f[density] = D(n),
+// f[prev density] = the density the step started from, and the two velocity sets / the density that were current and
+// previous BEFORE the step become the spares the next step writes: nothing a step writes is read by the step before it
+// anywhere but in the block being written.
+// *done = false: this grid / these parameters have no such configuration; nothing has been changed.
+int chained_step(fsb_sim *s, float dt, bool *done)
+{
+    *done = false;
+    if (s->chain_level < 2 || !s->chain_overlap || s->is_block || s->tune_strips || s->tune_levels || s->tune_stages) return FSB_OK;
+    if (s->chain_level < 3 && s->W > 2 * s->H && s->H < 4096) return FSB_OK;      // see chained_launch
+    if (s->prm.advect_scheme != FSB_ADVECT_RK4) return FSB_OK;
+    if (s->prm.noise_mode != FSB_NOISE_GLIBC && s->prm.noise_mode != FSB_NOISE_ZERO) return FSB_OK;
+    const float ad = dt * s->prm.diffusion * (float)s->W * (float)s->H;
+    if (ad != 0.0f) return FSB_OK;               // the density diffusion would run between the launches
+    ChainArgs A{};
+    A.W = s->W;
+    A.H = s->H;
+    A.gs_sweeps = s->prm.proj_iters;
+    A.omega = s->prm.omega;
+    A.dt = dt;
+    A.a = dt * s->prm.viscosity * (float)s->W * (float)s->H;       // ((dt*diff)*W)*H, src/fluid_sim.cpp:45
+    A.c_recip = 1.0f / (1.0f + 4.0f * A.a);                        // :46
+    A.sor_sweeps = s->prm.diff_iters;
+    if (A.sor_sweeps <= 0 || A.a == 0.0f) return FSB_OK;
+    A.with_advect = 1;
+    A.with_density = 1;
+    A.density_pz = s->prm.diff_iters > 0 ? 1 : 0;
+    A.overlap = 1;
+    A.noise_zero = s->prm.noise_mode == FSB_NOISE_ZERO;
+    // any non-null pointers do for the query
+    A.vin_u = s->f[FSB_VELOCITY_X];
+    A.vin_v = s->f[FSB_VELOCITY_Y];
+    NoiseWindow nw{};
+    A.noise_base = nw.w;
+    cudaError_t e = launch_chain(A, s->chain, s->sweep, s->stream, 1);
+    if (e == cudaErrorNotSupported) return FSB_OK;
+    if (e != cudaSuccess) return fail_cuda(e, "chained step");
+    for (float *&b : s->spare)
+        if (!b) {
+            FSB_CUDA(cudaMalloc(&b, s->ncells * sizeof(float)));
+            FSB_CUDA(cudaMemsetAsync(b, 0, s->ncells * sizeof(float), s->stream));
+        }
+    take_noise_window(s, &nw);
+    A.u = s->spare[0];
+    A.v = s->spare[1];
+    A.yu = s->spare[2];
+    A.yv = s->spare[3];
+    A.p = s->spare[4];
+    A.div = s->spare[5];
+    A.d = s->f[FSB_DENSITY];
+    A.nd = s->spare[6];
+    {
+        ProfScope ps(s, FSB_PROF_CHAIN);
+        e = launch_chain(A, s->chain, s->sweep, s->stream, 0);
+    }
+    if (e != cudaSuccess) return fail_cuda(e, "chained step");
+    s->launches += 1;
+    float *const vin_u = s->f[FSB_VELOCITY_X], *const vin_v = s->f[FSB_VELOCITY_Y];
+    float *const prev_u = s->f[FSB_PREV_VEL_X], *const prev_v = s->f[FSB_PREV_VEL_Y];
+    s->f[FSB_VELOCITY_X] = A.yu;
+    s->f[FSB_VELOCITY_Y] = A.yv;
+    s->f[FSB_PREV_VEL_X] = A.u;
+    s->f[FSB_PREV_VEL_Y] = A.v;
+    s->spare[0] = vin_u;
+    s->spare[1] = vin_v;
+    s->spare[2] = prev_u;
+    s->spare[3] = prev_v;
+    float *const prev_d = s->f[FSB_PREV_DENSITY];
+    s->f[FSB_PREV_DENSITY] = s->f[FSB_DENSITY];
+    s->f[FSB_DENSITY] = A.nd;
+    s->spare[6] = prev_d;
+    *done = true;
     return FSB_OK;
 }
 
@@ -791,6 +878,9 @@ static int create_common(const fsb_params *p, const GridView *block, fsb_sim **o
         // the whole step after the noise as one chained launch where that is faster, 3: wherever it is possible
         const char *e = std::getenv("FSB_CHAIN");
         if (e && e[0] >= '0' && e[0] <= '3') s->chain_level = e[0] - '0';
+        // FSB_CHAIN_OVERLAP = 0: the noise as its own launch and every step's launch after the one before has drained
+        const char *o = std::getenv("FSB_CHAIN_OVERLAP");
+        if (o && (o[0] == '0' || o[0] == '1')) s->chain_overlap = o[0] - '0';
     }
     s->noise_step_jump = jump_matrix(2ull * (uint64_t)prm.width * (uint64_t)prm.height);
     set_noise_window(s, prm.noise_seed, prm.noise_pos);
@@ -812,6 +902,8 @@ int fsb_destroy(fsb_sim *s)
             if (s->f[k]) cudaFree(s->f[k]);
         for (int k = 0; k < 2; ++k)
             if (s->temp[k]) cudaFree(s->temp[k]);
+        for (float *b : s->spare)
+            if (b) cudaFree(b);
         if (s->sweep.xchg) cudaFree(s->sweep.xchg);
         if (s->sweep.flags) cudaFree(s->sweep.flags);
         chain_state_destroy(s->chain);
@@ -872,6 +964,8 @@ int fsb_step(fsb_sim *s, float dt)
         // everything after the noise as one launch, when this grid / these parameters have a chained configuration
         bool query = false, dens = false;
         if (s->chain_level >= 2 && !s->is_block) {
+            FSB_TRY(chained_step(s, dt, &query));
+            if (query) return FSB_OK;
             FSB_TRY(add_noise(s));
             FSB_TRY(chained_launch(s, true, true, dt, &query, &dens));
             if (query) {
@@ -1205,6 +1299,13 @@ int fsb_set_chain_level(fsb_sim *s, int level)
 {
     if (!s || level < 0 || level > 3) return fail(FSB_EINVAL, "fsb_set_chain_level: bad argument");
     s->chain_level = level;
+    return FSB_OK;
+}
+
+int fsb_set_chain_overlap(fsb_sim *s, int on)
+{
+    if (!s || on < 0 || on > 1) return fail(FSB_EINVAL, "fsb_set_chain_overlap: bad argument");
+    s->chain_overlap = on;
     return FSB_OK;
 }
 

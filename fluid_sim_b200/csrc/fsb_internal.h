@@ -125,6 +125,15 @@ struct ChainArgs {
     float dt;
     float *d, *nd;             // density and the buffer that receives the advected density
     int density_pz;            // diffusion sweeps ran with a == 0: boundaries of d + folded (v + 0.0f) taps
+    // The whole step including its noise, in buffers that let consecutive steps overlap (one GPU, see launch_chain):
+    // vin_u / vin_v: the velocity the step starts from; the noise phase writes vin + noise into u, v (nullptr: the caller
+    // has added the noise to u, v itself).  yu / yv: receive the advected velocity, which the second projection then
+    // works on (nullptr: p, div are reused for that, as the reference reuses its prev arrays).
+    const float *vin_u = nullptr, *vin_v = nullptr;
+    float *yu = nullptr, *yv = nullptr;
+    const uint32_t *noise_base = nullptr;      // window of the rand() stream at the step's first output (31 words)
+    int noise_zero = 0;                        // FSB_NOISE_ZERO
+    int overlap = 0;                           // the next step's launch may start before this one has drained
     const ChainBlock *blk = nullptr;   // column block of a multi-rank run (nullptr: the whole grid on this GPU)
 };
 // mode 0: launch; 1: only tell whether a configuration exists; 2: also allocate the scratch (so that its IPC handles can

@@ -11,6 +11,7 @@
 //   store -> noise is staged in shared memory and applied with the warp walking one lane's run at a
 //            time, so u / v are read and written in 124-byte contiguous pieces.
 #include "fsb_internal.h"
+#include "noise.cuh"
 
 namespace fsb {
 
@@ -27,13 +28,6 @@ __device__ __forceinline__ uint32_t matvec(const uint32_t *__restrict__ mt, uint
 #pragma unroll
     for (int j = 0; j < kRandDeg; ++j) acc += __ldg(mt + j * 32 + lane) * __shfl_sync(0xffffffffu, win, j);
     return acc;
-}
-
-__device__ __forceinline__ float noise_of(uint32_t word)
-{
-    const int r = (int)(word >> 1);                       // rand() output
-    const float f = __fmul_rn((float)r, 4.656612873077393e-10f);   // (float)rand() / RAND_MAX, RAND_MAX -> 2^31
-    return __fmul_rn(__fsub_rn(f, 0.5f), 1e-4f);
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) noise_kernel(float *__restrict__ u, float *__restrict__ v,

@@ -291,6 +291,14 @@ int fsb_set_tuning(fsb_sim *s, int strips_per_cta, int sweeps_per_warp, int max_
  * noise as one chained launch on the grid shapes where that was measured faster; 3: wherever a chained configuration
  * exists.  Results are bit-identical at every level.  The environment variable FSB_CHAIN sets the initial level. */
 int fsb_set_chain_level(fsb_sim *s, int level);
+/* Also without counterpart in the reference: at chain level >= 2, with DIFFUSION == 0 and the RK4 advection, fsb_step is
+ * ONE launch that contains the noise as well, and consecutive calls overlap on the GPU: the launch of step n+1 starts on
+ * the SMs the first thread blocks of step n have left while the last ones are still at work (the launches order
+ * themselves block by block through words in device memory).  on = 0: the noise is its own launch and every step's launch
+ * starts after the one before has drained (round-2 structure before this).  Results are bit-identical either way; the
+ * fields rotate through seven more buffers of the grid's size.  Default 1; the environment variable FSB_CHAIN_OVERLAP
+ * sets the initial value. */
+int fsb_set_chain_overlap(fsb_sim *s, int on);
 
 const char *fsb_last_error(void);
 const char *fsb_version(void);

@@ -269,6 +269,42 @@ def test_whole_step_as_one_chained_launch(w, h, p, d, steps, inject):
         assert_bits(a, b, f"{w}x{h} P={p} D={d} {inject}: field {n}")
 
 
+@pytest.mark.parametrize("w,h,p,d", [(300, 1100, 40, 10), (96, 200, 20, 5), (40, 257, 30, 5), (1024, 4096, 40, 5),
+                                     (400, 7168, 20, 5)])      # the last one: 64-column blocks, as at 8192^2
+@pytest.mark.parametrize("noise", ["glibc", "zero"])
+def test_overlapping_steps(w, h, p, d, noise):
+    """fsb_step as one launch that contains the noise, consecutive steps overlapping on the GPU (the default where a
+    chained configuration exists): seven steps back to back (the velocity sets rotate with period 2, the densities with
+    period 3), then calls that put other work between the steps (sources, reads, a velocityStep of its own) and more
+    steps; compared with the oracle after every stage, and with the same library run without the overlap."""
+    gpu, ora = make_pair(w, h, p, d, chain=3, noise=noise)
+    ser = fsb.FluidSim(w, h, p, d, chain=3, noise=noise, overlap=False)
+    dd, uu, vv = vortex_lattice(w, h)
+    for s, ids in ((gpu, (fsb.DENSITY, fsb.VELOCITY_X, fsb.VELOCITY_Y)), (ser, (fsb.DENSITY, fsb.VELOCITY_X, fsb.VELOCITY_Y)),
+                   (ora, (0, 1, 2))):
+        s.write(ids[0], dd); s.write(ids[1], uu); s.write(ids[2], vv)
+    n0 = gpu.launch_count()
+    for _ in range(7):
+        gpu.step(0.01); ser.step(0.01); ora.step(0.01)
+    assert gpu.launch_count() - n0 == 7                     # one launch per step, noise included
+    for a, b, c, n in zip(gpu.fields(), ora.fields(), ser.fields(), "duv"):
+        assert_bits(a, b, f"{w}x{h} after 7 steps: field {n}")
+        assert_bits(c, b, f"{w}x{h} after 7 steps without overlap: field {n}")
+    for k in range(3):
+        for s in (gpu, ser, ora):
+            s.addDensity(w // 2, h // 3 + k, 2.0)
+            s.addVelocity(w // 3, h // 2, 0.5, -0.25)
+            s.step(0.01)
+    for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+        assert_bits(a, b, f"{w}x{h} with sources between the steps: field {n}")
+    for s in (gpu, ora):
+        s.velocityStep(0.01); s.densityStep(0.01)
+        s.step(0.01); s.step(0.01)
+    for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
+        assert_bits(a, b, f"{w}x{h} after velocityStep / densityStep / two more steps: field {n}")
+    ser.close()
+
+
 def test_velocity_and_density_step_entry_points():
     """fsb_op_velocity_step / fsb_op_density_step (velocityStep, densityStep of src/fluid_sim.cpp:370-422) called one after
     the other equal step(); checked against the oracle's two halves after each call."""

@@ -50,6 +50,17 @@ def test_rand_jump_model():
     assert out.returncode == 0, out.stdout + out.stderr
 
 
+def test_noise_phase_stream_positions():
+    """Noise as a phase of the chained launch (noise.cuh, chain.cu): every thread's schedule of polynomial jumps and
+    its circular generation reproduce the step's rand() outputs at the cells of its row pieces."""
+    src = os.path.join(ROOT, "tests", "noise_phase_check.cpp")
+    exe = "/tmp/fsb_noise_phase_check"
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I", os.path.join(ROOT, "fluid_sim_b200", "csrc"), src, "-o", exe],
+                   check=True)
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+
+
 @pytest.mark.parametrize("w,h,P", [(20, 24, 3), (40, 70, 20), (33, 31, 7)])
 def test_wavefront_model_projection(w, h, P):
     rng = np.random.default_rng(w + h)
