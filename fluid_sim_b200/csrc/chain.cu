@@ -39,6 +39,7 @@ constexpr int kChainMaxXDeps = 3;     // dependencies on the previous launch (ov
 constexpr int kChainMaxSweeps = 7;      // sweep phases per launch: diffusion + up to three passes per projection
 constexpr int kChainMaxGsPasses = 3;
 constexpr int kChainCols = 64;          // columns of a pointwise work item
+constexpr int kChainMaxSources = kChainSources;   // addDensity / addVelocity calls a launch can apply itself (kernel parameters)
 
 enum ChainKind { kPhSor = 1, kPhGs = 2, kPhDiv = 3, kPhGrad = 4, kPhAdvect = 5, kPhGsX0 = 6, kPhBndP = 7, kPhNoise = 8 };
 
@@ -88,8 +89,12 @@ struct ChainPhase {
     int push_cols;
     int reach_phase;    // advection: the gradient phase that published u, v (its per-block max |v| bounds the trace)
     int ba, bb;         // advection: setBoundary's b of dst_a / dst_b
+    float *snap;        // advection of one field: a second copy of the result (walls included), or nullptr
     int pz;             // advection: interior taps of src_a are read as (v + 0.0f) (diffuse with a == 0)
 };
+
+// One pending addDensity (field 0) / addVelocity (fields 1, 2: x and y component) call, src/fluid_sim.cpp:425-438
+struct ChainSrc { int row, col, field; float amount; };
 
 struct ChainParams {
     int W, H, nphases;
@@ -110,6 +115,11 @@ struct ChainParams {
     int nz_zero;                    // FSB_NOISE_ZERO: every cell gets + 0.0f
     uint32_t nz_base[kRandDeg];     // window of the rand() stream at the step's first output
     const uint32_t *nz_polys;       // jump polynomials
+    // sources the noise phase applies before it adds the noise (velocity) / to the density the step starts from, in call
+    // order per cell; `density`: that field
+    int nsrc, nsrc_density;
+    float *density;
+    ChainSrc src[kChainMaxSources];
     unsigned epoch;                 // number of this launch (done[] words hold the epoch of their last completion)
     unsigned *done;                 // [kChainMaxPhases][kChainMaxItems]
     unsigned long long *err;        // watchdog report: (phase << 32 | item) + 1 of the first wait that timed out
@@ -675,6 +685,7 @@ __device__ __forceinline__ bool chain_advect_tiled(const ChainPhase &ph, const C
                     const long long c = CAT(g, ci[n], cj[n]);
                     store_pushed<MR>(dst_a, ph.peer_l[0], ph.peer_r[0], P, c, ra);
                     if (TWO) store_pushed<MR>(dst_b, ph.peer_l[1], ph.peer_r[1], P, c, rb);
+                    if (!TWO && !MR && ph.snap) ph.snap[c] = ra;
                 }
             }
         }
@@ -684,6 +695,7 @@ __device__ __forceinline__ bool chain_advect_tiled(const ChainPhase &ph, const C
     __syncthreads();
     chain_boundary<MR, CW>(dst_a, ph.peer_l[0], ph.peer_r[0], P, ph.ba, 0, g, c0);
     if (TWO) chain_boundary<MR, CW>(dst_b, ph.peer_l[1], ph.peer_r[1], P, ph.bb, 0, g, c0);
+    if (!TWO && !MR && ph.snap) chain_boundary<MR, CW>(ph.snap, nullptr, nullptr, P, ph.ba, 0, g, c0);
     return true;
 }
 
@@ -764,12 +776,14 @@ __device__ __forceinline__ void chain_advect(const ChainPhase &ph, const ChainGr
                 const long long c = CAT(g, ci[n], cj[n]);
                 store_pushed<MR>(dst_a, ph.peer_l[0], ph.peer_r[0], P, c, ra);
                 if (TWO) store_pushed<MR>(dst_b, ph.peer_l[1], ph.peer_r[1], P, c, rb);
+                if (!TWO && !MR && ph.snap) ph.snap[c] = ra;
             }
         }
     }
     __syncthreads();
     chain_boundary<MR, CW>(dst_a, ph.peer_l[0], ph.peer_r[0], P, ph.ba, 0, g, c0);
     if (TWO) chain_boundary<MR, CW>(dst_b, ph.peer_l[1], ph.peer_r[1], P, ph.bb, 0, g, c0);
+    if (!TWO && !MR && ph.snap) chain_boundary<MR, CW>(ph.snap, nullptr, nullptr, P, ph.ba, 0, g, c0);
 }
 
 
@@ -794,22 +808,69 @@ __device__ __forceinline__ void chain_noise(const ChainParams &C, const ChainPha
     const int c0 = blk * CW;
     const float *su = ph.src_a, *sv = ph.src_b;
     float *du = ph.u, *dv = ph.v;
+    // Pending addDensity / addVelocity calls (src/fluid_sim.cpp:425-438) that fall into this block, in call order: the
+    // density ones are applied to the density the step starts from right here (that block is final: the launch waits
+    // for the previous step's density advection of it), the velocity ones to the value read below, before the noise.
+    int *s_nvs = reinterpret_cast<int *>(smem) + kNzPolys * 32;
+    int *s_list = s_nvs + 4;
+    int nvs = 0;
+    if (C.nsrc > 0) {
+        if (tid == 0) {
+            int m = 0;
+            for (int k = 0; k < C.nsrc; ++k) {
+                const ChainSrc e = C.src[k];
+                if (e.col < c0 || e.col >= c0 + CW) continue;
+                if (e.field == 0) {
+                    float *q = C.density + CAT(g, e.row, e.col);
+                    *q = __fadd_rn(__ldcg(q), e.amount);
+                } else {
+                    s_list[m++] = k;
+                }
+            }
+            s_nvs[0] = m;
+        }
+        __syncthreads();
+        nvs = s_nvs[0];
+    }
+    // is one of the block's velocity sources in the rows [lo, hi)?  (warp-uniform)
+    auto rows_have_sources = [&](const int lo, const int hi) {
+        bool any = false;
+        for (int k0 = 0; k0 < nvs; k0 += 32) {
+            const int k = k0 + lane;
+            const int r = k < nvs ? C.src[s_list[k]].row : -1;
+            any = any || __any_sync(0xffffffffu, r >= lo && r < hi);
+        }
+        return any;
+    };
+    auto add_sources = [&](const int i, const int j, float &uu, float &vv) {
+        for (int k = 0; k < nvs; ++k) {
+            const ChainSrc e = C.src[s_list[k]];
+            if (e.row == i && e.col == j) {
+                if (e.field == 1) uu = __fadd_rn(uu, e.amount);
+                else vv = __fadd_rn(vv, e.amount);
+            }
+        }
+    };
     if (C.nz_zero) {
         // rand() replaced by the value that makes the noise + 0.0f (FSB_NOISE_ZERO): the reference still adds it
-        for (int i = wid; i < W; i += kNzWarps)
+        for (int i = wid; i < W; i += kNzWarps) {
+            const bool srcs = nvs > 0 && rows_have_sources(i, i + 1);
 #pragma unroll
             for (int k = 0; k < CW / 32; ++k) {
                 const int j = c0 + 32 * k + lane;
                 if (j < H) {
                     const long long c = CAT(g, i, j);
-                    du[c] = __fadd_rn(__ldcg(su + c), 0.0f);
-                    dv[c] = __fadd_rn(__ldcg(sv + c), 0.0f);
+                    float uu = __ldcg(su + c), vv = __ldcg(sv + c);
+                    if (srcs) add_sources(i, j, uu, vv);
+                    du[c] = __fadd_rn(uu, 0.0f);
+                    dv[c] = __fadd_rn(vv, 0.0f);
                 }
             }
+        }
         return;
     }
     uint32_t *s_poly = reinterpret_cast<uint32_t *>(smem);
-    float *stg = smem + kNzPolys * 32 + wid * (32 * kNzPitch);
+    float *stg = smem + kNzPolys * 32 + 4 + kChainMaxSources + wid * (32 * kNzPitch);
     for (int i = tid; i < kNzPolys * 32; i += blockDim.x) s_poly[i] = C.nz_polys[i];
     __syncthreads();
     uint32_t w[kRandDeg];
@@ -831,6 +892,7 @@ __device__ __forceinline__ void chain_noise(const ChainParams &C, const ChainPha
             p = s_poly + (kNzLanePoly + it - 14) * 32;
         } else {
             if (R0 >= W) break;
+            const bool srcs = nvs > 0 && rows_have_sources(R0, R0 + 32);
 #pragma unroll
             for (int round = 0; round < CW / 32; ++round) {
                 // w[] is a circular buffer: output number n overwrites index n mod 31; 64 mod 31 = 2, so round r starts
@@ -854,6 +916,10 @@ __device__ __forceinline__ void chain_noise(const ChainParams &C, const ChainPha
                         const long long c = CAT(g, ok ? i : 0, ok ? j : g.jbase);
                         uu[r] = ok ? __ldcg(su + c) : 0.0f;
                         vv[r] = ok ? __ldcg(sv + c) : 0.0f;
+                    }
+                    if (srcs) {
+#pragma unroll
+                        for (int r = 0; r < 8; ++r) add_sources(R0 + r0 + r, j, uu[r], vv[r]);
                     }
 #pragma unroll
                     for (int r = 0; r < 8; ++r) {
@@ -1296,6 +1362,8 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     const bool ovl = A.overlap && !multi;      // launches of consecutive steps may overlap
     if (with_noise && (multi || !A.vin_v || !A.with_advect || (!A.noise_zero && !A.noise_base))) return cudaErrorInvalidValue;
     if ((A.yu == nullptr) != (A.yv == nullptr) || (A.yu && !A.with_advect)) return cudaErrorInvalidValue;
+    if (A.nsources < 0 || A.nsources > kChainMaxSources || (A.nsources > 0 && (!with_noise || !A.sources))) return cudaErrorInvalidValue;
+    if (A.snap && (multi || !A.with_density)) return cudaErrorInvalidValue;
     if (mode == 1) return cudaSuccess;
 
     const GridView G = multi ? B->G : whole_grid(A.W, A.H);
@@ -1391,6 +1459,17 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     C.nz_zero = A.noise_zero;
     C.nz_polys = cs->nz_polys;
     if (with_noise && !A.noise_zero) std::memcpy(C.nz_base, A.noise_base, sizeof(C.nz_base));
+    C.nsrc = A.nsources;
+    C.nsrc_density = 0;
+    C.density = A.d;
+    for (int k = 0; k < A.nsources; ++k) {
+        const SourceEntry &q = A.sources[k];
+        C.src[k] = ChainSrc{q.cell / G.pitch, q.cell % G.pitch + G.jbase, q.field, q.amount};
+        if (q.field == 0) {
+            if (!A.d) return cudaErrorInvalidValue;
+            C.nsrc_density += 1;
+        }
+    }
     // Is this the step after the one the previous launch ran, in buffers that rotate as the overlap needs?  Then it may
     // start while that launch drains.  What this launch writes must not be anything the previous one reads far from
     // the writing block: its two velocity sets (traced by its advection phases), the density it advects from; its
@@ -1604,6 +1683,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             ph.pz = A.density_pz;
             ph.c0 = -(A.dt * (float)A.W);
             ph.reach_phase = ph_grad2;
+            ph.snap = A.snap;
             ph.peer_l[0] = PL.nd;
             ph.peer_r[0] = PR.nd;
             ph.push_cols = multi ? B->halo : 0;        // the next step's density traces reach into these columns
@@ -1619,6 +1699,8 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             ChainPhase &nz = C.ph[ph_noise];
             nz.xdep[nz.nxdeps++] = ChainDep{ph_grad2, 0, 1, 1};
             nz.xdep[nz.nxdeps++] = ChainDep{ph_noise, 0, 0, 0};
+            // density sources are added to the previous step's result where it lies: that block must be final
+            if (C.nsrc_density > 0 && A.with_density) nz.xdep[nz.nxdeps++] = ChainDep{np - 1, 0, 0, 0};
         }
     }
     C.nphases = np;

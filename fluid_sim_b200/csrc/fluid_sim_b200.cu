@@ -80,6 +80,16 @@ struct fsb_sim {
     // write what the step before still traces through), [4..5] pressure / divergence of the first projection (f[]'s prev
     // arrays hold a velocity set then), [6] a third density.  Allocated on the first such step.
     float *spare[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    // Asynchronous density reads of a caller that reads after every step (fsb_read_field_async): the step's launch
+    // writes a second copy of its density (two buffers, alternating) which the copy stream then transfers, instead of
+    // a device-to-device snapshot between two launches (which would keep them from overlapping).
+    float *snap[2] = {nullptr, nullptr};
+    cudaEvent_t ev_snap_copied[2] = {nullptr, nullptr};
+    bool snap_busy[2] = {false, false};    // a transfer out of snap[k] has been queued and not yet waited for
+    int snap_next = 0, snap_idx = -1;      // buffer the next step writes; buffer that holds the current density (-1: none)
+    bool want_snap = false;                // the caller has been reading the density after its steps
+    int steps_since_read = 0;
+    cudaEvent_t last_copy = nullptr;       // completion of the most recent asynchronous read
     NoiseTables noise_tables;
     uint32_t noise_win[kRandDeg];          // window of the emulated rand() stream at noise_pos
     uint64_t noise_pos = 0;
@@ -288,6 +298,7 @@ int flush_sources(fsb_sim *s, SourceSel sel = kAllSources)
 {
     if (sel == kAllSources) FSB_TRY(order_after_copy(s));      // every entry point but fsb_step comes through here
     if (s->pending.empty()) return FSB_OK;
+    s->snap_idx = -1;                                           // the density is about to change
     std::vector<SourceEntry> chosen, rest;
     if (sel != kAllSources) {
         for (const SourceEntry &q : s->pending) ((sel == kDensitySources) == (q.field == 0) ? chosen : rest).push_back(q);
@@ -639,6 +650,23 @@ int chained_step(fsb_sim *s, float dt, bool *done)
             FSB_CUDA(cudaMalloc(&b, s->ncells * sizeof(float)));
             FSB_CUDA(cudaMemsetAsync(b, 0, s->ncells * sizeof(float), s->stream));
         }
+    // pending sources: a few (the reference's mouse handler, src/main.cpp:216-252) travel as parameters of the launch
+    // and are applied by its noise phase; more than that go through the staged copy + kernel
+    if ((int)s->pending.size() > kChainSources) FSB_TRY(flush_sources(s));
+    std::stable_sort(s->pending.begin(), s->pending.end(), [](const SourceEntry &a, const SourceEntry &b) {
+        return a.field != b.field ? a.field < b.field : a.cell < b.cell;
+    });
+    A.sources = s->pending.data();
+    A.nsources = (int)s->pending.size();
+    int snap_k = -1;
+    if (s->want_snap) {
+        snap_k = s->snap_next;
+        if (!s->snap[snap_k]) FSB_CUDA(cudaMalloc(&s->snap[snap_k], s->ncells * sizeof(float)));
+        if (!s->ev_snap_copied[snap_k]) FSB_CUDA(cudaEventCreateWithFlags(&s->ev_snap_copied[snap_k], cudaEventDisableTiming));
+        // the transfer out of this buffer was queued two steps ago
+        if (s->snap_busy[snap_k]) FSB_CUDA(cudaStreamWaitEvent(s->stream, s->ev_snap_copied[snap_k], 0));
+        A.snap = s->snap[snap_k];
+    }
     take_noise_window(s, &nw);
     A.u = s->spare[0];
     A.v = s->spare[1];
@@ -668,6 +696,12 @@ int chained_step(fsb_sim *s, float dt, bool *done)
     s->f[FSB_PREV_DENSITY] = s->f[FSB_DENSITY];
     s->f[FSB_DENSITY] = A.nd;
     s->spare[6] = prev_d;
+    s->pending.clear();
+    s->snap_idx = snap_k;
+    if (snap_k >= 0) {
+        s->snap_next ^= 1;
+        if (++s->steps_since_read > 2) s->want_snap = false;       // nobody reads: stop writing the second copy
+    }
     *done = true;
     return FSB_OK;
 }
@@ -717,6 +751,7 @@ int velocity_step(fsb_sim *s, float dt)
 
 int density_step(fsb_sim *s, float dt)
 {
+    s->snap_idx = -1;
     float *xs[1] = {s->f[FSB_DENSITY]};
     const int bs[1] = {0};
     int folded = 0;
@@ -928,6 +963,10 @@ int fsb_destroy(fsb_sim *s)
         if (s->view_buf) cudaFree(s->view_buf);
         if (s->glyph_buf) cudaFree(s->glyph_buf);
         if (s->snapshot) cudaFree(s->snapshot);
+        for (int k = 0; k < 2; ++k) {
+            if (s->snap[k]) cudaFree(s->snap[k]);
+            if (s->ev_snap_copied[k]) cudaEventDestroy(s->ev_snap_copied[k]);
+        }
         if (s->vmax_word) cudaFree(s->vmax_word);
         for (auto &r : s->prof_open) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         for (auto &e : s->prof_free) cudaEventDestroy(e);
@@ -946,6 +985,7 @@ int fsb_reset(fsb_sim *s)
     if (!s) return fail(FSB_EINVAL, "fsb_reset: null handle");
     DeviceGuard guard(s->device);
     s->pending.clear();
+    s->snap_idx = -1;
     FSB_TRY(order_after_copy(s));
     for (int k = 0; k < kNumFields; ++k) FSB_CUDA(cudaMemsetAsync(s->f[k], 0, s->ncells * sizeof(float), s->stream));
     for (int k = 0; k < 2; ++k)
@@ -958,14 +998,16 @@ int fsb_step(fsb_sim *s, float dt)
 {
     if (!s) return fail(FSB_EINVAL, "fsb_step: null handle");
     DeviceGuard guard(s->device);
-    FSB_TRY(flush_sources(s));       // density sources too: the velocity step never reads the density
     invalidate_mirror(s);
+    s->snap_idx = -1;
     {
-        // everything after the noise as one launch, when this grid / these parameters have a chained configuration
+        // the whole step as one launch (which also applies the pending sources), or everything after the noise as one
+        // launch, when this grid / these parameters have a chained configuration
         bool query = false, dens = false;
         if (s->chain_level >= 2 && !s->is_block) {
             FSB_TRY(chained_step(s, dt, &query));
             if (query) return FSB_OK;
+            FSB_TRY(flush_sources(s));       // density sources too: the velocity step never reads the density
             FSB_TRY(add_noise(s));
             FSB_TRY(chained_launch(s, true, true, dt, &query, &dens));
             if (query) {
@@ -976,6 +1018,7 @@ int fsb_step(fsb_sim *s, float dt)
             return density_step(s, dt);
         }
     }
+    FSB_TRY(flush_sources(s));
     FSB_TRY(velocity_step(s, dt));   // src/fluid_sim.cpp:26
     FSB_TRY(density_step(s, dt));    // src/fluid_sim.cpp:27
     return FSB_OK;
@@ -1121,6 +1164,7 @@ int fsb_write_field(fsb_sim *s, int field, const float *host_src)
     if (!s || !host_src || !valid_field(field)) return fail(FSB_EINVAL, "fsb_write_field: bad argument");
     DeviceGuard guard(s->device);
     FSB_TRY(flush_sources(s));
+    s->snap_idx = -1;
     FSB_CUDA(cudaMemcpyAsync(s->f[field], host_src, s->ncells * sizeof(float), cudaMemcpyHostToDevice, s->stream));
     FSB_CUDA(cudaStreamSynchronize(s->stream));
     if (field < 3) s->mirror_valid[field] = false;
@@ -1141,6 +1185,24 @@ int fsb_read_field_async(fsb_sim *s, int field, float *host_dst)
         FSB_CUDA(cudaEventCreateWithFlags(&s->ev_ready, cudaEventDisableTiming));
         FSB_CUDA(cudaEventCreateWithFlags(&s->ev_copied, cudaEventDisableTiming));
     }
+    if (field == FSB_DENSITY) {
+        // a caller that reads the density after its steps: from now on the steps' launches leave a second copy of it
+        s->want_snap = true;
+        s->steps_since_read = 0;
+        if (s->snap_idx >= 0) {
+            // the last step did: transfer that copy once the step has finished (an event, nothing else, goes between
+            // this step's launch and the next one's, so they still overlap)
+            const int k = s->snap_idx;
+            FSB_CUDA(cudaEventRecord(s->ev_ready, s->stream));
+            FSB_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_ready, 0));
+            FSB_CUDA(cudaMemcpyAsync(host_dst, s->snap[k], s->ncells * sizeof(float), cudaMemcpyDeviceToHost, s->copy_stream));
+            FSB_CUDA(cudaEventRecord(s->ev_snap_copied[k], s->copy_stream));
+            s->snap_busy[k] = true;
+            s->last_copy = s->ev_snap_copied[k];
+            s->copy_pending = true;
+            return FSB_OK;
+        }
+    }
     if (!s->snapshot) FSB_CUDA(cudaMalloc(&s->snapshot, s->ncells * sizeof(float)));
     if (s->copy_pending) FSB_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied, 0));   // the snapshot buffer is free again
     FSB_CUDA(cudaMemcpyAsync(s->snapshot, s->f[field], s->ncells * sizeof(float), cudaMemcpyDeviceToDevice, s->stream));
@@ -1148,6 +1210,7 @@ int fsb_read_field_async(fsb_sim *s, int field, float *host_dst)
     FSB_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_ready, 0));
     FSB_CUDA(cudaMemcpyAsync(host_dst, s->snapshot, s->ncells * sizeof(float), cudaMemcpyDeviceToHost, s->copy_stream));
     FSB_CUDA(cudaEventRecord(s->ev_copied, s->copy_stream));
+    s->last_copy = s->ev_copied;
     s->copy_pending = true;
     return FSB_OK;
 }
@@ -1158,8 +1221,9 @@ int fsb_read_wait(fsb_sim *s)
     if (!s) return fail(FSB_EINVAL, "fsb_read_wait: null handle");
     if (!s->copy_pending) return FSB_OK;
     DeviceGuard guard(s->device);
-    FSB_CUDA(cudaEventSynchronize(s->ev_copied));
+    FSB_CUDA(cudaEventSynchronize(s->last_copy));     // the copy stream is in order: every earlier read has arrived too
     s->copy_pending = false;
+    s->snap_busy[0] = s->snap_busy[1] = false;
     return FSB_OK;
 }
 

@@ -115,6 +115,7 @@ struct ChainBlock {
     int ncols;                                 // columns every rank owns
     unsigned long long step;                   // number of this step, identical on all ranks
 };
+constexpr int kChainSources = 256;
 struct ChainArgs {
     int W, H;
     float *u, *v, *p, *div;
@@ -134,6 +135,11 @@ struct ChainArgs {
     const uint32_t *noise_base = nullptr;      // window of the rand() stream at the step's first output (31 words)
     int noise_zero = 0;                        // FSB_NOISE_ZERO
     int overlap = 0;                           // the next step's launch may start before this one has drained
+    // pending addDensity / addVelocity calls, sorted by (field, cell) in call order: applied by the noise phase instead
+    // of a separate copy + kernel between two launches (which would keep them from overlapping); at most kChainSources
+    const struct SourceEntry *sources = nullptr;
+    int nsources = 0;
+    float *snap = nullptr;                     // a second copy of the advected density (for an asynchronous read)
     const ChainBlock *blk = nullptr;   // column block of a multi-rank run (nullptr: the whole grid on this GPU)
 };
 // mode 0: launch; 1: only tell whether a configuration exists; 2: also allocate the scratch (so that its IPC handles can

@@ -201,23 +201,34 @@ def test_step_with_diffusion_and_zero_noise():
 
 def test_async_read_is_a_snapshot():
     """fsb_read_field_async returns the field as of the call, even though the following steps (and source injections)
-    are queued while the copy is still in flight."""
+    are queued while the copy is still in flight.  After the first read the steps' launches leave a second copy of the
+    density for the transfer and apply the pending sources themselves (so consecutive steps still overlap); a step with
+    more sources than a launch carries, and a source added between a step and its read, take the other paths."""
     w, h = 512, 384
     gpu, ora = make_pair(w, h, 20, 5)
     demo_injection(gpu, w, h); demo_injection(ora, w, h)
     bufs = [gpu.pinned_array(), gpu.pinned_array()]
     snaps = []
-    for k in range(4):
-        gpu.addDensity(w // 3 + k, h // 2, 2.5); ora.addDensity(w // 3 + k, h // 2, 2.5)
-        gpu.addVelocity(w // 3, h // 2 + k, 0.3, -0.2); ora.addVelocity(w // 3, h // 2 + k, 0.3, -0.2)
-        gpu.step(0.01); ora.step(0.01)
+    n = 8
+    for k in range(n):
+        for s in (gpu, ora):
+            s.addDensity(w // 3 + k, h // 2, 2.5)
+            s.addVelocity(w // 3, h // 2 + k, 0.3, -0.2)
+            s.addVelocity(w // 3, h // 2 + k, -0.1, 0.05)       # twice the same cell: applied in call order
+            s.addDensity(0, 5 + k, 1.0)                          # a wall cell
+            if k == 4:
+                for q in range(300):
+                    s.addDensity(10 + q % 50, 20 + q // 50, 0.01 * (q + 1))
+            s.step(0.01)
+            if k == 5:
+                s.addDensity(w // 2, h // 2, 4.0)                # after the step, before its read
         gpu.read_wait()                                  # the previous snapshot has arrived ...
         if k:
             assert_bits(bufs[(k - 1) % 2].reshape(w, h), snaps[-1], f"density snapshot of step {k - 1}")
         gpu.read_async(fsb.DENSITY, bufs[k % 2])         # ... queue this one and go on
         snaps.append(ora.read(0).copy())
     gpu.read_wait()
-    assert_bits(bufs[3 % 2].reshape(w, h), snaps[-1], "density snapshot of the last step")
+    assert_bits(bufs[(n - 1) % 2].reshape(w, h), snaps[-1], "density snapshot of the last step")
     for a, b, n in zip(gpu.fields(), ora.fields(), "duv"):
         assert_bits(a, b, f"field {n}")
     # velocity snapshots take the conservative path (the next step waits for the copy)
