@@ -61,6 +61,14 @@ struct SweepPlan { int levels, stages; };   // one launch of the sweep pipeline:
 std::mutex g_proc_noise_mu;
 uint64_t g_proc_noise_pos = 0;
 
+// Live simulations of this process (whole-grid ones).  Overlapping steps give up the co-residency guarantee of a
+// cooperative launch: a launch is resident as a whole because its predecessor in the stream was.  Two simulations that
+// step concurrently on one device could each hold part of the SMs and wait for the rest, so the overlap is used only
+// by a simulation that is the only one of its device that has it enabled.
+// (never destroyed: a namespace-scope FluidSim, src/main.cpp:7, is torn down after this file's own statics)
+std::mutex &g_sims_mu = *new std::mutex;
+std::vector<struct fsb_sim *> &g_sims = *new std::vector<struct fsb_sim *>;
+
 }  // namespace
 
 struct fsb_sim {
@@ -613,10 +621,13 @@ int chained_launch(fsb_sim *s, bool with_diffuse, bool whole_step, float dt, boo
 // previous BEFORE the step become the spares the next step writes: nothing a step writes is read by the step before it
 // anywhere but in the block being written.
 // *done = false: this grid / these parameters have no such configuration; nothing has been changed.
+bool only_overlapping_sim_of_its_device(const fsb_sim *s);
+
 int chained_step(fsb_sim *s, float dt, bool *done)
 {
     *done = false;
     if (s->chain_level < 2 || !s->chain_overlap || s->is_block || s->tune_strips || s->tune_levels || s->tune_stages) return FSB_OK;
+    if (!only_overlapping_sim_of_its_device(s)) return FSB_OK;
     if (s->chain_level < 3 && s->W > 2 * s->H && s->H < 4096) return FSB_OK;      // see chained_launch
     if (s->prm.advect_scheme != FSB_ADVECT_RK4) return FSB_OK;
     if (s->prm.noise_mode != FSB_NOISE_GLIBC && s->prm.noise_mode != FSB_NOISE_ZERO) return FSB_OK;
@@ -704,6 +715,14 @@ int chained_step(fsb_sim *s, float dt, bool *done)
     }
     *done = true;
     return FSB_OK;
+}
+
+bool only_overlapping_sim_of_its_device(const fsb_sim *s)
+{
+    std::lock_guard<std::mutex> lock(g_sims_mu);
+    for (const fsb_sim *o : g_sims)
+        if (o != s && o->device == s->device && o->chain_overlap && o->chain_level >= 2) return false;
+    return true;
 }
 
 int chained_project(fsb_sim *s, bool with_diffuse, float dt, bool *done)
@@ -921,6 +940,10 @@ static int create_common(const fsb_params *p, const GridView *block, fsb_sim **o
     set_noise_window(s, prm.noise_seed, prm.noise_pos);
     FSB_CREATE_CUDA(cudaStreamSynchronize(s->stream));
 #undef FSB_CREATE_CUDA
+    if (!s->is_block) {
+        std::lock_guard<std::mutex> lock(g_sims_mu);
+        g_sims.push_back(s);
+    }
     *out = s;
     return FSB_OK;
 }
@@ -928,6 +951,10 @@ static int create_common(const fsb_params *p, const GridView *block, fsb_sim **o
 int fsb_destroy(fsb_sim *s)
 {
     if (!s) return FSB_OK;
+    {
+        std::lock_guard<std::mutex> lock(g_sims_mu);
+        g_sims.erase(std::remove(g_sims.begin(), g_sims.end(), s), g_sims.end());
+    }
     {
         DeviceGuard guard(s->device);
         // tolerate a runtime that is already shutting down (a namespace-scope FluidSim, src/main.cpp:7,

@@ -177,7 +177,7 @@ class BlockFluidSim:
         self._connect()
         self.chained = False
         # chain="auto": the chained launch where it was measured faster than pass-by-pass launches (blocks of at least
-        # 4096 columns: 32768 x 4096 per rank at 8 ranks 72.1 against 78.9 ms per step; with 2048 columns per rank,
+        # 4096 columns: 32768 x 4096 per rank at 8 ranks 71.7 against 78.9 ms per step; with 2048 columns per rank,
         # config 4 at 8 ranks, a rank has too few blocks for it: 20.1 against 19.1 ms)
         if chain is True or (chain == "auto" and self.ncols >= 4096):
             self._connect_chain()

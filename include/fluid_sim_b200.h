@@ -296,8 +296,10 @@ int fsb_set_chain_level(fsb_sim *s, int level);
  * the SMs the first thread blocks of step n have left while the last ones are still at work (the launches order
  * themselves block by block through words in device memory).  on = 0: the noise is its own launch and every step's launch
  * starts after the one before has drained (round-2 structure before this).  Results are bit-identical either way; the
- * fields rotate through seven more buffers of the grid's size.  Default 1; the environment variable FSB_CHAIN_OVERLAP
- * sets the initial value. */
+ * fields rotate through seven more buffers of the grid's size.  Used only while the simulation is the only one of its
+ * device (in this process) that has it enabled: overlapping launches are not cooperative launches, and two simulations
+ * stepping concurrently could each hold part of the SMs while waiting for the rest.  Default 1; the environment variable
+ * FSB_CHAIN_OVERLAP sets the initial value. */
 int fsb_set_chain_overlap(fsb_sim *s, int on);
 
 const char *fsb_last_error(void);
