@@ -1,4 +1,4 @@
-// Several passes of FluidSim::step chained inside ONE cooperative launch (sm_100a).
+// Several passes of FluidSim::step -- on one GPU all of them -- chained inside ONE launch (sm_100a).
 //
 // Why: an exact-order sweep pass (wavefront.cuh) is a wave that crosses the grid's columns from left to right; the
 // CTA that owns the last columns starts when the wave arrives and finishes one full column walk later, so a
@@ -18,6 +18,10 @@
 //   * the pointwise phases in between (divergence, gradient + boundaries) evaluate wall values on the fly from the
 //     adjacent interior cell, as setBoundary() (src/fluid_sim.cpp:347-361) defines them, so no separate boundary
 //     pass sits between two phases.  The final walls and corners of u and v are written by the gradient phase.
+//   * on one GPU the whole step is such a launch, the noise included (chain_noise), and the launches of consecutive
+//     steps overlap: launch n + 1 is given the SMs launch n's CTAs leave one by one (programmatic stream serialization)
+//     and orders itself against launch n block by block through the same done-words (ChainPhase::xdep); the fields
+//     rotate through enough buffers that what a launch overwrites was last read two launches ago (launch_chain).
 //
 // Every wait loop carries a watchdog (global timer): a protocol error traps instead of hanging the GPU.
 // All arithmetic uses round-to-nearest intrinsics in the reference's association order (no FMA).
