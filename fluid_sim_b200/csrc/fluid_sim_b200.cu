@@ -658,7 +658,19 @@ int chained_step(fsb_sim *s, float dt, bool *done)
     if (e != cudaSuccess) return fail_cuda(e, "chained step");
     for (float *&b : s->spare)
         if (!b) {
-            FSB_CUDA(cudaMalloc(&b, s->ncells * sizeof(float)));
+            if (cudaMalloc(&b, s->ncells * sizeof(float)) != cudaSuccess) {
+                // not enough device memory for the rotation: this simulation keeps the noise as its own launch and its
+                // steps one after the other (seven fields fewer)
+                (void)cudaGetLastError();
+                b = nullptr;
+                FSB_CUDA(cudaStreamSynchronize(s->stream));
+                for (float *&q : s->spare) {
+                    if (q) cudaFree(q);
+                    q = nullptr;
+                }
+                s->chain_overlap = 0;
+                return FSB_OK;
+            }
             FSB_CUDA(cudaMemsetAsync(b, 0, s->ncells * sizeof(float), s->stream));
         }
     // pending sources: a few (the reference's mouse handler, src/main.cpp:216-252) travel as parameters of the launch
@@ -672,7 +684,14 @@ int chained_step(fsb_sim *s, float dt, bool *done)
     int snap_k = -1;
     if (s->want_snap) {
         snap_k = s->snap_next;
-        if (!s->snap[snap_k]) FSB_CUDA(cudaMalloc(&s->snap[snap_k], s->ncells * sizeof(float)));
+        if (!s->snap[snap_k] && cudaMalloc(&s->snap[snap_k], s->ncells * sizeof(float)) != cudaSuccess) {
+            (void)cudaGetLastError();          // no memory for the second copy: reads go through the device-side snapshot
+            s->snap[snap_k] = nullptr;
+            s->want_snap = false;
+            snap_k = -1;
+        }
+    }
+    if (snap_k >= 0) {
         if (!s->ev_snap_copied[snap_k]) FSB_CUDA(cudaEventCreateWithFlags(&s->ev_snap_copied[snap_k], cudaEventDisableTiming));
         // the transfer out of this buffer was queued two steps ago
         if (s->snap_busy[snap_k]) FSB_CUDA(cudaStreamWaitEvent(s->stream, s->ev_snap_copied[snap_k], 0));
