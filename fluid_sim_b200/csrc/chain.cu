@@ -1430,7 +1430,9 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     unsigned char *b = cs->buf;
     unsigned *done = reinterpret_cast<unsigned *>(b);
     unsigned long long *err = reinterpret_cast<unsigned long long *>(b + kDoneBytes);
-    const unsigned epoch = ++cs->epoch;
+    // (committed to cs->epoch only when the launch has been queued: the launch after next waits for THIS number to
+    // appear in `completed`, so a number that never ran must not exist)
+    const unsigned epoch = cs->epoch + 1;
     const int par = ovl ? (int)(epoch & 1u) : 0;          // overlapping launches alternate between two sets of these
     float *vmax = reinterpret_cast<float *>(b + kVmaxOff + par * kVmaxOne);
     const int trace_idx = kind + 2 * par;
@@ -1750,7 +1752,10 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         at[0].val.programmaticStreamSerializationAllowed = 1;
         lc.numAttrs = 1;
     }
-    return cudaLaunchKernelExC(&lc, kern, args);
+    e = cudaLaunchKernelExC(&lc, kern, args);
+    if (e == cudaSuccess) cs->epoch = epoch;
+    else cs->last.valid = false;
+    return e;
 }
 
 // Start / end times of every work item of the most recent chained launch of one kind (which = 0: launches that begin
