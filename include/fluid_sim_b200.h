@@ -118,8 +118,10 @@ int fsb_get_height(const fsb_sim *s);
 int fsb_read_field(fsb_sim *s, int field, float *host_dst);
 /* The same copy without stalling the frame loop (the reference's loop reads every cell after every step,
  * src/main.cpp:388-396): fsb_read_field_async queues the device-to-host copy of the field as it is after all work
- * queued so far on a second stream and returns; later fsb_step calls overlap with it (the library orders whatever
- * overwrites that buffer after the copy: for the density that is only the density half of the next step).
+ * queued so far on a second stream and returns; later fsb_step calls overlap with it.  The copy reads a device-side
+ * snapshot, never the live field: taken on the simulation's stream at the first such read; once a caller reads the
+ * density after its steps, written by the steps' own launches (two more buffers of the grid's size), so that nothing
+ * but an event sits between two consecutive steps and they keep overlapping (fsb_set_chain_overlap).
  * fsb_read_wait blocks until the data is in host_dst.  One outstanding read per simulation; host_dst should be
  * page-locked (fsb_host_alloc) or the copy will not overlap.  Not available on column blocks. */
 int fsb_read_field_async(fsb_sim *s, int field, float *host_dst);
