@@ -1170,16 +1170,19 @@ namespace {
 
 // Can (D diffusion sweeps of u and v +) P pressure sweeps run as phases of one launch on this grid (or on a column
 // block of `ncols` columns of it: every rank must arrive at the same strips per CTA, so only W, H, ncols enter)?
-ChainPlan make_plan(int W, int H, int D, int P, int ncols, bool multi)
+// dry_nsm > 0: no device is asked anything; the plan is made for a GPU of that many SMs (chain_describe)
+ChainPlan make_plan(int W, int H, int D, int P, int ncols, bool multi, int dry_nsm = 0)
 {
     ChainPlan pl;
     pl.W = W; pl.H = H; pl.D = D; pl.P = P; pl.ncols = ncols; pl.multi = multi;
     if (P < kChainSP || P % kChainSP != 0) return pl;
     if (D != 0 && D % kChainSD != 0) return pl;
     if (multi && D == 0) return pl;
-    int dev = 0, nsm = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return pl;
-    if (cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return pl;
+    int dev = 0, nsm = dry_nsm;
+    if (dry_nsm <= 0) {
+        if (cudaGetDevice(&dev) != cudaSuccess) return pl;
+        if (cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return pl;
+    }
     size_t smem_gs = 0, smem_sor = 0;
     // strips a rank may have to run: its own columns, plus (last rank) the strips the result shift adds
     auto strips_of = [&](int shift) { return multi ? ncols / 32 + (shift + 31) / 32 + 1 : (H + shift + 31) / 32; };
@@ -1240,17 +1243,19 @@ ChainPlan make_plan(int W, int H, int D, int P, int ncols, bool multi)
     const int nblk = (ncols + pl.cw - 1) / pl.cw;
     pl.grid = std::max(std::max(pl.gs_ncta, 2 * pl.sor_ncta), std::min(nblk, nsm));
     if (pl.grid > nsm || (H + pl.cw - 1) / pl.cw > kChainMaxItems || pl.grid > kChainMaxItems) return pl;
-    const void *kern = chain_kernel_ptr(D > 0, multi, pl.cw);
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem) != cudaSuccess) {
-        (void)cudaGetLastError();
-        return pl;
+    if (dry_nsm <= 0) {
+        const void *kern = chain_kernel_ptr(D > 0, multi, pl.cw);
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem) != cudaSuccess) {
+            (void)cudaGetLastError();
+            return pl;
+        }
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kChainThreads, pl.smem) != cudaSuccess) {
+            (void)cudaGetLastError();
+            return pl;
+        }
+        if ((long long)per_sm * nsm < pl.grid) return pl;
     }
-    int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kChainThreads, pl.smem) != cudaSuccess) {
-        (void)cudaGetLastError();
-        return pl;
-    }
-    if ((long long)per_sm * nsm < pl.grid) return pl;
     pl.gs_ring_floats = (size_t)pl.gs_stages[0] * pl.gs_ncta * WfLayout<kChainSP>::kBoundaryFloats;   // of the widest pass
     pl.sor_ring_floats = D > 0 ? (size_t)2 * (D / kChainSD) * pl.sor_ncta * WfLayout<kChainSD>::kBoundaryFloats : 0;
     pl.ok = true;
@@ -1354,9 +1359,11 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     const int kind = A.sor_sweeps > 0 ? 0 : 1;
     const int ncols = multi ? B->ncols : A.H;
     ChainPlan &pl = cs->plan[kind];
-    if (pl.W != A.W || pl.H != A.H || pl.D != A.sor_sweeps || pl.P != A.gs_sweeps || pl.ncols != ncols || pl.multi != multi)
+    const bool dry = mode == 3;                // describe only: no device call, no allocation, no launch
+    if (dry && (!A.describe || A.describe_nsm <= 0 || multi)) return cudaErrorInvalidValue;
+    if (dry || pl.W != A.W || pl.H != A.H || pl.D != A.sor_sweeps || pl.P != A.gs_sweeps || pl.ncols != ncols || pl.multi != multi)
     {
-        pl = make_plan(A.W, A.H, A.sor_sweeps, A.gs_sweeps, ncols, multi);
+        pl = make_plan(A.W, A.H, A.sor_sweeps, A.gs_sweeps, ncols, multi, dry ? A.describe_nsm : 0);
         cs->last.valid = false;
     }
     if (!pl.ok) return cudaErrorNotSupported;
@@ -1372,7 +1379,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
 
     const GridView G = multi ? B->G : whole_grid(A.W, A.H);
     cudaError_t e;
-    if (A.with_advect) {
+    if (A.with_advect && !dry) {
         const size_t nfl = (size_t)A.W * G.pitch;
         if (nfl > cs->extra_floats) {
             if (multi && cs->extra[0]) return cudaErrorInvalidValue;   // the neighbours have these buffers mapped
@@ -1398,7 +1405,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     const size_t sor_rings = std::max(cs->plan[0].sor_ring_floats, pl.sor_ring_floats) * sizeof(float);
     const size_t gs_rings = std::max(std::max(cs->plan[0].gs_ring_floats, cs->plan[1].gs_ring_floats), pl.gs_ring_floats) * sizeof(float);
     const size_t need = kFixedBytes + kChainMaxSweeps * flag_bytes + sor_rings + 2 * kChainMaxGsPasses * gs_rings;
-    if (need > cs->bytes) {
+    if (need > cs->bytes && !dry) {
         if (multi && cs->buf) return cudaErrorInvalidValue;            // mapped by the neighbours: must not move
         e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) return e;
@@ -1412,7 +1419,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         cs->bytes = need;
     }
     if (mode == 2) return cudaStreamSynchronize(st);
-    if (with_noise && !A.noise_zero && (cs->nz_H != A.H || cs->nz_cw != pl.cw || !cs->nz_polys)) {
+    if (!dry && with_noise && !A.noise_zero && (cs->nz_H != A.H || cs->nz_cw != pl.cw || !cs->nz_polys)) {
         // jump polynomials of the noise phase (chain_noise): x^k mod (x^31 - x^28 - 1), 32 words each
         std::vector<uint32_t> host((size_t)kNzPolys * 32, 0u);
         nz_fill_polys(A.H, pl.cw, host.data());
@@ -1427,7 +1434,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         cs->nz_H = A.H;
         cs->nz_cw = pl.cw;
     }
-    unsigned char *b = cs->buf;
+    unsigned char *b = dry ? reinterpret_cast<unsigned char *>(0x100000000ull) : cs->buf;   // (dry: addresses are never used)
     unsigned *done = reinterpret_cast<unsigned *>(b);
     unsigned long long *err = reinterpret_cast<unsigned long long *>(b + kDoneBytes);
     // (committed to cs->epoch only when the launch has been queued: the launch after next waits for THIS number to
@@ -1710,6 +1717,30 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
         }
     }
     C.nphases = np;
+    if (dry) {
+        ChainDesc &D = *A.describe;
+        D = ChainDesc{};
+        D.nphases = np;
+        D.grid = pl.grid;
+        D.cw = pl.cw;
+        for (int q = 0; q < np; ++q) {
+            const ChainPhase &ph = C.ph[q];
+            ChainPhaseDesc &d = D.ph[q];
+            d.kind = ph.kind; d.nitems = ph.nitems; d.ncl = ph.ncl; d.nf = ph.nf; d.cpv = ph.cpv; d.shift = ph.shift;
+            d.ndeps = ph.ndeps; d.nxdeps = ph.nxdeps;
+            for (int k = 0; k < ph.ndeps; ++k) { d.dep[k][0] = ph.dep[k].phase; d.dep[k][1] = ph.dep[k].from_out; d.dep[k][2] = ph.dep[k].lo; d.dep[k][3] = ph.dep[k].hi; }
+            for (int k = 0; k < ph.nxdeps; ++k) { d.xdep[k][0] = ph.xdep[k].phase; d.xdep[k][1] = ph.xdep[k].from_out; d.xdep[k][2] = ph.xdep[k].lo; d.xdep[k][3] = ph.xdep[k].hi; }
+            const void *ptrs[8] = {ph.u, ph.v, ph.q, ph.dst_a, ph.dst_b, ph.src_a, ph.src_b, ph.bnd_extra};
+            for (int k = 0; k < 8; ++k) d.ptr[k] = ptrs[k];
+            d.reach_phase = ph.reach_phase;
+            if (ph.kind == kPhSor || ph.kind == kPhGs || ph.kind == kPhGsX0)
+                for (int f = 0; f < 2; ++f) {
+                    const SweepField &F = C.wf[ph.wf].fld[f];
+                    d.wf[f][0] = F.x0; d.wf[f][1] = F.rhs; d.wf[f][2] = F.out;
+                }
+        }
+        return cudaSuccess;
+    }
     C.xstep = C.xstep && cs->last.nphases == np;
     cs->last_nphases[kind] = np;
     cs->last_trace[kind] = trace_idx;
@@ -1755,6 +1786,24 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     e = cudaLaunchKernelExC(&lc, kern, args);
     if (e == cudaSuccess) cs->epoch = epoch;
     else cs->last.valid = false;
+    return e;
+}
+
+// The phase table launch_chain would build for these arguments on a GPU of `nsm` SMs, without touching a device: the
+// items, their dependencies inside the launch and on the previous launch, and the arrays they read and write (the field
+// pointers of `A` may be any distinct addresses).  For the CPU check of the overlap protocol (tests/test_chain_deps.py).
+cudaError_t chain_describe(const ChainArgs &A0, int nsm, float *extra0, float *extra1, ChainDesc *out)
+{
+    ChainArgs A = A0;
+    A.describe = out;
+    A.describe_nsm = nsm;
+    ChainState *cs = new ChainState();
+    cs->extra[0] = extra0;      // stand-ins for the second projection's scratch
+    cs->extra[1] = extra1;
+    SweepScratch scr{};
+    const cudaError_t e = launch_chain(A, cs, scr, nullptr, 3);
+    cs->extra[0] = cs->extra[1] = nullptr;
+    chain_state_destroy(cs);
     return e;
 }
 

@@ -1412,6 +1412,58 @@ int fsb_set_chain_level(fsb_sim *s, int level)
     return FSB_OK;
 }
 
+int fsb_dbg_chain_describe(int width, int height, int diff_iters, int proj_iters, int nsm, long long *out, int max_words,
+                           int *nphases, int *grid, int *cw)
+{
+    if (!out || !nphases || !grid || !cw || width < 3 || height < 3 || nsm < 1) return fail(FSB_EINVAL, "fsb_dbg_chain_describe: bad argument");
+    // the arguments chained_step passes, with small integers standing in for the arrays
+    auto arr = [](int id) { return reinterpret_cast<float *>((size_t)id * 0x1000); };
+    ChainArgs A{};
+    A.W = width;
+    A.H = height;
+    A.gs_sweeps = proj_iters;
+    A.sor_sweeps = diff_iters;
+    A.a = 1.0f;
+    A.c_recip = 0.2f;
+    A.omega = 1.5f;
+    A.dt = 0.01f;
+    A.with_advect = 1;
+    A.with_density = 1;
+    A.density_pz = 1;
+    A.overlap = 1;
+    A.noise_zero = 1;
+    A.vin_u = arr(1); A.vin_v = arr(2);
+    A.u = arr(3); A.v = arr(4);
+    A.yu = arr(5); A.yv = arr(6);
+    A.p = arr(7); A.div = arr(8);
+    A.d = arr(9); A.nd = arr(10);
+    ChainDesc D;
+    const cudaError_t e = chain_describe(A, nsm, arr(11), arr(12), &D);
+    if (e == cudaErrorNotSupported) return fail(FSB_ELIMIT, "fsb_dbg_chain_describe: no chained configuration for this grid");
+    if (e != cudaSuccess) return fail_cuda(e, "fsb_dbg_chain_describe");
+    constexpr int kWords = 51;
+    if (D.nphases * kWords > max_words) return fail(FSB_EINVAL, "fsb_dbg_chain_describe: output too small");
+    auto id = [](const void *q) { return (long long)((size_t)q / 0x1000); };
+    for (int q = 0; q < D.nphases; ++q) {
+        const ChainPhaseDesc &d = D.ph[q];
+        long long *o = out + (size_t)q * kWords;
+        const int head[8] = {d.kind, d.nitems, d.ncl, d.nf, d.cpv, d.shift, d.ndeps, d.nxdeps};
+        for (int k = 0; k < 8; ++k) o[k] = head[k];
+        for (int k = 0; k < 4; ++k)
+            for (int m = 0; m < 4; ++m) o[8 + 4 * k + m] = d.dep[k][m];
+        for (int k = 0; k < 3; ++k)
+            for (int m = 0; m < 4; ++m) o[24 + 4 * k + m] = d.xdep[k][m];
+        for (int k = 0; k < 8; ++k) o[36 + k] = id(d.ptr[k]);
+        for (int f = 0; f < 2; ++f)
+            for (int m = 0; m < 3; ++m) o[44 + 3 * f + m] = id(d.wf[f][m]);
+        o[50] = d.reach_phase;
+    }
+    *nphases = D.nphases;
+    *grid = D.grid;
+    *cw = D.cw;
+    return FSB_OK;
+}
+
 int fsb_set_chain_overlap(fsb_sim *s, int on)
 {
     if (!s || on < 0 || on > 1) return fail(FSB_EINVAL, "fsb_set_chain_overlap: bad argument");

@@ -116,6 +116,19 @@ struct ChainBlock {
     unsigned long long step;                   // number of this step, identical on all ranks
 };
 constexpr int kChainSources = 256;
+// The phase table of a chained launch as plain data (chain_describe): what tests/test_chain_deps.py checks the
+// dependency lists against.  dep / xdep rows: {phase, from_out, lo, hi} (see ChainDep in chain.cu).
+struct ChainPhaseDesc {
+    int kind, nitems, ncl, nf, cpv, shift, ndeps, nxdeps;
+    int dep[4][4], xdep[3][4];
+    const void *ptr[8];        // u, v, q, dst_a, dst_b, src_a, src_b, bnd_extra
+    const void *wf[2][3];      // sweep phases: {initial iterate, right-hand side, result} of fields 0 and 1
+    int reach_phase;           // advection: the gradient phase whose blocks it waits for
+};
+struct ChainDesc {
+    int nphases, grid, cw;
+    ChainPhaseDesc ph[24];
+};
 struct ChainArgs {
     int W, H;
     float *u, *v, *p, *div;
@@ -140,6 +153,8 @@ struct ChainArgs {
     const struct SourceEntry *sources = nullptr;
     int nsources = 0;
     float *snap = nullptr;                     // a second copy of the advected density (for an asynchronous read)
+    ChainDesc *describe = nullptr;             // mode 3: fill this in instead of launching (no device is touched) ...
+    int describe_nsm = 0;                      // ... planning for a GPU of this many SMs
     const ChainBlock *blk = nullptr;   // column block of a multi-rank run (nullptr: the whole grid on this GPU)
 };
 // mode 0: launch; 1: only tell whether a configuration exists; 2: also allocate the scratch (so that its IPC handles can
@@ -151,6 +166,8 @@ void chain_shared_buffers(ChainState *cs, void *out[3]);
 cudaError_t chain_read_error(ChainState *cs, unsigned long long *word);
 void chain_state_destroy(ChainState *cs);
 cudaError_t chain_read_trace(ChainState *cs, int which, unsigned long long *out, int max_phases, int max_items, int *nphases);
+// the phase table of a launch as data, no device involved (see ChainDesc)
+cudaError_t chain_describe(const ChainArgs &A, int nsm, float *extra0, float *extra1, ChainDesc *out);
 
 // Allocation-free pressure sweeps on caller-owned device buffers (wavefront.cu); see fsb_pressure_sweeps_noalloc.
 int pressure_sweeps_noalloc(const float *d_div, float *d_p, int W, int H, int sweeps, cudaStream_t st, std::string &msg);

@@ -1,0 +1,216 @@
+"""CPU check of the protocol that lets the launches of consecutive steps overlap (fluid_sim_b200/csrc/chain.cu,
+DESIGN.md section 4 "Overlapping steps").
+
+fsb_dbg_chain_describe returns the phase table the library builds for the one-launch step -- items, dependencies inside
+the launch, dependencies on the previous launch, the arrays every phase touches -- without a device.  This test turns two
+consecutive launches into a happens-before graph (those dependencies, the advection phases' wait for the gradient blocks
+in reach, program order of the items one CTA runs) and checks that EVERY pair of accesses to the same array that
+overlap in columns, at least one of them a write, is ordered: within a launch across phases, and between launch n and
+launch n+1 with the arrays rotated as chained_step rotates them.  (Launch n+2 starts only after launch n has finished
+altogether, which every CTA checks at its start; items of one sweep phase synchronise through their rings.)
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import fluid_sim_b200 as fsb
+
+SOR, GS, DIV, GRAD, ADV, GSX0, BNDP, NOISE = 1, 2, 3, 4, 5, 6, 7, 8
+WORDS = 51
+
+
+def describe(w, h, d, p, nsm=148):
+    lib = fsb.load_library()
+    out = (C.c_longlong * (24 * WORDS))()
+    n, grid, cw = C.c_int(), C.c_int(), C.c_int()
+    rc = lib.fsb_dbg_chain_describe(w, h, d, p, nsm, out, 24 * WORDS, C.byref(n), C.byref(grid), C.byref(cw))
+    if rc != 0:
+        return None
+    a = np.array(out[:n.value * WORDS], dtype=np.int64).reshape(n.value, WORDS)
+    phases = []
+    for r in a:
+        phases.append(dict(kind=int(r[0]), nitems=int(r[1]), ncl=int(r[2]), nf=int(r[3]), cpv=int(r[4]), shift=int(r[5]),
+                           deps=[tuple(int(v) for v in r[8 + 4 * k:12 + 4 * k]) for k in range(int(r[6]))],
+                           xdeps=[tuple(int(v) for v in r[24 + 4 * k:28 + 4 * k]) for k in range(int(r[7]))],
+                           ptr=[int(v) for v in r[36:44]], wf=[[int(v) for v in r[44:47]], [int(v) for v in r[47:50]]],
+                           reach=int(r[50])))
+    return phases, grid.value, cw.value
+
+
+# the arrays behind the roles of a launch, rotated as chained_step (fluid_sim_b200.cu) rotates them
+def physical(launch):
+    vel = [("Q0", "Q2", "Q3"), ("Q3", "Q0", "Q1"), ("Q1", "Q3", "Q2")][launch % 3 if launch < 3 else 0]
+    den = [("Da", "Db"), ("Db", "Dc"), ("Dc", "Da")][launch % 3]
+    m = {1: vel[0] + ".u", 2: vel[0] + ".v", 3: vel[1] + ".u", 4: vel[1] + ".v", 5: vel[2] + ".u", 6: vel[2] + ".v",
+         7: "P1.p", 8: "P1.div", 9: den[0], 10: den[1], 11: "P2.p", 12: "P2.div"}
+    return m
+
+
+def dep_items(ph, cl, dep, phases):
+    """items of phase dep[0] an item with column range index `cl` of phase `ph` waits for (chain_wait in chain.cu)"""
+    q = phases[dep[0]]
+    b0 = cl * ph["cpv"] - (ph["shift"] if dep[1] else 0)
+    b1 = b0 + ph["cpv"] - 1
+    a = (b0 - dep[2] + q["shift"]) // q["cpv"]
+    b = (b1 + dep[3] + q["shift"]) // q["cpv"]
+    a, b = max(a, 0), min(b, q["ncl"] - 1)
+    return [x for x in range(a * q["nf"], (b + 1) * q["nf"])]
+
+
+def accesses(ph, item, H, reach_cols, density_sources):
+    """[(role, lo, hi, is_write)] of one item; rows are not modelled (every item covers all rows of its columns)"""
+    cl, fi = item // ph["nf"], item % ph["nf"]
+    k = ph["kind"]
+    b0, b1 = cl * ph["cpv"], min(cl * ph["cpv"] + ph["cpv"] - 1, H - 1)
+    acc = []
+
+    def walls(lo, hi):      # columns whose wall cells the block writes: its own, and a wall column whose interior neighbour it owns
+        cols = [(lo, hi)]
+        if lo <= 1 <= hi:
+            cols.append((0, 0))
+        if lo <= H - 2 <= hi:
+            cols.append((H - 1, H - 1))
+        return cols
+
+    u, v, q, dst_a, dst_b, src_a, src_b, bnd_extra = ph["ptr"]
+    if k == NOISE:
+        acc += [(src_a, b0, b1, False), (src_b, b0, b1, False), (u, b0, b1, True), (v, b0, b1, True)]
+        if density_sources:
+            acc += [(9, b0, b1, True)]
+    elif k in (SOR, GS, GSX0):
+        x0, rhs, out = ph["wf"][fi]
+        if b0 <= H - 1:
+            for r in (x0, rhs):
+                if r:
+                    acc.append((r, b0, b1, False))
+        lo, hi = max(b0 - ph["shift"], 1), min(b0 - ph["shift"] + ph["cpv"] - 1, H - 2)
+        if lo <= hi:
+            acc.append((out, lo, hi, True))
+        acc.append((("ring", id(ph)), cl, cl, True))                 # to the item on the right
+        if cl > 0:
+            acc.append((("ring", id(ph)), cl - 1, cl - 1, False))    # from the item on the left
+    elif k == DIV:
+        acc += [(u, max(b0 - 1, 0), min(b1 + 1, H - 1), False), (v, max(b0 - 1, 0), min(b1 + 1, H - 1), False), (q, b0, b1, True)]
+    elif k == BNDP:
+        acc += [(q, b0, b1, False)] + [(q, lo, hi, True) for lo, hi in walls(b0, b1)]
+    elif k == GRAD:
+        acc += [(q, max(b0 - 1, 0), min(b1 + 1, H - 1), False)]
+        for f in (u, v):
+            acc += [(f, b0, b1, False)] + [(f, lo, hi, True) for lo, hi in walls(b0, b1)]
+        if bnd_extra:
+            acc += [(bnd_extra, b0, b1, False)] + [(bnd_extra, lo, hi, True) for lo, hi in walls(b0, b1)]
+    elif k == ADV:
+        lo, hi = max(b0 - reach_cols, 0), min(b1 + reach_cols, H - 1)
+        for f in (u, v, src_a, src_b):
+            if f:
+                acc.append((f, lo, hi, False))
+        for f in (dst_a, dst_b):
+            if f:
+                acc += [(f, a, b, True) for a, b in walls(b0, b1)]
+    return acc
+
+
+def check(phases, grid, h, reach_cols, density_sources):
+    # nodes: (launch, phase, item) for two consecutive launches
+    index, nodes = {}, []
+    for L in (0, 1):
+        for pi, ph in enumerate(phases):
+            for it in range(ph["nitems"]):
+                index[(L, pi, it)] = len(nodes)
+                nodes.append((L, pi, it))
+    n = len(nodes)
+    pred = [set() for _ in range(n)]
+    for (L, pi, it), me in index.items():
+        ph = phases[pi]
+        cl = it // ph["nf"]
+        for dep in ph["deps"]:
+            for x in dep_items(ph, cl, dep, phases):
+                pred[me].add(index[(L, dep[0], x)])
+        if L == 1:
+            for dep in ph["xdeps"]:
+                for x in dep_items(ph, cl, dep, phases):
+                    pred[me].add(index[(0, dep[0], x)])
+        if ph["kind"] == ADV:
+            # chain_advect_wait: the gradient blocks [b - k, b + k] with k blocks covering the reach
+            gr = phases[ph["reach"]]
+            bg = cl * ph["cpv"] // gr["cpv"]
+            k = max(1, -(-reach_cols // gr["cpv"]))
+            for x in range(max(bg - k, 0), min(bg + k, gr["ncl"] - 1) + 1):
+                pred[me].add(index[(L, ph["reach"], x)])
+    # Sweep phases: item c stores into the last `shift` columns of item c-1's range (the result shift) -- values that
+    # reach it through the ring from item c-1, which produced them after its own dependencies were met.  So whatever
+    # item c-1 of the same field waited for also precedes item c's stores.
+    for L in (0, 1):
+        for pi, ph in enumerate(phases):
+            if ph["kind"] in (SOR, GS, GSX0):
+                for it in range(ph["nf"], ph["nitems"]):
+                    pred[index[(L, pi, it)]] |= pred[index[(L, pi, it - ph["nf"])]]
+    # program order of the items one CTA runs (item i of every phase on CTA i mod grid, phases in order)
+    for L in (0, 1):
+        last = {}
+        for pi, ph in enumerate(phases):
+            for it in range(ph["nitems"]):
+                cta = it % grid
+                if cta in last:
+                    pred[index[(L, pi, it)]].add(last[cta])
+                last[cta] = index[(L, pi, it)]
+    # reachability (nodes are in a topological order: launch, phase, item; same-phase items never depend on each other)
+    reach = np.zeros((n, n), dtype=bool)
+    for me in range(n):
+        for q in pred[me]:
+            assert q < me or nodes[q][:2] == nodes[me][:2], "dependency on a later item"
+            reach[me] |= reach[q]
+            reach[me, q] = True
+    # accesses by physical array
+    by_array = {}
+    for (L, pi, it), me in index.items():
+        roles = physical(L)
+        for role, lo, hi, wr in accesses(phases[pi], it, h, reach_cols, density_sources):
+            arr = (roles[role] if isinstance(role, int) else role)
+            by_array.setdefault(arr, []).append((me, lo, hi, wr))
+    bad = []
+    for arr, acc in by_array.items():
+        acc.sort()
+        for i, (a, alo, ahi, awr) in enumerate(acc):
+            for (b, blo, bhi, bwr) in acc[i + 1:]:
+                if not (awr or bwr) or ahi < blo or bhi < alo or a == b:
+                    continue
+                (La, pa, _), (Lb, pb, _) = nodes[a], nodes[b]
+                if La == Lb and pa == pb:
+                    continue            # items of one phase: independent columns, or a sweep phase's own pipeline
+                if not reach[b, a]:
+                    bad.append((arr, nodes[a], (alo, ahi, "W" if awr else "R"), nodes[b], (blo, bhi, "W" if bwr else "R")))
+    return bad
+
+
+@pytest.mark.parametrize("w,h,d,p", [(512, 2048, 5, 40), (256, 1024, 10, 100), (128, 640, 5, 20), (64, 7232, 5, 20)])
+@pytest.mark.parametrize("reach_cols", [3, 70, 100000])
+@pytest.mark.parametrize("density_sources", [False, True])
+def test_every_conflicting_access_is_ordered(w, h, d, p, reach_cols, density_sources):
+    got = describe(w, h, d, p)
+    assert got is not None, "no chained configuration"
+    phases, grid, cw = got
+    if density_sources:
+        # launch_chain adds this dependency of the noise phase only to launches that carry density sources: the
+        # previous launch's density advection of the block the sources are added to
+        advd = len(phases) - 1
+        assert phases[advd]["kind"] == ADV and phases[0]["kind"] == NOISE
+        phases[0]["xdeps"].append((advd, 0, 0, 0))
+    bad = check(phases, grid, h, reach_cols, density_sources)
+    assert not bad, f"{len(bad)} unordered pairs, first: {bad[:3]}"
+
+
+def test_the_check_sees_a_missing_dependency():
+    """Without the second gradient phase's wait for the previous launch's density advection the density walls it
+    rewrites (and the next density advection's source) would race with that advection: the check must say so."""
+    phases, grid, cw = describe(512, 2048, 5, 40)
+    g2 = [q for q in phases if q["kind"] == GRAD][-1]
+    assert g2["xdeps"]
+    g2["xdeps"] = []
+    assert check(phases, grid, 2048, 3, False)
+    # ... and without the noise phase's wait for the previous launch's second gradient phase the step would start from
+    # a velocity that is still being written
+    phases, grid, cw = describe(512, 2048, 5, 40)
+    phases[0]["xdeps"] = []
+    assert check(phases, grid, 2048, 3, False)
