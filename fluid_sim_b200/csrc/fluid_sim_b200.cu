@@ -1412,11 +1412,13 @@ int fsb_set_chain_level(fsb_sim *s, int level)
     return FSB_OK;
 }
 
-int fsb_dbg_chain_describe(int width, int height, int diff_iters, int proj_iters, int nsm, long long *out, int max_words,
-                           int *nphases, int *grid, int *cw)
+int fsb_dbg_chain_describe(int variant, int width, int height, int diff_iters, int proj_iters, int nsm, long long *out,
+                           int max_words, int *nphases, int *grid, int *cw)
 {
-    if (!out || !nphases || !grid || !cw || width < 3 || height < 3 || nsm < 1) return fail(FSB_EINVAL, "fsb_dbg_chain_describe: bad argument");
-    // the arguments chained_step passes, with small integers standing in for the arrays
+    if (!out || !nphases || !grid || !cw || width < 3 || height < 3 || nsm < 1 || variant < 0 || variant > 1)
+        return fail(FSB_EINVAL, "fsb_dbg_chain_describe: bad argument");
+    // the arguments chained_step (variant 0) / chained_launch for a whole step (variant 1) pass, with small integers
+    // standing in for the arrays
     auto arr = [](int id) { return reinterpret_cast<float *>((size_t)id * 0x1000); };
     ChainArgs A{};
     A.W = width;
@@ -1432,9 +1434,13 @@ int fsb_dbg_chain_describe(int width, int height, int diff_iters, int proj_iters
     A.density_pz = 1;
     A.overlap = 1;
     A.noise_zero = 1;
-    A.vin_u = arr(1); A.vin_v = arr(2);
+    if (variant == 0) {
+        A.vin_u = arr(1); A.vin_v = arr(2);
+        A.yu = arr(5); A.yv = arr(6);
+    } else {
+        A.overlap = 0;      // the noise is its own launch; the advected velocity goes where the first projection had its scratch
+    }
     A.u = arr(3); A.v = arr(4);
-    A.yu = arr(5); A.yv = arr(6);
     A.p = arr(7); A.div = arr(8);
     A.d = arr(9); A.nd = arr(10);
     ChainDesc D;

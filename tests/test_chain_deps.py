@@ -20,11 +20,11 @@ SOR, GS, DIV, GRAD, ADV, GSX0, BNDP, NOISE = 1, 2, 3, 4, 5, 6, 7, 8
 WORDS = 51
 
 
-def describe(w, h, d, p, nsm=148):
+def describe(w, h, d, p, nsm=148, variant=0):
     lib = fsb.load_library()
     out = (C.c_longlong * (24 * WORDS))()
     n, grid, cw = C.c_int(), C.c_int(), C.c_int()
-    rc = lib.fsb_dbg_chain_describe(w, h, d, p, nsm, out, 24 * WORDS, C.byref(n), C.byref(grid), C.byref(cw))
+    rc = lib.fsb_dbg_chain_describe(variant, w, h, d, p, nsm, out, 24 * WORDS, C.byref(n), C.byref(grid), C.byref(cw))
     if rc != 0:
         return None
     a = np.array(out[:n.value * WORDS], dtype=np.int64).reshape(n.value, WORDS)
@@ -111,10 +111,10 @@ def accesses(ph, item, H, reach_cols, density_sources):
     return acc
 
 
-def check(phases, grid, h, reach_cols, density_sources):
-    # nodes: (launch, phase, item) for two consecutive launches
+def check(phases, grid, h, reach_cols, density_sources, launches=(0, 1), rotate=True):
+    # nodes: (launch, phase, item) for two consecutive launches (or one)
     index, nodes = {}, []
-    for L in (0, 1):
+    for L in launches:
         for pi, ph in enumerate(phases):
             for it in range(ph["nitems"]):
                 index[(L, pi, it)] = len(nodes)
@@ -141,13 +141,13 @@ def check(phases, grid, h, reach_cols, density_sources):
     # Sweep phases: item c stores into the last `shift` columns of item c-1's range (the result shift) -- values that
     # reach it through the ring from item c-1, which produced them after its own dependencies were met.  So whatever
     # item c-1 of the same field waited for also precedes item c's stores.
-    for L in (0, 1):
+    for L in launches:
         for pi, ph in enumerate(phases):
             if ph["kind"] in (SOR, GS, GSX0):
                 for it in range(ph["nf"], ph["nitems"]):
                     pred[index[(L, pi, it)]] |= pred[index[(L, pi, it - ph["nf"])]]
     # program order of the items one CTA runs (item i of every phase on CTA i mod grid, phases in order)
-    for L in (0, 1):
+    for L in launches:
         last = {}
         for pi, ph in enumerate(phases):
             for it in range(ph["nitems"]):
@@ -165,7 +165,7 @@ def check(phases, grid, h, reach_cols, density_sources):
     # accesses by physical array
     by_array = {}
     for (L, pi, it), me in index.items():
-        roles = physical(L)
+        roles = physical(L) if rotate else {k: f"A{k}" for k in range(1, 13)}
         for role, lo, hi, wr in accesses(phases[pi], it, h, reach_cols, density_sources):
             arr = (roles[role] if isinstance(role, int) else role)
             by_array.setdefault(arr, []).append((me, lo, hi, wr))
@@ -214,3 +214,17 @@ def test_the_check_sees_a_missing_dependency():
     phases, grid, cw = describe(512, 2048, 5, 40)
     phases[0]["xdeps"] = []
     assert check(phases, grid, 2048, 3, False)
+
+
+@pytest.mark.parametrize("w,h,d,p", [(512, 2048, 5, 40), (256, 1024, 10, 100), (64, 7232, 5, 20)])
+@pytest.mark.parametrize("reach_cols", [3, 100000])
+def test_one_launch_after_the_noise(w, h, d, p, reach_cols):
+    """The whole step after the noise as one launch (chain level 2 without the overlap, and what column blocks of a
+    multi-GPU run do): the advected velocity is written where the first projection had its pressure and divergence, so
+    the advection phase also waits for the gradient blocks and sweep items that still read them."""
+    got = describe(w, h, d, p, variant=1)
+    assert got is not None
+    phases, grid, cw = got
+    assert phases[0]["kind"] == SOR
+    bad = check(phases, grid, h, reach_cols, False, launches=(0,), rotate=False)
+    assert not bad, f"{len(bad)} unordered pairs, first: {bad[:3]}"
