@@ -228,3 +228,17 @@ def test_one_launch_after_the_noise(w, h, d, p, reach_cols):
     assert phases[0]["kind"] == SOR
     bad = check(phases, grid, h, reach_cols, False, launches=(0,), rotate=False)
     assert not bad, f"{len(bad)} unordered pairs, first: {bad[:3]}"
+
+
+def test_plan_of_the_headline_workload():
+    """8192^2, 40 projection sweeps on 148 SMs: ten phases (noise, diffusion, 2 x (divergence, one sweep pass, gradient),
+    two advections), 64-column blocks, 130 CTAs; 100 sweeps take two passes per projection with a wall update of the
+    pressure between them."""
+    phases, grid, cw = describe(8192, 8192, 5, 40)
+    assert [q["kind"] for q in phases] == [NOISE, SOR, DIV, GS, GRAD, ADV, DIV, GS, GRAD, ADV]
+    assert (grid, cw) == (130, 64)
+    assert phases[1]["nitems"] == 130 and phases[3]["nitems"] == 129 and phases[0]["nitems"] == 128
+    phases, grid, cw = describe(32768, 4096, 5, 100)
+    kinds = [q["kind"] for q in phases]
+    assert kinds.count(GS) == 2 and kinds.count(GSX0) == 2 and kinds.count(BNDP) == 2 and cw == 32
+    assert describe(100, 100, 5, 33) is None          # sweep counts without a chained configuration
