@@ -124,7 +124,8 @@ ABI = [
     ("fsb_set_tuning", C.c_int, [_SIM, C.c_int, C.c_int, C.c_int]),
     ("fsb_set_chain_level", C.c_int, [_SIM, C.c_int]),
     ("fsb_set_chain_overlap", C.c_int, [_SIM, C.c_int]),
-    ("fsb_dbg_chain_describe", C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_longlong), C.c_int,
+    ("fsb_dbg_chain_describe", C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                         C.POINTER(C.c_longlong), C.c_int,
                                          C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     ("fsb_last_error", C.c_char_p, []),
     ("fsb_version", C.c_char_p, []),

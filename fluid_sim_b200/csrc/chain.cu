@@ -37,7 +37,8 @@ namespace {
 
 constexpr int kChainThreads = 320;      // 8 compute warps + 2 transfer warps: the widest sweep pass
 constexpr int kChainMaxPhases = 24;
-constexpr int kChainMaxItems = 1024;    // items per phase the done[] array is sized for
+constexpr int kChainMaxItems = 1088;    // items per phase (numbered along the whole grid) the done[] array is sized for:
+                                        // 1024 column blocks, and the few more items a sweep phase's result shift adds
 constexpr int kChainMaxDeps = 4;
 constexpr int kChainMaxXDeps = 3;     // dependencies on the previous launch (overlapped steps)
 constexpr int kChainMaxSweeps = 7;      // sweep phases per launch: diffusion + up to three passes per projection
@@ -1205,6 +1206,9 @@ ChainPlan make_plan(int W, int H, int D, int P, int ncols, bool multi, int dry_n
             const int NS = strips_of(kChainSP * widest);
             const int ncta = (NS + std::min(nstr, NS) - 1) / std::min(nstr, NS);
             if (ncta > nsm || ncta > kWfMaxCtas) continue;
+            // items are numbered along the whole grid (every rank's done[] array is indexed that way)
+            const int NS_all = (H + kChainSP * widest + 31) / 32;
+            if ((NS_all + std::min(nstr, NS) - 1) / std::min(nstr, NS) > kChainMaxItems) continue;
             pl.gs_nstr = std::min(nstr, NS);
             pl.gs_ncta = ncta;
             pl.gs_npass = npass;
@@ -1230,6 +1234,7 @@ ChainPlan make_plan(int W, int H, int D, int P, int ncols, bool multi, int dry_n
         pl.sor_nstr = nstr;
         pl.sor_ncta = (NS + nstr - 1) / nstr;
         if (2 * pl.sor_ncta > nsm || pl.sor_ncta > kWfMaxCtas) return pl;
+        if (2 * (((H + D + 31) / 32 + nstr - 1) / nstr) > kChainMaxItems) return pl;     // numbered along the whole grid
         smem_sor = wf_smem_bytes<kChainSD>(nstr, nstg);
     }
     // the advection phases stage their fields in the same shared memory: give them room on small grids too
@@ -1360,7 +1365,7 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
     const int ncols = multi ? B->ncols : A.H;
     ChainPlan &pl = cs->plan[kind];
     const bool dry = mode == 3;                // describe only: no device call, no allocation, no launch
-    if (dry && (!A.describe || A.describe_nsm <= 0 || multi)) return cudaErrorInvalidValue;
+    if (dry && (!A.describe || A.describe_nsm <= 0)) return cudaErrorInvalidValue;
     if (dry || pl.W != A.W || pl.H != A.H || pl.D != A.sor_sweeps || pl.P != A.gs_sweeps || pl.ncols != ncols || pl.multi != multi)
     {
         pl = make_plan(A.W, A.H, A.sor_sweeps, A.gs_sweeps, ncols, multi, dry ? A.describe_nsm : 0);
@@ -1733,6 +1738,8 @@ cudaError_t launch_chain(const ChainArgs &A, ChainState *&cs, SweepScratch &scr,
             const void *ptrs[8] = {ph.u, ph.v, ph.q, ph.dst_a, ph.dst_b, ph.src_a, ph.src_b, ph.bnd_extra};
             for (int k = 0; k < 8; ++k) d.ptr[k] = ptrs[k];
             d.reach_phase = ph.reach_phase;
+            d.item0 = ph.item0;
+            d.push_cols = ph.push_cols;
             if (ph.kind == kPhSor || ph.kind == kPhGs || ph.kind == kPhGsX0)
                 for (int f = 0; f < 2; ++f) {
                     const SweepField &F = C.wf[ph.wf].fld[f];

@@ -1412,11 +1412,13 @@ int fsb_set_chain_level(fsb_sim *s, int level)
     return FSB_OK;
 }
 
-int fsb_dbg_chain_describe(int variant, int width, int height, int diff_iters, int proj_iters, int nsm, long long *out,
-                           int max_words, int *nphases, int *grid, int *cw)
+int fsb_dbg_chain_describe(int variant, int width, int height, int diff_iters, int proj_iters, int nsm, int col_begin,
+                           int col_end, int halo, long long *out, int max_words, int *nphases, int *grid, int *cw)
 {
-    if (!out || !nphases || !grid || !cw || width < 3 || height < 3 || nsm < 1 || variant < 0 || variant > 1)
+    if (!out || !nphases || !grid || !cw || width < 3 || height < 3 || nsm < 1 || variant < 0 || variant > 2)
         return fail(FSB_EINVAL, "fsb_dbg_chain_describe: bad argument");
+    if (variant == 2 && (col_begin < 0 || col_end > height || col_begin >= col_end || halo < 0 || (halo & 31) || (col_begin & 31)))
+        return fail(FSB_EINVAL, "fsb_dbg_chain_describe: bad column block");
     // the arguments chained_step (variant 0) / chained_launch for a whole step (variant 1) pass, with small integers
     // standing in for the arrays
     auto arr = [](int id) { return reinterpret_cast<float *>((size_t)id * 0x1000); };
@@ -1440,6 +1442,29 @@ int fsb_dbg_chain_describe(int variant, int width, int height, int diff_iters, i
     } else {
         A.overlap = 0;      // the noise is its own launch; the advected velocity goes where the first projection had its scratch
     }
+    ChainBlock B{};
+    if (variant == 2) {
+        // a column block of a multi-rank run, as fsb_create_block / blk_chain_block set it up (the neighbours' arrays:
+        // the same stand-ins, 16 / 32 higher)
+        B.G.W = width; B.G.H = height;
+        B.G.pitch = ((col_end - col_begin) + 2 * halo + 3) & ~3;
+        B.G.jbase = col_begin - halo; B.G.j0 = col_begin; B.G.j1 = col_end;
+        B.halo = halo;
+        B.strip_begin = col_begin / 32;
+        B.strip_end = col_end >= height ? -1 : col_end / 32;
+        B.has_left = col_begin > 0;
+        B.has_right = col_end < height;
+        B.ncols = col_end - col_begin;
+        B.step = 1;
+        auto peer = [&](ChainPeer &P, int base) {
+            P.u = arr(base + 3); P.v = arr(base + 4); P.p = arr(base + 7); P.div = arr(base + 8); P.d = arr(base + 9); P.nd = arr(base + 10);
+            P.extra[0] = arr(base + 11); P.extra[1] = arr(base + 12);
+            P.chain_buf = reinterpret_cast<unsigned char *>(0x200000000ull + (size_t)base * 0x10000000ull);
+        };
+        if (B.has_left) peer(B.left, 16);
+        if (B.has_right) peer(B.right, 32);
+        A.blk = &B;
+    }
     A.u = arr(3); A.v = arr(4);
     A.p = arr(7); A.div = arr(8);
     A.d = arr(9); A.nd = arr(10);
@@ -1447,7 +1472,7 @@ int fsb_dbg_chain_describe(int variant, int width, int height, int diff_iters, i
     const cudaError_t e = chain_describe(A, nsm, arr(11), arr(12), &D);
     if (e == cudaErrorNotSupported) return fail(FSB_ELIMIT, "fsb_dbg_chain_describe: no chained configuration for this grid");
     if (e != cudaSuccess) return fail_cuda(e, "fsb_dbg_chain_describe");
-    constexpr int kWords = 51;
+    constexpr int kWords = 53;
     if (D.nphases * kWords > max_words) return fail(FSB_EINVAL, "fsb_dbg_chain_describe: output too small");
     auto id = [](const void *q) { return (long long)((size_t)q / 0x1000); };
     for (int q = 0; q < D.nphases; ++q) {
@@ -1463,6 +1488,8 @@ int fsb_dbg_chain_describe(int variant, int width, int height, int diff_iters, i
         for (int f = 0; f < 2; ++f)
             for (int m = 0; m < 3; ++m) o[44 + 3 * f + m] = id(d.wf[f][m]);
         o[50] = d.reach_phase;
+        o[51] = d.item0;
+        o[52] = d.push_cols;
     }
     *nphases = D.nphases;
     *grid = D.grid;

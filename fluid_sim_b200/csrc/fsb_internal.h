@@ -124,6 +124,7 @@ struct ChainPhaseDesc {
     const void *ptr[8];        // u, v, q, dst_a, dst_b, src_a, src_b, bnd_extra
     const void *wf[2][3];      // sweep phases: {initial iterate, right-hand side, result} of fields 0 and 1
     int reach_phase;           // advection: the gradient phase whose blocks it waits for
+    int item0, push_cols;      // column block of a multi-rank run: global index of the rank's first item; see ChainPhase
 };
 struct ChainDesc {
     int nphases, grid, cw;

@@ -306,16 +306,18 @@ int fsb_set_chain_overlap(fsb_sim *s, int on);
 
 /* Diagnostics, no counterpart in the reference and no device needed: the phase table of the one-launch step
  * (fsb_set_chain_overlap; variant 0) or of the one launch after the noise (variant 1: the advected velocity is written
- * where the first projection had its pressure and divergence) for a grid and sweep counts on a GPU of `nsm` SMs, as 51
- * integers per phase: kind, items,
+ * where the first projection had its pressure and divergence) for a grid and sweep counts on a GPU of `nsm` SMs, as 53
+ * integers per phase (variant 2: the same launch on the column block [col_begin, col_end) with `halo` stored columns either
+ * side, as a rank of a multi-GPU run builds it; items are numbered along the whole grid): kind, items,
  * column ranges, fields per range, columns per range, result shift, number of dependencies inside the launch / on the
  * previous launch, 4 x {phase, from_out, lo, hi}, 3 x the same for the previous launch, the arrays it touches as small
  * integers (u, v, q, dst_a, dst_b, src_a, src_b, bnd_extra; per sweep field: iterate, right-hand side, result; 1, 2 =
  * the velocity the step starts from, 3, 4 / 5, 6 = the two velocity sets it writes, 7, 8 / 11, 12 = pressure and
- * divergence of the two projections, 9 / 10 = density in / out), and the gradient phase an advection phase waits for.
+ * divergence of the two projections, 9 / 10 = density in / out), the gradient phase an advection phase waits for, the global
+ * index of the rank's first item and the columns from a rank boundary within which results are also stored in the neighbour.
  * tests/test_chain_deps.py checks on the CPU that these dependencies order every pair of conflicting accesses. */
-int fsb_dbg_chain_describe(int variant, int width, int height, int diff_iters, int proj_iters, int nsm, long long *out,
-                           int max_words, int *nphases, int *grid, int *cw);
+int fsb_dbg_chain_describe(int variant, int width, int height, int diff_iters, int proj_iters, int nsm, int col_begin,
+                           int col_end, int halo, long long *out, int max_words, int *nphases, int *grid, int *cw);
 
 const char *fsb_last_error(void);
 const char *fsb_version(void);

@@ -17,14 +17,15 @@ import pytest
 import fluid_sim_b200 as fsb
 
 SOR, GS, DIV, GRAD, ADV, GSX0, BNDP, NOISE = 1, 2, 3, 4, 5, 6, 7, 8
-WORDS = 51
+WORDS = 53
 
 
-def describe(w, h, d, p, nsm=148, variant=0):
+def describe(w, h, d, p, nsm=148, variant=0, block=(0, 0, 0)):
     lib = fsb.load_library()
     out = (C.c_longlong * (24 * WORDS))()
     n, grid, cw = C.c_int(), C.c_int(), C.c_int()
-    rc = lib.fsb_dbg_chain_describe(variant, w, h, d, p, nsm, out, 24 * WORDS, C.byref(n), C.byref(grid), C.byref(cw))
+    rc = lib.fsb_dbg_chain_describe(variant, w, h, d, p, nsm, block[0], block[1], block[2], out, 24 * WORDS, C.byref(n),
+                                    C.byref(grid), C.byref(cw))
     if rc != 0:
         return None
     a = np.array(out[:n.value * WORDS], dtype=np.int64).reshape(n.value, WORDS)
@@ -34,7 +35,7 @@ def describe(w, h, d, p, nsm=148, variant=0):
                            deps=[tuple(int(v) for v in r[8 + 4 * k:12 + 4 * k]) for k in range(int(r[6]))],
                            xdeps=[tuple(int(v) for v in r[24 + 4 * k:28 + 4 * k]) for k in range(int(r[7]))],
                            ptr=[int(v) for v in r[36:44]], wf=[[int(v) for v in r[44:47]], [int(v) for v in r[47:50]]],
-                           reach=int(r[50])))
+                           reach=int(r[50]), item0=int(r[51]), push_cols=int(r[52])))
     return phases, grid.value, cw.value
 
 
@@ -242,3 +243,60 @@ def test_plan_of_the_headline_workload():
     kinds = [q["kind"] for q in phases]
     assert kinds.count(GS) == 2 and kinds.count(GSX0) == 2 and kinds.count(BNDP) == 2 and cw == 32
     assert describe(100, 100, 5, 33) is None          # sweep counts without a chained configuration
+
+
+def publishes_to(owner, ph, item, side):
+    """Does the rank `owner` (its block description) publish the done-word of its `item` of phase `ph` in the arrays of
+    its left (-1) / right (+1) neighbour?  (the publish rule at the end of chain_kernel's item loop)"""
+    j0, j1, halo = owner["block"]
+    cl = item // ph["nf"]
+    lo = cl * ph["cpv"] - ph["shift"]
+    hi = lo + ph["cpv"] - 1
+    reach = halo + 2 * ph["cpv"]
+    return lo < j0 + reach if side < 0 else hi >= j1 - reach
+
+
+@pytest.mark.parametrize("h,ncols,halo,p,d", [(32768, 4096, 128, 100, 5), (16384, 4096, 128, 40, 5), (2048, 512, 128, 20, 5),
+                                              (1024, 512, 256, 20, 10), (8192, 4096, 64, 20, 5)])
+def test_column_blocks_only_wait_for_items_that_publish_there(h, ncols, halo, p, d):
+    """Multi-GPU: a rank's items are numbered along the whole grid and wait for done-words in the rank's own array, which
+    its own items and the neighbours' items near the boundary set.  Every item a dependency (or an advection phase's
+    wait for the gradient blocks it can see) names must be one of those, or the wait could never end; and the global
+    item numbers must fit the done[] array."""
+    w = 256
+    ranks = []
+    for r in range(h // ncols):
+        got = describe(w, h, d, p, variant=2, block=(r * ncols, (r + 1) * ncols, halo))
+        assert got is not None
+        ranks.append(dict(phases=got[0], cw=got[2], block=(r * ncols, (r + 1) * ncols, halo)))
+
+    def owner_of(pi, x):
+        for r, R in enumerate(ranks):
+            q = R["phases"][pi]
+            if q["item0"] <= x < q["item0"] + q["nitems"]:
+                return r
+        return None
+
+    for r, R in enumerate(ranks):
+        phases = R["phases"]
+        j0, j1, _ = R["block"]
+        for pi, ph in enumerate(phases):
+            assert ph["item0"] + ph["nitems"] <= 1088
+            for li in range(ph["nitems"]):
+                item = ph["item0"] + li
+                cl = item // ph["nf"]
+                awaited = [(dep[0], x) for dep in ph["deps"] for x in dep_items(ph, cl, dep, phases)]
+                if ph["kind"] == ADV:
+                    gr = phases[ph["reach"]]
+                    cw = R["cw"]
+                    vis_lo = max((j0 - halo) // cw, 0) if r > 0 else 0
+                    vis_hi = min((j1 + halo) // cw - 1, gr["ncl"] - 1) if r < len(ranks) - 1 else gr["ncl"] - 1
+                    awaited += [(ph["reach"], x) for x in range(vis_lo, vis_hi + 1)]      # the widest wait: every visible block
+                for (qi, x) in awaited:
+                    o = owner_of(qi, x)
+                    assert o is not None, f"rank {r} phase {pi} item {item} waits for item {x} of phase {qi}, which no rank runs"
+                    if o == r:
+                        continue
+                    assert abs(o - r) == 1, f"rank {r} phase {pi} item {item} waits for item {x} of phase {qi}, owned by rank {o}"
+                    assert publishes_to(ranks[o], ranks[o]["phases"][qi], x, r - o), \
+                        f"rank {r} phase {pi} item {item} waits for item {x} of phase {qi}: rank {o} does not publish it there"
