@@ -612,7 +612,10 @@ def main():
             roofline["traffic"] = tr[key]
     Bp = algorithmic_bytes_per_cell(P)
     step_gbs = Bp * cells / (ms_per_step * 1e-3) / 1e9
-    step_roofline = {"bytes_per_cell": Bp, "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak}
+    step_roofline = {"bytes_per_cell": Bp, "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak,
+                     "note": "the whole step counted at the reference's pass structure, B(P) = 356 + 24 P bytes per cell (the figure "
+                             "north_star's 0.70 target is stated in): an effective rate, not DRAM utilisation -- it exceeds 1 once "
+                             "fused passes no longer move those bytes (real traffic: roofline.traffic)"}
     shares = {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items()}
     # per kernel class: effective GB/s at SURVEY.md 8(d)'s algorithmic bytes per cell and launch
     per_launch_bytes = {"noise": 16.0, "divergence": 16.0, "gradient": 20.0, "advect_velocity": 16.0, "advect_scalar": 16.0,
