@@ -300,3 +300,166 @@ def test_column_blocks_only_wait_for_items_that_publish_there(h, ncols, halo, p,
                     assert abs(o - r) == 1, f"rank {r} phase {pi} item {item} waits for item {x} of phase {qi}, owned by rank {o}"
                     assert publishes_to(ranks[o], ranks[o]["phases"][qi], x, r - o), \
                         f"rank {r} phase {pi} item {item} waits for item {x} of phase {qi}: rank {o} does not publish it there"
+
+
+# ---- column blocks of a multi-GPU run: the same check across ranks ------------------------------------------------------
+# Every rank runs the one launch after the noise on its block of columns (stored with `halo` columns either side) and
+# ONLY READS ITS OWN ARRAYS: items near a rank boundary store their results in the neighbour's array as well (pointwise
+# phases: within `push_cols` columns of the boundary; sweep phases: the result columns up to the left rank's first halo
+# column) and publish their done-word there; an item that writes into a neighbour first waits for that neighbour to have
+# finished the previous step; a rank's own launches follow one another.  Arrays swap roles from step to step as
+# fsb_blk_step swaps them.
+
+def mr_accesses(R, ph, item, H, reach_cols, step):
+    """[(array rank, array name, lo, hi, is_write)] of one item of rank R (dict with index, block, neighbours)"""
+    r, (j0, j1, halo) = R["r"], R["block"]
+    nranks = R["nranks"]
+    has_left, has_right = r > 0, r < nranks - 1
+    lo_st, hi_st = max(j0 - halo, 0), min(j1 + halo, H) - 1           # columns this rank stores
+    name = {3: f"F{step % 2}.u", 4: f"F{step % 2}.v", 7: f"F{1 - step % 2}.u", 8: f"F{1 - step % 2}.v", 9: f"D{step % 2}",
+            10: f"D{1 - step % 2}", 11: "P2.p", 12: "P2.div"}
+    out = []
+    push_l = push_r = False
+    cl = item // ph["nf"]
+    if ph["kind"] in (SOR, GS, GSX0):
+        push_l = has_left and cl * ph["cpv"] - ph["shift"] < j0 + 1
+    elif ph["push_cols"] > 0:
+        b0 = cl * ph["cpv"]
+        push_l = has_left and b0 < j0 + ph["push_cols"]
+        push_r = has_right and b0 + ph["cpv"] - 1 >= j1 - ph["push_cols"]
+    for role, lo, hi, wr in accesses(ph, item, H, reach_cols, False):
+        if not isinstance(role, int):
+            out.append((-1, role, lo, hi, wr))                        # a ring of the sweep chain: one object for all ranks
+            continue
+        lo2, hi2 = max(lo, lo_st), min(hi, hi_st)
+        if lo2 <= hi2:
+            out.append((r, name[role], lo2, hi2, wr))
+        if wr and ph["kind"] in (SOR, GS, GSX0):
+            if push_l and lo <= j0:                                   # result columns < j0 + 1 also go to the left rank
+                out.append((r - 1, name[role], lo, min(hi, j0), True))
+        elif wr:
+            if push_l:
+                out.append((r - 1, name[role], lo, hi, True))
+            if push_r:
+                out.append((r + 1, name[role], lo, hi, True))
+    return out, push_l, push_r
+
+
+def mr_check(h, ncols, halo, p, d, reach_cols):
+    w = 256
+    nranks = h // ncols
+    ranks = []
+    for r in range(nranks):
+        got = describe(w, h, d, p, variant=2, block=(r * ncols, (r + 1) * ncols, halo))
+        assert got is not None
+        ranks.append(dict(r=r, nranks=nranks, phases=got[0], grid=got[1], cw=got[2], block=(r * ncols, (r + 1) * ncols, halo)))
+    nph = len(ranks[0]["phases"])
+    index, nodes = {}, []
+    for s in (0, 1):
+        for R in ranks:
+            for pi, ph in enumerate(R["phases"]):
+                for li in range(ph["nitems"]):
+                    key = (s, pi, ph["item0"] + li)                    # global item numbers: one owner each
+                    assert key not in index
+                    index[key] = len(nodes)
+                    nodes.append((s, R["r"], pi, ph["item0"] + li))
+        for R in ranks:                                               # "rank r has finished step s"
+            index[("end", s, R["r"])] = len(nodes)
+            nodes.append((s, R["r"], nph, -1))
+    n = len(nodes)
+    pred = [set() for _ in range(n)]
+    acc_of = {}
+    for s in (0, 1):
+        for R in ranks:
+            phases, (j0, j1, _) = R["phases"], R["block"]
+            for pi, ph in enumerate(phases):
+                for li in range(ph["nitems"]):
+                    item = ph["item0"] + li
+                    me = index[(s, pi, item)]
+                    cl = item // ph["nf"]
+                    for dep in ph["deps"]:
+                        for x in dep_items(ph, cl, dep, phases):
+                            pred[me].add(index[(s, dep[0], x)])
+                    if ph["kind"] == ADV:
+                        gr = phases[ph["reach"]]
+                        cw = R["cw"]
+                        vis_lo = max((j0 - halo) // cw, 0) if R["r"] > 0 else 0
+                        vis_hi = min((j1 + halo) // cw - 1, gr["ncl"] - 1) if R["r"] < nranks - 1 else gr["ncl"] - 1
+                        bg = cl * ph["cpv"] // gr["cpv"]
+                        k = max(1, -(-reach_cols // gr["cpv"]))
+                        for x in range(max(bg - k, vis_lo), min(bg + k, vis_hi) + 1):
+                            pred[me].add(index[(s, ph["reach"], x)])
+                    acc, push_l, push_r = mr_accesses(R, ph, item, h, reach_cols, s)
+                    acc_of[me] = acc
+                    pred[index[("end", s, R["r"])]].add(me)
+                    if s == 1:
+                        pred[me].add(index[("end", 0, R["r"])])        # a rank's launches follow one another
+                        if push_l:
+                            pred[me].add(index[("end", 0, R["r"] - 1)])   # step word of the neighbour it writes into
+                        if push_r:
+                            pred[me].add(index[("end", 0, R["r"] + 1)])
+    # the ring order inside a sweep phase, across ranks as well (items are numbered along the whole grid)
+    for s in (0, 1):
+        for pi, ph in enumerate(ranks[0]["phases"]):
+            if ph["kind"] in (SOR, GS, GSX0):
+                total = max(R["phases"][pi]["item0"] + R["phases"][pi]["nitems"] for R in ranks)
+                for it in range(ph["nf"], total):
+                    pred[index[(s, pi, it)]] |= {q for q in pred[index[(s, pi, it - ph["nf"])]] if nodes[q][2] != nph}
+    # program order of the items one CTA of a rank runs
+    for s in (0, 1):
+        for R in ranks:
+            last = {}
+            for pi, ph in enumerate(R["phases"]):
+                for li in range(ph["nitems"]):
+                    cta = li % R["grid"]
+                    me = index[(s, pi, ph["item0"] + li)]
+                    if cta in last:
+                        pred[me].add(last[cta])
+                    last[cta] = me
+    # reachability by depth-first search from every node (the node order is not topological across ranks)
+    order, state = [], [0] * n
+    for root in range(n):
+        if state[root]:
+            continue
+        stack = [(root, iter(pred[root]))]
+        state[root] = 1
+        while stack:
+            v, it = stack[-1]
+            nxt = next(it, None)
+            if nxt is None:
+                state[v] = 2
+                order.append(v)
+                stack.pop()
+            elif state[nxt] == 0:
+                state[nxt] = 1
+                stack.append((nxt, iter(pred[nxt])))
+            else:
+                assert state[nxt] == 2, "cyclic dependencies"
+    reach = np.zeros((n, n), dtype=bool)
+    for v in order:                                                   # predecessors first
+        for q in pred[v]:
+            reach[v] |= reach[q]
+            reach[v, q] = True
+    by_array = {}
+    for me, acc in acc_of.items():
+        for arr_rank, arr, lo, hi, wr in acc:
+            by_array.setdefault((arr_rank, arr), []).append((me, lo, hi, wr))
+    bad = []
+    for arr, acc in by_array.items():
+        for i, (a, alo, ahi, awr) in enumerate(acc):
+            for (b, blo, bhi, bwr) in acc[i + 1:]:
+                if not (awr or bwr) or ahi < blo or bhi < alo or a == b:
+                    continue
+                (sa, _, pa, _), (sb, _, pb, _) = nodes[a], nodes[b]
+                if sa == sb and pa == pb:
+                    continue
+                if not (reach[b, a] or reach[a, b]):
+                    bad.append((arr, nodes[a], (alo, ahi, "W" if awr else "R"), nodes[b], (blo, bhi, "W" if bwr else "R")))
+    return bad
+
+
+@pytest.mark.parametrize("h,ncols,halo,p,d", [(1536, 512, 128, 20, 5), (3072, 1024, 128, 40, 10)])
+@pytest.mark.parametrize("reach_cols", [3, 70])
+def test_column_blocks_conflicting_accesses_are_ordered(h, ncols, halo, p, d, reach_cols):
+    bad = mr_check(h, ncols, halo, p, d, reach_cols)
+    assert not bad, f"{len(bad)} unordered pairs, first: {bad[:4]}"
