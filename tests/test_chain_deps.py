@@ -345,7 +345,7 @@ def mr_accesses(R, ph, item, H, reach_cols, step):
     return out, push_l, push_r
 
 
-def mr_check(h, ncols, halo, p, d, reach_cols):
+def mr_check(h, ncols, halo, p, d, reach_cols, step_words=True, cross_rank_done=True):
     w = 256
     nranks = h // ncols
     ranks = []
@@ -379,7 +379,8 @@ def mr_check(h, ncols, halo, p, d, reach_cols):
                     cl = item // ph["nf"]
                     for dep in ph["deps"]:
                         for x in dep_items(ph, cl, dep, phases):
-                            pred[me].add(index[(s, dep[0], x)])
+                            if cross_rank_done or nodes[index[(s, dep[0], x)]][1] == R["r"]:
+                                pred[me].add(index[(s, dep[0], x)])
                     if ph["kind"] == ADV:
                         gr = phases[ph["reach"]]
                         cw = R["cw"]
@@ -394,9 +395,9 @@ def mr_check(h, ncols, halo, p, d, reach_cols):
                     pred[index[("end", s, R["r"])]].add(me)
                     if s == 1:
                         pred[me].add(index[("end", 0, R["r"])])        # a rank's launches follow one another
-                        if push_l:
+                        if push_l and step_words:
                             pred[me].add(index[("end", 0, R["r"] - 1)])   # step word of the neighbour it writes into
-                        if push_r:
+                        if push_r and step_words:
                             pred[me].add(index[("end", 0, R["r"] + 1)])
     # the ring order inside a sweep phase, across ranks as well (items are numbered along the whole grid)
     for s in (0, 1):
@@ -463,3 +464,11 @@ def mr_check(h, ncols, halo, p, d, reach_cols):
 def test_column_blocks_conflicting_accesses_are_ordered(h, ncols, halo, p, d, reach_cols):
     bad = mr_check(h, ncols, halo, p, d, reach_cols)
     assert not bad, f"{len(bad)} unordered pairs, first: {bad[:4]}"
+
+
+def test_the_cross_rank_check_sees_missing_synchronisation():
+    """Without the step words a rank's next step would store into a neighbour's array that the neighbour's current step
+    still reads; without the done-words published across the boundary nothing orders a rank's reads after the
+    neighbour's stores."""
+    assert mr_check(1536, 512, 128, 20, 5, 3, step_words=False)
+    assert mr_check(1536, 512, 128, 20, 5, 3, cross_rank_done=False)
