@@ -1415,7 +1415,7 @@ int fsb_set_chain_level(fsb_sim *s, int level)
 int fsb_dbg_chain_describe(int variant, int width, int height, int diff_iters, int proj_iters, int nsm, int col_begin,
                            int col_end, int halo, long long *out, int max_words, int *nphases, int *grid, int *cw)
 {
-    if (!out || !nphases || !grid || !cw || width < 3 || height < 3 || nsm < 1 || variant < 0 || variant > 2)
+    if (!out || !nphases || !grid || !cw || width < 3 || height < 3 || nsm < 1 || variant < 0 || variant > 3)
         return fail(FSB_EINVAL, "fsb_dbg_chain_describe: bad argument");
     if (variant == 2 && (col_begin < 0 || col_end > height || col_begin >= col_end || halo < 0 || (halo & 31) || (col_begin & 31)))
         return fail(FSB_EINVAL, "fsb_dbg_chain_describe: bad column block");
@@ -1436,9 +1436,14 @@ int fsb_dbg_chain_describe(int variant, int width, int height, int diff_iters, i
     A.density_pz = 1;
     A.overlap = 1;
     A.noise_zero = 1;
-    if (variant == 0) {
+    const SourceEntry some_sources[2] = {SourceEntry{width + 1, 0, 1.0f}, SourceEntry{width + 1, 1, 1.0f}};
+    if (variant == 0 || variant == 3) {
         A.vin_u = arr(1); A.vin_v = arr(2);
         A.yu = arr(5); A.yv = arr(6);
+        if (variant == 3) {         // the same launch carrying pending sources (one addDensity, one addVelocity)
+            A.sources = some_sources;
+            A.nsources = 2;
+        }
     } else {
         A.overlap = 0;      // the noise is its own launch; the advected velocity goes where the first projection had its scratch
     }

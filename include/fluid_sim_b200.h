@@ -305,7 +305,7 @@ int fsb_set_chain_level(fsb_sim *s, int level);
 int fsb_set_chain_overlap(fsb_sim *s, int on);
 
 /* Diagnostics, no counterpart in the reference and no device needed: the phase table of the one-launch step
- * (fsb_set_chain_overlap; variant 0) or of the one launch after the noise (variant 1: the advected velocity is written
+ * (fsb_set_chain_overlap; variant 0, variant 3: carrying pending sources) or of the one launch after the noise (variant 1: the advected velocity is written
  * where the first projection had its pressure and divergence) for a grid and sweep counts on a GPU of `nsm` SMs, as 53
  * integers per phase (variant 2: the same launch on the column block [col_begin, col_end) with `halo` stored columns either
  * side, as a rank of a multi-GPU run builds it; items are numbered along the whole grid): kind, items,
